@@ -1,0 +1,252 @@
+/* include/cabm.h -- C ABI of the B200-native covid-abm daily transmission cycle.
+ *
+ * The reference has no FFI for this path: its boundary is the C++ class surface of `Community`
+ * (Community.h:138-441) consumed by simulator.h. A drop-in `Community` facade forwards each of the
+ * calls below to this library (see INTEGRATION.md for the binding a maintainer adds). Every entry
+ * point cites the reference interface it replaces.
+ *
+ * Conventions: plain pointers and sizes only; the library owns all device memory behind the
+ * handle; caller owns every host buffer and may free it when the call returns; return 0 = ok,
+ * <0 = error with text in cabm_last_error(). One host thread per handle; a handle is bound to the
+ * CUDA device that was current at cabm_create(). There is NO CPU fallback: cabm_create fails with
+ * CABM_E_NODEVICE when no CUDA device is usable.
+ */
+#ifndef CABM_H
+#define CABM_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CABM_N_STRAINS   4      /* Parameters.h:168-174 */
+#define CABM_N_AGES      121    /* Parameters.h:315 */
+#define CABM_MAX_DOSES   4
+#define CABM_N_OUTCOMES  5      /* Parameters.h:127-134 */
+#define CABM_N_LOCTYPES  5      /* Parameters.h:74-81 */
+#define CABM_INCUB_MAX   64
+#define CABM_T_GAMMA     128
+#define CABM_T_NEGBIN    128
+#define CABM_T_GEOM      64
+#define CABM_T_DEATHLAG  256
+#define CABM_T_POISSON   32
+#define CABM_N_SEVERE_CDF   71  /* Parameters.h:291-299 */
+#define CABM_N_CRITICAL_CDF 60  /* Parameters.h:303-309 */
+
+/* error codes */
+#define CABM_OK          0
+#define CABM_E_ARG      -1
+#define CABM_E_NODEVICE -2
+#define CABM_E_CUDA     -3
+#define CABM_E_STATE    -4
+#define CABM_E_NOMEM    -5
+
+/* location types / public-transmission risk (Parameters.h:74-81, 98-103) */
+enum { CABM_HOUSE = 0, CABM_WORK = 1, CABM_SCHOOL = 2, CABM_HOSPITAL = 3, CABM_NURSINGHOME = 4 };
+enum { CABM_PT_NONE = 0, CABM_PT_LOW = 1, CABM_PT_HIGH = 2 };
+/* timed interventions (Parameters.h:206-211) */
+enum { CABM_TI_SCHOOL_CLOSURE = 0, CABM_TI_BUSINESS_CLOSURE = 1, CABM_TI_SOCIAL_DISTANCING = 2 };
+
+/* Philox purpose slots: counter = (sub<<16 | block, a, b, day<<8 | purpose), key = seed */
+enum {
+    CABM_P_INIT = 1,          /* a = person                      : load-time immunity attributes            */
+    CABM_P_VISIT = 2,         /* a = person                      : Community.cpp:1013-1017                  */
+    CABM_P_EXPOSE_HH = 3,     /* a = person, b = source location : Community.cpp:842-850 -> :971-996        */
+    CABM_P_EXPOSE_NB = 4,     /*                                   Community.cpp:853-875                    */
+    CABM_P_EXPOSE_WORK_VIS = 5, /*                                 Community.cpp:904 (visitors)             */
+    CABM_P_EXPOSE_WORK = 6,   /*                                   Community.cpp:905 (staff)                */
+    CABM_P_EXPOSE_SCHOOL = 7, /*                                   Community.cpp:914-928                    */
+    CABM_P_EXPOSE_NH = 8,     /*                                   Community.cpp:959-969                    */
+    CABM_P_EXPOSE_HOSP = 9,   /* staff                             Community.cpp:931-941                    */
+    CABM_P_EXPOSE_HOSP_PAT = 10, /* admitted patients (sub = occurrence in the hospital list)               */
+    CABM_P_IMPORT = 11,       /* a = import index of the day     : simulator.h:201-223                      */
+    CABM_P_SEED = 12,         /* a = person, b = call sequence   : Community::infect, simulator.h:94-131    */
+    CABM_P_IMPORT_COUNT = 13, /* a = chunk                       : simulator.h:209 Poisson count            */
+    CABM_P_TRACE = 14,        /* a = person                      : Community.cpp:1064                       */
+    CABM_P_QUARANTINE = 15,   /* a = person                      : Community.cpp:1135                       */
+    CABM_P_REPORTING = 0x80   /* OR-ed onto an event's purpose   : REPORTING_RNG draws (Person.cpp:424,452,459) */
+};
+
+/* Daily ledger series (CommunityLedger, Community.h:112-130). */
+enum {
+    CABM_C_NEW_INFECTED = 0, CABM_C_NEW_SYMPTOMATIC, CABM_C_NEW_SEVERE, CABM_C_NEW_CRITICAL, CABM_C_NEW_DEAD,
+    CABM_C_VACCINATED_CASES, CABM_C_SEVERE_PREV, CABM_C_HOSP_INC, CABM_C_HOSP_PREV, CABM_C_ICU_INC, CABM_C_ICU_PREV,
+    CABM_C_DET_CASES_ONSET, CABM_C_DET_CASES_REPORT, CABM_C_DET_HOSP, CABM_C_DET_DEATHS_ONSET, CABM_C_DET_DEATHS_REPORT,
+    CABM_C_NEW_INF_STRAIN0, CABM_C_NEW_INF_STRAIN1, CABM_C_NEW_INF_STRAIN2, CABM_C_NEW_INF_STRAIN3,
+    CABM_N_COUNTERS
+};
+
+/* Work counters of the byte model in SURVEY.md 8(d), accumulated on device every day. */
+enum {
+    CABM_W_AGENTS = 0,      /* N  : agents scanned                                   */
+    CABM_W_ACTIVE,          /* A  : agents with an unresolved infection              */
+    CABM_W_FLAGS,           /* F  : (infectious agent, location) pressure updates    */
+    CABM_W_PATRONS,         /* P  : agents drawing visits                            */
+    CABM_W_VISITS,          /* V0 : visits drawn                                     */
+    CABM_W_HOT_VISITS,      /* V  : visits landing on hot locations                  */
+    CABM_W_HOT_LOCS,        /* H  : hot locations                                    */
+    CABM_W_NBR_EDGES,       /* E  : neighbour edges of hot risky households          */
+    CABM_W_TRIALS,          /* X  : exposure trials                                  */
+    CABM_W_INFECTIONS,      /* I  : new infections                                   */
+    CABM_N_WORK
+};
+
+typedef struct cabm cabm_t;
+typedef struct cabm_snap cabm_snap_t;
+
+/* Flat model tables: the members of `Parameters` the hot path reads. */
+typedef struct cabm_params {
+    uint64_t seed;                        /* Parameters.h:465 randomseed -> Philox key                    */
+    int32_t  run_length;                  /* Parameters.h:466                                              */
+    int32_t  num_surveilled_people;       /* Parameters.h:661                                              */
+    double   haz_mult[CABM_N_LOCTYPES + 1]; /* household, work, school, hospital, nursinghome, social (Parameters.h:467-472) */
+    double   seasonality[366];            /* Parameters.h:473, indexed by julian day - 1 (Parameters.cpp:252) */
+    float    susceptibility_by_age[CABM_N_AGES];      /* Parameters.h:476 */
+    float    pathogenicity_by_age[CABM_N_AGES];       /* Parameters.h:477 */
+    float    prob_severe[2][CABM_N_AGES];             /* probSeriousOutcome[SEVERE][comorbid][age]   Parameters.h:479 */
+    float    prob_critical[2][CABM_N_AGES];           /* probSeriousOutcome[CRITICAL]                                 */
+    float    prob_icu_death[2][CABM_N_AGES];          /* probSeriousOutcome[DEATH]                                    */
+    double   VES[CABM_N_STRAINS][CABM_MAX_DOSES];     /* Parameters.h:481-486, stretchy_vector already applied        */
+    double   VES_NAIVE[CABM_N_STRAINS][CABM_MAX_DOSES];
+    double   VEP[CABM_N_STRAINS][CABM_MAX_DOSES];
+    double   VEH[CABM_N_STRAINS][CABM_MAX_DOSES];
+    double   VEF[CABM_N_STRAINS][CABM_MAX_DOSES];
+    double   VEI[CABM_N_STRAINS][CABM_MAX_DOSES];
+    double   IEP, IEH, IEF, IEI;                      /* Parameters.h:491-494 */
+    int32_t  vaccine_dose_to_protection_lag;          /* Parameters.h:488 */
+    int32_t  immunity_leaky, immunity_wanes, retroactive_mature_vaccine;  /* Parameters.h:572-573,649 */
+    double   strain_rel_infectiousness[CABM_N_STRAINS];   /* StrainPars, Parameters.h:327-351 */
+    double   strain_rel_pathogenicity[CABM_N_STRAINS];
+    double   strain_rel_severity[CABM_N_STRAINS];
+    double   strain_rel_mortality[CABM_N_STRAINS];
+    double   strain_rel_icu_mortality[CABM_N_STRAINS];
+    double   strain_immune_escape[CABM_N_STRAINS];
+    int32_t  strain_infectious_period[CABM_N_STRAINS];
+    int32_t  cross_protection[CABM_N_STRAINS][CABM_N_STRAINS]; /* Parameters.h:659 */
+    int32_t  symptom_to_test_lag, default_reporting_lag;       /* Parameters.h:534,536 (no ReportingLagModel) */
+    int32_t  begin_contact_tracing, contact_tracing_depth, quarantine_duration; /* Parameters.h:509-512,696 */
+    double   contact_tracing_coverage;
+    double   quarantine_probability[4];                       /* Parameters.h:695 */
+    double   seroconversion_lag, seropositivity_threshold;    /* Parameters.h:650-651 */
+    /* integer-support CDF tables for the discretised duration draws (see covid-abm_b200/params.py) */
+    double   incub_cdf[CABM_N_STRAINS][CABM_INCUB_MAX];        /* 1+floor(Gamma)      Parameters.h:515-520 */
+    double   onset_cdf[CABM_INCUB_MAX + 1][CABM_INCUB_MAX + 1];/* Binomial(p, n)      Parameters.h:521-524 */
+    double   presev_cdf[CABM_T_GAMMA];                         /* Parameters.h:525-527 */
+    double   mild_cdf[CABM_T_GAMMA];                           /* Parameters.h:528-530 */
+    double   severe_only_cdf[CABM_N_SEVERE_CDF];               /* Parameters.h:531 */
+    double   critical_cdf[CABM_N_CRITICAL_CDF];                /* Parameters.h:532 */
+    double   p_high_asym, p_high_sym;                          /* Person.cpp:340-355 Weibull > 8.04 */
+    double   icu_death_cdf[CABM_T_NEGBIN];                     /* Parameters.h:450-456 */
+    double   community_death_cdf[CABM_T_GEOM];                 /* Parameters.h:458-461 */
+    double   death_lag_cdf[CABM_T_DEATHLAG];                   /* Parameters.h:547-553 */
+    double   visit_cdf[CABM_T_POISSON];                        /* Community.cpp:1012-1013 Poisson(1) */
+    double   trace_ev_cdf[CABM_N_LOCTYPES][CABM_T_POISSON];    /* Community.cpp:1089,1105,1120 */
+    /* per-day tables, length run_length; copied during the call */
+    const double* prob_first_detection;   /* [run_length][5]  Parameters.h:566 */
+    const double* icu_mortality_reduction;/* [run_length] or NULL  Parameters.h:671 */
+} cabm_params;
+
+/* Population as structure-of-arrays + CSR (what loadLocations/loadPopulation build, Community.cpp:174-524). */
+typedef struct cabm_population {
+    uint32_t n_people, n_loc;
+    /* per location */
+    const uint8_t*  loc_type;        /* CABM_HOUSE..            Location.h:97-109 */
+    const uint8_t*  loc_essential;   /* 1 = essential            */
+    const uint8_t*  loc_pubrisk;     /* CABM_PT_*                */
+    const float*    loc_risk;        /* riskiness (float, Location.h:85) */
+    const int32_t*  loc_hospital;    /* associated hospital id or -1 (Location.h:105) */
+    const int64_t*  nbr_off;         /* [n_loc+1] neighbour CSR, ascending ids (std::set order, Location.h:60) */
+    const int32_t*  nbr;
+    const int64_t*  roster_off;      /* [n_loc+1] residents+workers in load order (Community.cpp:219-224) */
+    const int32_t*  roster;
+    /* per person */
+    const int32_t*  home;            /* Person.h:355 */
+    const int32_t*  day;             /* day location or -1 (Person.h:356) */
+    const uint8_t*  age;
+    const uint8_t*  sex;
+    const uint8_t*  comorbid;
+    const uint8_t*  ltc;             /* long-term-care resident */
+    const int32_t*  patron;          /* [n_people][n_patron] patronised locations, -1 padded (Person.h:357) */
+    uint32_t        n_patron;
+    /* load-time immunity attributes (Community.cpp:212-215); NULL => drawn from Philox(CABM_P_INIT) */
+    const double*   starting_natural_efficacy;
+    const float*    cross_protection_probability;
+    const int32_t*  natural_immunity_duration;
+} cabm_population;
+
+/* One record of Person::infectionHistory, as returned by cabm_sync_histories (Person.h:35-175). */
+typedef struct cabm_infection {
+    uint32_t person;
+    int32_t  infected_by;        /* -1: imported / unknown */
+    int32_t  infected_place;     /* -1: none */
+    int16_t  t[12];              /* infectedBegin, infectiousBegin, infectiousEnd, symptomBegin, symptomEnd, severeBegin,
+                                    severeEnd, hospitalizedBegin, criticalBegin, criticalEnd, icuBegin, deathTime;
+                                    32767 / -32768 stand for INT_MAX / INT_MIN */
+    int16_t  report_day;         /* Detection::reported_time or 32767 */
+    uint8_t  strain, detected_state; /* detected_state = CABM_N_OUTCOMES when undetected */
+    float    rel_infectiousness;
+} cabm_infection;
+
+/* Parity hook: one row per hot location of the day (what _tally_infectiousness and the six
+ * *_transmission functions compute, Community.cpp:833-969). */
+typedef struct cabm_foi_row {
+    uint32_t loc; uint8_t type; uint8_t pad[3];
+    double   w[CABM_N_STRAINS];  /* infectious weight by strain */
+    uint32_t size;               /* denominator census used (roster, + visitors for WORK) */
+    double   T;                  /* exposure probability of the location's own pass (0 if gated off) */
+    double   T_social;           /* HOUSE only: between-household T (0 if gated off) */
+} cabm_foi_row;
+
+/* lifecycle: replaces `new Community(par,date)` / `delete` (Community.cpp:32-73,126-152) */
+int  cabm_create(cabm_t** out);
+int  cabm_destroy(cabm_t* h);
+const char* cabm_last_error(const cabm_t* h);
+
+/* replaces loadLocations + loadPopulation (Community.cpp:174-524) */
+int  cabm_load_population(cabm_t* h, const cabm_population* pop);
+/* replaces the `static const Parameters* _par` reads (Community.cpp:28, Person.cpp:24); re-callable */
+int  cabm_set_params(cabm_t* h, const cabm_params* par);
+/* replaces setSocialDistancingTimedIntervention / updateTimedIntervention (Community.h:396-425) */
+int  cabm_set_timed_intervention(cabm_t* h, int which, const double* v, size_t n);
+
+/* replaces Community::tick() (Community.cpp:1147-1192); julian_day/is_weekday come from Date (Date.h) */
+int  cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday);
+/* replaces seed_epidemic(par, community, date, strain_weights) (simulator.h:201-223) */
+int  cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[CABM_N_STRAINS], int32_t* out_infected);
+/* replaces Community::infect(id, strain) (Community.cpp:550-553) */
+int  cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected);
+/* run `n_days` of tick+import back to back without returning to the host (CUDA-graph replay) */
+int  cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
+                   const double* expected_imports, const double* strain_w /* [n_days][4] */);
+
+/* replaces Person::vaccinate via Vac_Campaign::vaccinate (Person.cpp:611-647, Vac_Campaign.h:550) */
+int  cabm_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_ok);
+/* replaces Person::scheduleQuarantine (Person.cpp:649-651) */
+int  cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, int until_day);
+
+/* replaces the ledger getters (Community.h:353-375) */
+int  cabm_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n);
+int  cabm_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]);
+int  cabm_cumulative_outcomes(cabm_t* h, uint64_t out[CABM_N_OUTCOMES]);
+int  cabm_work_counters(cabm_t* h, uint64_t out[CABM_N_WORK]);
+
+/* lazy D2H of every infection record (Person::getInfectionHistory, Person.h:281) */
+int  cabm_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_n);
+/* current (latest) infection of selected people; pids NULL => all */
+int  cabm_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infection* out);
+
+/* checkpoint / restore (SimulationCache + Community::load_from_cache, behavior_tuner.h:39-87, Community.cpp:154-171) */
+int  cabm_snapshot(cabm_t* h, cabm_snap_t** out);
+int  cabm_restore(cabm_t* h, const cabm_snap_t* s);
+int  cabm_snap_free(cabm_snap_t* s);
+
+/* parity hook: hazards of the most recent tick */
+int  cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n);
+/* device time (ms, CUDA events) spent in the day pipeline since the last call; resets the accumulator */
+int  cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

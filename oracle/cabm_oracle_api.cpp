@@ -1,0 +1,183 @@
+// oracle/cabm_oracle_api.cpp -- TEST INFRASTRUCTURE (oracle). Not part of the product path.
+// C entry points of the oracle; same signatures as include/cabm.h with the prefix cabm_oracle_.
+#include <algorithm>
+#include <cstring>
+#include <new>
+#include "cabm_oracle.h"
+
+using cabm_oracle::Sim;
+struct cabm { Sim sim; };
+struct cabm_snap { Sim sim; };
+
+#define H_OK(h) do { if (!(h)) return CABM_E_ARG; } while (0)
+
+extern "C" {
+
+int cabm_oracle_create(cabm_t** out) { if (!out) return CABM_E_ARG; *out = new (std::nothrow) cabm(); return *out ? CABM_OK : CABM_E_NOMEM; }
+int cabm_oracle_destroy(cabm_t* h) { delete h; return CABM_OK; }
+const char* cabm_oracle_last_error(const cabm_t* h) { return h ? h->sim.err.c_str() : "null handle"; }
+
+int cabm_oracle_load_population(cabm_t* h, const cabm_population* pop) {
+    H_OK(h); if (!pop) return CABM_E_ARG;
+    Sim& S = h->sim;
+    if (!pop->starting_natural_efficacy || !pop->cross_protection_probability || !pop->natural_immunity_duration) {
+        S.err = "oracle requires explicit load-time immunity attributes"; return CABM_E_ARG;
+    }
+    const uint32_t N = pop->n_people, L = pop->n_loc;
+    S.n_people = N; S.n_loc = L; S.n_patron = pop->n_patron;
+    S.loc_type.assign(pop->loc_type, pop->loc_type + L); S.loc_essential.assign(pop->loc_essential, pop->loc_essential + L);
+    S.loc_pubrisk.assign(pop->loc_pubrisk, pop->loc_pubrisk + L); S.loc_risk.assign(pop->loc_risk, pop->loc_risk + L);
+    S.loc_hospital.assign(pop->loc_hospital, pop->loc_hospital + L);
+    S.nbr_off.assign(pop->nbr_off, pop->nbr_off + L + 1); S.nbr.assign(pop->nbr, pop->nbr + pop->nbr_off[L]);
+    S.roster_off.assign(pop->roster_off, pop->roster_off + L + 1); S.roster.assign(pop->roster, pop->roster + pop->roster_off[L]);
+    S.home.assign(pop->home, pop->home + N); S.day_loc.assign(pop->day, pop->day + N);
+    S.age.assign(pop->age, pop->age + N); S.sex.assign(pop->sex, pop->sex + N);
+    S.comorbid.assign(pop->comorbid, pop->comorbid + N); S.ltc.assign(pop->ltc, pop->ltc + N);
+    S.patron.assign(pop->patron, pop->patron + (size_t) N * pop->n_patron);
+    S.nat_eff.assign(pop->starting_natural_efficacy, pop->starting_natural_efficacy + N);
+    S.xprot.assign(pop->cross_protection_probability, pop->cross_protection_probability + N);
+    S.nat_dur.assign(pop->natural_immunity_duration, pop->natural_immunity_duration + N);
+    S.people.assign(N, cabm_oracle::Person());
+    S.patients.clear(); S.log.clear(); S.seed_calls = 0;
+    S.have_pop = true;
+    return CABM_OK;
+}
+
+int cabm_oracle_set_params(cabm_t* h, const cabm_params* par) {
+    H_OK(h); if (!par || !par->prob_first_detection || par->run_length <= 0) return CABM_E_ARG;
+    Sim& S = h->sim;
+    const bool first = !S.have_par;
+    S.par = *par;
+    const size_t R = (size_t) par->run_length;
+    S.pfd.assign(par->prob_first_detection, par->prob_first_detection + R * CABM_N_OUTCOMES);
+    if (par->icu_mortality_reduction) S.imr.assign(par->icu_mortality_reduction, par->icu_mortality_reduction + R); else S.imr.clear();
+    S.par.prob_first_detection = nullptr; S.par.icu_mortality_reduction = nullptr;
+    if (first) {
+        S.hot.assign(R, {});
+        for (int c = 0; c < CABM_N_COUNTERS; ++c) S.ledger[c].assign(R, 0);
+        for (int t = 0; t < 3; ++t) S.ti[t].assign(R, 0.0);
+    }
+    S.have_par = true;
+    return CABM_OK;
+}
+
+int cabm_oracle_set_timed_intervention(cabm_t* h, int which, const double* v, size_t n) {
+    H_OK(h); Sim& S = h->sim;
+    if (!S.have_par || which < 0 || which > 2 || !v || n == 0) return CABM_E_ARG;
+    const size_t R = (size_t) S.par.run_length;
+    for (size_t d = 0; d < R; ++d) S.ti[which][d] = v[std::min(d, n - 1)];
+    return CABM_OK;
+}
+
+static int ready(Sim& S, int day) {
+    if (!S.have_par || !S.have_pop) { S.err = "population and parameters must be set first"; return CABM_E_STATE; }
+    if (day < 0 || day >= S.par.run_length) { S.err = "day outside run_length"; return CABM_E_ARG; }
+    return CABM_OK;
+}
+
+int cabm_oracle_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday) {
+    H_OK(h); int rc = ready(h->sim, sim_day); if (rc) return rc;
+    if (julian_day < 1 || julian_day > 366) return CABM_E_ARG;
+    h->sim.tick(sim_day, julian_day, is_weekday); return CABM_OK;
+}
+
+int cabm_oracle_import(cabm_t* h, int sim_day, double expected, const double strain_w[CABM_N_STRAINS], int32_t* out_infected) {
+    H_OK(h); int rc = ready(h->sim, sim_day); if (rc) return rc;
+    const int n = h->sim.import_day(sim_day, expected, strain_w);
+    if (out_infected) *out_infected = n;
+    return CABM_OK;
+}
+
+int cabm_oracle_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected) {
+    H_OK(h); Sim& S = h->sim; int rc = ready(S, sim_day); if (rc) return rc;
+    if (pid >= S.n_people || strain < 0 || strain >= CABM_N_STRAINS) return CABM_E_ARG;
+    const uint32_t seq = S.seed_calls++;
+    cabm_oracle::Stream s; s.begin(S.par.seed, (uint32_t) sim_day, CABM_P_SEED, pid, seq);
+    const bool ok = S.infect((int) pid, sim_day, -1, strain, false, s, CABM_P_SEED, pid, seq, 0);
+    if (out_infected) *out_infected = ok ? 1 : 0;
+    return CABM_OK;
+}
+
+int cabm_oracle_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
+                         const double* expected_imports, const double* strain_w) {
+    H_OK(h);
+    for (int i = 0; i < n_days; ++i) {
+        int rc = cabm_oracle_tick(h, first_day + i, julian_day[i], is_weekday[i]); if (rc) return rc;
+        rc = cabm_oracle_import(h, first_day + i, expected_imports[i], strain_w + (size_t) i * CABM_N_STRAINS, nullptr); if (rc) return rc;
+    }
+    return CABM_OK;
+}
+
+// Person::vaccinate (Person.cpp:611-647)
+int cabm_oracle_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_ok) {
+    H_OK(h); Sim& S = h->sim; int rc = ready(S, sim_day); if (rc) return rc;
+    if (!S.par.immunity_leaky) { S.err = "vaccination requires leaky immunity (Person.cpp:622)"; return CABM_E_STATE; }
+    for (size_t i = 0; i < n; ++i) {
+        if (pids[i] >= S.n_people) return CABM_E_ARG;
+        cabm_oracle::Person& p = S.people[pids[i]];
+        const bool alive = p.hist.empty() || !p.hist.back().isDead(sim_day);
+        if (alive) { p.naive_vax = p.hist.empty() && p.vax_days.empty(); p.vax_days.push_back(sim_day); }
+        if (out_ok) out_ok[i] = alive ? 1 : 0;
+    }
+    return CABM_OK;
+}
+
+// Person::scheduleQuarantine (Person.cpp:649-651)
+int cabm_oracle_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, int until_day) {
+    H_OK(h); Sim& S = h->sim;
+    for (size_t i = 0; i < n; ++i) {
+        if (pids[i] >= S.n_people) return CABM_E_ARG;
+        cabm_oracle::Person& p = S.people[pids[i]]; p.has_quar = true; p.quar_from = from_day; p.quar_until = until_day;
+    }
+    return CABM_OK;
+}
+
+int cabm_oracle_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n) {
+    H_OK(h); Sim& S = h->sim; if (counter < 0 || counter >= CABM_N_COUNTERS || !out) return CABM_E_ARG;
+    for (size_t d = 0; d < n; ++d) out[d] = d < S.ledger[counter].size() ? S.ledger[counter][d] : 0;
+    return CABM_OK;
+}
+int cabm_oracle_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]) {
+    H_OK(h); Sim& S = h->sim; int rc = ready(S, sim_day); if (rc) return rc;
+    for (int c = 0; c < CABM_N_COUNTERS; ++c) out[c] = S.ledger[c][sim_day];
+    return CABM_OK;
+}
+int cabm_oracle_cumulative_outcomes(cabm_t* h, uint64_t out[CABM_N_OUTCOMES]) { H_OK(h); std::memcpy(out, h->sim.cumul, sizeof(h->sim.cumul)); return CABM_OK; }
+int cabm_oracle_work_counters(cabm_t* h, uint64_t out[CABM_N_WORK]) { H_OK(h); std::memcpy(out, h->sim.work, sizeof(h->sim.work)); return CABM_OK; }
+
+int cabm_oracle_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_n) {
+    H_OK(h); Sim& S = h->sim;
+    if (out_n) *out_n = S.log.size();
+    if (out) std::memcpy(out, S.log.data(), std::min(cap, S.log.size()) * sizeof(cabm_infection));
+    return CABM_OK;
+}
+
+int cabm_oracle_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infection* out) {
+    H_OK(h); Sim& S = h->sim;
+    for (size_t i = 0; i < n; ++i) {
+        const uint32_t pid = pids ? pids[i] : (uint32_t) i; if (pid >= S.n_people) return CABM_E_ARG;
+        cabm_infection rec{}; rec.person = pid; rec.infected_by = -1; rec.infected_place = -1;
+        const cabm_oracle::Person& p = S.people[pid];
+        cabm_oracle::Infection inf; if (!p.hist.empty()) inf = p.hist.back();
+        for (int k = 0; k < 12; ++k) rec.t[k] = (int16_t) std::max(-32768, std::min(32767, inf.t[k]));
+        rec.report_day = (int16_t) std::min(32767, inf.report_day);
+        rec.strain = (uint8_t) inf.strain; rec.detected_state = (uint8_t) inf.detected_state;
+        rec.rel_infectiousness = p.hist.empty() ? 0.0f : inf.rel_inf; rec.infected_place = inf.place; rec.infected_by = inf.by;
+        out[i] = rec;
+    }
+    return CABM_OK;
+}
+
+int cabm_oracle_snapshot(cabm_t* h, cabm_snap_t** out) { H_OK(h); *out = new cabm_snap{ h->sim }; return CABM_OK; }
+int cabm_oracle_restore(cabm_t* h, const cabm_snap_t* s) { H_OK(h); if (!s) return CABM_E_ARG; h->sim = s->sim; return CABM_OK; }
+int cabm_oracle_snap_free(cabm_snap_t* s) { delete s; return CABM_OK; }
+
+int cabm_oracle_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n) {
+    H_OK(h); Sim& S = h->sim;
+    if (out_n) *out_n = S.foi.size();
+    if (out) std::memcpy(out, S.foi.data(), std::min(cap, S.foi.size()) * sizeof(cabm_foi_row));
+    return CABM_OK;
+}
+int cabm_oracle_device_time_ms(cabm_t*, double* out_ms, uint64_t* out_launches) { if (out_ms) *out_ms = 0; if (out_launches) *out_launches = 0; return CABM_OK; }
+
+} // extern "C"
