@@ -1,0 +1,501 @@
+// covid-abm_b200/csrc/cabm.cu -- C ABI of include/cabm.h over the sm_100a day pipeline.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=false -shared -Xcompiler -fPIC
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+#include "cabm_kernels2.cuh"
+
+namespace {
+
+struct Buf { void** slot; size_t bytes; };
+
+} // namespace
+
+struct cabm {
+    Dev d{};
+    std::string err;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    double acc_ms = 0.0; uint64_t launches = 0;
+    int device = 0, sms = 148;
+    bool have_par = false, have_pop = false;
+    cabm_params hpar{};                       // host copy (pointers nulled)
+    std::vector<double> h_ti[3];
+    std::vector<void*> allocs;
+    std::vector<std::pair<void*, size_t>> dyn;    // dynamic state buffers (snapshot set)
+    DayCtx* h_ctx = nullptr; DayCtx* d_ctx = nullptr; int ctx_cap = 0;
+    int* d_tmp_int = nullptr;
+    cudaGraphExec_t day_graph = nullptr;
+    cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
+    unsigned long long h_n_log_cap = 0;
+};
+
+struct cabm_snap {
+    std::vector<std::pair<void*, size_t>> bufs;   // device copies, same order as cabm::dyn
+    void* log = nullptr; unsigned long long n_log = 0;
+};
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return CABM_E_CUDA; } } while (0)
+
+template <typename T>
+static int dalloc(cabm_t* h, T** p, size_t n, bool dynamic = false, int fill = 0) {
+    const size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+    CK(cudaMalloc((void**) p, bytes));
+    CK(cudaMemsetAsync(*p, fill, bytes, h->stream));
+    h->allocs.push_back(*p);
+    if (dynamic) h->dyn.push_back({ (void*) *p, bytes });
+    return CABM_OK;
+}
+template <typename T>
+static int upload(cabm_t* h, T** p, const std::vector<T>& v) {
+    int rc = dalloc(h, p, v.size()); if (rc) return rc;
+    if (!v.empty()) CK(cudaMemcpyAsync(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return CABM_OK;
+}
+
+// ---- host-side keyed Poisson for the daily importation count (simulator.h:209) ----
+static void philox_host(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+    uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3], k0 = key[0], k1 = key[1];
+    for (int r = 0; r < 10; ++r) {
+        const uint64_t p0 = (uint64_t) 0xD2511F53u * c0, p1 = (uint64_t) 0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t) (p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t) p1, n2 = (uint32_t) (p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t) p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+static int import_count(uint64_t seed, int day, double mean) {
+    int total = 0; uint32_t chunk = 0;
+    const uint32_t key[2] = { (uint32_t) seed, (uint32_t) (seed >> 32) };
+    while (mean > 0.0) {
+        const double m = mean > 16.0 ? 16.0 : mean; mean -= m;
+        const double limit = cabm_exp(-m);
+        double prod = 1.0; int k = 0; uint32_t idx = 0, buf[4];
+        for (;;) {
+            if ((idx & 3u) == 0) { const uint32_t ctr[4] = { idx >> 2, chunk, 0u, ((uint32_t) day << 8) | CABM_P_IMPORT_COUNT }; philox_host(ctr, key, buf); }
+            prod *= (double) buf[idx & 3u] * (1.0 / 4294967296.0); idx++;
+            if (!(prod > limit)) break; ++k;
+        }
+        total += k; chunk++;
+    }
+    return total;
+}
+
+static unsigned int grid_for(const cabm_t* h, size_t n, int per_sm) {
+    const size_t want = (n + TPB - 1) / TPB;
+    return (unsigned int) std::max<size_t>(1, std::min<size_t>(want, (size_t) h->sms * per_sm));
+}
+
+static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is_weekday) {
+    c.day = day; c.julian_day = julian_day; c.is_weekday = is_weekday;
+    c.season = h->hpar.seasonality[julian_day - 1];
+    c.school_closure = h->h_ti[0][day]; c.business_closure = h->h_ti[1][day]; c.sd = h->h_ti[2][day];
+}
+
+// the launch sequence of one Community::tick (Community.cpp:1147-1192)
+static void launch_tick(cabm_t* h) {
+    const Dev& D = h->d; cudaStream_t st = h->stream;
+    const unsigned int gN = grid_for(h, D.N, 8), gL = h->sms * 4;
+    k_scan<<<gN, TPB, 0, st>>>(D);
+    k_visit<<<gN, TPB, 0, st>>>(D);
+    k_hazard<<<gL, TPB, 0, st>>>(D, 0);
+    k_expose_items<<<gL, TPB, 0, st>>>(D);
+    k_expose_visits<<<gL, TPB, 0, st>>>(D);
+    k_apply<<<h->sms, 128, 0, st>>>(D);
+    k_phase_end<<<1, 32, 0, st>>>(D);
+    k_status<<<gL, TPB, 0, st>>>(D, 0);
+    k_status<<<h->sms, TPB, 0, st>>>(D, 1);
+    k_compact_patients<<<1, TPB, 0, st>>>(D);
+    k_items_reset<<<1, 32, 0, st>>>(D);
+    k_hazard<<<gL, TPB, 0, st>>>(D, 1);
+    k_expose_items<<<h->sms, TPB, 0, st>>>(D);
+    k_expose_patients<<<h->sms, TPB, 0, st>>>(D);
+    k_apply<<<h->sms, 128, 0, st>>>(D);
+    k_end<<<gL, TPB, 0, st>>>(D);
+    k_tick_end<<<1, 32, 0, st>>>(D);
+    h->launches += 17;
+}
+static void launch_import(cabm_t* h, int advance) {
+    const Dev& D = h->d; cudaStream_t st = h->stream;
+    k_import<<<h->sms, 128, 0, st>>>(D);
+    k_apply<<<h->sms, 128, 0, st>>>(D);
+    k_import_end<<<1, 32, 0, st>>>(D, advance);
+    h->launches += 3;
+}
+
+static int ready(cabm_t* h, int day) {
+    if (!h->have_par || !h->have_pop) { h->err = "population and parameters must be set first"; return CABM_E_STATE; }
+    if (day < 0 || day >= h->hpar.run_length) { h->err = "day outside run_length"; return CABM_E_ARG; }
+    return CABM_OK;
+}
+static int check_overflow(cabm_t* h) {
+    unsigned int ov = 0;
+    CK(cudaMemcpy(&ov, &h->d.ctr->overflow, sizeof(ov), cudaMemcpyDeviceToHost));
+    if (ov & ~1u) { h->err = "device list capacity exceeded (mask " + std::to_string(ov) + ")"; return CABM_E_NOMEM; }
+    return CABM_OK;
+}
+static int timed_sync(cabm_t* h) {
+    CK(cudaEventRecord(h->e1, h->stream));
+    CK(cudaEventSynchronize(h->e1));
+    float ms = 0; CK(cudaEventElapsedTime(&ms, h->e0, h->e1)); h->acc_ms += ms;
+    CK(cudaGetLastError());
+    return CABM_OK;
+}
+
+extern "C" {
+
+int cabm_create(cabm_t** out) {
+    if (!out) return CABM_E_ARG;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { *out = nullptr; return CABM_E_NODEVICE; }
+    cabm_t* h = new (std::nothrow) cabm(); if (!h) return CABM_E_NOMEM;
+    cudaGetDevice(&h->device);
+    cudaDeviceProp prop; if (cudaGetDeviceProperties(&prop, h->device) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_NODEVICE; }
+    h->sms = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
+    cudaEventCreate(&h->e0); cudaEventCreate(&h->e1);
+    *out = h;
+    return CABM_OK;
+}
+
+int cabm_destroy(cabm_t* h) {
+    if (!h) return CABM_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    if (h->day_graph) cudaGraphExecDestroy(h->day_graph);
+    for (void* p : h->allocs) cudaFree(p);
+    if (h->h_ctx) cudaFreeHost(h->h_ctx);
+    cudaEventDestroy(h->e0); cudaEventDestroy(h->e1); cudaStreamDestroy(h->stream);
+    delete h;
+    return CABM_OK;
+}
+
+const char* cabm_last_error(const cabm_t* h) { return h ? h->err.c_str() : "null handle"; }
+
+int cabm_set_params(cabm_t* h, const cabm_params* par) {
+    if (!h || !par || !par->prob_first_detection || par->run_length <= 0 || par->run_length > 32000) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    const size_t R = (size_t) par->run_length;
+    if (h->have_par && par->run_length != h->hpar.run_length) { h->err = "run_length cannot change"; return CABM_E_STATE; }
+    if (!h->have_par) {
+        int rc;
+        if ((rc = dalloc(h, &h->d_par, 1))) return rc;
+        if ((rc = dalloc(h, &h->d_pfd, R * CABM_N_OUTCOMES))) return rc;
+        if ((rc = dalloc(h, &h->d_imr, R))) return rc;
+        if ((rc = dalloc(h, &h->d.ledger, (size_t) CABM_N_COUNTERS * R, true))) return rc;
+        if ((rc = dalloc(h, &h->d.ctr, 1, true))) return rc;
+        if ((rc = dalloc(h, &h->d_tmp_int, 4))) return rc;
+        h->ctx_cap = (int) R;
+        if ((rc = dalloc(h, &h->d_ctx, R))) return rc;
+        CK(cudaMallocHost((void**) &h->h_ctx, R * sizeof(DayCtx)));
+        for (int t = 0; t < 3; ++t) h->h_ti[t].assign(R, 0.0);
+    }
+    h->hpar = *par;
+    CK(cudaMemcpyAsync(h->d_pfd, par->prob_first_detection, R * CABM_N_OUTCOMES * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (par->icu_mortality_reduction) CK(cudaMemcpyAsync(h->d_imr, par->icu_mortality_reduction, R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    h->hpar.prob_first_detection = nullptr; h->hpar.icu_mortality_reduction = nullptr;
+    CK(cudaMemcpyAsync(h->d_par, &h->hpar, sizeof(cabm_params), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    h->d.par = h->d_par; h->d.pfd = h->d_pfd; h->d.imr = h->d_imr; h->d.n_imr = par->icu_mortality_reduction ? (int) R : 0;
+    h->d.R = (int) R; h->d.dayctx = h->d_ctx;
+    h->have_par = true;
+    return CABM_OK;
+}
+
+int cabm_set_timed_intervention(cabm_t* h, int which, const double* v, size_t n) {
+    if (!h || !h->have_par || which < 0 || which > 2 || !v || n == 0) return CABM_E_ARG;
+    const size_t R = (size_t) h->hpar.run_length;
+    for (size_t d = 0; d < R; ++d) h->h_ti[which][d] = v[std::min(d, n - 1)];
+    return CABM_OK;
+}
+
+int cabm_load_population(cabm_t* h, const cabm_population* pop) {
+    if (!h || !pop) return CABM_E_ARG;
+    if (!h->have_par) { h->err = "cabm_set_params must precede cabm_load_population"; return CABM_E_STATE; }
+    if (h->have_pop) { h->err = "population already loaded"; return CABM_E_STATE; }
+    if (!pop->starting_natural_efficacy || !pop->cross_protection_probability || !pop->natural_immunity_duration) {
+        h->err = "load-time immunity attributes are required"; return CABM_E_ARG; }
+    if (pop->n_patron > PB_NPAT) { h->err = "at most 7 patronised locations per person"; return CABM_E_ARG; }
+    cudaSetDevice(h->device);
+    const uint32_t N = pop->n_people, L = pop->n_loc, NP = pop->n_patron;
+    Dev& D = h->d; D.N = N; D.L = L; D.n_patron = std::max<uint32_t>(NP, 1);
+    int rc;
+    // ---- static agents ----
+    std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N), patron((size_t) N * D.n_patron, -1);
+    std::vector<unsigned char> age(pop->age, pop->age + N), pflags(N), pbyte(N, 0);
+    std::vector<float> home_risk(N);
+    for (uint32_t p = 0; p < N; ++p) {
+        if (home[p] < 0 || (uint32_t) home[p] >= L || dayl[p] >= (int) L) { h->err = "home/day location out of range"; return CABM_E_ARG; }
+        pflags[p] = (pop->comorbid[p] ? PF_COMORBID : 0) | (pop->ltc[p] ? PF_LTC : 0);
+        home_risk[p] = pop->loc_risk[home[p]];
+        unsigned int np = 0;
+        for (uint32_t k = 0; k < NP; ++k) {
+            const int loc = pop->patron[(size_t) p * NP + k]; if (loc < 0) break;
+            if ((uint32_t) loc >= L) { h->err = "patronised location out of range"; return CABM_E_ARG; }
+            patron[(size_t) p * D.n_patron + k] = loc | (pop->loc_pubrisk[loc] == CABM_PT_HIGH ? PATRON_HIGH : 0); np++;
+        }
+        pbyte[p] = (unsigned char) np;
+    }
+    std::vector<double> nat_eff(pop->starting_natural_efficacy, pop->starting_natural_efficacy + N);
+    std::vector<float> xprot(pop->cross_protection_probability, pop->cross_protection_probability + N);
+    std::vector<int> nat_dur(pop->natural_immunity_duration, pop->natural_immunity_duration + N);
+    if ((rc = upload(h, (int**) &D.home, home)) || (rc = upload(h, (int**) &D.day_loc, dayl)) || (rc = upload(h, (int**) &D.patron, patron)) ||
+        (rc = upload(h, (unsigned char**) &D.age, age)) || (rc = upload(h, (unsigned char**) &D.pflags, pflags)) ||
+        (rc = upload(h, (float**) &D.home_risk, home_risk)) || (rc = upload(h, (double**) &D.nat_eff, nat_eff)) ||
+        (rc = upload(h, (float**) &D.xprot, xprot)) || (rc = upload(h, (int**) &D.nat_dur, nat_dur))) return rc;
+    // ---- static locations ----
+    std::vector<unsigned char> ltype(pop->loc_type, pop->loc_type + L), lflags(L);
+    for (uint32_t l = 0; l < L; ++l) lflags[l] = (pop->loc_essential[l] ? LF_ESSENTIAL : 0) | ((pop->loc_pubrisk[l] & 3) << 1);
+    std::vector<float> lrisk(pop->loc_risk, pop->loc_risk + L);
+    std::vector<int> lhosp(pop->loc_hospital, pop->loc_hospital + L);
+    if (pop->roster_off[L] >= (int64_t) 0xFFFFFFFFll || pop->nbr_off[L] >= (int64_t) 0xFFFFFFFFll) { h->err = "CSR too large"; return CABM_E_ARG; }
+    std::vector<unsigned int> roff(L + 1), noff(L + 1);
+    for (uint32_t l = 0; l <= L; ++l) { roff[l] = (unsigned int) pop->roster_off[l]; noff[l] = (unsigned int) pop->nbr_off[l]; }
+    std::vector<int> roster(pop->roster, pop->roster + pop->roster_off[L]), nbr(pop->nbr, pop->nbr + pop->nbr_off[L]);
+    if ((rc = upload(h, (unsigned char**) &D.loc_type, ltype)) || (rc = upload(h, (unsigned char**) &D.loc_flags, lflags)) ||
+        (rc = upload(h, (float**) &D.loc_risk, lrisk)) || (rc = upload(h, (int**) &D.loc_hospital, lhosp)) ||
+        (rc = upload(h, (unsigned int**) &D.roster_off, roff)) || (rc = upload(h, (unsigned int**) &D.nbr_off, noff)) ||
+        (rc = upload(h, (int**) &D.roster, roster)) || (rc = upload(h, (int**) &D.nbr, nbr))) return rc;
+    // ---- dynamic state ----
+    if ((rc = dalloc(h, &D.win, N, true)) || (rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
+        (rc = dalloc(h, &D.imm, N, true)) || (rc = dalloc(h, &D.vax, N, true)) || (rc = dalloc(h, &D.vax_days, (size_t) N * CABM_MAX_DOSES, true)) ||
+        (rc = dalloc(h, &D.quar, N, true)) || (rc = dalloc(h, &D.hosp_count, N, true)) || (rc = dalloc(h, &D.pbyte, N, true)) ||
+        (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.hot_idx, L)) ||
+        (rc = dalloc(h, &D.nvis, L)) || (rc = dalloc(h, &D.pat_count, L, true))) return rc;
+    CK(cudaMemcpyAsync(D.pbyte, pbyte.data(), N, cudaMemcpyHostToDevice, h->stream));
+    // ---- day lists ----
+    D.cap_hot = L; D.cap_active = N; D.cap_vis = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
+    D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, (size_t) 2 * L + nbr.size() + roster.size() / CHUNK + 1024);
+    D.cap_log = (unsigned long long) 3 * N + 1024;
+    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, D.cap_hot)) || (rc = dalloc(h, &D.hot_Ts, D.cap_hot)) ||
+        (rc = dalloc(h, &D.hot_size, D.cap_hot)) || (rc = dalloc(h, &D.active_list, D.cap_active)) || (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
+        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) || (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) ||
+        (rc = dalloc(h, &D.patient_tmp, D.cap_pat)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||
+        (rc = dalloc(h, &D.n_foi, 1))) return rc;
+    k_init_state<<<grid_for(h, std::max(N, L), 8), TPB, 0, h->stream>>>(D);
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    h->have_pop = true;
+    return CABM_OK;
+}
+
+int cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday) {
+    if (!h) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (julian_day < 1 || julian_day > 366) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
+    fill_ctx(h, c, sim_day, julian_day, is_weekday);
+    CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
+    CK(cudaEventRecord(h->e0, h->stream));
+    launch_tick(h);
+    if ((rc = timed_sync(h))) return rc;
+    return check_overflow(h);
+}
+
+int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[CABM_N_STRAINS], int32_t* out_infected) {
+    if (!h || !strain_w) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    cudaSetDevice(h->device);
+    DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
+    c.day = sim_day; c.julian_day = 1; c.n_imports = expected > 0 ? import_count(h->hpar.seed, sim_day, expected) : 0;
+    for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
+    CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
+    CK(cudaEventRecord(h->e0, h->stream));
+    const Dev& D = h->d;
+    k_import<<<h->sms, 128, 0, h->stream>>>(D);
+    k_apply<<<h->sms, 128, 0, h->stream>>>(D);
+    if (out_infected) CK(cudaMemcpyAsync(out_infected, &D.ctr->n_new, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    k_import_end<<<1, 32, 0, h->stream>>>(D, 0);
+    h->launches += 3;
+    if ((rc = timed_sync(h))) return rc;
+    return check_overflow(h);
+}
+
+int cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected) {
+    if (!h) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (pid >= h->d.N || strain < 0 || strain >= CABM_N_STRAINS) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    k_seed_one<<<1, 32, 0, h->stream>>>(h->d, pid, strain, sim_day, h->d_tmp_int);
+    int res = 0;
+    CK(cudaMemcpyAsync(&res, h->d_tmp_int, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    if (out_infected) *out_infected = res;
+    return CABM_OK;
+}
+
+int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
+                  const double* expected_imports, const double* strain_w) {
+    if (!h || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;
+    int rc = ready(h, first_day); if (rc) return rc; if ((rc = ready(h, first_day + n_days - 1))) return rc;
+    cudaSetDevice(h->device);
+    for (int i = 0; i < n_days; ++i) {
+        DayCtx& c = h->h_ctx[i]; std::memset(&c, 0, sizeof(c));
+        if (julian_day[i] < 1 || julian_day[i] > 366) return CABM_E_ARG;
+        fill_ctx(h, c, first_day + i, julian_day[i], is_weekday[i]);
+        c.n_imports = expected_imports[i] > 0 ? import_count(h->hpar.seed, first_day + i, expected_imports[i]) : 0;
+        for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[(size_t) i * CABM_N_STRAINS + s];
+    }
+    CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, (size_t) n_days * sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
+    if (!h->day_graph) {             // capture one day (tick + importation) once; every day replays the same graph
+        cudaGraph_t g = nullptr;
+        CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+        const uint64_t l0 = h->launches;
+        launch_tick(h); launch_import(h, 1);
+        h->launches = l0;
+        CK(cudaStreamEndCapture(h->stream, &g));
+        CK(cudaGraphInstantiate(&h->day_graph, g, 0));
+        cudaGraphDestroy(g);
+    }
+    CK(cudaEventRecord(h->e0, h->stream));
+    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += 20; }
+    if ((rc = timed_sync(h))) return rc;
+    return check_overflow(h);
+}
+
+int cabm_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_ok) {
+    if (!h || (!pids && n)) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (!h->hpar.immunity_leaky) { h->err = "vaccination requires leaky immunity (Person.cpp:622)"; return CABM_E_STATE; }
+    if (n == 0) return CABM_OK;
+    for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    unsigned int* d_p = nullptr; unsigned char* d_ok = nullptr;
+    CK(cudaMalloc(&d_p, n * sizeof(unsigned int))); CK(cudaMalloc(&d_ok, n));
+    CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    k_vaccinate<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, d_p, (unsigned int) n, sim_day, d_ok);
+    std::vector<unsigned char> ok(n);
+    CK(cudaMemcpyAsync(ok.data(), d_ok, n, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    cudaFree(d_p); cudaFree(d_ok);
+    if (out_ok) std::memcpy(out_ok, ok.data(), n);
+    return CABM_OK;
+}
+
+int cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, int until_day) {
+    if (!h || (!pids && n)) return CABM_E_ARG;
+    if (!h->have_pop) return CABM_E_STATE;
+    if (n == 0) return CABM_OK;
+    for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    unsigned int* d_p = nullptr;
+    CK(cudaMalloc(&d_p, n * sizeof(unsigned int)));
+    CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    k_quarantine<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, d_p, (unsigned int) n, from_day, std::min(until_day, 32766));
+    CK(cudaStreamSynchronize(h->stream));
+    cudaFree(d_p);
+    if (!h->d.any_quarantine) { h->d.any_quarantine = 1; if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; } }
+    return CABM_OK;
+}
+
+int cabm_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n) {
+    if (!h || !h->have_par || counter < 0 || counter >= CABM_N_COUNTERS || !out) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    const size_t R = (size_t) h->hpar.run_length, m = std::min(n, R);
+    CK(cudaMemcpy(out, h->d.ledger + (size_t) counter * R, m * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    for (size_t d = m; d < n; ++d) out[d] = 0;
+    return CABM_OK;
+}
+int cabm_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]) {
+    if (!h || !out) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    cudaSetDevice(h->device);
+    CK(cudaMemcpy2D(out, sizeof(uint64_t), h->d.ledger + sim_day, (size_t) h->hpar.run_length * sizeof(uint64_t), sizeof(uint64_t), CABM_N_COUNTERS, cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+int cabm_cumulative_outcomes(cabm_t* h, uint64_t out[CABM_N_OUTCOMES]) {
+    if (!h || !h->have_par || !out) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    CK(cudaMemcpy(out, h->d.ctr->cumul, sizeof(uint64_t) * CABM_N_OUTCOMES, cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+int cabm_work_counters(cabm_t* h, uint64_t out[CABM_N_WORK]) {
+    if (!h || !h->have_par || !out) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    CK(cudaMemcpy(out, h->d.ctr->work, sizeof(uint64_t) * CABM_N_WORK, cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+
+int cabm_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_n) {
+    if (!h || !h->have_pop) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    unsigned long long n = 0;
+    CK(cudaMemcpy(&n, &h->d.ctr->n_log, sizeof(n), cudaMemcpyDeviceToHost));
+    n = std::min<unsigned long long>(n, h->d.cap_log);
+    if (out_n) *out_n = (size_t) n;
+    if (out && cap) CK(cudaMemcpy(out, h->d.log, std::min<size_t>(cap, (size_t) n) * sizeof(cabm_infection), cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+
+int cabm_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infection* out) {
+    if (!h || !h->have_pop || !out) return CABM_E_ARG;
+    if (n == 0) return CABM_OK;
+    if (pids) { for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG; } else if (n > h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    unsigned int* d_p = nullptr; cabm_infection* d_o = nullptr;
+    CK(cudaMalloc(&d_o, n * sizeof(cabm_infection)));
+    if (pids) { CK(cudaMalloc(&d_p, n * sizeof(unsigned int))); CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream)); }
+    k_gather_infections<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, d_p, (unsigned int) n, d_o);
+    CK(cudaMemcpyAsync(out, d_o, n * sizeof(cabm_infection), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    cudaFree(d_o); if (d_p) cudaFree(d_p);
+    return CABM_OK;
+}
+
+int cabm_snapshot(cabm_t* h, cabm_snap_t** out) {
+    if (!h || !out || !h->have_pop) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    cabm_snap_t* s = new cabm_snap();
+    for (auto& b : h->dyn) {
+        void* p = nullptr; CK(cudaMalloc(&p, b.second));
+        CK(cudaMemcpyAsync(p, b.first, b.second, cudaMemcpyDeviceToDevice, h->stream));
+        s->bufs.push_back({ p, b.second });
+    }
+    CK(cudaMemcpy(&s->n_log, &h->d.ctr->n_log, sizeof(s->n_log), cudaMemcpyDeviceToHost));
+    s->n_log = std::min<unsigned long long>(s->n_log, h->d.cap_log);
+    if (s->n_log) { CK(cudaMalloc(&s->log, s->n_log * sizeof(cabm_infection))); CK(cudaMemcpyAsync(s->log, h->d.log, s->n_log * sizeof(cabm_infection), cudaMemcpyDeviceToDevice, h->stream)); }
+    CK(cudaStreamSynchronize(h->stream));
+    *out = s;
+    return CABM_OK;
+}
+int cabm_restore(cabm_t* h, const cabm_snap_t* s) {
+    if (!h || !s || s->bufs.size() != h->dyn.size()) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    for (size_t i = 0; i < s->bufs.size(); ++i) CK(cudaMemcpyAsync(h->dyn[i].first, s->bufs[i].first, s->bufs[i].second, cudaMemcpyDeviceToDevice, h->stream));
+    if (s->n_log) CK(cudaMemcpyAsync(h->d.log, s->log, s->n_log * sizeof(cabm_infection), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return CABM_OK;
+}
+int cabm_snap_free(cabm_snap_t* s) {
+    if (!s) return CABM_OK;
+    for (auto& b : s->bufs) cudaFree(b.first);
+    if (s->log) cudaFree(s->log);
+    delete s;
+    return CABM_OK;
+}
+
+int cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n) {
+    if (!h || !h->have_pop) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    if (!h->d.foi_enabled) {       // first call switches the (otherwise skipped) row writes on; rows exist from the next tick
+        h->d.foi_enabled = 1; if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; }
+        if (out_n) *out_n = 0; return CABM_OK;
+    }
+    unsigned int n = 0;
+    CK(cudaMemcpy(&n, h->d.n_foi, sizeof(n), cudaMemcpyDeviceToHost));
+    if (out_n) *out_n = n;
+    if (out && cap) CK(cudaMemcpy(out, h->d.foi, std::min<size_t>(cap, n) * sizeof(cabm_foi_row), cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+
+int cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches) {
+    if (!h) return CABM_E_ARG;
+    if (out_ms) *out_ms = h->acc_ms; if (out_launches) *out_launches = h->launches;
+    h->acc_ms = 0.0; h->launches = 0;
+    return CABM_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,151 @@
+// covid-abm_b200/csrc/cabm_device.cuh -- device-side state layout, Philox stream and the
+// per-exposure state-transition sampler (Person::infect, Person.cpp:320-494) for sm_100a.
+//
+// Layout (all structure-of-arrays in HBM, one element per agent / location):
+//   agents   : win (active window), tl0/tl1 (latest Infection, 2 x 16 B), imm (infections per strain),
+//              vax (doses, last dose day, naive flag), quar, hosp_count, pbyte (patron count | flags),
+//              cand (64-bit winner key of today's exposure resolution)
+//   locations: press[4] (u64 fixed-point infectious pressure by strain, 2^-32 units), hot_idx, nvis,
+//              pat_count + static type/flags/risk/hospital, roster CSR, neighbour CSR
+// Day-scoped lists (hot locations, active agents, visits landing on hot locations, exposure work
+// items, newly infected agents) are appended with atomics and consumed by grid-stride kernels, so
+// a whole day runs without returning to the host.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/cabm.h"
+#include "../../include/cabm_det_math.h"
+
+#define CABM_I16_MAX 32767
+#define CABM_I16_MIN (-32768)
+#define CABM_CAND_EMPTY 0xFFFFFFFFFFFFFFFFull
+
+// exposure passes in tick() order (Community.cpp:1151-1171); the winner key sorts by (pass, source, role)
+enum { PASS_HH = 3, PASS_NB = 4, PASS_WORK = 5, PASS_SCHOOL = 7, PASS_NH = 8, PASS_HOSP = 9, PASS_IMPORT = 11, PASS_SEED = 12 };
+
+struct __align__(16) Tl0 { short infected, infectious_begin, infectious_end, symptom_begin, symptom_end, severe_begin, severe_end, hosp_begin; };
+struct __align__(16) Tl1 { short critical_begin, critical_end, icu_begin, death, report_day; unsigned char strain, detected; float rel_inf; };
+
+struct Item { int src; int begin; int count; int purpose; double T; };          // one exposure work item (a roster chunk)
+
+struct DayCtx {                     // per-day scalars, staged by the host for every day of a run_days() batch
+    int day, julian_day, is_weekday, n_imports;
+    double strain_w[CABM_N_STRAINS];
+    double season, sd, school_closure, business_closure;
+};
+
+// counters living in device memory (zeroed at end of day unless noted)
+struct Counters {
+    unsigned int n_hot, n_active, n_vis, n_items, n_new, n_new_applied, n_pat /*persistent*/, n_pat_tmp;
+    unsigned int overflow;                                   // sticky: a list ran out of capacity
+    unsigned int day_idx;                                    // persistent: index into the staged DayCtx array
+    unsigned long long n_log;                                // persistent
+    unsigned long long work[CABM_N_WORK];                    // persistent
+    unsigned long long cumul[CABM_N_OUTCOMES];               // persistent
+    unsigned int seed_calls;                                 // persistent
+};
+
+struct Dev {
+    // sizes
+    unsigned int N, L, n_patron; int R;
+    // static agents
+    const int* home; const int* day_loc; const int* patron; const unsigned char* age; const unsigned char* pflags;
+    const double* nat_eff; const float* xprot; const int* nat_dur; const float* home_risk;
+    // static locations
+    const unsigned char* loc_type; const unsigned char* loc_flags; const float* loc_risk; const int* loc_hospital;
+    const unsigned int* roster_off; const int* roster; const unsigned int* nbr_off; const int* nbr;
+    // dynamic agents
+    unsigned int* win; Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
+    unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand;
+    // dynamic locations
+    unsigned long long* press; int* hot_idx; unsigned int* nvis; unsigned int* pat_count;
+    // day lists
+    int* hot_list; double* hot_T; double* hot_Ts; unsigned int* hot_size;
+    unsigned int* active_list; uint2* visit_rec; Item* items; unsigned int* newinf_list; unsigned int* patient_list; unsigned int* patient_tmp;
+    unsigned int cap_hot, cap_active, cap_vis, cap_items, cap_new, cap_pat; unsigned long long cap_log;
+    // outputs
+    unsigned long long* ledger;          // [CABM_N_COUNTERS][R]
+    cabm_infection* log; cabm_foi_row* foi; unsigned int* n_foi; int foi_enabled;
+    Counters* ctr; const DayCtx* dayctx;
+    // parameters
+    const cabm_params* par; const double* pfd; const double* imr; int n_imr; const double* ti; // ti[3][R]
+    int any_quarantine;
+};
+
+// pflags bits
+#define PF_COMORBID 1
+#define PF_LTC 2
+// pbyte: low 3 bits patron count, bit 7 in hospital today, bit 6 newly infected today
+#define PB_NPAT 7
+#define PB_NEW 0x40
+#define PB_INHOSP 0x80
+// loc_flags: bit0 essential, bits 1-2 public transmission risk
+#define LF_ESSENTIAL 1
+#define LF_PUBRISK(f) (((f) >> 1) & 3)
+#define PATRON_HIGH 0x40000000
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10, counter = (sub<<16 | block, a, b, day<<8 | purpose), key = seed
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const unsigned int hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const unsigned int hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+
+struct Stream {
+    uint2 key; unsigned int a, b, dp, sub, idx; uint4 buf;
+    __device__ __forceinline__ void begin(unsigned long long seed, unsigned int day, unsigned int purpose, unsigned int a_, unsigned int b_, unsigned int sub_ = 0) {
+        key = make_uint2((unsigned int) seed, (unsigned int) (seed >> 32)); a = a_; b = b_; dp = (day << 8) | (purpose & 0xFFu); sub = sub_; idx = 0;
+    }
+    __device__ __forceinline__ unsigned int next() {
+        const unsigned int lane = idx & 3u;
+        if (lane == 0) buf = philox4x32_10(make_uint4((sub << 16) | (idx >> 2), a, b, dp), key);
+        idx++;
+        return lane == 0 ? buf.x : lane == 1 ? buf.y : lane == 2 ? buf.z : buf.w;
+    }
+    __device__ __forceinline__ double u01() { return (double) next() * (1.0 / 4294967296.0); }
+};
+
+__device__ __forceinline__ unsigned int table_draw(const double* __restrict__ cdf, int n, double u) {
+    int k = 0; while (k < n - 1 && !(u < cdf[k])) ++k; return (unsigned int) k;
+}
+// Parameters::sampler (Parameters.h:433-436)
+__device__ __forceinline__ int ref_sampler(const double* __restrict__ cdf, int n, double r) {
+    int i = 0; while (i < n && cdf[i] < r) ++i; return i;
+}
+
+__device__ __forceinline__ int pick_strain(const unsigned long long* __restrict__ w, unsigned int x) {
+    const unsigned long long w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
+    const unsigned long long total = w0 + w1 + w2 + w3;
+    unsigned long long t = (unsigned long long) x * (total >> 32) + (((unsigned long long) x * (total & 0xffffffffull)) >> 32);
+    if (t < w0) return 0; t -= w0;
+    if (t < w1) return 1; t -= w1;
+    if (t < w2) return 2;
+    return 3;
+}
+
+// Parameters::remainingEfficacy (Parameters.h:611-625)
+__device__ __forceinline__ double remaining_efficacy(const cabm_params* __restrict__ par, double start, double time_delta) {
+    if (!par->immunity_wanes) return start;
+    const double slope = 0.2, intcpt = 2.4603816;
+    const double month_delta = CABM_DIV(time_delta, 30.0);
+    const double est = CABM_DIV(CABM_ADD(cabm_log(CABM_SUB(CABM_DIV(1.0, start), 1.0)), intcpt), slope);
+    const double l = CABM_SUB(intcpt, CABM_MUL(slope, CABM_ADD(est, month_delta)));
+    return cabm_logistic(l);
+}
+
+__device__ __forceinline__ bool tl_in(short b, short e, int now) { return b <= now && now < e; }
+
+__device__ __forceinline__ unsigned long long make_key(int pass, unsigned int src, unsigned int role) {
+    return ((unsigned long long) pass << 40) | ((unsigned long long) src << 8) | (unsigned long long) (role & 0xFFu);
+}
+
+__device__ __forceinline__ void ledger_add(const Dev& D, int counter, long day) {
+    if (day >= 0 && day < (long) D.R) atomicAdd(&D.ledger[(size_t) counter * D.R + day], 1ull);
+}

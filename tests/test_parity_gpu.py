@@ -1,0 +1,147 @@
+"""Parity of the CUDA day pipeline against the CPU oracle, through the C ABI (run with -m gpu).
+
+Bar (BASELINE.json north_star): integer state transitions bit-exact under the shared Philox stream;
+per-location force of infection within rtol 1e-6 (here it is bit-equal as well, because both sides
+accumulate pressure in 2^-32 fixed point and share cabm_exp).
+"""
+import numpy as np
+import pytest
+
+import covid_abm_b200 as cabm
+import synthpop
+import oracle_lib
+
+pytestmark = pytest.mark.gpu
+
+FOI_RTOL = 1e-6
+
+
+def make_pair(n, days, seed=5, T=0.10, pde=1e-3, mutants=(), pop_seed=11):
+    pop = synthpop.generate(n, seed=pop_seed)
+    P = cabm.params.default_params(run_length=days, seed=seed, T=T, prob_daily_exposure=pde, mutant_intro_dates=mutants)
+    tab = cabm.params.build_tables(P)
+    attrs = cabm.abi.immunity_attributes(int(pop["n_people"]), P["seed"])
+    g = cabm.Community(P, pop, tab, attrs=attrs)
+    o = oracle_lib.oracle_community(P, pop, tab, attrs=attrs)
+    return pop, P, g, o
+
+
+def assert_same_state(g, o, day_label=""):
+    lg, lo = g.ledger_table(), o.ledger_table()
+    bad = np.argwhere(lg != lo)
+    assert bad.size == 0, f"{day_label} ledger differs first at (day, counter) {bad[:5].tolist()}: gpu {lg[tuple(bad[0])]} oracle {lo[tuple(bad[0])]}"
+    assert np.array_equal(g.getCumulIncidenceByOutcome(), o.getCumulIncidenceByOutcome())
+    cg, co = g.current_infections(), o.current_infections()
+    diff = np.flatnonzero(cg != co)
+    assert diff.size == 0, f"{day_label} {diff.size} agents differ, first {diff[:3]}: gpu {cg[diff[:1]]} oracle {co[diff[:1]]}"
+
+
+def sorted_hist(c):
+    h = c.infection_histories()
+    return h[np.lexsort((h["t"][:, 0], h["person"]))]
+
+
+def test_small_community_daily_state_bit_exact():
+    pop, P, g, o = make_pair(20000, 60, T=0.12, pde=2e-3)
+    g.foi(); o.foi()
+    for c in (g, o):
+        for pid in range(0, 3000, 7):
+            c.infect(pid, 0, 0)
+    for d in range(60):
+        g.step(); o.step()
+        if d % 10 == 9 or d < 3:
+            assert_same_state(g, o, f"day {d}")
+    assert g.getNumNewlyInfected().sum() > 500          # the epidemic actually ran
+    hg, ho = sorted_hist(g), sorted_hist(o)
+    assert hg.size == ho.size and np.array_equal(hg, ho)
+
+
+def test_force_of_infection_rows():
+    pop, P, g, o = make_pair(30000, 30, T=0.15, pde=3e-3, seed=9)
+    g.foi(); o.foi()
+    for c in (g, o):
+        for pid in range(0, 5000, 5):
+            c.infect(pid, 0, 0)
+    seen = set()
+    for d in range(30):
+        g.tick(d); o.tick(d)
+        fg, fo = g.foi(), o.foi()
+        assert fg.size == fo.size and np.array_equal(fg["loc"], fo["loc"]), f"day {d}: hot sets differ"
+        assert np.array_equal(fg["size"], fo["size"])
+        np.testing.assert_allclose(fg["w"], fo["w"], rtol=FOI_RTOL, atol=0)
+        np.testing.assert_allclose(fg["T"], fo["T"], rtol=FOI_RTOL, atol=0)
+        np.testing.assert_allclose(fg["T_social"], fo["T_social"], rtol=FOI_RTOL, atol=0)
+        seen |= set(np.unique(fg["type"][fg["T"] > 0]).tolist())
+        g.update_strain_mix(d); o.update_strain_mix(d)
+        assert g.seed_epidemic(d) == o.seed_epidemic(d)
+        g.day = o.day = d + 1
+    assert seen == {0, 1, 2, 3, 4}, f"location types with positive hazard: {seen}"
+
+
+def test_multi_variant_vaccination_quarantine():
+    mut = ("2020-02-20", "2020-03-05", "2020-03-20")
+    pop, P, g, o = make_pair(25000, 75, T=0.14, pde=3e-3, mutants=mut, seed=21)
+    rng = np.random.default_rng(0)
+    n = int(pop["n_people"])
+    for c in (g, o):
+        for pid in range(0, 4000, 9):
+            c.infect(pid, 0, 0)
+    for d in range(75):
+        if d in (10, 31, 52):                      # three dose rounds (Person::vaccinate)
+            pids = rng.choice(n, size=n // 3, replace=False)
+            ok_g, ok_o = g.vaccinate(pids, d), o.vaccinate(pids, d)
+            assert np.array_equal(ok_g, ok_o)
+        if d in (20, 40):                          # self-quarantine windows (Person::scheduleQuarantine)
+            pids = rng.choice(n, size=n // 10, replace=False)
+            g.quarantine(pids, d, d + 10); o.quarantine(pids, d, d + 10)
+        g.step(); o.step()
+        if d % 15 == 14:
+            assert_same_state(g, o, f"day {d}")
+    assert_same_state(g, o, "end")
+    strains = g.ledger_table()[:, 16:20].sum(axis=0)
+    assert (strains > 0).sum() >= 3, f"variants seen: {strains}"
+    assert g.ledger("vaccinated_cases").sum() > 0
+
+
+def test_run_days_graph_equals_stepwise():
+    pop, P, g, o = make_pair(20000, 50, T=0.12, pde=2e-3, seed=33)
+    for c in (g, o):
+        for pid in range(0, 2000, 4):
+            c.infect(pid, 0, 0)
+    g.run_days(25); g.run_days(25)
+    for _ in range(50):
+        o.step()
+    assert_same_state(g, o, "run_days")
+    w = g.work_counters()
+    assert w["agents"] == 50 * int(pop["n_people"]) and w["infections"] == o.work_counters()["infections"]
+
+
+def test_snapshot_restore_replays_identically():
+    pop, P, g, o = make_pair(15000, 40, T=0.12, pde=2e-3, seed=41)
+    for pid in range(0, 1500, 3):
+        g.infect(pid, 0, 0)
+    g.run_days(15)
+    snap = g.snapshot()
+    g.run_days(25)
+    first = g.ledger_table().copy(); cur = g.current_infections().copy()
+    g.restore(snap)
+    g.run_days(25)
+    assert np.array_equal(first, g.ledger_table()) and np.array_equal(cur, g.current_infections())
+    g.snap_free(snap)
+
+
+def test_edge_cases_empty_and_tiny():
+    # no infections at all: nothing is hot, nothing happens
+    pop, P, g, o = make_pair(3000, 10, T=0.1, pde=0.0, seed=2)
+    for d in range(10):
+        g.step(); o.step()
+    assert g.ledger_table().sum() == 0 and o.ledger_table().sum() == 0
+    assert g.work_counters()["hot_locs"] == 0
+    # a tiny community below the nursing-home threshold, everyone seeded
+    pop, P, g, o = make_pair(300, 30, T=0.3, pde=0.0, seed=4)
+    for c in (g, o):
+        for pid in range(int(pop["n_people"])):
+            c.infect(pid, 1, 0)
+    for d in range(30):
+        g.step(); o.step()
+    assert_same_state(g, o, "tiny")
