@@ -263,7 +263,7 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     if ((rc = dalloc(h, &D.win, N, true)) || (rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
         (rc = dalloc(h, &D.imm, N, true)) || (rc = dalloc(h, &D.vax, N, true)) || (rc = dalloc(h, &D.vax_days, (size_t) N * CABM_MAX_DOSES, true)) ||
         (rc = dalloc(h, &D.quar, N, true)) || (rc = dalloc(h, &D.hosp_count, N, true)) || (rc = dalloc(h, &D.pbyte, N, true)) ||
-        (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.hot_idx, L)) ||
+        (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.inf_place, N, true, 0xFF)) || (rc = dalloc(h, &D.inf_by, N, true, 0xFF)) || (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.hot_idx, L)) ||
         (rc = dalloc(h, &D.nvis, L)) || (rc = dalloc(h, &D.pat_count, L, true))) return rc;
     CK(cudaMemcpyAsync(D.pbyte, pbyte.data(), N, cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----

@@ -56,7 +56,7 @@ struct Dev {
     const unsigned int* roster_off; const int* roster; const unsigned int* nbr_off; const int* nbr;
     // dynamic agents
     unsigned int* win; Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
-    unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand;
+    unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand; int* inf_place; int* inf_by;
     // dynamic locations
     unsigned long long* press; int* hot_idx; unsigned int* nvis; unsigned int* pat_count;
     // day lists

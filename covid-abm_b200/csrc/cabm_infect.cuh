@@ -182,6 +182,7 @@ __device__ __noinline__ bool infect_event(const Dev& D, Stream& s, const InfectC
     n1.death = (short) t_death; n1.report_day = (short) report_day; n1.strain = (unsigned char) strain; n1.detected = (unsigned char) detected_state;
     n1.rel_inf = rel_inf;
     D.tl0[pid] = n0; D.tl1[pid] = n1;
+    D.inf_place[pid] = c.has_source ? c.source : -1; D.inf_by[pid] = -1;
     int until = max(max(t_infectious_end, t_symptom_end), max(t_severe_end, t_critical_end));
     if (t_death != CABM_I16_MAX) until = max(until, t_death);
     if (report_day != CABM_I16_MAX) until = max(until, report_day);

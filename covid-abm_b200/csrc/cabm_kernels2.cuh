@@ -215,6 +215,7 @@ __global__ void k_gather_infections(const Dev D, const unsigned int* pids, const
             r.t[0] = a.infected; r.t[1] = a.infectious_begin; r.t[2] = a.infectious_end; r.t[3] = a.symptom_begin; r.t[4] = a.symptom_end;
             r.t[5] = a.severe_begin; r.t[6] = a.severe_end; r.t[7] = a.hosp_begin; r.t[8] = b.critical_begin; r.t[9] = b.critical_end;
             r.t[10] = b.icu_begin; r.t[11] = b.death; r.report_day = b.report_day; r.strain = b.strain; r.detected_state = b.detected; r.rel_infectiousness = b.rel_inf;
+            r.infected_place = D.inf_place[p]; r.infected_by = D.inf_by[p];
         } else {
             for (int k = 0; k < 12; ++k) r.t[k] = CABM_I16_MAX;
             r.t[2] = r.t[4] = r.t[6] = r.t[9] = CABM_I16_MIN;
