@@ -1,0 +1,289 @@
+#!/usr/bin/env python3
+"""Benchmark of the daily transmission cycle: agent-days/s on synthetic populations (BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" is DAYS_PER_STEP consecutive simulated days (Community::tick + daily importation) of the
+Miami-Dade-scale configuration: ~2.7 M synthetic agents, wild type + alpha + delta entering inside
+the window, the active-vac parameter set (covid-abm_b200/params.py). Every rank prints nothing; rank 0
+prints ONE JSON line.
+
+  value      device-timed whole-job agent-days/s with all state resident in HBM (CUDA-graph replay of the
+             day pipeline, CUDA events on the library's stream, max over ranks)
+  e2e        the same days driven the way simulator.h drives them: one cabm_tick + cabm_import +
+             ledger-row read per day through the C ABI with host buffers (H2D of the day context,
+             D2H of the ledger row and import count inside the timed region)
+  roofline   dominant kernel of the pipeline: algorithmic bytes (SURVEY.md 8d byte model, counted on
+             device) / its CUDA-event time, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline  the unmodified reference (oracle/_ref/ref_driver) on one host core, first days of the
+             same workload
+
+With --gpus N > 1 (torchrun, one rank per GPU) each rank advances an independent replicate of the
+same population (seed 1 + rank) -- the reference's own scaling mode (SLURM arrays of replicates);
+no collective sits on the data path ("scaling": "weak").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+DAYS_PER_STEP = 10
+N_AGENTS = int(os.environ.get("CABM_BENCH_AGENTS", 2_700_000))
+MUTANTS = ("2020-03-21", "2020-05-20", "2030-01-01")          # alpha ~day 40, delta ~day 100 (start 2020-02-10)
+REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+BYTES = dict(agents=4, active=40, flags=12, patrons=16.6, visits=4, hot_visits=20, hot_locs=28, nbr_edges=8, trials=10, infections=64)
+KERNEL_TERMS = {     # which byte-model terms each kernel moves (DESIGN.md "kernels")
+    "k_scan": ("agents", "active", "flags"), "k_visit": ("patrons", "visits", "hot_visits"),
+    "k_hazard": ("hot_locs", "nbr_edges"), "k_expose_items": ("trials",), "k_apply": ("infections",),
+}
+
+
+def rank_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi SM clock / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True); self.index = index; self.rows = []; self.stop_flag = False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        import statistics
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def make_workload(total_days, seed):
+    import covid_abm_b200 as cabm
+    import synthpop
+    pop = synthpop.generate(N_AGENTS)
+    P = cabm.params.default_params(run_length=total_days, seed=seed, mutant_intro_dates=MUTANTS)
+    T = cabm.params.build_tables(P)
+    return cabm, pop, P, T
+
+
+def algorithmic_bytes(work: dict, terms=None) -> float:
+    return sum(BYTES[k] * work[k] for k in (terms or BYTES))
+
+
+def run_reference_sample(pop, P, T, warm_days, timed_days, procs=1):
+    """Time the unmodified reference on the same population: `procs` concurrent single-threaded replicates."""
+    import covid_abm_b200 as cabm
+    import synthpop
+    if not os.path.exists(REF_DRIVER):
+        return None
+    tmp = tempfile.mkdtemp(prefix="cabm_ref_")
+    synthpop.write_reference_files(pop, tmp, "bench")
+    jobs = []
+    for r in range(procs):
+        Pr = dict(P); Pr["seed"] = int(P["seed"]) + r
+        pfile = os.path.join(tmp, f"params{r}.txt")
+        cabm.params.write_text(Pr, T, pfile)
+        jobs.append(subprocess.Popen([REF_DRIVER, "run", pfile, tmp, "bench", os.path.join(tmp, f"out{r}.csv"),
+                                      str(warm_days + timed_days), str(warm_days)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True))
+    outs = []
+    for j in jobs:
+        o, _ = j.communicate()
+        outs.append(json.loads(o.strip().splitlines()[-1]))
+    agent_days = sum(o["agents"] * o["days"] for o in outs)
+    secs = max(o["tick_import_s"] for o in outs)
+    subprocess.run(["rm", "-rf", tmp])
+    return {"value": agent_days / secs, "seconds": secs, "agent_days": agent_days, "procs": procs}
+
+
+def bench_ours(args):
+    rank, local_rank, world = rank_env()
+    if world > 1:
+        os.environ["CUDA_VISIBLE_DEVICES"] = str(local_rank)        # the C-ABI library binds to device 0 of its own runtime
+    import numpy as np
+    import torch
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", 0))
+    torch.cuda.set_device(0)
+    K, W = args.steps, args.warmup
+    total_days = (K + W) * DAYS_PER_STEP
+    cabm, pop, P, T = make_workload(total_days, seed=1 + rank)
+    n = int(pop["n_people"])
+    attrs = cabm.abi.immunity_attributes(n, P["seed"])
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident run: CUDA-graph replay, DAYS_PER_STEP days per call ----
+    A = cabm.Community(P, pop, T, attrs=attrs)
+    for _ in range(W):
+        A.run_days(DAYS_PER_STEP)
+    snap = A.snapshot(); work0 = A.work_counters(); A.device_time_ms()
+    sampler = ClockSampler(local_rank if world > 1 else 0); sampler.start()
+    barrier(); t0 = time.perf_counter(); dev_ms = 0.0; launches = 0
+    for _ in range(K):
+        flush.fill_(1); torch.cuda.synchronize()
+        A.run_days(DAYS_PER_STEP)
+        ms, l = A.device_time_ms(); dev_ms += ms; launches += l
+    barrier(); wall = time.perf_counter() - t0
+    sampler.stop_flag = True; sampler.join(timeout=2)
+    work1 = A.work_counters()
+    work = {k: work1[k] - work0[k] for k in work1}
+    ledger = A.ledger_table()
+
+    # ---- per-kernel CUDA-event timing of the same days (stream launches, one event per kernel) ----
+    A.restore(snap); A.set_profile(True); A.kernel_times()
+    A.run_days(K * DAYS_PER_STEP)
+    ktimes = A.kernel_times(); A.set_profile(False)
+    assert np.array_equal(ledger, A.ledger_table()), "profiled replay diverged from the timed run"
+    A.snap_free(snap); A.close()
+
+    # ---- end to end through the per-day C-ABI calls with host buffers ----
+    B = cabm.Community(P, pop, T, attrs=attrs)
+    row = np.zeros(cabm.abi.N_COUNTERS, dtype=np.uint64)
+    import ctypes as C
+
+    def day_by_day(days):
+        for _ in range(days):
+            B.step()
+            B._check(B.fn.ledger_row(B._h, B.day - 1, row.ctypes.data_as(C.POINTER(C.c_uint64))))
+    day_by_day(W * DAYS_PER_STEP)
+    barrier(); t1 = time.perf_counter()
+    day_by_day(K * DAYS_PER_STEP)
+    barrier(); e2e_wall = time.perf_counter() - t1
+    assert np.array_equal(ledger, B.ledger_table()), "per-day path diverged from run_days"
+    B.close()
+
+    # ---- reduce over ranks ----
+    agent_days = float(n) * K * DAYS_PER_STEP
+    vals = torch.tensor([dev_ms, wall, e2e_wall], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([agent_days], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX); dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    dev_ms_max, wall_max, e2e_max = (float(x) for x in vals.tolist()); agent_days_all = float(tot.item())
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    # dominant kernel: largest total CUDA-event time among the kernels the byte model covers
+    dom = max(KERNEL_TERMS, key=lambda k: ktimes.get(k, (0, 0))[0])
+    dom_ms, dom_n = ktimes[dom]
+    dom_bytes = algorithmic_bytes(work, KERNEL_TERMS[dom])
+    achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    total_k_ms = sum(v[0] for v in ktimes.values())
+    day_bytes = algorithmic_bytes(work)
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu_days = 10
+        r = run_reference_sample(pop, P, T, 0, cpu_days, procs=1)
+        if r:
+            cpu = {"value": r["value"], "unit": "agent-days/s", "cores": 1, "kind": "reference",
+                   "sample": f"unmodified reference (oracle/_ref/ref_driver, g++ -O2 + GSL shim), first {cpu_days} days of the same population and parameters, tick+import only"}
+    out = {
+        "metric": "agent-days/sec", "value": agent_days_all / (dev_ms_max * 1e-3), "unit": "agent-days/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": dev_ms_max / K, "wall_ms_per_step": wall_max * 1e3 / K, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64 fixed-point pressure / f64 hazard / i16 timelines", "data": "synthetic",
+        "config": {"workload": f"configs[1]: {n} synthetic agents (tools/synthpop.py seed 20200210), WT+alpha+delta, active-vac parameter set",
+                   "days_per_step": DAYS_PER_STEP, "agents": n, "locations": int(pop["n_loc"]), "parallelism": "1 community per GPU" + ("" if world == 1 else f" x {world} replicates"),
+                   "l2": "256 MiB flush between steps; consecutive days inside a step reuse L2 as a real run does"},
+        "e2e": {"value": agent_days_all / e2e_max, "unit": "agent-days/s", "h2d_bytes_per_step": DAYS_PER_STEP * (2 * 80 + 2 * 4),
+                "d2h_bytes_per_step": DAYS_PER_STEP * (cabm.abi.N_COUNTERS * 8 + 4 + 2 * 4), "calls_per_step": DAYS_PER_STEP * 3},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "kernel_avg_us": dom_ms * 1e3 / max(dom_n, 1),
+                     "kernel_share_of_day": dom_ms / total_k_ms if total_k_ms else None,
+                     "pipeline_achieved": day_bytes / (dev_ms_max * 1e-3) / 1e9, "pipeline_frac": day_bytes / (dev_ms_max * 1e-3) / 1e9 / peak,
+                     "bytes_per_agent_day": day_bytes / (n * K * DAYS_PER_STEP),
+                     "kernels_us_per_day": {k: round(v[0] * 1e3 / (K * DAYS_PER_STEP), 3) for k, v in ktimes.items() if v[1]}},
+        "cpu_baseline": cpu,
+        "clocks": sampler.summary(),
+        "work": work, "epidemic": {"infections": int(ledger[:, 0].sum()), "deaths": int(ledger[:, 4].sum())},
+    }
+    print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def bench_reference(args):
+    rank, _, world = rank_env()
+    if rank != 0:
+        return
+    K, W = args.steps, args.warmup
+    if not os.path.exists(REF_DRIVER):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (reference sources absent at build time)"}))
+        return
+    ref_days_per_step = 1                       # bounded sample: one simulated day per step
+    total_days = (K + W) * DAYS_PER_STEP
+    cabm, pop, P, T = make_workload(total_days, seed=1)
+    n = int(pop["n_people"])
+    cores = os.cpu_count() or 1
+    mem_gb = os.sysconf("SC_PAGE_SIZE") * os.sysconf("SC_PHYS_PAGES") / 2**30
+    procs = int(max(1, min(cores, (mem_gb * 0.5) // (1.0 + 0.8 * n / 1e6), 64)))
+    r = run_reference_sample(pop, P, T, W * ref_days_per_step, K * ref_days_per_step, procs=procs)
+    sample = (f"{procs} concurrent single-threaded replicates of the unmodified reference (seeds 1..{procs}), "
+              f"{W}+{K} steps of {ref_days_per_step} day each from day 0 of the same population and parameters; tick+import only")
+    out = {"impl": "reference", "metric": "agent-days/sec", "value": r["value"], "unit": "agent-days/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
+           "ms_per_step": r["seconds"] * 1e3 / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": f"configs[1]: {n} synthetic agents (tools/synthpop.py seed 20200210), WT+alpha+delta, active-vac parameter set",
+                      "days_per_step": ref_days_per_step, "agents": n, "locations": int(pop["n_loc"]), "parallelism": f"{procs} host processes"},
+           "cpu_baseline": {"value": r["value"], "unit": "agent-days/s", "cores": procs, "kind": "reference", "sample": sample},
+           "e2e": {"value": r["value"], "unit": "agent-days/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0, "host_cores": cores}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        bench_reference(args)
+    else:
+        bench_ours(args)
+
+
+if __name__ == "__main__":
+    main()

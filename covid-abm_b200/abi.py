@@ -89,7 +89,11 @@ _PROTOS = {
     "snapshot": [_vp, C.POINTER(_vp)], "restore": [_vp, _vp], "snap_free": [_vp],
     "dump_foi": [_vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)], "device_time_ms": [_vp, C.POINTER(d), C.POINTER(C.c_uint64)],
 }
-SYMBOLS = sorted(list(_PROTOS) + ["last_error"])
+_OPTIONAL = {
+    "set_profile": [_vp, C.c_int],
+    "kernel_times": [_vp, C.POINTER(d), C.POINTER(C.c_uint64), C.POINTER(C.c_char_p), C.c_size_t, C.POINTER(C.c_size_t)],
+}
+SYMBOLS = sorted(list(_OPTIONAL) + list(_PROTOS) + ["last_error"])
 
 
 class Bound:
@@ -99,6 +103,11 @@ class Bound:
             fn = getattr(lib, prefix + name); fn.argtypes = args; fn.restype = C.c_int
             setattr(self, "import_" if name == "import" else name, fn)
         self.last_error = getattr(lib, prefix + "last_error"); self.last_error.argtypes = [_vp]; self.last_error.restype = C.c_char_p
+        for name, args in _OPTIONAL.items():            # measurement-only entry points (absent from the oracle)
+            fn = getattr(lib, prefix + name, None)
+            if fn is not None:
+                fn.argtypes = args; fn.restype = C.c_int
+            setattr(self, name, fn)
 
 
 def bind(lib, prefix="cabm_") -> Bound:

@@ -219,6 +219,15 @@ class Community:
         self._check(self.fn.device_time_ms(self._h, C.byref(ms), C.byref(k)))
         return ms.value, k.value
 
+    def set_profile(self, on: bool):
+        self._check(self.fn.set_profile(self._h, 1 if on else 0))
+
+    def kernel_times(self) -> dict:
+        """{kernel name: (total ms, launches)} accumulated since the last call (profile mode only)."""
+        ms = (C.c_double * 32)(); cnt = (C.c_uint64 * 32)(); names = (C.c_char_p * 32)(); n = C.c_size_t(0)
+        self._check(self.fn.kernel_times(self._h, ms, cnt, names, 32, C.byref(n)))
+        return {names[i].decode(): (ms[i], int(cnt[i])) for i in range(n.value)}
+
     def snapshot(self):
         s = C.c_void_p()
         self._check(self.fn.snapshot(self._h, C.byref(s)))

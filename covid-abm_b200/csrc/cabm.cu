@@ -31,6 +31,8 @@ struct cabm {
     cudaGraphExec_t day_graph = nullptr;
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
+    uint64_t launches_per_day = 20;
+    int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
 };
 
 struct cabm_snap {
@@ -95,35 +97,55 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
     c.school_closure = h->h_ti[0][day]; c.business_closure = h->h_ti[1][day]; c.sd = h->h_ti[2][day];
 }
 
+// kernel ids for per-kernel timing (cabm_kernel_times)
+enum { KID_SCAN = 0, KID_VISIT, KID_HAZARD, KID_EXPOSE_ITEMS, KID_EXPOSE_VISITS, KID_APPLY, KID_STATUS, KID_COMPACT, KID_HAZARD_HOSP,
+       KID_EXPOSE_HOSP, KID_EXPOSE_PATIENTS, KID_APPLY_HOSP, KID_END, KID_IMPORT, KID_APPLY_IMPORT, KID_SMALL, KID_N };
+static const char* const KID_NAMES[KID_N] = { "k_scan", "k_visit", "k_hazard", "k_expose_items", "k_expose_visits", "k_apply", "k_status",
+    "k_compact_patients", "k_hazard(hosp)", "k_expose_items(hosp)", "k_expose_patients", "k_apply(hosp)", "k_end", "k_import", "k_apply(import)", "bookkeeping" };
+
+// LAUNCH records an event in front of every kernel when per-kernel profiling is on (stream path only, never under graph capture)
+#define LAUNCH(id, ...) do { if (h->profile) prof_mark(h, id); __VA_ARGS__; h->launches++; } while (0)
+static void prof_mark(cabm_t* h, int id) {
+    if (h->n_marks < (int) h->marks.size()) { cudaEventRecord(h->marks[h->n_marks], h->stream); h->mark_id[h->n_marks] = id; h->n_marks++; }
+}
+static void prof_collect(cabm_t* h) {      // call after the stream has been synchronised
+    if (!h->profile || h->n_marks == 0) return;
+    for (int i = 0; i + 1 < h->n_marks; ++i) {
+        float ms = 0; cudaEventElapsedTime(&ms, h->marks[i], h->marks[i + 1]);
+        if (h->mark_id[i] >= 0) { h->ktime[h->mark_id[i]] += ms; h->kcount[h->mark_id[i]]++; }
+    }
+    h->n_marks = 0;
+}
+
 // the launch sequence of one Community::tick (Community.cpp:1147-1192)
 static void launch_tick(cabm_t* h) {
     const Dev& D = h->d; cudaStream_t st = h->stream;
     const unsigned int gN = grid_for(h, D.N, 8), gL = h->sms * 4;
-    k_scan<<<gN, TPB, 0, st>>>(D);
-    k_visit<<<gN, TPB, 0, st>>>(D);
-    k_hazard<<<gL, TPB, 0, st>>>(D, 0);
-    k_expose_items<<<gL, TPB, 0, st>>>(D);
-    k_expose_visits<<<gL, TPB, 0, st>>>(D);
-    k_apply<<<h->sms, 128, 0, st>>>(D);
-    k_phase_end<<<1, 32, 0, st>>>(D);
-    k_status<<<gL, TPB, 0, st>>>(D, 0);
-    k_status<<<h->sms, TPB, 0, st>>>(D, 1);
-    k_compact_patients<<<1, TPB, 0, st>>>(D);
-    k_items_reset<<<1, 32, 0, st>>>(D);
-    k_hazard<<<gL, TPB, 0, st>>>(D, 1);
-    k_expose_items<<<h->sms, TPB, 0, st>>>(D);
-    k_expose_patients<<<h->sms, TPB, 0, st>>>(D);
-    k_apply<<<h->sms, 128, 0, st>>>(D);
-    k_end<<<gL, TPB, 0, st>>>(D);
-    k_tick_end<<<1, 32, 0, st>>>(D);
-    h->launches += 17;
+    LAUNCH(KID_SCAN, k_scan<<<gN, TPB, 0, st>>>(D));
+    LAUNCH(KID_VISIT, k_visit<<<gN, TPB, 0, st>>>(D));
+    LAUNCH(KID_HAZARD, k_hazard<<<gL, TPB, 0, st>>>(D, 0));
+    LAUNCH(KID_EXPOSE_ITEMS, k_expose_items<<<gL, TPB, 0, st>>>(D));
+    LAUNCH(KID_EXPOSE_VISITS, k_expose_visits<<<gL, TPB, 0, st>>>(D));
+    LAUNCH(KID_APPLY, k_apply<<<h->sms, 128, 0, st>>>(D));
+    LAUNCH(KID_SMALL, k_phase_end<<<1, 32, 0, st>>>(D));
+    LAUNCH(KID_STATUS, k_status<<<gL, TPB, 0, st>>>(D, 0));
+    LAUNCH(KID_STATUS, k_status<<<h->sms, TPB, 0, st>>>(D, 1));
+    LAUNCH(KID_COMPACT, k_compact_patients<<<1, TPB, 0, st>>>(D));
+    LAUNCH(KID_SMALL, k_items_reset<<<1, 32, 0, st>>>(D));
+    LAUNCH(KID_HAZARD_HOSP, k_hazard<<<gL, TPB, 0, st>>>(D, 1));
+    LAUNCH(KID_EXPOSE_HOSP, k_expose_items<<<h->sms, TPB, 0, st>>>(D));
+    LAUNCH(KID_EXPOSE_PATIENTS, k_expose_patients<<<h->sms, TPB, 0, st>>>(D));
+    LAUNCH(KID_APPLY_HOSP, k_apply<<<h->sms, 128, 0, st>>>(D));
+    LAUNCH(KID_END, k_end<<<gL, TPB, 0, st>>>(D));
+    LAUNCH(KID_SMALL, k_tick_end<<<1, 32, 0, st>>>(D));
+    if (h->profile) prof_mark(h, -1);
 }
 static void launch_import(cabm_t* h, int advance) {
     const Dev& D = h->d; cudaStream_t st = h->stream;
-    k_import<<<h->sms, 128, 0, st>>>(D);
-    k_apply<<<h->sms, 128, 0, st>>>(D);
-    k_import_end<<<1, 32, 0, st>>>(D, advance);
-    h->launches += 3;
+    LAUNCH(KID_IMPORT, k_import<<<h->sms, 128, 0, st>>>(D));
+    LAUNCH(KID_APPLY_IMPORT, k_apply<<<h->sms, 128, 0, st>>>(D));
+    LAUNCH(KID_SMALL, k_import_end<<<1, 32, 0, st>>>(D, advance));
+    if (h->profile) prof_mark(h, -1);
 }
 
 static int ready(cabm_t* h, int day) {
@@ -142,6 +164,7 @@ static int timed_sync(cabm_t* h) {
     CK(cudaEventSynchronize(h->e1));
     float ms = 0; CK(cudaEventElapsedTime(&ms, h->e0, h->e1)); h->acc_ms += ms;
     CK(cudaGetLastError());
+    prof_collect(h);
     return CABM_OK;
 }
 
@@ -306,11 +329,12 @@ int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[C
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
     CK(cudaEventRecord(h->e0, h->stream));
     const Dev& D = h->d;
-    k_import<<<h->sms, 128, 0, h->stream>>>(D);
-    k_apply<<<h->sms, 128, 0, h->stream>>>(D);
+    LAUNCH(KID_IMPORT, k_import<<<h->sms, 128, 0, h->stream>>>(D));
+    LAUNCH(KID_APPLY_IMPORT, k_apply<<<h->sms, 128, 0, h->stream>>>(D));
+    if (h->profile) prof_mark(h, -1);
     if (out_infected) CK(cudaMemcpyAsync(out_infected, &D.ctr->n_new, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-    k_import_end<<<1, 32, 0, h->stream>>>(D, 0);
-    h->launches += 3;
+    LAUNCH(KID_SMALL, k_import_end<<<1, 32, 0, h->stream>>>(D, 0));
+    if (h->profile) prof_mark(h, -1);
     if ((rc = timed_sync(h))) return rc;
     return check_overflow(h);
 }
@@ -342,18 +366,27 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
     }
     CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, (size_t) n_days * sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
+    if (h->profile) {                // per-kernel timing: plain stream launches, one event in front of every kernel
+        CK(cudaEventRecord(h->e0, h->stream));
+        for (int i = 0; i < n_days; ++i) {
+            launch_tick(h); launch_import(h, 1);
+            CK(cudaStreamSynchronize(h->stream)); prof_collect(h);
+        }
+        if ((rc = timed_sync(h))) return rc;
+        return check_overflow(h);
+    }
     if (!h->day_graph) {             // capture one day (tick + importation) once; every day replays the same graph
         cudaGraph_t g = nullptr;
         CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
         const uint64_t l0 = h->launches;
         launch_tick(h); launch_import(h, 1);
-        h->launches = l0;
+        h->launches_per_day = h->launches - l0; h->launches = l0;
         CK(cudaStreamEndCapture(h->stream, &g));
         CK(cudaGraphInstantiate(&h->day_graph, g, 0));
         cudaGraphDestroy(g);
     }
     CK(cudaEventRecord(h->e0, h->stream));
-    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += 20; }
+    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day; }
     if ((rc = timed_sync(h))) return rc;
     return check_overflow(h);
 }
@@ -495,6 +528,24 @@ int cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches) {
     if (!h) return CABM_E_ARG;
     if (out_ms) *out_ms = h->acc_ms; if (out_launches) *out_launches = h->launches;
     h->acc_ms = 0.0; h->launches = 0;
+    return CABM_OK;
+}
+
+// per-kernel device time of the day pipeline; switching it on makes tick/import/run_days use plain stream launches
+int cabm_set_profile(cabm_t* h, int on) {
+    if (!h) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    if (on && h->marks.empty()) { h->marks.resize(64); h->mark_id.resize(64); for (auto& e : h->marks) cudaEventCreate(&e); }
+    h->profile = on ? 1 : 0; h->n_marks = 0;
+    return CABM_OK;
+}
+int cabm_kernel_times(cabm_t* h, double* out_ms, uint64_t* out_count, const char** out_names, size_t cap, size_t* out_n) {
+    if (!h) return CABM_E_ARG;
+    if (out_n) *out_n = KID_N;
+    for (size_t k = 0; k < std::min<size_t>(cap, KID_N); ++k) {
+        if (out_ms) out_ms[k] = h->ktime[k]; if (out_count) out_count[k] = h->kcount[k]; if (out_names) out_names[k] = KID_NAMES[k];
+        h->ktime[k] = 0; h->kcount[k] = 0;
+    }
     return CABM_OK;
 }
 

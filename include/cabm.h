@@ -246,6 +246,10 @@ int  cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n);
 /* device time (ms, CUDA events) spent in the day pipeline since the last call; resets the accumulator */
 int  cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches);
 
+/* per-kernel CUDA-event timing of the day pipeline (measurement only; no reference counterpart) */
+int  cabm_set_profile(cabm_t* h, int on);
+int  cabm_kernel_times(cabm_t* h, double* out_ms, uint64_t* out_count, const char** out_names, size_t cap, size_t* out_n);
+
 #ifdef __cplusplus
 }
 #endif

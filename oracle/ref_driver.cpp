@@ -138,11 +138,12 @@ void update_strain_mix(const Date* date, const vector<string>& mid, vector<doubl
 }
 
 int mode_run(int argc, char** argv) {
-    if (argc < 6) { cerr << "run <params> <pop_dir> <tag> <out.csv> [max_days]\n"; return 2; }
+    if (argc < 6) { cerr << "run <params> <pop_dir> <tag> <out.csv> [max_days] [warmup_days]\n"; return 2; }
     const KV kv = read_kv(argv[2]);
     Parameters* par = make_parameters(kv);
     set_pop_files(par, argv[3], argv[4]);
     const long max_days = argc > 6 ? atol(argv[6]) : (long) par->runLength;
+    const long warmup_days = argc > 7 ? atol(argv[7]) : 0;                     // excluded from the timed total
     gsl_rng_set(RNG, par->randomseed); gsl_rng_set(VAX_RNG, par->randomseed); gsl_rng_set(REPORTING_RNG, par->randomseed); // main.cpp:536-538
 
     auto t0 = chrono::steady_clock::now();
@@ -160,7 +161,7 @@ int mode_run(int argc, char** argv) {
         community->tick();                                                             // simulator.h:338
         update_strain_mix(date, mid, strains);
         seed_epidemic(par, community, date, strains);                                  // simulator.h:374
-        hot_s += chrono::duration<double>(chrono::steady_clock::now() - a).count();
+        if (days >= warmup_days) hot_s += chrono::duration<double>(chrono::steady_clock::now() - a).count();
     }
 
     ofstream out(argv[5]);
@@ -180,7 +181,7 @@ int mode_run(int argc, char** argv) {
     const double n = community->getNumPeople();
     printf("{\"impl\": \"reference\", \"agents\": %.0f, \"days\": %ld, \"load_s\": %.3f, \"tick_import_s\": %.6f, "
            "\"agent_days_per_s\": %.6g, \"cumul_asymptomatic\": %zu, \"cumul_death\": %zu}\n",
-           n, days, load_s, hot_s, n * days / hot_s, community->getCumulIncidenceByOutcome(ASYMPTOMATIC),
+           n, days - warmup_days, load_s, hot_s, n * (days - warmup_days) / hot_s, community->getCumulIncidenceByOutcome(ASYMPTOMATIC),
            community->getCumulIncidenceByOutcome(DEATH));
     return 0;
 }
