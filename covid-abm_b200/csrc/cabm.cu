@@ -1,6 +1,7 @@
 // covid-abm_b200/csrc/cabm.cu -- C ABI of include/cabm.h over the sm_100a day pipeline.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=false -shared -Xcompiler -fPIC
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -31,7 +32,8 @@ struct cabm {
     cudaGraphExec_t day_graph = nullptr;
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
-    uint64_t launches_per_day = 20;
+    uint64_t launches_per_day = 12;
+    unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr;
     int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
 };
 
@@ -98,10 +100,10 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
 }
 
 // kernel ids for per-kernel timing (cabm_kernel_times)
-enum { KID_SCAN = 0, KID_VISIT, KID_HAZARD, KID_EXPOSE_ITEMS, KID_EXPOSE_VISITS, KID_APPLY, KID_STATUS, KID_COMPACT, KID_HAZARD_HOSP,
-       KID_EXPOSE_HOSP, KID_EXPOSE_PATIENTS, KID_APPLY_HOSP, KID_END, KID_IMPORT, KID_APPLY_IMPORT, KID_SMALL, KID_N };
-static const char* const KID_NAMES[KID_N] = { "k_scan", "k_visit", "k_hazard", "k_expose_items", "k_expose_visits", "k_apply", "k_status",
-    "k_compact_patients", "k_hazard(hosp)", "k_expose_items(hosp)", "k_expose_patients", "k_apply(hosp)", "k_end", "k_import", "k_apply(import)", "bookkeeping" };
+enum { KID_SCAN = 0, KID_ACTIVE, KID_VISIT, KID_HAZARD, KID_TRIALS, KID_GATE0, KID_APPLY_STATUS, KID_HOSP_IMPORT, KID_GATE1, KID_APPLY1,
+       KID_END, KID_SMALL, KID_N };
+static const char* const KID_NAMES[KID_N] = { "k_scan", "k_active", "k_visit", "k_hazard", "k_trials", "k_gate(phase0)", "k_apply_status",
+    "k_hosp_import", "k_gate(phase1)", "k_apply(phase1)", "k_end", "k_day_end" };
 
 // LAUNCH records an event in front of every kernel when per-kernel profiling is on (stream path only, never under graph capture)
 #define LAUNCH(id, ...) do { if (h->profile) prof_mark(h, id); __VA_ARGS__; h->launches++; } while (0)
@@ -117,34 +119,28 @@ static void prof_collect(cabm_t* h) {      // call after the stream has been syn
     h->n_marks = 0;
 }
 
-// the launch sequence of one Community::tick (Community.cpp:1147-1192)
-static void launch_tick(cabm_t* h) {
+// The launch sequence of one day. tick = Community::tick (Community.cpp:1147-1192), import = the daily
+// seed_epidemic (simulator.h:201-223). With both set the importation draws share the hospital pass's gate/apply
+// launches: an agent hit by both keeps the hospital exposure (lower order key), exactly what running
+// seed_epidemic after tick() yields.
+static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     const Dev& D = h->d; cudaStream_t st = h->stream;
-    const unsigned int gN = grid_for(h, D.N, 8), gL = h->sms * 4;
-    LAUNCH(KID_SCAN, k_scan<<<gN, TPB, 0, st>>>(D));
-    LAUNCH(KID_VISIT, k_visit<<<gN, TPB, 0, st>>>(D));
-    LAUNCH(KID_HAZARD, k_hazard<<<gL, TPB, 0, st>>>(D, 0));
-    LAUNCH(KID_EXPOSE_ITEMS, k_expose_items<<<gL, TPB, 0, st>>>(D));
-    LAUNCH(KID_EXPOSE_VISITS, k_expose_visits<<<gL, TPB, 0, st>>>(D));
-    LAUNCH(KID_APPLY, k_apply<<<h->sms, 128, 0, st>>>(D));
-    LAUNCH(KID_SMALL, k_phase_end<<<1, 32, 0, st>>>(D));
-    LAUNCH(KID_STATUS, k_status<<<gL, TPB, 0, st>>>(D, 0));
-    LAUNCH(KID_STATUS, k_status<<<h->sms, TPB, 0, st>>>(D, 1));
-    LAUNCH(KID_COMPACT, k_compact_patients<<<1, TPB, 0, st>>>(D));
-    LAUNCH(KID_SMALL, k_items_reset<<<1, 32, 0, st>>>(D));
-    LAUNCH(KID_HAZARD_HOSP, k_hazard<<<gL, TPB, 0, st>>>(D, 1));
-    LAUNCH(KID_EXPOSE_HOSP, k_expose_items<<<h->sms, TPB, 0, st>>>(D));
-    LAUNCH(KID_EXPOSE_PATIENTS, k_expose_patients<<<h->sms, TPB, 0, st>>>(D));
-    LAUNCH(KID_APPLY_HOSP, k_apply<<<h->sms, 128, 0, st>>>(D));
-    LAUNCH(KID_END, k_end<<<gL, TPB, 0, st>>>(D));
-    LAUNCH(KID_SMALL, k_tick_end<<<1, 32, 0, st>>>(D));
-    if (h->profile) prof_mark(h, -1);
-}
-static void launch_import(cabm_t* h, int advance) {
-    const Dev& D = h->d; cudaStream_t st = h->stream;
-    LAUNCH(KID_IMPORT, k_import<<<h->sms, 128, 0, st>>>(D));
-    LAUNCH(KID_APPLY_IMPORT, k_apply<<<h->sms, 128, 0, st>>>(D));
-    LAUNCH(KID_SMALL, k_import_end<<<1, 32, 0, st>>>(D, advance));
+    const unsigned int gScan = (unsigned int) ((D.N + TPB * 4 - 1) / (TPB * 4)), gSM = h->sms;
+    if (tick) {
+        LAUNCH(KID_SCAN, k_scan<<<gScan, TPB, 0, st>>>(D));
+        LAUNCH(KID_ACTIVE, k_active<<<gSM * 8, TPB, 0, st>>>(D));
+        LAUNCH(KID_VISIT, k_visit<<<std::min<unsigned int>((D.N + TPB - 1) / TPB, gSM * 6), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words));
+        LAUNCH(KID_HAZARD, k_hazard<<<gSM * 8, TPB, 0, st>>>(D));
+        LAUNCH(KID_TRIALS, k_trials<<<gSM * 8, TPB, 0, st>>>(D));
+        LAUNCH(KID_GATE0, k_gate<<<gSM * 4, 128, 0, st>>>(D, 0));
+        LAUNCH(KID_APPLY_STATUS, k_apply_status<<<gSM * 8, 128, 0, st>>>(D, 0, 1));
+    }
+    LAUNCH(KID_HOSP_IMPORT, k_hosp_import<<<gSM, TPB, 0, st>>>(D, tick ? 1 : 0, import ? 1 : 0));
+    LAUNCH(KID_GATE1, k_gate<<<gSM * 2, 128, 0, st>>>(D, 1));
+    LAUNCH(KID_APPLY1, k_apply_status<<<gSM * 2, 128, 0, st>>>(D, 1, 0));
+    if (!tick && h->d_out_new) cudaMemcpyAsync(h->d_out_new, &D.ctr->n_new[1], sizeof(unsigned int), cudaMemcpyDeviceToDevice, st);
+    LAUNCH(KID_END, k_end<<<gSM * 4, TPB, 0, st>>>(D, tick ? 1 : 0));
+    LAUNCH(KID_SMALL, k_day_end<<<1, 32, 0, st>>>(D, tick ? 1 : 0, advance));
     if (h->profile) prof_mark(h, -1);
 }
 
@@ -211,6 +207,8 @@ int cabm_set_params(cabm_t* h, const cabm_params* par) {
         if ((rc = dalloc(h, &h->d.ledger, (size_t) CABM_N_COUNTERS * R, true))) return rc;
         if ((rc = dalloc(h, &h->d.ctr, 1, true))) return rc;
         if ((rc = dalloc(h, &h->d_tmp_int, 4))) return rc;
+        if ((rc = dalloc(h, &h->d_out_new, 1))) return rc;
+        if ((rc = dalloc(h, &h->d_today, 1))) return rc;
         h->ctx_cap = (int) R;
         if ((rc = dalloc(h, &h->d_ctx, R))) return rc;
         CK(cudaMallocHost((void**) &h->h_ctx, R * sizeof(DayCtx)));
@@ -223,7 +221,12 @@ int cabm_set_params(cabm_t* h, const cabm_params* par) {
     CK(cudaMemcpyAsync(h->d_par, &h->hpar, sizeof(cabm_params), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     h->d.par = h->d_par; h->d.pfd = h->d_pfd; h->d.imr = h->d_imr; h->d.n_imr = par->icu_mortality_reduction ? (int) R : 0;
-    h->d.R = (int) R; h->d.dayctx = h->d_ctx;
+    h->d.R = (int) R; h->d.dayctx = h->d_ctx; h->d.today = h->d_today; h->d.seed = par->seed;
+    for (int k = 0; k < 4; ++k) {                // u01 < cdf  <=>  x < ceil(cdf * 2^32) for a 32-bit draw x (exact: power-of-two scaling)
+        const double c = std::ceil(par->visit_cdf[k] * 4294967296.0);
+        h->d.visit_thr[k] = c >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned int) c;
+    }
+    if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; }    // kernel arguments are baked into the graph
     h->have_par = true;
     return CABM_OK;
 }
@@ -250,6 +253,8 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N), patron((size_t) N * D.n_patron, -1);
     std::vector<unsigned char> age(pop->age, pop->age + N), pflags(N), pbyte(N, 0);
     std::vector<float> home_risk(N);
+    // patronised ("public") locations get a dense index q: the visit pass tests hotness in a shared-memory bitmap over q
+    std::vector<int> loc_pub(L, -1), pub_loc;
     for (uint32_t p = 0; p < N; ++p) {
         if (home[p] < 0 || (uint32_t) home[p] >= L || dayl[p] >= (int) L) { h->err = "home/day location out of range"; return CABM_E_ARG; }
         pflags[p] = (pop->comorbid[p] ? PF_COMORBID : 0) | (pop->ltc[p] ? PF_LTC : 0);
@@ -258,17 +263,24 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         for (uint32_t k = 0; k < NP; ++k) {
             const int loc = pop->patron[(size_t) p * NP + k]; if (loc < 0) break;
             if ((uint32_t) loc >= L) { h->err = "patronised location out of range"; return CABM_E_ARG; }
-            patron[(size_t) p * D.n_patron + k] = loc | (pop->loc_pubrisk[loc] == CABM_PT_HIGH ? PATRON_HIGH : 0); np++;
+            if (loc_pub[loc] < 0) { loc_pub[loc] = (int) pub_loc.size(); pub_loc.push_back(loc); }
+            patron[(size_t) p * D.n_patron + k] = loc_pub[loc] | (pop->loc_pubrisk[loc] == CABM_PT_HIGH ? PATRON_HIGH : 0); np++;
         }
         pbyte[p] = (unsigned char) np;
     }
+    D.Q = (unsigned int) pub_loc.size();
+    h->bitmap_words = std::max<unsigned int>(1, (D.Q + 31) / 32);
+    if (h->bitmap_words * sizeof(unsigned int) > 160 * 1024) { h->err = "too many patronised locations for the shared-memory hot bitmap"; return CABM_E_ARG; }
+    CK(cudaFuncSetAttribute(k_visit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (h->bitmap_words * sizeof(unsigned int))));
+    if (pub_loc.empty()) pub_loc.push_back(0);
     std::vector<double> nat_eff(pop->starting_natural_efficacy, pop->starting_natural_efficacy + N);
     std::vector<float> xprot(pop->cross_protection_probability, pop->cross_protection_probability + N);
     std::vector<int> nat_dur(pop->natural_immunity_duration, pop->natural_immunity_duration + N);
     if ((rc = upload(h, (int**) &D.home, home)) || (rc = upload(h, (int**) &D.day_loc, dayl)) || (rc = upload(h, (int**) &D.patron, patron)) ||
         (rc = upload(h, (unsigned char**) &D.age, age)) || (rc = upload(h, (unsigned char**) &D.pflags, pflags)) ||
         (rc = upload(h, (float**) &D.home_risk, home_risk)) || (rc = upload(h, (double**) &D.nat_eff, nat_eff)) ||
-        (rc = upload(h, (float**) &D.xprot, xprot)) || (rc = upload(h, (int**) &D.nat_dur, nat_dur))) return rc;
+        (rc = upload(h, (float**) &D.xprot, xprot)) || (rc = upload(h, (int**) &D.nat_dur, nat_dur)) ||
+        (rc = upload(h, (int**) &D.loc_pub, loc_pub)) || (rc = upload(h, (int**) &D.pub_loc, pub_loc))) return rc;
     // ---- static locations ----
     std::vector<unsigned char> ltype(pop->loc_type, pop->loc_type + L), lflags(L);
     for (uint32_t l = 0; l < L; ++l) lflags[l] = (pop->loc_essential[l] ? LF_ESSENTIAL : 0) | ((pop->loc_pubrisk[l] & 3) << 1);
@@ -283,20 +295,22 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = upload(h, (unsigned int**) &D.roster_off, roff)) || (rc = upload(h, (unsigned int**) &D.nbr_off, noff)) ||
         (rc = upload(h, (int**) &D.roster, roster)) || (rc = upload(h, (int**) &D.nbr, nbr))) return rc;
     // ---- dynamic state ----
-    if ((rc = dalloc(h, &D.win, N, true)) || (rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
+    const size_t Q1 = std::max<size_t>(D.Q, 1);
+    if ((rc = dalloc(h, &D.win, (size_t) N + 4, true)) || (rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
         (rc = dalloc(h, &D.imm, N, true)) || (rc = dalloc(h, &D.vax, N, true)) || (rc = dalloc(h, &D.vax_days, (size_t) N * CABM_MAX_DOSES, true)) ||
         (rc = dalloc(h, &D.quar, N, true)) || (rc = dalloc(h, &D.hosp_count, N, true)) || (rc = dalloc(h, &D.pbyte, N, true)) ||
-        (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.inf_place, N, true, 0xFF)) || (rc = dalloc(h, &D.inf_by, N, true, 0xFF)) || (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.hot_idx, L)) ||
-        (rc = dalloc(h, &D.nvis, L)) || (rc = dalloc(h, &D.pat_count, L, true))) return rc;
+        (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.inf_place, N, true, 0xFF)) || (rc = dalloc(h, &D.inf_by, N, true, 0xFF)) ||
+        (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.loc_head, L)) || (rc = dalloc(h, &D.pat_count, L, true)) ||
+        (rc = dalloc(h, &D.nvis, Q1)) || (rc = dalloc(h, &D.pub_T, Q1)) || (rc = dalloc(h, &D.pub_hot, h->bitmap_words))) return rc;
     CK(cudaMemcpyAsync(D.pbyte, pbyte.data(), N, cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----
-    D.cap_hot = L; D.cap_active = N; D.cap_vis = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
-    D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, (size_t) 2 * L + nbr.size() + roster.size() / CHUNK + 1024);
+    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
+    D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + (size_t) L / 64 + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
-    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, D.cap_hot)) || (rc = dalloc(h, &D.hot_Ts, D.cap_hot)) ||
-        (rc = dalloc(h, &D.hot_size, D.cap_hot)) || (rc = dalloc(h, &D.active_list, D.cap_active)) || (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
-        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) || (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) ||
-        (rc = dalloc(h, &D.patient_tmp, D.cap_pat)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||
+    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
+        (rc = dalloc(h, &D.active_list, D.cap_active)) || (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
+        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
+        (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||
         (rc = dalloc(h, &D.n_foi, 1))) return rc;
     k_init_state<<<grid_for(h, std::max(N, L), 8), TPB, 0, h->stream>>>(D);
     CK(cudaStreamSynchronize(h->stream));
@@ -314,7 +328,7 @@ int cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday) {
     CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
     CK(cudaEventRecord(h->e0, h->stream));
-    launch_tick(h);
+    launch_day(h, true, false, 0);
     if ((rc = timed_sync(h))) return rc;
     return check_overflow(h);
 }
@@ -325,17 +339,13 @@ int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[C
     DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
     c.day = sim_day; c.julian_day = 1; c.n_imports = expected > 0 ? import_count(h->hpar.seed, sim_day, expected) : 0;
     for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
-    CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
+    CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));   // no k_scan in front: publish the context directly
     CK(cudaEventRecord(h->e0, h->stream));
-    const Dev& D = h->d;
-    LAUNCH(KID_IMPORT, k_import<<<h->sms, 128, 0, h->stream>>>(D));
-    LAUNCH(KID_APPLY_IMPORT, k_apply<<<h->sms, 128, 0, h->stream>>>(D));
-    if (h->profile) prof_mark(h, -1);
-    if (out_infected) CK(cudaMemcpyAsync(out_infected, &D.ctr->n_new, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-    LAUNCH(KID_SMALL, k_import_end<<<1, 32, 0, h->stream>>>(D, 0));
-    if (h->profile) prof_mark(h, -1);
+    launch_day(h, false, true, 0);
+    int32_t n_new = 0;
+    CK(cudaMemcpyAsync(&n_new, h->d_out_new, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
     if ((rc = timed_sync(h))) return rc;
+    if (out_infected) *out_infected = n_new;
     return check_overflow(h);
 }
 
@@ -369,7 +379,7 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
     if (h->profile) {                // per-kernel timing: plain stream launches, one event in front of every kernel
         CK(cudaEventRecord(h->e0, h->stream));
         for (int i = 0; i < n_days; ++i) {
-            launch_tick(h); launch_import(h, 1);
+            launch_day(h, true, true, 1);
             CK(cudaStreamSynchronize(h->stream)); prof_collect(h);
         }
         if ((rc = timed_sync(h))) return rc;
@@ -379,7 +389,7 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
         cudaGraph_t g = nullptr;
         CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
         const uint64_t l0 = h->launches;
-        launch_tick(h); launch_import(h, 1);
+        launch_day(h, true, true, 1);
         h->launches_per_day = h->launches - l0; h->launches = l0;
         CK(cudaStreamEndCapture(h->stream, &g));
         CK(cudaGraphInstantiate(&h->day_graph, g, 0));

@@ -26,7 +26,13 @@ enum { PASS_HH = 3, PASS_NB = 4, PASS_WORK = 5, PASS_SCHOOL = 7, PASS_NH = 8, PA
 struct __align__(16) Tl0 { short infected, infectious_begin, infectious_end, symptom_begin, symptom_end, severe_begin, severe_end, hosp_begin; };
 struct __align__(16) Tl1 { short critical_begin, critical_end, icu_begin, death, report_day; unsigned char strain, detected; float rel_inf; };
 
-struct Item { int src; int begin; int count; int purpose; double T; };          // one exposure work item (a roster chunk)
+struct __align__(16) Item { int src; int begin; int count; int purpose; double T; double pad; };   // a 256-member chunk of a big roster
+struct __align__(16) Hit  { unsigned int pid; unsigned int src; unsigned int purpose; unsigned int sub; }; // a trial with U < T, to be gated
+// one (infectious agent, location) flag of the day (Community::flagInfectedLocation, Community.cpp:788-791);
+// c = pressure contribution in 2^-32 units, strain in the top byte; next = previous head of the location's chain
+struct __align__(16) Flag { unsigned int pid; int next; unsigned long long c; };
+#define FLAG_C(f) ((f).c & 0x00FFFFFFFFFFFFFFull)
+#define FLAG_STRAIN(f) ((int) ((f).c >> 56))
 
 struct DayCtx {                     // per-day scalars, staged by the host for every day of a run_days() batch
     int day, julian_day, is_weekday, n_imports;
@@ -34,50 +40,61 @@ struct DayCtx {                     // per-day scalars, staged by the host for e
     double season, sd, school_closure, business_closure;
 };
 
-// counters living in device memory (zeroed at end of day unless noted)
+// counters living in device memory
 struct Counters {
-    unsigned int n_hot, n_active, n_vis, n_items, n_new, n_new_applied, n_pat /*persistent*/, n_pat_tmp;
+    // ---- day-scoped: zeroed by k_day_end ----
+    unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items;
+    unsigned int n_hits[2], n_new[2];                        // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
+    unsigned int day_pad[6];
+    // ---- persistent ----
+    unsigned int n_pat;                                      // admitted-patient list length (entries are never removed, see k_status)
     unsigned int overflow;                                   // sticky: a list ran out of capacity
-    unsigned int day_idx;                                    // persistent: index into the staged DayCtx array
-    unsigned long long n_log;                                // persistent
-    unsigned long long work[CABM_N_WORK];                    // persistent
-    unsigned long long cumul[CABM_N_OUTCOMES];               // persistent
-    unsigned int seed_calls;                                 // persistent
+    unsigned int day_idx;                                    // index into the staged DayCtx array
+    unsigned int seed_calls;
+    unsigned long long n_log;
+    unsigned long long work[CABM_N_WORK];
+    unsigned long long cumul[CABM_N_OUTCOMES];
 };
+#define CABM_DAY_SCOPED_WORDS 16
 
 struct Dev {
     // sizes
-    unsigned int N, L, n_patron; int R;
+    unsigned int N, L, Q, n_patron; int R;
     // static agents
     const int* home; const int* day_loc; const int* patron; const unsigned char* age; const unsigned char* pflags;
     const double* nat_eff; const float* xprot; const int* nat_dur; const float* home_risk;
     // static locations
     const unsigned char* loc_type; const unsigned char* loc_flags; const float* loc_risk; const int* loc_hospital;
     const unsigned int* roster_off; const int* roster; const unsigned int* nbr_off; const int* nbr;
+    const int* loc_pub;                  // location -> index among patronised ("public") locations, or -1
+    const int* pub_loc;                  // [Q] inverse
     // dynamic agents
     unsigned int* win; Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
-    unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand; int* inf_place; int* inf_by;
+    unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand; int* inf_place; int* inf_by; unsigned int* n_caused;
     // dynamic locations
-    unsigned long long* press; int* hot_idx; unsigned int* nvis; unsigned int* pat_count;
+    unsigned long long* press; int* loc_head; unsigned int* pat_count;
+    unsigned int* nvis; double* pub_T; unsigned int* pub_hot;     // [Q], [Q], [ceil(Q/32)] public-location visitor census, T, hot bitmap
     // day lists
-    int* hot_list; double* hot_T; double* hot_Ts; unsigned int* hot_size;
-    unsigned int* active_list; uint2* visit_rec; Item* items; unsigned int* newinf_list; unsigned int* patient_list; unsigned int* patient_tmp;
-    unsigned int cap_hot, cap_active, cap_vis, cap_items, cap_new, cap_pat; unsigned long long cap_log;
+    int* hot_list; int* hot_hosp; Flag* flags;
+    unsigned int* active_list; uint2* visit_rec; Item* items; Hit* hits; unsigned int* newinf_list; unsigned int* patient_list;
+    unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_hits, cap_new, cap_pat; unsigned long long cap_log;
     // outputs
     unsigned long long* ledger;          // [CABM_N_COUNTERS][R]
     cabm_infection* log; cabm_foi_row* foi; unsigned int* n_foi; int foi_enabled;
-    Counters* ctr; const DayCtx* dayctx;
+    Counters* ctr; const DayCtx* dayctx; DayCtx* today;
     // parameters
-    const cabm_params* par; const double* pfd; const double* imr; int n_imr; const double* ti; // ti[3][R]
+    const cabm_params* par; const double* pfd; const double* imr; int n_imr;
     int any_quarantine;
+    unsigned int visit_thr[4];           // ceil(visit_cdf[k] * 2^32), k < 4 (Poisson(1) draw of public_activity in integer form)
+    unsigned long long seed;
 };
 
 // pflags bits
 #define PF_COMORBID 1
 #define PF_LTC 2
-// pbyte: low 3 bits patron count, bit 7 in hospital today, bit 6 newly infected today
+// pbyte: low 3 bits patron count, bit 7 in hospital today, bit 5 on the admitted-patient list
 #define PB_NPAT 7
-#define PB_NEW 0x40
+#define PB_ONLIST 0x20
 #define PB_INHOSP 0x80
 // loc_flags: bit0 essential, bits 1-2 public transmission risk
 #define LF_ESSENTIAL 1
@@ -120,14 +137,16 @@ __device__ __forceinline__ int ref_sampler(const double* __restrict__ cdf, int n
     int i = 0; while (i < n && cdf[i] < r) ++i; return i;
 }
 
-__device__ __forceinline__ int pick_strain(const unsigned long long* __restrict__ w, unsigned int x) {
+// strain of the traced infector (Community.cpp:795-825, :982): the draw x picks a point t in [0, total pressure) and the
+// strain whose share contains it; *t_res is the offset inside that strain's share (used by pick_infector)
+__device__ __forceinline__ int pick_strain(const unsigned long long* __restrict__ w, unsigned int x, unsigned long long* t_res = nullptr) {
     const unsigned long long w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
     const unsigned long long total = w0 + w1 + w2 + w3;
     unsigned long long t = (unsigned long long) x * (total >> 32) + (((unsigned long long) x * (total & 0xffffffffull)) >> 32);
-    if (t < w0) return 0; t -= w0;
-    if (t < w1) return 1; t -= w1;
-    if (t < w2) return 2;
-    return 3;
+    int s = 3;
+    if (t < w0) s = 0; else { t -= w0; if (t < w1) s = 1; else { t -= w1; if (t < w2) s = 2; else t -= w2; } }
+    if (t_res) *t_res = t;
+    return s;
 }
 
 // Parameters::remainingEfficacy (Parameters.h:611-625)

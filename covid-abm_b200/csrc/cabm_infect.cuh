@@ -10,7 +10,7 @@
 #pragma once
 #include "cabm_device.cuh"
 
-struct InfectCtx { int pid, time, source, strain; bool has_source; unsigned int purpose, key_a, key_b, key_sub; };
+struct InfectCtx { int pid, time, source, strain, infector; bool has_source; unsigned int purpose, key_a, key_b, key_sub; };
 
 __device__ __noinline__ bool infect_event(const Dev& D, Stream& s, const InfectCtx c, const bool commit) {
     const cabm_params* __restrict__ par = D.par;
@@ -182,7 +182,7 @@ __device__ __noinline__ bool infect_event(const Dev& D, Stream& s, const InfectC
     n1.death = (short) t_death; n1.report_day = (short) report_day; n1.strain = (unsigned char) strain; n1.detected = (unsigned char) detected_state;
     n1.rel_inf = rel_inf;
     D.tl0[pid] = n0; D.tl1[pid] = n1;
-    D.inf_place[pid] = c.has_source ? c.source : -1; D.inf_by[pid] = -1;
+    D.inf_place[pid] = c.has_source ? c.source : -1; D.inf_by[pid] = c.infector;
     int until = max(max(t_infectious_end, t_symptom_end), max(t_severe_end, t_critical_end));
     if (t_death != CABM_I16_MAX) until = max(until, t_death);
     if (report_day != CABM_I16_MAX) until = max(until, report_day);
@@ -191,14 +191,13 @@ __device__ __noinline__ bool infect_event(const Dev& D, Stream& s, const InfectC
     const unsigned int cnt = (imm >> (8 * strain)) & 0xFF;
     if (cnt < 255) D.imm[pid] = imm + (1u << (8 * strain));
     if (par->retroactive_mature_vaccine && n_doses > 0) D.vax[pid] = vax & ~0x100u;
-    D.pbyte[pid] |= PB_NEW;
 #pragma unroll
     for (int o = 0; o < CABM_N_OUTCOMES; ++o) if (tally & (1ull << o)) atomicAdd(&D.ctr->cumul[o], 1ull);
     atomicAdd(&D.ctr->work[CABM_W_INFECTIONS], 1ull);
     const unsigned long long li = atomicAdd(&D.ctr->n_log, 1ull);
     if (li < D.cap_log) {
         cabm_infection rec;
-        rec.person = (unsigned int) pid; rec.infected_by = -1; rec.infected_place = c.has_source ? c.source : -1;
+        rec.person = (unsigned int) pid; rec.infected_by = c.infector; rec.infected_place = c.has_source ? c.source : -1;
         rec.t[0] = n0.infected; rec.t[1] = n0.infectious_begin; rec.t[2] = n0.infectious_end; rec.t[3] = n0.symptom_begin; rec.t[4] = n0.symptom_end;
         rec.t[5] = n0.severe_begin; rec.t[6] = n0.severe_end; rec.t[7] = n0.hosp_begin; rec.t[8] = n1.critical_begin; rec.t[9] = n1.critical_end;
         rec.t[10] = n1.icu_begin; rec.t[11] = n1.death; rec.report_day = n1.report_day; rec.strain = n1.strain; rec.detected_state = n1.detected;

@@ -1,4 +1,15 @@
-// covid-abm_b200/csrc/cabm_kernels2.cuh -- winner application, status pass, importation, end of day.
+// covid-abm_b200/csrc/cabm_kernels2.cuh -- second half of the day pipeline: susceptibility gate, winner
+// application fused with the status pass, hospital pass + importation, end of day.
+//
+//   k_gate          hits of a phase : calculate_event_probabilities + the Person::infect bail-out (Person.cpp:322-326)
+//                                     against the start-of-phase state; survivors race with atomicMin on the
+//                                     agent's 64-bit order key, so the first exposure in reference order wins
+//   k_apply_status  winners + active: Person::infect for each winner (disease course, detection, ledger writes) and,
+//                                     for phase 0, Community::updatePersonStatus (Community.cpp:682-741)
+//   k_hosp_import   hospitals/imports: hospital_transmission (Community.cpp:931-941) after the status pass, and
+//                                     the daily importation draws of seed_epidemic (simulator.h:201-223)
+//   k_end           hot locations   : updateHotLocations + clear_public_activity (Community.cpp:999-1003,1042-1046)
+//   k_day_end       1 thread        : counter reset, next day
 #pragma once
 #include "cabm_kernels.cuh"
 
@@ -10,36 +21,87 @@ __device__ __forceinline__ int weighted_strain(const double* __restrict__ w, dou
     return CABM_N_STRAINS - 1;
 }
 
-// Person::infect for the winning exposure of each newly infected agent (first in reference order)
-__global__ void __launch_bounds__(128) k_apply(const Dev D) {
-    const DayCtx& cx = day_ctx(D);
-    const unsigned int lo = D.ctr->n_new_applied, hi = min(D.ctr->n_new, D.cap_new);
-    for (unsigned int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
-        const unsigned int pid = D.newinf_list[i];
-        const unsigned long long key = D.cand[pid];
-        D.cand[pid] = CABM_CAND_EMPTY;
-        const int pass = (int) (key >> 40); const unsigned int src = (unsigned int) (key >> 8); const unsigned int role = (unsigned int) (key & 0xFF);
-        Stream s; InfectCtx c; c.pid = (int) pid; c.time = cx.day;
-        if (pass == PASS_IMPORT) {
-            s.begin(D.par->seed, (unsigned int) cx.day, CABM_P_IMPORT, src, 0);
-            (void) s.next();
-            c.strain = weighted_strain(cx.strain_w, s.u01());
-            c.source = -1; c.has_source = false; c.purpose = CABM_P_IMPORT; c.key_a = src; c.key_b = 0; c.key_sub = 0;
-        } else {
-            int purpose = pass; unsigned int sub = 0;
-            if (pass == PASS_WORK) purpose = role ? CABM_P_EXPOSE_WORK : CABM_P_EXPOSE_WORK_VIS;
-            else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
-            s.begin(D.par->seed, (unsigned int) cx.day, (unsigned int) purpose, pid, src, sub);
-            (void) s.next();
-            c.strain = pick_strain(&D.press[(size_t) src * CABM_N_STRAINS], s.next());
-            (void) s.next();
-            c.source = (int) src; c.has_source = true; c.purpose = (unsigned int) purpose; c.key_a = pid; c.key_b = src; c.key_sub = sub;
+// Community::trace_contact (Community.cpp:795-825): infector ~ relInf-weighted among the agents that flagged the source
+// location today. The same draw that picked the strain picks the infector: within the strain's share the flags are laid
+// out by ascending person id, t is the offset into that share.
+#define INFECTOR_CACHE 48
+__device__ __noinline__ int pick_infector(const Dev& D, const int src, const int strain, const unsigned long long t) {
+    unsigned int pids[INFECTOR_CACHE]; unsigned long long cs[INFECTOR_CACHE]; int n = 0; bool over = false;
+    for (int f = D.loc_head[src]; f >= 0;) {
+        const Flag r = D.flags[f];
+        if (FLAG_STRAIN(r) == strain) { if (n < INFECTOR_CACHE) { pids[n] = r.pid; cs[n] = FLAG_C(r); ++n; } else over = true; }
+        f = r.next;
+    }
+    if (!over) {
+        for (int i = 0; i < n; ++i) {
+            unsigned long long lower = 0, eq = 0;
+            for (int j = 0; j < n; ++j) { if (pids[j] < pids[i]) lower += cs[j]; else if (pids[j] == pids[i]) eq += cs[j]; }
+            if (t >= lower && t - lower < eq) return (int) pids[i];
         }
-        infect_event(D, s, c, true);
+        return -1;
+    }
+    for (int f = D.loc_head[src]; f >= 0;) {                       // chains longer than the cache: quadratic walk
+        const Flag r = D.flags[f];
+        if (FLAG_STRAIN(r) == strain) {
+            unsigned long long lower = 0, eq = 0;
+            for (int g = D.loc_head[src]; g >= 0;) {
+                const Flag q = D.flags[g];
+                if (FLAG_STRAIN(q) == strain) { if (q.pid < r.pid) lower += FLAG_C(q); else if (q.pid == r.pid) eq += FLAG_C(q); }
+                g = q.next;
+            }
+            if (t >= lower && t - lower < eq) return (int) r.pid;
+        }
+        f = r.next;
+    }
+    return -1;
+}
+
+// rebuild the event (stream position, strain, keys) of a hit / winner; returns false for malformed input
+__device__ __forceinline__ void event_setup(const Dev& D, const DayCtx& cx, const unsigned int pid, const unsigned int src, const unsigned int purpose,
+                                            const unsigned int sub, const bool want_infector, Stream& s, InfectCtx& c) {
+    c.pid = (int) pid; c.time = cx.day; c.infector = -1; c.purpose = purpose; c.key_sub = sub;
+    if (purpose == CABM_P_IMPORT) {
+        s.begin(D.seed, (unsigned int) cx.day, CABM_P_IMPORT, src, 0);
+        (void) s.next();                                            // the draw that chose the person
+        c.strain = weighted_strain(cx.strain_w, s.u01());
+        c.source = -1; c.has_source = false; c.key_a = src; c.key_b = 0;
+    } else {
+        s.begin(D.seed, (unsigned int) cx.day, purpose, pid, src, sub);
+        (void) s.next();                                            // the U < T draw
+        unsigned long long t_res = 0;
+        c.strain = pick_strain(&D.press[(size_t) src * CABM_N_STRAINS], s.next(), &t_res);
+        (void) s.next();                                            // reserved (reference: uniform_choice inside the group)
+        if (want_infector) c.infector = pick_infector(D, (int) src, c.strain, t_res);
+        c.source = (int) src; c.has_source = true; c.key_a = pid; c.key_b = src;
     }
 }
 
-__global__ void k_phase_end(const Dev D) { if (threadIdx.x == 0 && blockIdx.x == 0) D.ctr->n_new_applied = min(D.ctr->n_new, D.cap_new); }
+__device__ __forceinline__ unsigned long long order_key(const unsigned int purpose, const unsigned int src, const unsigned int sub) {
+    int pass = (int) purpose, role = 0;
+    if (purpose == CABM_P_EXPOSE_WORK_VIS) { pass = PASS_WORK; role = 0; }
+    else if (purpose == CABM_P_EXPOSE_WORK) { pass = PASS_WORK; role = 1; }
+    else if (purpose == CABM_P_EXPOSE_HOSP_PAT) { pass = PASS_HOSP; role = 1 + (int) sub; }
+    return make_key(pass, src, (unsigned int) role);
+}
+
+__global__ void __launch_bounds__(128) k_gate(const Dev D, const int phase) {
+    const DayCtx& cx = day_ctx(D);
+    const unsigned int lo = phase ? min(D.ctr->n_hits[0], D.cap_hits) : 0u;
+    const unsigned int hi = min(lo + D.ctr->n_hits[phase], D.cap_hits);
+    const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
+    for (unsigned int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
+        const Hit h = D.hits[i];
+        Stream s; InfectCtx c;
+        event_setup(D, cx, h.pid, h.src, h.purpose, h.sub, false, s, c);
+        if (infect_event(D, s, c, false)) {
+            const unsigned long long old = atomicMin(&D.cand[h.pid], order_key(h.purpose, h.src, h.sub));
+            if (old == CABM_CAND_EMPTY) {
+                const unsigned int ni = nbase + list_reserve(&D.ctr->n_new[phase]);
+                if (ni < D.cap_new) D.newinf_list[ni] = h.pid; else atomicOr(&D.ctr->overflow, 32u);
+            }
+        }
+    }
+}
 
 // Community::updatePersonStatus (Community.cpp:682-741) for one agent; returns the ledger increments as a bit mask
 __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p, int day) {
@@ -51,9 +113,9 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
             if (t0.hosp_begin == day) {                                             // goToHospital (Person.h:248)
                 D.hosp_count[p] = D.hosp_count[p] + 1; atomicAdd(&D.pat_count[hosp], 1u);
                 const unsigned char pb = D.pbyte[p];
-                if (!(pb & 0x20)) {
-                    D.pbyte[p] = pb | 0x20;
-                    const unsigned int pi = atomicAdd(&D.ctr->n_pat, 1u);
+                if (!(pb & PB_ONLIST)) {                                            // entries stay on the list; hosp_count == 0 means discharged
+                    D.pbyte[p] = pb | PB_ONLIST;
+                    const unsigned int pi = list_reserve(&D.ctr->n_pat);
                     if (pi < D.cap_pat) D.patient_list[pi] = p; else atomicOr(&D.ctr->overflow, 64u);
                 }
             }
@@ -79,110 +141,139 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
     return m;
 }
 
-// mode 0: agents active at the start of the day (skipping those re-infected today); mode 1: today's phase-1 infections
-__global__ void __launch_bounds__(TPB) k_status(const Dev D, const int mode) {
-    __shared__ unsigned int sm[CABM_N_COUNTERS]; BlockTally<CABM_N_COUNTERS> bt; bt.init(sm);
-    const int day = day_ctx(D).day;
-    const unsigned int n = mode == 0 ? min(D.ctr->n_active, D.cap_active) : min(D.ctr->n_new, D.cap_new);
-    const unsigned int* list = mode == 0 ? D.active_list : D.newinf_list;
+// Work index space: [0, n_w) = winners of `phase` (Person::infect, then the status tally of the new infection when
+// with_status), [n_w, n_w + n_active) = agents active at the start of the day that were not re-infected in phase 0
+// (status only; with_status). cand[] keeps the winner keys until k_end so the status half can tell who was re-infected.
+__global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int phase, const int with_status) {
+    __shared__ unsigned int sm[CABM_N_COUNTERS];
+    if (threadIdx.x < CABM_N_COUNTERS) sm[threadIdx.x] = 0;
+    __syncthreads();
+    const DayCtx& cx = day_ctx(D); const int day = cx.day;
+    const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
+    const unsigned int n_w = min(nbase + D.ctr->n_new[phase], D.cap_new) - nbase;
+    const unsigned int n_a = with_status ? min(D.ctr->n_active, D.cap_active) : 0u;
+    const unsigned int n = n_w + n_a;
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int n_round = (n + stride - 1) / stride * stride;
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         unsigned int m = 0;
-        if (i < n) {
-            const unsigned int p = list[i];
-            const unsigned char pb = D.pbyte[p];
-            if (mode == 0) { if (!(pb & PB_NEW)) m = status_one(D, p, day); }
-            else { D.pbyte[p] = pb & ~PB_NEW; m = status_one(D, p, day); }
+        if (i < n_w) {
+            const unsigned int pid = D.newinf_list[nbase + i];
+            const unsigned long long key = D.cand[pid];
+            const int pass = (int) (key >> 40); const unsigned int src = (unsigned int) (key >> 8); const unsigned int role = (unsigned int) (key & 0xFF);
+            unsigned int purpose = (unsigned int) pass, sub = 0;
+            if (pass == PASS_WORK) purpose = role ? CABM_P_EXPOSE_WORK : CABM_P_EXPOSE_WORK_VIS;
+            else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
+            Stream s; InfectCtx c;
+            event_setup(D, cx, pid, src, purpose, sub, true, s, c);
+            infect_event(D, s, c, true);
+            if (with_status) m = status_one(D, pid, day);
+        } else if (i < n) {
+            const unsigned int p = D.active_list[i - n_w];
+            if (D.cand[p] == CABM_CAND_EMPTY) m = status_one(D, p, day);
         }
-        bt.add(m);
+#pragma unroll
+        for (int c = 0; c < CABM_N_COUNTERS; ++c) {
+            const unsigned int b = __ballot_sync(0xffffffffu, (m >> c) & 1u);
+            if (b && (threadIdx.x & 31) == 0) atomicAdd(&sm[c], __popc(b));
+        }
     }
     __syncthreads();
     if (threadIdx.x < CABM_N_COUNTERS && sm[threadIdx.x]) atomicAdd(&D.ledger[(size_t) threadIdx.x * D.R + day], (unsigned long long) sm[threadIdx.x]);
 }
 
-// drop discharged agents from the persistent patient list (single block; the list is tiny)
-__global__ void __launch_bounds__(TPB) k_compact_patients(const Dev D) {
-    __shared__ unsigned int base;
-    const unsigned int n = min(D.ctr->n_pat, D.cap_pat);
-    if (threadIdx.x == 0) base = 0;
-    __syncthreads();
-    for (unsigned int i0 = 0; i0 < n; i0 += blockDim.x) {
-        const unsigned int i = i0 + threadIdx.x;
-        unsigned int pid = 0; bool keep = false;
-        if (i < n) { pid = D.patient_list[i]; keep = D.hosp_count[pid] > 0; if (!keep) D.pbyte[pid] &= ~0x20; }
-        const unsigned int b = __ballot_sync(0xffffffffu, keep);
-        __shared__ unsigned int wbase[TPB / 32];
-        if ((threadIdx.x & 31) == 0) wbase[threadIdx.x >> 5] = __popc(b);
-        __syncthreads();
-        if (threadIdx.x == 0) { unsigned int acc = base; for (int w = 0; w < TPB / 32; ++w) { const unsigned int c = wbase[w]; wbase[w] = acc; acc += c; } base = acc; }
-        __syncthreads();
-        if (keep) D.patient_tmp[wbase[threadIdx.x >> 5] + __popc(b & ((1u << (threadIdx.x & 31)) - 1))] = pid;
-        __syncthreads();
-    }
-    for (unsigned int i = threadIdx.x; i < base; i += blockDim.x) D.patient_list[i] = D.patient_tmp[i];
-    __syncthreads();
-    if (threadIdx.x == 0) D.ctr->n_pat = base;
+// hospital_transmission (Community.cpp:931-941): census = staff + admitted patients; every consumer computes T itself
+__device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, const int hosp, unsigned int* denom_out, unsigned long long* pws) {
+    const unsigned long long* pw = &D.press[(size_t) hosp * CABM_N_STRAINS];
+    pws[0] = pw[0]; pws[1] = pw[1]; pws[2] = pw[2]; pws[3] = pw[3];
+    const unsigned long long tot = pws[0] + pws[1] + pws[2] + pws[3];
+    const unsigned int denom = D.roster_off[hosp + 1] - D.roster_off[hosp] + D.pat_count[hosp];
+    *denom_out = denom;
+    if (tot == 0 || denom < 2) return 0.0;
+    const double w = CABM_MUL((double) tot, 1.0 / 4294967296.0);
+    return hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(D.par->haz_mult[CABM_HOSPITAL], cx.season), w), CABM_SUB((double) (int) denom, 1.0)));
 }
 
-// seed_epidemic(par, community, date, strain_weights) (simulator.h:201-223): gate of every import of the day
-__global__ void __launch_bounds__(128) k_import(const Dev D) {
-    const DayCtx& cx = day_ctx(D);
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < (unsigned int) cx.n_imports; i += gridDim.x * blockDim.x) {
-        Stream s; s.begin(D.par->seed, (unsigned int) cx.day, CABM_P_IMPORT, i, 0);
-        const unsigned int pid = __umulhi(s.next(), D.N);
-        InfectCtx c; c.pid = (int) pid; c.time = cx.day; c.source = -1; c.has_source = false;
-        c.strain = weighted_strain(cx.strain_w, s.u01());
-        c.purpose = CABM_P_IMPORT; c.key_a = i; c.key_b = 0; c.key_sub = 0;
-        if (infect_event(D, s, c, false)) {
-            const unsigned long long old = atomicMin(&D.cand[pid], make_key(PASS_IMPORT, i, 0));
-            if (old == CABM_CAND_EMPTY) {
-                const unsigned int ni = atomicAdd(&D.ctr->n_new, 1u);
-                if (ni < D.cap_new) D.newinf_list[ni] = pid; else atomicOr(&D.ctr->overflow, 32u);
-            }
+// do_hosp: warps [0, n_hot_hosp) expose the staff of one hot hospital each, then all threads walk the admitted-patient
+// list; do_import: all threads walk today's importation draws (every draw is a "hit": the person is chosen, not exposed)
+__global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_hosp, const int do_import) {
+    const DayCtx& cx = day_ctx(D); const int day = cx.day;
+    const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    const unsigned int lane = threadIdx.x & 31, warp = tid >> 5, n_warps = nth >> 5;
+    unsigned int trials = 0;
+    if (do_hosp) {
+        const unsigned int nh = min(D.ctr->n_hot_hosp, D.cap_hot);
+        for (unsigned int j = warp; j < nh; j += n_warps) {
+            const unsigned int i = (unsigned int) D.hot_hosp[j];                        // index of the hospital in the hot list
+            const int hosp = D.hot_list[i];
+            unsigned int denom; unsigned long long pws[4];
+            const double T = hospital_T(D, cx, hosp, &denom, pws);
+            const unsigned int rb = D.roster_off[hosp], size = D.roster_off[hosp + 1] - rb;
+            if (T > 0.0) for (unsigned int m = lane; m < size; m += 32) trial(D, day, 1, (unsigned int) D.roster[rb + m], hosp, CABM_P_EXPOSE_HOSP, 0, T, trials);
+            if (D.foi_enabled && lane == 0) write_foi(D, i, hosp, CABM_HOSPITAL, pws, denom, T, 0.0);
+        }
+        const unsigned int np = min(D.ctr->n_pat, D.cap_pat);
+        for (unsigned int i = tid; i < np; i += nth) {
+            const unsigned int pid = D.patient_list[i];
+            const unsigned int c = D.hosp_count[pid];
+            if (c == 0) continue;
+            const int hosp = D.loc_hospital[D.home[pid]];
+            if (hosp < 0 || D.loc_head[hosp] == -1) continue;
+            unsigned int denom; unsigned long long pws[4];
+            const double T = hospital_T(D, cx, hosp, &denom, pws);
+            if (T > 0.0) for (unsigned int sub = 0; sub < c; ++sub) trial(D, day, 1, pid, hosp, CABM_P_EXPOSE_HOSP_PAT, sub, T, trials);
         }
     }
+    if (do_import) {
+        const unsigned int base = min(D.ctr->n_hits[0], D.cap_hits);
+        for (unsigned int i = tid; i < (unsigned int) cx.n_imports; i += nth) {
+            const uint4 b = philox4x32_10(make_uint4(0u, i, 0u, ((unsigned int) day << 8) | CABM_P_IMPORT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
+            const unsigned int pid = __umulhi(b.x, D.N);
+            const unsigned int h = base + list_reserve(&D.ctr->n_hits[1]);
+            if (h < D.cap_hits) { Hit r; r.pid = pid; r.src = i; r.purpose = CABM_P_IMPORT; r.sub = 0; D.hits[h] = r; }
+            else atomicOr(&D.ctr->overflow, 256u);
+        }
+    }
+    trials = warp_sum(trials);
+    if (lane == 0 && trials) atomicAdd(&D.ctr->work[CABM_W_TRIALS], (unsigned long long) trials);
 }
 
 // Community::infect(id, strain) (Community.cpp:550-553): one agent, gate and commit in one go
 __global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain, const int day, int* out) {
     if (threadIdx.x || blockIdx.x) return;
     const unsigned int seq = D.ctr->seed_calls++;
-    Stream s; s.begin(D.par->seed, (unsigned int) day, CABM_P_SEED, pid, seq);
-    InfectCtx c; c.pid = (int) pid; c.time = day; c.source = -1; c.has_source = false; c.strain = strain;
+    Stream s; s.begin(D.seed, (unsigned int) day, CABM_P_SEED, pid, seq);
+    InfectCtx c; c.pid = (int) pid; c.time = day; c.source = -1; c.has_source = false; c.strain = strain; c.infector = -1;
     c.purpose = CABM_P_SEED; c.key_a = pid; c.key_b = seq; c.key_sub = 0;
     *out = infect_event(D, s, c, true) ? 1 : 0;
 }
 
-// updateHotLocations (Community.cpp:999-1003) + clear_public_activity (:1042-1046): reset what today's hot set touched
-__global__ void __launch_bounds__(TPB) k_end(const Dev D) {
-    const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_hot; i += gridDim.x * blockDim.x) {
-        const int loc = D.hot_list[i];
-        unsigned long long* pw = &D.press[(size_t) loc * CABM_N_STRAINS];
-        if (D.foi_enabled) {
-            cabm_foi_row r; r.loc = (unsigned int) loc; r.type = D.loc_type[loc]; r.pad[0] = r.pad[1] = r.pad[2] = 0;
-            for (int s = 0; s < CABM_N_STRAINS; ++s) r.w[s] = CABM_MUL((double) pw[s], 1.0 / 4294967296.0);
-            r.size = D.hot_size[i]; r.T = D.hot_T[i]; r.T_social = D.hot_Ts[i];
-            D.foi[i] = r;
+// reset what today's hot set and today's winners touched
+__global__ void __launch_bounds__(TPB) k_end(const Dev D, const int reset_hot) {
+    const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    if (reset_hot) {
+        const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
+        for (unsigned int i = tid; i < n_hot; i += nth) {
+            const int loc = D.hot_list[i];
+            ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
+            pw[0] = make_ulonglong2(0, 0); pw[1] = make_ulonglong2(0, 0);
+            D.loc_head[loc] = -1;
+            const int q = D.loc_pub[loc];
+            if (q >= 0) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }      // the whole bitmap word: every set bit belongs to a hot location
         }
-        pw[0] = 0; pw[1] = 0; pw[2] = 0; pw[3] = 0;
-        D.hot_idx[loc] = -1; D.nvis[loc] = 0;
     }
+    const unsigned int n_new = min(D.ctr->n_new[0] + D.ctr->n_new[1], D.cap_new);
+    for (unsigned int i = tid; i < n_new; i += nth) D.cand[D.newinf_list[i]] = CABM_CAND_EMPTY;
 }
 
-__global__ void k_tick_end(const Dev D) {
+__global__ void k_day_end(const Dev D, const int tick_done, const int advance) {
     if (threadIdx.x || blockIdx.x) return;
     Counters* c = D.ctr;
-    c->work[CABM_W_HOT_LOCS] += min(c->n_hot, D.cap_hot);
-    if (D.foi_enabled) *D.n_foi = min(c->n_hot, D.cap_hot);
-    c->n_hot = 0; c->n_active = 0; c->n_vis = 0; c->n_items = 0; c->n_new = 0; c->n_new_applied = 0;
-}
-__global__ void k_items_reset(const Dev D) { if (threadIdx.x == 0 && blockIdx.x == 0) D.ctr->n_items = 0; }
-__global__ void k_import_end(const Dev D, const int advance) {
-    if (threadIdx.x || blockIdx.x) return;
-    D.ctr->n_new = 0; D.ctr->n_new_applied = 0;
-    if (advance) D.ctr->day_idx++;
+    if (tick_done) { c->work[CABM_W_HOT_LOCS] += min(c->n_hot, D.cap_hot); if (D.foi_enabled) *D.n_foi = min(c->n_hot, D.cap_hot); }
+    unsigned int* w = reinterpret_cast<unsigned int*>(c);
+#pragma unroll
+    for (int k = 0; k < CABM_DAY_SCOPED_WORDS; ++k) w[k] = 0;
+    if (advance) c->day_idx++;
 }
 
 // Person::vaccinate (Person.cpp:611-647), leaky model
@@ -231,5 +322,5 @@ __global__ void k_init_state(const Dev D) {
         D.win[p] = 0x80007FFFu;                       // from = 32767, until = -32768: never active
         D.cand[p] = CABM_CAND_EMPTY;
     }
-    for (unsigned int l = blockIdx.x * blockDim.x + threadIdx.x; l < D.L; l += stride) D.hot_idx[l] = -1;
+    for (unsigned int l = blockIdx.x * blockDim.x + threadIdx.x; l < D.L; l += stride) D.loc_head[l] = -1;
 }

@@ -118,7 +118,7 @@ bool Sim::infect(int pid, int time, int source_loc, int strain, bool has_source,
     // ---- new infection record ----
     const int incubation = 1 + (int) table_draw(par.incub_cdf[strain], CABM_INCUB_MAX, s.u01()); // Parameters.h:515-520
     Infection inf;
-    inf.t[T_INFECTED] = time; inf.place = has_source ? source_loc : -1; inf.strain = strain;
+    inf.t[T_INFECTED] = time; inf.place = has_source ? source_loc : -1; inf.strain = strain; inf.by = has_source ? pending_infector : -1;
     const int onset = 1 + (int) table_draw(par.onset_cdf[incubation - 1], CABM_INCUB_MAX + 1, s.u01()); // Parameters.h:521-524
     inf.t[T_INFECTIOUS_BEGIN] = time + onset;
     const int period_strain = has_source ? strain : 0;                                            // :153,156 (WILDTYPE period for imports)

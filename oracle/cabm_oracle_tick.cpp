@@ -8,13 +8,25 @@
 
 namespace cabm_oracle {
 
-// pick a strain with probability w_fx[s] / total from one 32-bit draw (exact integer arithmetic);
-// stands in for "strain of the traced infector" (Community.cpp:795-825, :982)
-static int pick_strain(const uint64_t w_fx[CABM_N_STRAINS], uint32_t x) {
+// One 32-bit draw picks a point t in [0, total pressure) of the source location: the strain whose share contains t
+// is the strain transmitted, and inside that share the flags are laid out by ascending person id, so t also names
+// the infector. Stands in for Community::trace_contact (Community.cpp:795-825): weighted_choice over relInf groups,
+// uniform inside the group, i.e. infector ~ relInf-weighted; exact integer arithmetic.
+static int pick_strain(const uint64_t w_fx[CABM_N_STRAINS], uint32_t x, uint64_t* t_res) {
     const uint64_t total = w_fx[0] + w_fx[1] + w_fx[2] + w_fx[3];
     uint64_t t = (uint64_t) x * (total >> 32) + (((uint64_t) x * (total & 0xffffffffull)) >> 32);
-    for (int s = 0; s < CABM_N_STRAINS - 1; ++s) { if (t < w_fx[s]) return s; t -= w_fx[s]; }
-    return CABM_N_STRAINS - 1;
+    int s = 0;
+    for (; s < CABM_N_STRAINS - 1; ++s) { if (t < w_fx[s]) break; t -= w_fx[s]; }
+    *t_res = t;
+    return s;
+}
+static int pick_infector(const LocHot& H, int strain, uint64_t t) {
+    std::vector<std::pair<int32_t, uint64_t>> v;
+    for (const HotRec& r : H.recs) if (r.strain == strain) v.push_back({ r.pid, r.c_fx });
+    std::sort(v.begin(), v.end());
+    uint64_t acc = 0;
+    for (auto& e : v) { acc += e.second; if (t < acc) return e.first; }
+    return -1;
 }
 
 // Community::_transmission (Community.cpp:971-996)
@@ -30,8 +42,10 @@ void Sim::transmission(int day, int source, const int32_t* at_risk, size_t n, co
         work[CABM_W_TRIALS]++;
         Stream s; s.begin(par.seed, (uint32_t) day, purpose, (uint32_t) pid, (uint32_t) source, sub);
         if (s.u01() < T) {                                                                 // :976
-            const int strain = pick_strain(H.w_fx, s.next());                              // :980-982
-            (void) s.next();                                                               // reserved: infector choice
+            uint64_t t_res = 0;
+            const int strain = pick_strain(H.w_fx, s.next(), &t_res);                      // :980-982
+            (void) s.next();                                                               // reserved (reference: uniform_choice inside the group)
+            pending_infector = pick_infector(H, strain, t_res);
             infect(pid, day, source, strain, true, s, purpose, (uint32_t) pid, (uint32_t) source, sub);
         }
     }
