@@ -129,7 +129,7 @@ static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     if (tick) {
         LAUNCH(KID_SCAN, k_scan<<<gScan, TPB, 0, st>>>(D));
         LAUNCH(KID_ACTIVE, k_active<<<gSM * 8, TPB, 0, st>>>(D));
-        LAUNCH(KID_VISIT, k_visit<<<std::min<unsigned int>((D.N + TPB - 1) / TPB, gSM * 6), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words));
+        LAUNCH(KID_VISIT, k_visit<<<std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), gSM * 4), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words));
         LAUNCH(KID_HAZARD, k_hazard<<<gSM * 8, TPB, 0, st>>>(D));
         LAUNCH(KID_TRIALS, k_trials<<<gSM * 8, TPB, 0, st>>>(D));
         LAUNCH(KID_GATE0, k_gate<<<gSM * 4, 128, 0, st>>>(D, 0));
@@ -244,13 +244,13 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     if (h->have_pop) { h->err = "population already loaded"; return CABM_E_STATE; }
     if (!pop->starting_natural_efficacy || !pop->cross_protection_probability || !pop->natural_immunity_duration) {
         h->err = "load-time immunity attributes are required"; return CABM_E_ARG; }
-    if (pop->n_patron > PB_NPAT) { h->err = "at most 7 patronised locations per person"; return CABM_E_ARG; }
+    if (pop->n_patron > 5) { h->err = "at most 5 patronised locations per person (Community.cpp:279-288)"; return CABM_E_ARG; }
     cudaSetDevice(h->device);
     const uint32_t N = pop->n_people, L = pop->n_loc, NP = pop->n_patron;
     Dev& D = h->d; D.N = N; D.L = L; D.n_patron = std::max<uint32_t>(NP, 1);
     int rc;
     // ---- static agents ----
-    std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N), patron((size_t) N * D.n_patron, -1);
+    std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N), patron((size_t) N * PATRON_ROW, 0);
     std::vector<unsigned char> age(pop->age, pop->age + N), pflags(N), pbyte(N, 0);
     std::vector<float> home_risk(N);
     // patronised ("public") locations get a dense index q: the visit pass tests hotness in a shared-memory bitmap over q
@@ -259,12 +259,13 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         if (home[p] < 0 || (uint32_t) home[p] >= L || dayl[p] >= (int) L) { h->err = "home/day location out of range"; return CABM_E_ARG; }
         pflags[p] = (pop->comorbid[p] ? PF_COMORBID : 0) | (pop->ltc[p] ? PF_LTC : 0);
         home_risk[p] = pop->loc_risk[home[p]];
+        std::memcpy(&patron[(size_t) p * PATRON_ROW + PATRON_RISK], &home_risk[p], sizeof(float));
         unsigned int np = 0;
         for (uint32_t k = 0; k < NP; ++k) {
             const int loc = pop->patron[(size_t) p * NP + k]; if (loc < 0) break;
             if ((uint32_t) loc >= L) { h->err = "patronised location out of range"; return CABM_E_ARG; }
             if (loc_pub[loc] < 0) { loc_pub[loc] = (int) pub_loc.size(); pub_loc.push_back(loc); }
-            patron[(size_t) p * D.n_patron + k] = loc_pub[loc] | (pop->loc_pubrisk[loc] == CABM_PT_HIGH ? PATRON_HIGH : 0); np++;
+            patron[(size_t) p * PATRON_ROW + k] = loc_pub[loc] | (pop->loc_pubrisk[loc] == CABM_PT_HIGH ? PATRON_HIGH : 0); np++;
         }
         pbyte[p] = (unsigned char) np;
     }
@@ -300,14 +301,14 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = dalloc(h, &D.imm, N, true)) || (rc = dalloc(h, &D.vax, N, true)) || (rc = dalloc(h, &D.vax_days, (size_t) N * CABM_MAX_DOSES, true)) ||
         (rc = dalloc(h, &D.quar, N, true)) || (rc = dalloc(h, &D.hosp_count, N, true)) || (rc = dalloc(h, &D.pbyte, N, true)) ||
         (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.inf_place, N, true, 0xFF)) || (rc = dalloc(h, &D.inf_by, N, true, 0xFF)) ||
-        (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.loc_head, L)) || (rc = dalloc(h, &D.pat_count, L, true)) ||
+        (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.loc_cnt, L)) || (rc = dalloc(h, &D.loc_hot, L)) || (rc = dalloc(h, &D.pat_count, L, true)) ||
         (rc = dalloc(h, &D.nvis, Q1)) || (rc = dalloc(h, &D.pub_T, Q1)) || (rc = dalloc(h, &D.pub_hot, h->bitmap_words))) return rc;
     CK(cudaMemcpyAsync(D.pbyte, pbyte.data(), N, cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----
     D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
-    D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + (size_t) L / 64 + 1024);
+    D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + roster.size() / SMALL_ROSTER + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
-    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
+    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
         (rc = dalloc(h, &D.active_list, D.cap_active)) || (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
         (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
         (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||

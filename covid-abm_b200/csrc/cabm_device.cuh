@@ -29,8 +29,10 @@ struct __align__(16) Tl1 { short critical_begin, critical_end, icu_begin, death,
 struct __align__(16) Item { int src; int begin; int count; int purpose; double T; double pad; };   // a 256-member chunk of a big roster
 struct __align__(16) Hit  { unsigned int pid; unsigned int src; unsigned int purpose; unsigned int sub; }; // a trial with U < T, to be gated
 // one (infectious agent, location) flag of the day (Community::flagInfectedLocation, Community.cpp:788-791);
-// c = pressure contribution in 2^-32 units, strain in the top byte; next = previous head of the location's chain
-struct __align__(16) Flag { unsigned int pid; int next; unsigned long long c; };
+// c = pressure contribution in 2^-32 units with the strain in the top byte. k_active appends FlagRaw records;
+// k_trials scatters them into one contiguous segment per hot location (Flag), which k_apply_status searches.
+struct __align__(8)  FlagRaw { int loc; unsigned int slot; unsigned int pid; unsigned int pad; unsigned long long c; };
+struct __align__(16) Flag { unsigned int pid; unsigned int pad; unsigned long long c; };
 #define FLAG_C(f) ((f).c & 0x00FFFFFFFFFFFFFFull)
 #define FLAG_STRAIN(f) ((int) ((f).c >> 56))
 
@@ -43,9 +45,9 @@ struct DayCtx {                     // per-day scalars, staged by the host for e
 // counters living in device memory
 struct Counters {
     // ---- day-scoped: zeroed by k_day_end ----
-    unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items;
+    unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg;
     unsigned int n_hits[2], n_new[2];                        // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
-    unsigned int day_pad[6];
+    unsigned int day_pad[5];
     // ---- persistent ----
     unsigned int n_pat;                                      // admitted-patient list length (entries are never removed, see k_status)
     unsigned int overflow;                                   // sticky: a list ran out of capacity
@@ -72,10 +74,10 @@ struct Dev {
     unsigned int* win; Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
     unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand; int* inf_place; int* inf_by; unsigned int* n_caused;
     // dynamic locations
-    unsigned long long* press; int* loc_head; unsigned int* pat_count;
+    unsigned long long* press; unsigned int* loc_cnt; int* loc_hot; unsigned int* pat_count;   // loc_cnt: flags today (0 = not hot), loc_hot: index in hot_list
     unsigned int* nvis; double* pub_T; unsigned int* pub_hot;     // [Q], [Q], [ceil(Q/32)] public-location visitor census, T, hot bitmap
     // day lists
-    int* hot_list; int* hot_hosp; Flag* flags;
+    int* hot_list; int* hot_hosp; unsigned int* hot_off; FlagRaw* flags_raw; Flag* flags;
     unsigned int* active_list; uint2* visit_rec; Item* items; Hit* hits; unsigned int* newinf_list; unsigned int* patient_list;
     unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_hits, cap_new, cap_pat; unsigned long long cap_log;
     // outputs

@@ -12,7 +12,7 @@
 
 struct InfectCtx { int pid, time, source, strain, infector; bool has_source; unsigned int purpose, key_a, key_b, key_sub; };
 
-__device__ __noinline__ bool infect_event(const Dev& D, Stream& s, const InfectCtx c, const bool commit) {
+__device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const InfectCtx c, const bool commit) {
     const cabm_params* __restrict__ par = D.par;
     const int pid = c.pid, time = c.time, strain = c.strain;
     const int a = D.age[pid]; const unsigned int pf = D.pflags[pid]; const int com = (pf & PF_COMORBID) ? 1 : 0;

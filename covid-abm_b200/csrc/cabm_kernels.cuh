@@ -12,7 +12,8 @@
 //   k_hazard   hot locations   : _tally_infectiousness + the hazard of every pass (Community.cpp:833-969); one warp
 //                                per location runs the household / neighbour / small-roster trials in place and
 //                                splits big rosters into 256-member items
-//   k_trials   items + visits  : _transmission's `U < T` (Community.cpp:976) for big rosters and visitors
+//   k_trials   items + visits  : _transmission's `U < T` (Community.cpp:976) for big rosters and visitors; also scatters
+//                                the day's flag records into one contiguous segment per hot location
 //
 // A trial that succeeds is appended to the hit list; the (rare, heavy) susceptibility gate and the state
 // transition run in k_gate / k_apply (cabm_kernels2.cuh) so the streaming kernels stay convergent.
@@ -25,9 +26,10 @@ namespace cg = cooperative_groups;
 
 #define TPB 256
 #define CHUNK 256
-#define SMALL_ROSTER 512
+#define SMALL_ROSTER 64
 #define MAXV 8
-#define VIS_BUF 2048
+#define PATRON_ROW 8          // ints per agent: 5 patronised public-location indices, household riskiness (float bits), 2 pad
+#define PATRON_RISK 5
 
 __device__ __forceinline__ const DayCtx& day_ctx(const Dev& D) { return *D.today; }
 
@@ -92,20 +94,17 @@ __global__ void __launch_bounds__(TPB) k_scan(const Dev D) {
     for (int k = 0; k < 4; ++k) if (mask & (1u << k)) { if (o < D.cap_active) D.active_list[o] = p0 + k; else atomicOr(&D.ctr->overflow, 4u); ++o; }
 }
 
-// Community::flagInfectedLocation (Community.cpp:788-791) on device: add to the per-strain pressure and push a flag
-// record on the location's chain; whoever finds the chain empty appends the location to the hot list.
-__device__ __forceinline__ void add_pressure(const Dev& D, int loc, int strain, unsigned long long c, unsigned int pid) {
-    if (loc < 0 || c == 0) return;
-    atomicAdd(&D.press[(size_t) loc * CABM_N_STRAINS + strain], c);
-    const unsigned int f = list_reserve(&D.ctr->n_flags);
-    if (f >= D.cap_flags) { atomicOr(&D.ctr->overflow, 128u); return; }
-    const int old = atomicExch(&D.loc_head[loc], (int) f);
-    Flag r; r.pid = pid; r.next = old; r.c = c | ((unsigned long long) strain << 56);
-    D.flags[f] = r;
-    if (old == -1) {
+// Community::flagInfectedLocation (Community.cpp:788-791) on device, second half: the flag record, and for the first
+// flag of a location the hot-list entry. `slot` is what atomicAdd(&loc_cnt[loc], 1) returned, f the record index.
+__device__ __forceinline__ void flag_location(const Dev& D, int loc, int strain, unsigned long long c, unsigned int pid, unsigned int slot, unsigned int f) {
+    if (f < D.cap_flags) { FlagRaw r; r.loc = loc; r.slot = slot; r.pid = pid; r.pad = 0; r.c = c | ((unsigned long long) strain << 56); D.flags_raw[f] = r; }
+    else atomicOr(&D.ctr->overflow, 128u);
+    if (slot == 0) {
         const unsigned int i = list_reserve(&D.ctr->n_hot);
-        if (i < D.cap_hot) D.hot_list[i] = loc; else atomicOr(&D.ctr->overflow, 2u);
-        if (D.loc_type[loc] == CABM_HOSPITAL && i < D.cap_hot) { const unsigned int j = list_reserve(&D.ctr->n_hot_hosp); if (j < D.cap_hot) D.hot_hosp[j] = (int) i; }
+        if (i < D.cap_hot) {
+            D.hot_list[i] = loc; D.loc_hot[loc] = (int) i;
+            if (D.loc_type[loc] == CABM_HOSPITAL) { const unsigned int j = list_reserve(&D.ctr->n_hot_hosp); if (j < D.cap_hot) D.hot_hosp[j] = (int) i; }
+        } else atomicOr(&D.ctr->overflow, 2u);
         const int q = D.loc_pub[loc];
         if (q >= 0) atomicOr(&D.pub_hot[q >> 5], 1u << (q & 31));
     }
@@ -123,7 +122,7 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
     else if (b.x < D.visit_thr[3]) k = 3;
     else k = (int) table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
     int nv = 0, avoiding = -1;
-    const int* __restrict__ row = D.patron + (size_t) pid * D.n_patron;
+    const int* __restrict__ row = D.patron + (size_t) pid * PATRON_ROW;
     for (int i = 0; i < k; ++i) {
         const unsigned int idx1 = (unsigned int) i + 1u;              // draw index within the stream (0 was the Poisson draw)
         if ((idx1 & 3u) == 0) b = philox4x32_10(make_uint4(idx1 >> 2, pid, 0u, ((unsigned int) cx.day << 8) | CABM_P_VISIT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
@@ -131,7 +130,7 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
         const unsigned int x = lane == 0 ? b.x : lane == 1 ? b.y : lane == 2 ? b.z : b.w;
         const int e = row[__umulhi(x, (unsigned int) npat)];
         if (e & PATRON_HIGH) {
-            if (avoiding < 0) avoiding = ((double) D.home_risk[pid] < cx.sd) ? 1 : 0;
+            if (avoiding < 0) avoiding = ((double) __int_as_float(row[PATRON_RISK]) < cx.sd) ? 1 : 0;
             if (avoiding) continue;
         }
         const int q = e & 0x3FFFFFFF;
@@ -157,19 +156,39 @@ __global__ void __launch_bounds__(TPB) k_active(const Dev D) {
         const unsigned char npb = (unsigned char) ((pb & ~PB_INHOSP) | (inhosp ? PB_INHOSP : 0));
         if (npb != pb) D.pbyte[p] = npb;
         if (!tl_in(t0.infectious_begin, t0.infectious_end, day)) continue;
+        // where this agent is infectious today (Person.cpp:475-486, Community.cpp:1031-1035): up to 2 + MAXV places
+        int locs[2 + MAXV]; unsigned long long cs[2 + MAXV]; int nl = 0;
         const unsigned long long c = (unsigned long long) __double2ll_rn(CABM_MUL((double) t1.rel_inf, 4294967296.0));
-        if (inhosp) { add_pressure(D, D.loc_hospital[hm], t1.strain, c, p); nflag++; continue; }
-        add_pressure(D, hm, t1.strain, c, p); nflag++;
-        if (dl >= 0 && !(tl_in(t0.severe_begin, t0.severe_end, day) || tl_in(t1.critical_begin, t1.critical_end, day))) { add_pressure(D, dl, t1.strain, c, p); nflag++; }
-        const int npat = pb & PB_NPAT;
-        if (npat) {
-            int qs[MAXV], hours[MAXV];
-            const int nv = gen_visits(D, cx, p, npat, qs, hours);
-            for (int j = 0; j < nv; ++j) {
-                const unsigned long long cv = (unsigned long long) __double2ll_rn(CABM_MUL(CABM_MUL((double) t1.rel_inf, (double) hours[j]), 536870912.0));
-                if (cv) { add_pressure(D, D.pub_loc[qs[j]], t1.strain, cv, p); nflag++; }
+        if (inhosp) { const int h = D.loc_hospital[hm]; if (h >= 0 && c) { locs[0] = h; cs[0] = c; nl = 1; } }
+        else {
+            if (c) { locs[0] = hm; cs[0] = c; nl = 1; }
+            if (dl >= 0 && c && !(tl_in(t0.severe_begin, t0.severe_end, day) || tl_in(t1.critical_begin, t1.critical_end, day))) { locs[nl] = dl; cs[nl] = c; nl++; }
+            const int npat = pb & PB_NPAT;
+            if (npat) {
+                int qs[MAXV], hours[MAXV];
+                const int nv = gen_visits(D, cx, p, npat, qs, hours);
+                for (int j = 0; j < nv; ++j) {
+                    const unsigned long long cv = (unsigned long long) __double2ll_rn(CABM_MUL(CABM_MUL((double) t1.rel_inf, (double) hours[j]), 536870912.0));
+                    if (cv) { locs[nl] = D.pub_loc[qs[j]]; cs[nl] = cv; nl++; }
+                }
             }
         }
+        if (nl == 0) continue;
+        // all atomics of the agent are issued back to back so their round trips overlap
+        unsigned int slots[2 + MAXV];
+        cg::coalesced_group g = cg::coalesced_threads();
+        const unsigned int mine = (unsigned int) nl;
+        unsigned int incl = mine;                                                  // inclusive scan over the group for one reservation
+        for (unsigned int o = 1; o < g.size(); o <<= 1) { const unsigned int t = g.shfl_up(incl, o); if (g.thread_rank() >= o) incl += t; }
+        unsigned int base = 0;
+        if (g.thread_rank() == g.size() - 1) base = atomicAdd(&D.ctr->n_flags, incl);
+        base = g.shfl(base, g.size() - 1) + incl - mine;
+        for (int k = 0; k < nl; ++k) {
+            atomicAdd(&D.press[(size_t) locs[k] * CABM_N_STRAINS + t1.strain], cs[k]);
+            slots[k] = atomicAdd(&D.loc_cnt[locs[k]], 1u);
+        }
+        for (int k = 0; k < nl; ++k) flag_location(D, locs[k], t1.strain, cs[k], p, slots[k], base + k);
+        nflag += mine;
     }
     nflag = warp_sum(nflag);
     if ((threadIdx.x & 31) == 0 && nflag) atomicAdd(&D.ctr->work[CABM_W_FLAGS], (unsigned long long) nflag);
@@ -177,58 +196,102 @@ __global__ void __launch_bounds__(TPB) k_active(const Dev D) {
 
 // ---------------------------------------------------------------------------------------------
 // k_visit: every agent with patronised locations that is not in hospital draws its visits.
-// dynamic shared memory: hot bitmap of the Q patronised locations (ceil(Q/32) words)
+// Four agents per thread. Per agent the only memory on the path is the status byte and, when k > 0, the agent's
+// 32-byte patron row (5 public-location indices + the household's riskiness); the Philox block needs no memory.
+// Hotness is tested against a shared-memory bitmap over the Q patronised locations (dynamic shared memory,
+// ceil(Q/32) words); visits that land on a hot location are counted (nvis) and recorded with one warp-aggregated
+// reservation per round. There is no block-level synchronisation in the loop.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB) k_visit(const Dev D, const unsigned int bitmap_words) {
+__device__ __forceinline__ int row_pick(const uint4& ra, const uint4& rb, const unsigned int idx) {
+    return (int) (idx == 0 ? ra.x : idx == 1 ? ra.y : idx == 2 ? ra.z : idx == 3 ? ra.w : rb.x);
+}
+
+__global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned int bitmap_words) {
     extern __shared__ unsigned int s_hot[];
-    __shared__ uint2 s_buf[VIS_BUF];
-    __shared__ unsigned int s_cnt, s_gbase;
     const DayCtx& cx = day_ctx(D);
     for (unsigned int i = threadIdx.x; i < bitmap_words; i += blockDim.x) s_hot[i] = D.pub_hot[i];
-    if (threadIdx.x == 0) s_cnt = 0;
     __syncthreads();
-    const unsigned int stride = gridDim.x * blockDim.x;
+    const unsigned int stride = gridDim.x * blockDim.x * 4u;
     const unsigned int n_round = (D.N + stride - 1) / stride * stride;
+    const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
+    const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
+    const double sd = cx.sd;
+    const unsigned int lane = threadIdx.x & 31;
+    const uint4* __restrict__ rows = reinterpret_cast<const uint4*>(D.patron);
     unsigned int w_pat = 0, w_v0 = 0, w_v = 0;
-    for (unsigned int p = blockIdx.x * blockDim.x + threadIdx.x; p < n_round; p += stride) {
-        if (p < D.N) {
-            const unsigned char pb = D.pbyte[p];
-            const int npat = pb & PB_NPAT;
-            if (npat && !(pb & PB_INHOSP)) {
-                w_pat++;
-                int qs[MAXV], hours[MAXV];
-                const int nv = gen_visits(D, cx, p, npat, qs, hours);
-                w_v0 += (unsigned int) nv;
-                for (int j = 0; j < nv; ++j) {
-                    const int q = qs[j];
+    for (unsigned int p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u; p0 < n_round; p0 += stride) {
+        unsigned int pb4 = 0;
+        if (p0 + 3 < D.N) pb4 = *reinterpret_cast<const unsigned int*>(D.pbyte + p0);
+        else for (unsigned int a = 0; a < 4; ++a) if (p0 + a < D.N) pb4 |= (unsigned int) D.pbyte[p0 + a] << (8 * a);
+        unsigned int recq[12]; unsigned int nrec = 0, recmask = 0;            // hot visits of this thread's four agents (k <= 3 path)
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const unsigned int pb = (pb4 >> (8 * a)) & 0xFFu, p = p0 + a;
+            const unsigned int npat = pb & PB_NPAT;
+            if (!npat || (pb & PB_INHOSP)) continue;
+            w_pat++;
+            // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017)
+            const uint4 b = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
+            const unsigned int k = (b.x >= D.visit_thr[0]) + (b.x >= D.visit_thr[1]) + (b.x >= D.visit_thr[2]) + (b.x >= D.visit_thr[3]);
+            if (k == 0) continue;
+            const uint4 ra = rows[(size_t) p * 2], rb = rows[(size_t) p * 2 + 1];
+            const bool avoiding = (double) __uint_as_float(rb.y) < sd;          // Community.cpp:1020: compliant households skip high-risk places
+            if (k <= 3) {
+                bool v0 = true, v1 = k > 1, v2 = k > 2;
+                const int e0 = row_pick(ra, rb, __umulhi(b.y, npat));
+                const int e1 = row_pick(ra, rb, __umulhi(b.z, npat));
+                const int e2 = row_pick(ra, rb, __umulhi(b.w, npat));
+                if (avoiding) { v0 = !(e0 & PATRON_HIGH); v1 = v1 && !(e1 & PATRON_HIGH); v2 = v2 && !(e2 & PATRON_HIGH); }
+                const int q0 = e0 & 0x3FFFFFFF, q1 = e1 & 0x3FFFFFFF, q2 = e2 & 0x3FFFFFFF;
+                v2 = v2 && !(v0 && q2 == q0) && !(v1 && q2 == q1);             // visit_map (Community.cpp:1014): one entry per distinct place
+                v1 = v1 && !(v0 && q1 == q0);
+                w_v0 += (unsigned int) v0 + (unsigned int) v1 + (unsigned int) v2;
+                if (v0 && (s_hot[q0 >> 5] & (1u << (q0 & 31)))) { recq[a * 3 + 0] = (unsigned int) q0; recmask |= 1u << (a * 3 + 0); nrec++; }
+                if (v1 && (s_hot[q1 >> 5] & (1u << (q1 & 31)))) { recq[a * 3 + 1] = (unsigned int) q1; recmask |= 1u << (a * 3 + 1); nrec++; }
+                if (v2 && (s_hot[q2 >> 5] & (1u << (q2 & 31)))) { recq[a * 3 + 2] = (unsigned int) q2; recmask |= 1u << (a * 3 + 2); nrec++; }
+            } else {                                                           // 1.9 % of the drawing agents: generic loop, own reservation
+                const unsigned int kk = table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
+                unsigned int qs[5]; unsigned int nv = 0; uint4 bb = b;
+                for (unsigned int i = 1; i <= kk; ++i) {
+                    if ((i & 3u) == 0) bb = philox4x32_10(make_uint4(i >> 2, p, 0u, dp), key);
+                    const unsigned int x = (i & 3u) == 0 ? bb.x : (i & 3u) == 1 ? bb.y : (i & 3u) == 2 ? bb.z : bb.w;
+                    const int e = row_pick(ra, rb, __umulhi(x, npat));
+                    if (avoiding && (e & PATRON_HIGH)) continue;
+                    const unsigned int q = (unsigned int) (e & 0x3FFFFFFF);
+                    bool seen = false;
+#pragma unroll
+                    for (int j = 0; j < 5; ++j) if (j < (int) nv && qs[j] == q) seen = true;
+                    if (seen) continue;
+#pragma unroll
+                    for (int j = 0; j < 5; ++j) if (j == (int) nv) qs[j] = q;
+                    nv++;
+                    w_v0++;
                     if (s_hot[q >> 5] & (1u << (q & 31))) {
                         atomicAdd(&D.nvis[q], 1u);
-                        s_buf[atomicAdd(&s_cnt, 1u)] = make_uint2(p, (unsigned int) q);
+                        const unsigned int vi = list_reserve(&D.ctr->n_vis);
+                        if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
                         w_v++;
                     }
                 }
             }
         }
-        __syncthreads();
-        const unsigned int c = s_cnt;
-        __syncthreads();                                     // everyone has read s_cnt before the next round appends to it
-        if (c > VIS_BUF - TPB * (MAXV - 1)) {                // not enough room for another round: flush (uniform branch)
-            if (threadIdx.x == 0) s_gbase = atomicAdd(&D.ctr->n_vis, c);
-            __syncthreads();
-            const unsigned int gb = s_gbase;
-            if (gb + c <= D.cap_vis) { for (unsigned int i = threadIdx.x; i < c; i += blockDim.x) D.visit_rec[gb + i] = s_buf[i]; }
-            else if (threadIdx.x == 0) atomicOr(&D.ctr->overflow, 8u);
-            __syncthreads();
-            if (threadIdx.x == 0) s_cnt = 0;
-            __syncthreads();
+        // one reservation per warp round for the k <= 3 records
+        unsigned int incl = nrec;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
+        if (total) {
+            unsigned int base = 0;
+            if (lane == 31) base = atomicAdd(&D.ctr->n_vis, total);
+            base = __shfl_sync(0xffffffffu, base, 31) + incl - nrec;
+#pragma unroll
+            for (int r = 0; r < 12; ++r) if (recmask & (1u << r)) {
+                atomicAdd(&D.nvis[recq[r]], 1u);
+                if (base < D.cap_vis) D.visit_rec[base] = make_uint2(p0 + r / 3, recq[r]); else atomicOr(&D.ctr->overflow, 8u);
+                ++base;
+            }
+            w_v += nrec;
         }
-    }
-    {
-        const unsigned int c = s_cnt;
-        if (threadIdx.x == 0 && c) s_gbase = atomicAdd(&D.ctr->n_vis, c);
-        __syncthreads();
-        const unsigned int gb = s_gbase;
-        if (c) { if (gb + c <= D.cap_vis) { for (unsigned int i = threadIdx.x; i < c; i += blockDim.x) D.visit_rec[gb + i] = s_buf[i]; } else if (threadIdx.x == 0) atomicOr(&D.ctr->overflow, 8u); }
     }
     const int ids[3] = { CABM_W_PATRONS, CABM_W_VISITS, CABM_W_HOT_VISITS }; const unsigned int vals[3] = { w_pat, w_v0, w_v };
     block_work_add<3>(D, ids, vals);
@@ -264,20 +327,26 @@ __device__ __forceinline__ void write_foi(const Dev& D, unsigned int i, int loc,
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_hazard: one warp per hot location (hospitals are left to k_hosp, after the status pass).
+// k_hazard: eight lanes per hot location (hospitals are left to k_hosp_import, after the status pass). The per-location
+// dependent chain (hot list -> type -> pressure -> roster -> members) is what bounds this kernel, so four locations share
+// a warp; rosters above SMALL_ROSTER are cut into 256-member items for k_trials.
 // ---------------------------------------------------------------------------------------------
+#define HZ_LANES 8
 __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const cabm_params* __restrict__ par = D.par;
     const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
-    const unsigned int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    const unsigned int lane = threadIdx.x & 31, gl = lane & (HZ_LANES - 1);
+    const unsigned int grp = (blockIdx.x * blockDim.x + threadIdx.x) / HZ_LANES, n_grp = (gridDim.x * blockDim.x) / HZ_LANES;
     unsigned int trials = 0, edges = 0;
-    for (unsigned int i = warp; i < n_hot; i += n_warps) {
+    for (unsigned int i = grp; i < n_hot; i += n_grp) {
         const int loc = D.hot_list[i];
         const int type = D.loc_type[loc];
+        if (gl == 0) D.hot_off[i] = atomicAdd(&D.ctr->n_seg, D.loc_cnt[loc]);        // this location's segment of the sorted flag array
         if (type == CABM_HOSPITAL) continue;
-        const unsigned long long* pw = &D.press[(size_t) loc * CABM_N_STRAINS];
-        const unsigned long long pws[4] = { pw[0], pw[1], pw[2], pw[3] };
+        const ulonglong2* pw = reinterpret_cast<const ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
+        const ulonglong2 pa = pw[0], pb = pw[1];
+        const unsigned long long pws[4] = { pa.x, pa.y, pb.x, pb.y };
         const double w = CABM_MUL((double) (pws[0] + pws[1] + pws[2] + pws[3]), 1.0 / 4294967296.0);
         const unsigned int rb = D.roster_off[loc], size = D.roster_off[loc + 1] - rb;
         double T = 0.0, Ts = 0.0; unsigned int denom = size; int purpose = 0;
@@ -285,20 +354,23 @@ __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
             T = hazard_to_T(CABM_MUL(CABM_MUL(par->haz_mult[CABM_HOUSE], cx.season), w));
             const unsigned int nb0 = D.nbr_off[loc], deg = D.nbr_off[loc + 1] - nb0;
             const bool risky = (double) D.loc_risk[loc] > cx.sd;
-            if (risky) { Ts = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_N_LOCTYPES], cx.season), w), (double) (int) size)); if (lane == 0) edges += deg; }
-            // segment 0 = own household (within_household_transmission), segment s >= 1 = neighbour s-1 (between_household_transmission);
-            // 8 lanes per segment, 4 segments per warp round
-            const unsigned int n_seg = 1 + ((risky && Ts > 0.0) ? deg : 0);
-            for (unsigned int s0 = 0; s0 < n_seg; s0 += 4) {
-                const unsigned int s = s0 + (lane >> 3);
-                if (s < n_seg) {
-                    unsigned int b = rb, cnt = size; double Tt = T; int pp = CABM_P_EXPOSE_HH; bool go = T > 0.0;
-                    if (s > 0) {
-                        const int nb = D.nbr[nb0 + s - 1];
-                        go = (double) D.loc_risk[nb] > cx.sd;
-                        b = D.roster_off[nb]; cnt = D.roster_off[nb + 1] - b; Tt = Ts; pp = CABM_P_EXPOSE_NB;
+            if (risky) { Ts = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_N_LOCTYPES], cx.season), w), (double) (int) size)); if (gl == 0) edges += deg; }
+            // within_household_transmission: own residents
+            if (T > 0.0) for (unsigned int m = gl; m < size; m += HZ_LANES) trial(D, day, 0, (unsigned int) D.roster[rb + m], loc, CABM_P_EXPOSE_HH, 0, T, trials);
+            // between_household_transmission: lane e takes neighbour e (its riskiness and roster bounds), then the group walks the neighbours
+            if (risky && Ts > 0.0) {
+                for (unsigned int e0 = 0; e0 < deg; e0 += HZ_LANES) {
+                    unsigned int nbb = 0, nbc = 0;
+                    if (e0 + gl < deg) {
+                        const int nb = D.nbr[nb0 + e0 + gl];
+                        if ((double) D.loc_risk[nb] > cx.sd) { nbb = D.roster_off[nb]; nbc = D.roster_off[nb + 1] - nbb; }
                     }
-                    if (go) for (unsigned int m = lane & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[b + m], loc, pp, 0, Tt, trials);
+                    const unsigned int gmask = 0xFFu << (lane & 24);
+                    const unsigned int ne = min((unsigned int) HZ_LANES, deg - e0);
+                    for (unsigned int e = 0; e < ne; ++e) {
+                        const unsigned int b = __shfl_sync(gmask, nbb, (lane & 24) + e), cnt = __shfl_sync(gmask, nbc, (lane & 24) + e);
+                        for (unsigned int m = gl; m < cnt; m += HZ_LANES) trial(D, day, 0, (unsigned int) D.roster[b + m], loc, CABM_P_EXPOSE_NB, 0, Ts, trials);
+                    }
                 }
             }
         } else {
@@ -311,7 +383,7 @@ __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
                     const double f = LF_PUBRISK(lf) == CABM_PT_HIGH ? 4.0 : 0.25;
                     T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(CABM_MUL(par->haz_mult[CABM_WORK], f), cx.season), w), CABM_SUB((double) (int) denom, 1.0)));
                 }
-                if (q >= 0 && lane == 0) D.pub_T[q] = T;
+                if (q >= 0 && gl == 0) D.pub_T[q] = T;
                 purpose = CABM_P_EXPOSE_WORK;
             } else if (type == CABM_SCHOOL) {
                 const bool open = cx.is_weekday && cx.school_closure < 1;
@@ -324,24 +396,25 @@ __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
             }
             if (T > 0.0) {
                 if (size <= SMALL_ROSTER) {
-                    for (unsigned int m = lane; m < size; m += 32) trial(D, day, 0, (unsigned int) D.roster[rb + m], loc, purpose, 0, T, trials);
+                    for (unsigned int m = gl; m < size; m += HZ_LANES) trial(D, day, 0, (unsigned int) D.roster[rb + m], loc, purpose, 0, T, trials);
                 } else {
                     const unsigned int nch = (size + CHUNK - 1) / CHUNK;
                     unsigned int base = 0;
-                    if (lane == 0) base = atomicAdd(&D.ctr->n_items, nch);
-                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (gl == 0) base = atomicAdd(&D.ctr->n_items, nch);
+                    base = __shfl_sync(0xFFu << (lane & 24), base, lane & 24);
                     if (base + nch <= D.cap_items) {
-                        for (unsigned int k = lane; k < nch; k += 32) {
+                        for (unsigned int k = gl; k < nch; k += HZ_LANES) {
                             Item it; it.src = loc; it.begin = (int) (rb + k * CHUNK); it.count = (int) min((unsigned int) CHUNK, size - k * CHUNK); it.purpose = purpose; it.T = T; it.pad = 0.0;
                             D.items[base + k] = it;
                         }
-                    } else if (lane == 0) atomicOr(&D.ctr->overflow, 16u);
+                    } else if (gl == 0) atomicOr(&D.ctr->overflow, 16u);
                 }
             }
         }
-        if (D.foi_enabled && lane == 0) write_foi(D, i, loc, type, pws, denom, T, Ts);
+        if (D.foi_enabled && gl == 0) write_foi(D, i, loc, type, pws, denom, T, Ts);
     }
-    trials = warp_sum(trials);
+    __syncwarp();
+    trials = warp_sum(trials); edges = warp_sum(edges);
     if (lane == 0) { if (trials) atomicAdd(&D.ctr->work[CABM_W_TRIALS], (unsigned long long) trials); if (edges) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges); }
 }
 
@@ -351,10 +424,19 @@ __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
 __global__ void __launch_bounds__(TPB) k_trials(const Dev D) {
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n_items = min(D.ctr->n_items, D.cap_items), n_vis = min(D.ctr->n_vis, D.cap_vis);
-    const unsigned int units = n_items + (n_vis + TPB - 1) / TPB;
+    const unsigned int n_flags = min(D.ctr->n_flags, D.cap_flags);
+    const unsigned int u_vis = n_items + (n_vis + TPB - 1) / TPB;
+    const unsigned int units = u_vis + (n_flags + TPB - 1) / TPB;
     unsigned int trials = 0;
     for (unsigned int u = blockIdx.x; u < units; u += gridDim.x) {
-        if (u < n_items) {
+        if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
+            const unsigned int f = (u - u_vis) * TPB + threadIdx.x;
+            if (f < n_flags) {
+                const FlagRaw r = D.flags_raw[f];
+                Flag o; o.pid = r.pid; o.pad = 0; o.c = r.c;
+                D.flags[D.hot_off[D.loc_hot[r.loc]] + r.slot] = o;
+            }
+        } else if (u < n_items) {
             const Item it = D.items[u];
             if ((int) threadIdx.x < it.count) trial(D, day, 0, (unsigned int) D.roster[it.begin + threadIdx.x], it.src, it.purpose, 0, it.T, trials);
         } else {

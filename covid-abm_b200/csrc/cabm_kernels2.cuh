@@ -23,42 +23,65 @@ __device__ __forceinline__ int weighted_strain(const double* __restrict__ w, dou
 
 // Community::trace_contact (Community.cpp:795-825): infector ~ relInf-weighted among the agents that flagged the source
 // location today. The same draw that picked the strain picks the infector: within the strain's share the flags are laid
-// out by ascending person id, t is the offset into that share.
-#define INFECTOR_CACHE 48
-__device__ __noinline__ int pick_infector(const Dev& D, const int src, const int strain, const unsigned long long t) {
-    unsigned int pids[INFECTOR_CACHE]; unsigned long long cs[INFECTOR_CACHE]; int n = 0; bool over = false;
-    for (int f = D.loc_head[src]; f >= 0;) {
-        const Flag r = D.flags[f];
-        if (FLAG_STRAIN(r) == strain) { if (n < INFECTOR_CACHE) { pids[n] = r.pid; cs[n] = FLAG_C(r); ++n; } else over = true; }
-        f = r.next;
-    }
-    if (!over) {
-        for (int i = 0; i < n; ++i) {
-            unsigned long long lower = 0, eq = 0;
-            for (int j = 0; j < n; ++j) { if (pids[j] < pids[i]) lower += cs[j]; else if (pids[j] == pids[i]) eq += cs[j]; }
-            if (t >= lower && t - lower < eq) return (int) pids[i];
+// out by ascending person id and t is the offset into that share. The location's flags sit in one contiguous segment in
+// arrival order, so this is a weighted quickselect on person id (result independent of the arrival order).
+// Short segments (households, small workplaces) are searched by the winner's own thread ...
+__device__ __forceinline__ int pick_infector_thread(const Flag* __restrict__ seg, const unsigned int n, const int strain, unsigned long long t) {
+    unsigned int lo = 0, hi = 0xFFFFFFFFu;
+    for (;;) {
+        bool have = false; unsigned int pivot = 0; unsigned long long lower = 0, eq = 0;
+        for (unsigned int k = 0; k < n; ++k) {
+            const Flag e = seg[k];
+            if (FLAG_STRAIN(e) != strain || e.pid < lo || e.pid > hi) continue;
+            if (!have) { have = true; pivot = e.pid; }
+            if (e.pid < pivot) lower += FLAG_C(e); else if (e.pid == pivot) eq += FLAG_C(e);
         }
-        return -1;
+        if (!have) return -1;
+        if (t < lower) hi = pivot - 1;                      // lower > 0 implies pivot > lo >= 0
+        else if (t - lower < eq) return (int) pivot;
+        else { t -= lower + eq; if (pivot == 0xFFFFFFFFu) return -1; lo = pivot + 1; }
     }
-    for (int f = D.loc_head[src]; f >= 0;) {                       // chains longer than the cache: quadratic walk
-        const Flag r = D.flags[f];
-        if (FLAG_STRAIN(r) == strain) {
-            unsigned long long lower = 0, eq = 0;
-            for (int g = D.loc_head[src]; g >= 0;) {
-                const Flag q = D.flags[g];
-                if (FLAG_STRAIN(q) == strain) { if (q.pid < r.pid) lower += FLAG_C(q); else if (q.pid == r.pid) eq += FLAG_C(q); }
-                g = q.next;
-            }
-            if (t >= lower && t - lower < eq) return (int) r.pid;
-        }
-        f = r.next;
-    }
-    return -1;
 }
+__device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// ... long ones (hospitals, big workplaces and schools at the peak) by the whole warp: one strided sweep per pivot,
+// the next pivot is any element seen on the side the search continues in. All 32 lanes call with the same arguments.
+__device__ __forceinline__ int pick_infector_warp(const Flag* __restrict__ seg, const unsigned int n, const int strain, unsigned long long t) {
+    const unsigned int lane = threadIdx.x & 31;
+    unsigned int lo = 0, hi = 0xFFFFFFFFu, pivot;
+    {
+        unsigned int cand = 0; bool h = false;
+        for (unsigned int k = lane; k < n && !h; k += 32) { const Flag e = seg[k]; if (FLAG_STRAIN(e) == strain) { cand = e.pid; h = true; } }
+        const unsigned int b = __ballot_sync(0xffffffffu, h);
+        if (!b) return -1;
+        pivot = __shfl_sync(0xffffffffu, cand, __ffs(b) - 1);
+    }
+    for (;;) {
+        unsigned long long lower = 0, eq = 0; unsigned int cl = 0, ch = 0; bool hl = false, hh = false;
+        for (unsigned int k = lane; k < n; k += 32) {
+            const Flag e = seg[k];
+            if (FLAG_STRAIN(e) != strain || e.pid < lo || e.pid > hi) continue;
+            if (e.pid < pivot) { lower += FLAG_C(e); cl = e.pid; hl = true; } else if (e.pid == pivot) eq += FLAG_C(e); else { ch = e.pid; hh = true; }
+        }
+        lower = warp_sum64(lower); eq = warp_sum64(eq);
+        if (t < lower) { hi = pivot - 1; const unsigned int b = __ballot_sync(0xffffffffu, hl); pivot = __shfl_sync(0xffffffffu, cl, __ffs(b) - 1); }
+        else if (t - lower < eq) return (int) pivot;
+        else {
+            t -= lower + eq;
+            const unsigned int b = __ballot_sync(0xffffffffu, hh);
+            if (!b) return -1;
+            lo = pivot + 1; pivot = __shfl_sync(0xffffffffu, ch, __ffs(b) - 1);
+        }
+    }
+}
+#define INFECTOR_THREAD_MAX 32
 
 // rebuild the event (stream position, strain, keys) of a hit / winner; returns false for malformed input
 __device__ __forceinline__ void event_setup(const Dev& D, const DayCtx& cx, const unsigned int pid, const unsigned int src, const unsigned int purpose,
-                                            const unsigned int sub, const bool want_infector, Stream& s, InfectCtx& c) {
+                                            const unsigned int sub, Stream& s, InfectCtx& c, unsigned long long& t_res) {
     c.pid = (int) pid; c.time = cx.day; c.infector = -1; c.purpose = purpose; c.key_sub = sub;
     if (purpose == CABM_P_IMPORT) {
         s.begin(D.seed, (unsigned int) cx.day, CABM_P_IMPORT, src, 0);
@@ -68,10 +91,8 @@ __device__ __forceinline__ void event_setup(const Dev& D, const DayCtx& cx, cons
     } else {
         s.begin(D.seed, (unsigned int) cx.day, purpose, pid, src, sub);
         (void) s.next();                                            // the U < T draw
-        unsigned long long t_res = 0;
         c.strain = pick_strain(&D.press[(size_t) src * CABM_N_STRAINS], s.next(), &t_res);
         (void) s.next();                                            // reserved (reference: uniform_choice inside the group)
-        if (want_infector) c.infector = pick_infector(D, (int) src, c.strain, t_res);
         c.source = (int) src; c.has_source = true; c.key_a = pid; c.key_b = src;
     }
 }
@@ -91,8 +112,8 @@ __global__ void __launch_bounds__(128) k_gate(const Dev D, const int phase) {
     const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
     for (unsigned int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
         const Hit h = D.hits[i];
-        Stream s; InfectCtx c;
-        event_setup(D, cx, h.pid, h.src, h.purpose, h.sub, false, s, c);
+        Stream s; InfectCtx c; unsigned long long t_res = 0;
+        event_setup(D, cx, h.pid, h.src, h.purpose, h.sub, s, c, t_res);
         if (infect_event(D, s, c, false)) {
             const unsigned long long old = atomicMin(&D.cand[h.pid], order_key(h.purpose, h.src, h.sub));
             if (old == CABM_CAND_EMPTY) {
@@ -157,15 +178,34 @@ __global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int pha
     const unsigned int n_round = (n + stride - 1) / stride * stride;
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         unsigned int m = 0;
-        if (i < n_w) {
-            const unsigned int pid = D.newinf_list[nbase + i];
+        const bool winner = i < n_w;
+        Stream s; InfectCtx c; unsigned long long t_res = 0;
+        const Flag* seg = nullptr; unsigned int seg_n = 0; unsigned int pid = 0;
+        if (winner) {
+            pid = D.newinf_list[nbase + i];
             const unsigned long long key = D.cand[pid];
             const int pass = (int) (key >> 40); const unsigned int src = (unsigned int) (key >> 8); const unsigned int role = (unsigned int) (key & 0xFF);
             unsigned int purpose = (unsigned int) pass, sub = 0;
             if (pass == PASS_WORK) purpose = role ? CABM_P_EXPOSE_WORK : CABM_P_EXPOSE_WORK_VIS;
             else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
-            Stream s; InfectCtx c;
-            event_setup(D, cx, pid, src, purpose, sub, true, s, c);
+            event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);
+            if (c.has_source) {
+                seg_n = D.loc_cnt[src]; seg = D.flags + D.hot_off[D.loc_hot[src]];
+                if (seg_n <= INFECTOR_THREAD_MAX) c.infector = pick_infector_thread(seg, seg_n, c.strain, t_res);
+            }
+        }
+        // winners whose source has a long flag segment: the warp searches them one after another
+        unsigned int todo = __ballot_sync(0xffffffffu, winner && c.has_source && seg_n > INFECTOR_THREAD_MAX);
+        while (todo) {
+            const int l = __ffs(todo) - 1; todo &= todo - 1;
+            const Flag* sg = (const Flag*) __shfl_sync(0xffffffffu, (unsigned long long) seg, l);
+            const unsigned int sn = __shfl_sync(0xffffffffu, seg_n, l);
+            const int st = __shfl_sync(0xffffffffu, c.strain, l);
+            const unsigned long long tt = __shfl_sync(0xffffffffu, t_res, l);
+            const int inf = pick_infector_warp(sg, sn, st, tt);
+            if ((int) (threadIdx.x & 31) == l) c.infector = inf;
+        }
+        if (winner) {
             infect_event(D, s, c, true);
             if (with_status) m = status_one(D, pid, day);
         } else if (i < n) {
@@ -218,7 +258,7 @@ __global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_h
             const unsigned int c = D.hosp_count[pid];
             if (c == 0) continue;
             const int hosp = D.loc_hospital[D.home[pid]];
-            if (hosp < 0 || D.loc_head[hosp] == -1) continue;
+            if (hosp < 0 || D.loc_cnt[hosp] == 0) continue;
             unsigned int denom; unsigned long long pws[4];
             const double T = hospital_T(D, cx, hosp, &denom, pws);
             if (T > 0.0) for (unsigned int sub = 0; sub < c; ++sub) trial(D, day, 1, pid, hosp, CABM_P_EXPOSE_HOSP_PAT, sub, T, trials);
@@ -257,7 +297,7 @@ __global__ void __launch_bounds__(TPB) k_end(const Dev D, const int reset_hot) {
             const int loc = D.hot_list[i];
             ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
             pw[0] = make_ulonglong2(0, 0); pw[1] = make_ulonglong2(0, 0);
-            D.loc_head[loc] = -1;
+            D.loc_cnt[loc] = 0;
             const int q = D.loc_pub[loc];
             if (q >= 0) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }      // the whole bitmap word: every set bit belongs to a hot location
         }
@@ -322,5 +362,4 @@ __global__ void k_init_state(const Dev D) {
         D.win[p] = 0x80007FFFu;                       // from = 32767, until = -32768: never active
         D.cand[p] = CABM_CAND_EMPTY;
     }
-    for (unsigned int l = blockIdx.x * blockDim.x + threadIdx.x; l < D.L; l += stride) D.loc_head[l] = -1;
 }
