@@ -202,10 +202,6 @@ __global__ void __launch_bounds__(TPB) k_active(const Dev D) {
 // ceil(Q/32) words); visits that land on a hot location are counted (nvis) and recorded with one warp-aggregated
 // reservation per round. There is no block-level synchronisation in the loop.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ int row_pick(const uint4& ra, const uint4& rb, const unsigned int idx) {
-    return (int) (idx == 0 ? ra.x : idx == 1 ? ra.y : idx == 2 ? ra.z : idx == 3 ? ra.w : rb.x);
-}
-
 __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned int bitmap_words) {
     extern __shared__ unsigned int s_hot[];
     const DayCtx& cx = day_ctx(D);
@@ -217,63 +213,42 @@ __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned in
     const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
     const double sd = cx.sd;
     const unsigned int lane = threadIdx.x & 31;
-    const uint4* __restrict__ rows = reinterpret_cast<const uint4*>(D.patron);
+    const unsigned int thr0 = D.visit_thr[0], thr1 = D.visit_thr[1], thr2 = D.visit_thr[2], thr3 = D.visit_thr[3];
     unsigned int w_pat = 0, w_v0 = 0, w_v = 0;
-    for (unsigned int p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u; p0 < n_round; p0 += stride) {
+    // a warp takes tiles of 128 consecutive agents; in slot a lane l handles agent tile + 32 a + l, so the 32-byte patron
+    // rows a load instruction touches are consecutive (8 cache lines per request instead of 32)
+    for (unsigned int t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 128u; t0 < n_round; t0 += stride) {
         unsigned int pb4 = 0;
-        if (p0 + 3 < D.N) pb4 = *reinterpret_cast<const unsigned int*>(D.pbyte + p0);
-        else for (unsigned int a = 0; a < 4; ++a) if (p0 + a < D.N) pb4 |= (unsigned int) D.pbyte[p0 + a] << (8 * a);
-        unsigned int recq[12]; unsigned int nrec = 0, recmask = 0;            // hot visits of this thread's four agents (k <= 3 path)
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { const unsigned int p = t0 + a * 32 + lane; if (p < D.N) pb4 |= (unsigned int) D.pbyte[p] << (8 * a); }
+        unsigned int recq[12]; unsigned int nrec = 0, recmask = 0, slow = 0;       // hot visits of this lane's four agents (k <= 3)
 #pragma unroll
         for (int a = 0; a < 4; ++a) {
-            const unsigned int pb = (pb4 >> (8 * a)) & 0xFFu, p = p0 + a;
+            const unsigned int pb = (pb4 >> (8 * a)) & 0xFFu, p = t0 + a * 32 + lane;
             const unsigned int npat = pb & PB_NPAT;
-            if (!npat || (pb & PB_INHOSP)) continue;
-            w_pat++;
-            // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017)
+            const bool act = npat && !(pb & PB_INHOSP);
+            // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017); no memory needed
             const uint4 b = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
-            const unsigned int k = (b.x >= D.visit_thr[0]) + (b.x >= D.visit_thr[1]) + (b.x >= D.visit_thr[2]) + (b.x >= D.visit_thr[3]);
-            if (k == 0) continue;
-            const uint4 ra = rows[(size_t) p * 2], rb = rows[(size_t) p * 2 + 1];
-            const bool avoiding = (double) __uint_as_float(rb.y) < sd;          // Community.cpp:1020: compliant households skip high-risk places
-            if (k <= 3) {
-                bool v0 = true, v1 = k > 1, v2 = k > 2;
-                const int e0 = row_pick(ra, rb, __umulhi(b.y, npat));
-                const int e1 = row_pick(ra, rb, __umulhi(b.z, npat));
-                const int e2 = row_pick(ra, rb, __umulhi(b.w, npat));
-                if (avoiding) { v0 = !(e0 & PATRON_HIGH); v1 = v1 && !(e1 & PATRON_HIGH); v2 = v2 && !(e2 & PATRON_HIGH); }
-                const int q0 = e0 & 0x3FFFFFFF, q1 = e1 & 0x3FFFFFFF, q2 = e2 & 0x3FFFFFFF;
-                v2 = v2 && !(v0 && q2 == q0) && !(v1 && q2 == q1);             // visit_map (Community.cpp:1014): one entry per distinct place
-                v1 = v1 && !(v0 && q1 == q0);
-                w_v0 += (unsigned int) v0 + (unsigned int) v1 + (unsigned int) v2;
-                if (v0 && (s_hot[q0 >> 5] & (1u << (q0 & 31)))) { recq[a * 3 + 0] = (unsigned int) q0; recmask |= 1u << (a * 3 + 0); nrec++; }
-                if (v1 && (s_hot[q1 >> 5] & (1u << (q1 & 31)))) { recq[a * 3 + 1] = (unsigned int) q1; recmask |= 1u << (a * 3 + 1); nrec++; }
-                if (v2 && (s_hot[q2 >> 5] & (1u << (q2 & 31)))) { recq[a * 3 + 2] = (unsigned int) q2; recmask |= 1u << (a * 3 + 2); nrec++; }
-            } else {                                                           // 1.9 % of the drawing agents: generic loop, own reservation
-                const unsigned int kk = table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
-                unsigned int qs[5]; unsigned int nv = 0; uint4 bb = b;
-                for (unsigned int i = 1; i <= kk; ++i) {
-                    if ((i & 3u) == 0) bb = philox4x32_10(make_uint4(i >> 2, p, 0u, dp), key);
-                    const unsigned int x = (i & 3u) == 0 ? bb.x : (i & 3u) == 1 ? bb.y : (i & 3u) == 2 ? bb.z : bb.w;
-                    const int e = row_pick(ra, rb, __umulhi(x, npat));
-                    if (avoiding && (e & PATRON_HIGH)) continue;
-                    const unsigned int q = (unsigned int) (e & 0x3FFFFFFF);
-                    bool seen = false;
-#pragma unroll
-                    for (int j = 0; j < 5; ++j) if (j < (int) nv && qs[j] == q) seen = true;
-                    if (seen) continue;
-#pragma unroll
-                    for (int j = 0; j < 5; ++j) if (j == (int) nv) qs[j] = q;
-                    nv++;
-                    w_v0++;
-                    if (s_hot[q >> 5] & (1u << (q & 31))) {
-                        atomicAdd(&D.nvis[q], 1u);
-                        const unsigned int vi = list_reserve(&D.ctr->n_vis);
-                        if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
-                        w_v++;
-                    }
-                }
-            }
+            unsigned int k = (b.x >= thr0) + (b.x >= thr1) + (b.x >= thr2) + (b.x >= thr3);
+            if (!act) k = 0;
+            w_pat += act ? 1u : 0u;
+            if (k >= 4) { slow |= 1u << a; k = 0; }
+            const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
+            int e0 = 0, e1 = 0, e2 = 0; float risk = 0.0f;
+            if (k > 0) { e0 = row[__umulhi(b.y, npat)]; risk = __int_as_float(row[PATRON_RISK]); }
+            if (k > 1) e1 = row[__umulhi(b.z, npat)];
+            if (k > 2) e2 = row[__umulhi(b.w, npat)];
+            const bool avoiding = (double) risk < sd;                              // Community.cpp:1020: compliant households skip high-risk places
+            bool v0 = k > 0, v1 = k > 1, v2 = k > 2;
+            if (avoiding) { v0 = v0 && !(e0 & PATRON_HIGH); v1 = v1 && !(e1 & PATRON_HIGH); v2 = v2 && !(e2 & PATRON_HIGH); }
+            const int q0 = e0 & 0x3FFFFFFF, q1 = e1 & 0x3FFFFFFF, q2 = e2 & 0x3FFFFFFF;
+            v2 = v2 && !(v0 && q2 == q0) && !(v1 && q2 == q1);                     // visit_map (Community.cpp:1014): one entry per distinct place
+            v1 = v1 && !(v0 && q1 == q0);
+            w_v0 += (unsigned int) v0 + (unsigned int) v1 + (unsigned int) v2;
+            const bool h0 = v0 && (s_hot[q0 >> 5] & (1u << (q0 & 31))), h1 = v1 && (s_hot[q1 >> 5] & (1u << (q1 & 31))), h2 = v2 && (s_hot[q2 >> 5] & (1u << (q2 & 31)));
+            recq[a * 3 + 0] = (unsigned int) q0; recq[a * 3 + 1] = (unsigned int) q1; recq[a * 3 + 2] = (unsigned int) q2;
+            recmask |= ((unsigned int) h0 | ((unsigned int) h1 << 1) | ((unsigned int) h2 << 2)) << (a * 3);
+            nrec += (unsigned int) h0 + (unsigned int) h1 + (unsigned int) h2;
         }
         // one reservation per warp round for the k <= 3 records
         unsigned int incl = nrec;
@@ -287,10 +262,39 @@ __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned in
 #pragma unroll
             for (int r = 0; r < 12; ++r) if (recmask & (1u << r)) {
                 atomicAdd(&D.nvis[recq[r]], 1u);
-                if (base < D.cap_vis) D.visit_rec[base] = make_uint2(p0 + r / 3, recq[r]); else atomicOr(&D.ctr->overflow, 8u);
+                if (base < D.cap_vis) D.visit_rec[base] = make_uint2(t0 + (r / 3) * 32 + lane, recq[r]); else atomicOr(&D.ctr->overflow, 8u);
                 ++base;
             }
             w_v += nrec;
+        }
+        while (slow) {                                                             // k >= 4: 1.9 % of the drawing agents, generic loop
+            const unsigned int a = (unsigned int) __ffs(slow) - 1u; slow &= slow - 1u;
+            const unsigned int p = t0 + a * 32 + lane, npat = (pb4 >> (8 * a)) & PB_NPAT;
+            const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
+            uint4 bb = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
+            const unsigned int kk = table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) bb.x * (1.0 / 4294967296.0));
+            const bool avoiding = (double) __int_as_float(row[PATRON_RISK]) < sd;
+            unsigned int qs[5]; unsigned int nv = 0;
+            for (unsigned int i = 1; i <= kk; ++i) {
+                if ((i & 3u) == 0) bb = philox4x32_10(make_uint4(i >> 2, p, 0u, dp), key);
+                const unsigned int x = (i & 3u) == 0 ? bb.x : (i & 3u) == 1 ? bb.y : (i & 3u) == 2 ? bb.z : bb.w;
+                const int e = row[__umulhi(x, npat)];
+                if (avoiding && (e & PATRON_HIGH)) continue;
+                const unsigned int q = (unsigned int) (e & 0x3FFFFFFF);
+                bool seen = false;
+#pragma unroll
+                for (int j = 0; j < 5; ++j) if (j < (int) nv && qs[j] == q) seen = true;
+                if (seen) continue;
+#pragma unroll
+                for (int j = 0; j < 5; ++j) if (j == (int) nv) qs[j] = q;
+                nv++; w_v0++;
+                if (s_hot[q >> 5] & (1u << (q & 31))) {
+                    atomicAdd(&D.nvis[q], 1u);
+                    const unsigned int vi = list_reserve(&D.ctr->n_vis);
+                    if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
+                    w_v++;
+                }
+            }
         }
     }
     const int ids[3] = { CABM_W_PATRONS, CABM_W_VISITS, CABM_W_HOT_VISITS }; const unsigned int vals[3] = { w_pat, w_v0, w_v };
