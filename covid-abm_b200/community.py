@@ -18,7 +18,7 @@ from . import abi
 from . import params as _params
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libcabm.so")
+LIB_PATH = os.environ.get("CABM_LIB", os.path.join(_HERE, "csrc", "libcabm.so"))    # CABM_LIB: development override (kernel experiments)
 
 
 class CabmError(RuntimeError):

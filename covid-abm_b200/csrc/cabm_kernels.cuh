@@ -261,8 +261,12 @@ __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned in
             base = __shfl_sync(0xffffffffu, base, 31) + incl - nrec;
 #pragma unroll
             for (int r = 0; r < 12; ++r) if (recmask & (1u << r)) {
+#ifndef CABM_X_NO_NVIS
                 atomicAdd(&D.nvis[recq[r]], 1u);
+#endif
+#ifndef CABM_X_NO_REC
                 if (base < D.cap_vis) D.visit_rec[base] = make_uint2(t0 + (r / 3) * 32 + lane, recq[r]); else atomicOr(&D.ctr->overflow, 8u);
+#endif
                 ++base;
             }
             w_v += nrec;

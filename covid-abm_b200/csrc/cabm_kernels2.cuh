@@ -162,9 +162,11 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
     return m;
 }
 
-// Work index space: [0, n_w) = winners of `phase` (Person::infect, then the status tally of the new infection when
-// with_status), [n_w, n_w + n_active) = agents active at the start of the day that were not re-infected in phase 0
-// (status only; with_status). cand[] keeps the winner keys until k_end so the status half can tell who was re-infected.
+// Warp index space: warps [0, n_w) take one winner of `phase` each -- Person::infect is a long, branchy, latency-bound
+// routine, so winners are NOT packed into the lanes of a warp (32 divergent disease courses would run one after the
+// other); lane 0 commits, all lanes help with the infector search -- then warps [n_w, n_w + ceil(n_active/32)) run the
+// status pass (with_status) over the agents active at the start of the day that were not re-infected in phase 0.
+// cand[] keeps the winner keys until k_end so the status half can tell who was re-infected.
 __global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int phase, const int with_status) {
     __shared__ unsigned int sm[CABM_N_COUNTERS];
     if (threadIdx.x < CABM_N_COUNTERS) sm[threadIdx.x] = 0;
@@ -173,49 +175,40 @@ __global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int pha
     const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
     const unsigned int n_w = min(nbase + D.ctr->n_new[phase], D.cap_new) - nbase;
     const unsigned int n_a = with_status ? min(D.ctr->n_active, D.cap_active) : 0u;
-    const unsigned int n = n_w + n_a;
-    const unsigned int stride = gridDim.x * blockDim.x;
-    const unsigned int n_round = (n + stride - 1) / stride * stride;
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    const unsigned int n_units = n_w + (n_a + 31) / 32;
+    const unsigned int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (unsigned int u = warp; u < n_units; u += n_warps) {
         unsigned int m = 0;
-        const bool winner = i < n_w;
-        Stream s; InfectCtx c; unsigned long long t_res = 0;
-        const Flag* seg = nullptr; unsigned int seg_n = 0; unsigned int pid = 0;
-        if (winner) {
-            pid = D.newinf_list[nbase + i];
+        if (u < n_w) {
+            const unsigned int pid = D.newinf_list[nbase + u];
             const unsigned long long key = D.cand[pid];
             const int pass = (int) (key >> 40); const unsigned int src = (unsigned int) (key >> 8); const unsigned int role = (unsigned int) (key & 0xFF);
             unsigned int purpose = (unsigned int) pass, sub = 0;
             if (pass == PASS_WORK) purpose = role ? CABM_P_EXPOSE_WORK : CABM_P_EXPOSE_WORK_VIS;
             else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
-            event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);
+            Stream s; InfectCtx c; unsigned long long t_res = 0;
+            event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);                 // all lanes: same values
             if (c.has_source) {
-                seg_n = D.loc_cnt[src]; seg = D.flags + D.hot_off[D.loc_hot[src]];
-                if (seg_n <= INFECTOR_THREAD_MAX) c.infector = pick_infector_thread(seg, seg_n, c.strain, t_res);
+                const unsigned int seg_n = D.loc_cnt[src]; const Flag* seg = D.flags + D.hot_off[D.loc_hot[src]];
+                if (seg_n <= INFECTOR_THREAD_MAX) { if (lane == 0) c.infector = pick_infector_thread(seg, seg_n, c.strain, t_res); }
+                else c.infector = pick_infector_warp(seg, seg_n, c.strain, t_res);
+            }
+            if (lane == 0) {
+                infect_event(D, s, c, true);
+                if (with_status) m = status_one(D, pid, day);
+            }
+        } else {
+            const unsigned int i = (u - n_w) * 32 + lane;
+            if (i < n_a) {
+                const unsigned int p = D.active_list[i];
+                if (D.cand[p] == CABM_CAND_EMPTY) m = status_one(D, p, day);
             }
         }
-        // winners whose source has a long flag segment: the warp searches them one after another
-        unsigned int todo = __ballot_sync(0xffffffffu, winner && c.has_source && seg_n > INFECTOR_THREAD_MAX);
-        while (todo) {
-            const int l = __ffs(todo) - 1; todo &= todo - 1;
-            const Flag* sg = (const Flag*) __shfl_sync(0xffffffffu, (unsigned long long) seg, l);
-            const unsigned int sn = __shfl_sync(0xffffffffu, seg_n, l);
-            const int st = __shfl_sync(0xffffffffu, c.strain, l);
-            const unsigned long long tt = __shfl_sync(0xffffffffu, t_res, l);
-            const int inf = pick_infector_warp(sg, sn, st, tt);
-            if ((int) (threadIdx.x & 31) == l) c.infector = inf;
-        }
-        if (winner) {
-            infect_event(D, s, c, true);
-            if (with_status) m = status_one(D, pid, day);
-        } else if (i < n) {
-            const unsigned int p = D.active_list[i - n_w];
-            if (D.cand[p] == CABM_CAND_EMPTY) m = status_one(D, p, day);
-        }
+        __syncwarp();
 #pragma unroll
         for (int c = 0; c < CABM_N_COUNTERS; ++c) {
             const unsigned int b = __ballot_sync(0xffffffffu, (m >> c) & 1u);
-            if (b && (threadIdx.x & 31) == 0) atomicAdd(&sm[c], __popc(b));
+            if (b && lane == 0) atomicAdd(&sm[c], __popc(b));
         }
     }
     __syncthreads();
