@@ -308,7 +308,8 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
     D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + roster.size() / SMALL_ROSTER + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
-    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
+    D.cap_sitems = (unsigned int) std::min<size_t>(0x7FFFFFFF, (size_t) L + nbr.size() + 1024);
+    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, (size_t) 2 * D.cap_hot)) || (rc = dalloc(h, &D.sitems, D.cap_sitems)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
         (rc = dalloc(h, &D.active_list, D.cap_active)) || (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
         (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
         (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||

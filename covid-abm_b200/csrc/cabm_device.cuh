@@ -27,6 +27,7 @@ struct __align__(16) Tl0 { short infected, infectious_begin, infectious_end, sym
 struct __align__(16) Tl1 { short critical_begin, critical_end, icu_begin, death, report_day; unsigned char strain, detected; float rel_inf; };
 
 struct __align__(16) Item { int src; int begin; int count; int purpose; double T; double pad; };   // a 256-member chunk of a big roster
+struct __align__(16) SItem { int src; int begin; unsigned int count_purpose; unsigned int t_idx; };   // a small roster: count << 8 | purpose, T = hot_T[t_idx]
 struct __align__(16) Hit  { unsigned int pid; unsigned int src; unsigned int purpose; unsigned int sub; }; // a trial with U < T, to be gated
 // one (infectious agent, location) flag of the day (Community::flagInfectedLocation, Community.cpp:788-791);
 // c = pressure contribution in 2^-32 units with the strain in the top byte. k_active appends FlagRaw records;
@@ -45,9 +46,9 @@ struct DayCtx {                     // per-day scalars, staged by the host for e
 // counters living in device memory
 struct Counters {
     // ---- day-scoped: zeroed by k_day_end ----
-    unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg;
+    unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;
     unsigned int n_hits[2], n_new[2];                        // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
-    unsigned int day_pad[5];
+    unsigned int day_pad[4];
     // ---- persistent ----
     unsigned int n_pat;                                      // admitted-patient list length (entries are never removed, see k_status)
     unsigned int overflow;                                   // sticky: a list ran out of capacity
@@ -77,9 +78,9 @@ struct Dev {
     unsigned long long* press; unsigned int* loc_cnt; int* loc_hot; unsigned int* pat_count;   // loc_cnt: flags today (0 = not hot), loc_hot: index in hot_list
     unsigned int* nvis; double* pub_T; unsigned int* pub_hot;     // [Q], [Q], [ceil(Q/32)] public-location visitor census, T, hot bitmap
     // day lists
-    int* hot_list; int* hot_hosp; unsigned int* hot_off; FlagRaw* flags_raw; Flag* flags;
+    int* hot_list; int* hot_hosp; unsigned int* hot_off; double* hot_T; FlagRaw* flags_raw; Flag* flags; SItem* sitems;
     unsigned int* active_list; uint2* visit_rec; Item* items; Hit* hits; unsigned int* newinf_list; unsigned int* patient_list;
-    unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_hits, cap_new, cap_pat; unsigned long long cap_log;
+    unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_sitems, cap_hits, cap_new, cap_pat; unsigned long long cap_log;
     // outputs
     unsigned long long* ledger;          // [CABM_N_COUNTERS][R]
     cabm_infection* log; cabm_foi_row* foi; unsigned int* n_foi; int foi_enabled;

@@ -334,110 +334,127 @@ __device__ __forceinline__ void write_foi(const Dev& D, unsigned int i, int loc,
     D.foi[i] = r;
 }
 
+// reserve n consecutive entries of a device list for every calling thread (n may differ per thread): one atomic per
+// coalesced group of callers
+__device__ __forceinline__ unsigned int list_reserve_n(unsigned int* counter, const unsigned int n) {
+    cg::coalesced_group g = cg::coalesced_threads();
+    unsigned int incl = n;
+    for (unsigned int o = 1; o < g.size(); o <<= 1) { const unsigned int t = g.shfl_up(incl, o); if (g.thread_rank() >= o) incl += t; }
+    unsigned int base = 0;
+    if (g.thread_rank() == g.size() - 1) base = atomicAdd(counter, incl);
+    return g.shfl(base, g.size() - 1) + incl - n;
+}
+
 // ---------------------------------------------------------------------------------------------
-// k_hazard: eight lanes per hot location (hospitals are left to k_hosp_import, after the status pass). The per-location
-// dependent chain (hot list -> type -> pressure -> roster -> members) is what bounds this kernel, so four locations share
-// a warp; rosters above SMALL_ROSTER are cut into 256-member items for k_trials.
+// k_hazard: one thread per hot location (hospitals are left to k_hosp_import, after the status pass): hazard -> T of
+// the location's pass(es) (Community.cpp:833-969) and the trial work it implies, as descriptors for k_trials:
+//   small items : a roster (or a neighbour's roster) of at most SMALL_ROSTER members, T by reference into hot_T
+//   big items   : 256-member chunks of larger rosters
+// Every hot location's dependent chain (hot list -> type -> pressure -> roster/neighbour offsets) runs in its own thread,
+// so the chains of all hot locations overlap; the trials themselves are spread over lanes in k_trials.
 // ---------------------------------------------------------------------------------------------
-#define HZ_LANES 8
 __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
-    const DayCtx& cx = day_ctx(D); const int day = cx.day;
+    const DayCtx& cx = day_ctx(D);
     const cabm_params* __restrict__ par = D.par;
     const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
-    const unsigned int lane = threadIdx.x & 31, gl = lane & (HZ_LANES - 1);
-    const unsigned int grp = (blockIdx.x * blockDim.x + threadIdx.x) / HZ_LANES, n_grp = (gridDim.x * blockDim.x) / HZ_LANES;
-    unsigned int trials = 0, edges = 0;
-    for (unsigned int i = grp; i < n_hot; i += n_grp) {
+    unsigned int edges = 0;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_hot; i += gridDim.x * blockDim.x) {
         const int loc = D.hot_list[i];
         const int type = D.loc_type[loc];
-        if (gl == 0) D.hot_off[i] = atomicAdd(&D.ctr->n_seg, D.loc_cnt[loc]);        // this location's segment of the sorted flag array
+        D.hot_off[i] = list_reserve_n(&D.ctr->n_seg, D.loc_cnt[loc]);                // this location's segment of the sorted flag array
         if (type == CABM_HOSPITAL) continue;
         const ulonglong2* pw = reinterpret_cast<const ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
         const ulonglong2 pa = pw[0], pb = pw[1];
         const unsigned long long pws[4] = { pa.x, pa.y, pb.x, pb.y };
         const double w = CABM_MUL((double) (pws[0] + pws[1] + pws[2] + pws[3]), 1.0 / 4294967296.0);
         const unsigned int rb = D.roster_off[loc], size = D.roster_off[loc + 1] - rb;
-        double T = 0.0, Ts = 0.0; unsigned int denom = size; int purpose = 0;
+        double T = 0.0, Ts = 0.0; unsigned int denom = size; int purpose = CABM_P_EXPOSE_HH;
         if (type == CABM_HOUSE) {
             T = hazard_to_T(CABM_MUL(CABM_MUL(par->haz_mult[CABM_HOUSE], cx.season), w));
             const unsigned int nb0 = D.nbr_off[loc], deg = D.nbr_off[loc + 1] - nb0;
             const bool risky = (double) D.loc_risk[loc] > cx.sd;
-            if (risky) { Ts = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_N_LOCTYPES], cx.season), w), (double) (int) size)); if (gl == 0) edges += deg; }
-            // within_household_transmission: own residents
-            if (T > 0.0) for (unsigned int m = gl; m < size; m += HZ_LANES) trial(D, day, 0, (unsigned int) D.roster[rb + m], loc, CABM_P_EXPOSE_HH, 0, T, trials);
-            // between_household_transmission: lane e takes neighbour e (its riskiness and roster bounds), then the group walks the neighbours
-            if (risky && Ts > 0.0) {
-                for (unsigned int e0 = 0; e0 < deg; e0 += HZ_LANES) {
-                    unsigned int nbb = 0, nbc = 0;
-                    if (e0 + gl < deg) {
-                        const int nb = D.nbr[nb0 + e0 + gl];
-                        if ((double) D.loc_risk[nb] > cx.sd) { nbb = D.roster_off[nb]; nbc = D.roster_off[nb + 1] - nbb; }
+            if (risky) { Ts = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_N_LOCTYPES], cx.season), w), (double) (int) size)); edges += deg; }
+            D.hot_T[2 * i + 1] = Ts;
+            // between_household_transmission (Community.cpp:853-875): one small item per neighbour; count 0 = neighbour below the
+            // social-distancing threshold
+            if (risky && Ts > 0.0 && deg) {
+                const unsigned int base = list_reserve_n(&D.ctr->n_sitems, deg);
+                if (base + deg <= D.cap_sitems) {
+                    for (unsigned int e = 0; e < deg; ++e) {
+                        const int nb = D.nbr[nb0 + e];
+                        const unsigned int b = D.roster_off[nb], c = D.roster_off[nb + 1] - b;
+                        SItem it; it.src = loc; it.begin = (int) b; it.count_purpose = (((double) D.loc_risk[nb] > cx.sd ? c : 0u) << 8) | CABM_P_EXPOSE_NB; it.t_idx = 2 * i + 1;
+                        D.sitems[base + e] = it;
                     }
-                    const unsigned int gmask = 0xFFu << (lane & 24);
-                    const unsigned int ne = min((unsigned int) HZ_LANES, deg - e0);
-                    for (unsigned int e = 0; e < ne; ++e) {
-                        const unsigned int b = __shfl_sync(gmask, nbb, (lane & 24) + e), cnt = __shfl_sync(gmask, nbc, (lane & 24) + e);
-                        for (unsigned int m = gl; m < cnt; m += HZ_LANES) trial(D, day, 0, (unsigned int) D.roster[b + m], loc, CABM_P_EXPOSE_NB, 0, Ts, trials);
+                } else atomicOr(&D.ctr->overflow, 16u);
+            }
+        } else if (type == CABM_WORK) {
+            const unsigned char lf = D.loc_flags[loc];
+            const int q = D.loc_pub[loc];
+            denom = size + (q >= 0 ? D.nvis[q] : 0u);
+            const bool closed = !(lf & LF_ESSENTIAL) && cx.business_closure != 0.0;
+            if (!(denom < 2 || closed) && w > 0.0) {
+                const double f = LF_PUBRISK(lf) == CABM_PT_HIGH ? 4.0 : 0.25;
+                T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(CABM_MUL(par->haz_mult[CABM_WORK], f), cx.season), w), CABM_SUB((double) (int) denom, 1.0)));
+            }
+            if (q >= 0) D.pub_T[q] = T;
+            purpose = CABM_P_EXPOSE_WORK;
+        } else if (type == CABM_SCHOOL) {
+            const bool open = cx.is_weekday && cx.school_closure < 1;
+            const double coef = CABM_MUL(CABM_MUL(CABM_SUB(1.0, cx.school_closure), par->haz_mult[CABM_SCHOOL]), cx.season);
+            if (open && coef != 0.0 && size >= 2) T = hazard_to_T(CABM_DIV(CABM_MUL(coef, w), CABM_SUB((double) (int) size, 1.0)));
+            purpose = CABM_P_EXPOSE_SCHOOL;
+        } else {  // NURSINGHOME
+            if (size >= 2) T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_NURSINGHOME], cx.season), w), CABM_SUB((double) (int) size, 1.0)));
+            purpose = CABM_P_EXPOSE_NH;
+        }
+        D.hot_T[2 * i] = T;
+        if (T > 0.0) {                                       // the location's own roster
+            if (size <= SMALL_ROSTER) {
+                const unsigned int base = list_reserve_n(&D.ctr->n_sitems, 1u);
+                if (base < D.cap_sitems) { SItem it; it.src = loc; it.begin = (int) rb; it.count_purpose = (size << 8) | (unsigned int) purpose; it.t_idx = 2 * i; D.sitems[base] = it; }
+                else atomicOr(&D.ctr->overflow, 16u);
+            } else {
+                const unsigned int nch = (size + CHUNK - 1) / CHUNK;
+                const unsigned int base = list_reserve_n(&D.ctr->n_items, nch);
+                if (base + nch <= D.cap_items) {
+                    for (unsigned int k = 0; k < nch; ++k) {
+                        Item it; it.src = loc; it.begin = (int) (rb + k * CHUNK); it.count = (int) min((unsigned int) CHUNK, size - k * CHUNK); it.purpose = purpose; it.T = T; it.pad = 0.0;
+                        D.items[base + k] = it;
                     }
-                }
-            }
-        } else {
-            if (type == CABM_WORK) {
-                const unsigned char lf = D.loc_flags[loc];
-                const int q = D.loc_pub[loc];
-                denom = size + (q >= 0 ? D.nvis[q] : 0u);
-                const bool closed = !(lf & LF_ESSENTIAL) && cx.business_closure != 0.0;
-                if (!(denom < 2 || closed) && w > 0.0) {
-                    const double f = LF_PUBRISK(lf) == CABM_PT_HIGH ? 4.0 : 0.25;
-                    T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(CABM_MUL(par->haz_mult[CABM_WORK], f), cx.season), w), CABM_SUB((double) (int) denom, 1.0)));
-                }
-                if (q >= 0 && gl == 0) D.pub_T[q] = T;
-                purpose = CABM_P_EXPOSE_WORK;
-            } else if (type == CABM_SCHOOL) {
-                const bool open = cx.is_weekday && cx.school_closure < 1;
-                const double coef = CABM_MUL(CABM_MUL(CABM_SUB(1.0, cx.school_closure), par->haz_mult[CABM_SCHOOL]), cx.season);
-                if (open && coef != 0.0 && size >= 2) T = hazard_to_T(CABM_DIV(CABM_MUL(coef, w), CABM_SUB((double) (int) size, 1.0)));
-                purpose = CABM_P_EXPOSE_SCHOOL;
-            } else {  // NURSINGHOME
-                if (size >= 2) T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_NURSINGHOME], cx.season), w), CABM_SUB((double) (int) size, 1.0)));
-                purpose = CABM_P_EXPOSE_NH;
-            }
-            if (T > 0.0) {
-                if (size <= SMALL_ROSTER) {
-                    for (unsigned int m = gl; m < size; m += HZ_LANES) trial(D, day, 0, (unsigned int) D.roster[rb + m], loc, purpose, 0, T, trials);
-                } else {
-                    const unsigned int nch = (size + CHUNK - 1) / CHUNK;
-                    unsigned int base = 0;
-                    if (gl == 0) base = atomicAdd(&D.ctr->n_items, nch);
-                    base = __shfl_sync(0xFFu << (lane & 24), base, lane & 24);
-                    if (base + nch <= D.cap_items) {
-                        for (unsigned int k = gl; k < nch; k += HZ_LANES) {
-                            Item it; it.src = loc; it.begin = (int) (rb + k * CHUNK); it.count = (int) min((unsigned int) CHUNK, size - k * CHUNK); it.purpose = purpose; it.T = T; it.pad = 0.0;
-                            D.items[base + k] = it;
-                        }
-                    } else if (gl == 0) atomicOr(&D.ctr->overflow, 16u);
-                }
+                } else atomicOr(&D.ctr->overflow, 16u);
             }
         }
-        if (D.foi_enabled && gl == 0) write_foi(D, i, loc, type, pws, denom, T, Ts);
+        if (D.foi_enabled) write_foi(D, i, loc, type, pws, denom, T, Ts);
     }
-    __syncwarp();
-    trials = warp_sum(trials); edges = warp_sum(edges);
-    if (lane == 0) { if (trials) atomicAdd(&D.ctr->work[CABM_W_TRIALS], (unsigned long long) trials); if (edges) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges); }
+    edges = warp_sum(edges);
+    if ((threadIdx.x & 31) == 0 && edges) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges);
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_trials: 256-trial units: first the roster items of big locations, then the visit records.
+// k_trials: block-sized units: the 256-member items of big rosters, the visit records, the flag scatter, the small items.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB) k_trials(const Dev D) {
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n_items = min(D.ctr->n_items, D.cap_items), n_vis = min(D.ctr->n_vis, D.cap_vis);
     const unsigned int n_flags = min(D.ctr->n_flags, D.cap_flags);
+    const unsigned int n_sitems = min(D.ctr->n_sitems, D.cap_sitems);
     const unsigned int u_vis = n_items + (n_vis + TPB - 1) / TPB;
-    const unsigned int units = u_vis + (n_flags + TPB - 1) / TPB;
+    const unsigned int u_flag = u_vis + (n_flags + TPB - 1) / TPB;
+    const unsigned int units = u_flag + (n_sitems + TPB / 8 - 1) / (TPB / 8);
     unsigned int trials = 0;
     for (unsigned int u = blockIdx.x; u < units; u += gridDim.x) {
-        if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
+        if (u >= u_flag) {                                   // small items: eight lanes per item
+            const unsigned int si = (u - u_flag) * (TPB / 8) + (threadIdx.x >> 3);
+            if (si < n_sitems) {
+                const SItem it = D.sitems[si];
+                const unsigned int cnt = it.count_purpose >> 8;
+                if (cnt) {
+                    const double T = D.hot_T[it.t_idx];
+                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[it.begin + m], it.src, (int) (it.count_purpose & 0xFFu), 0, T, trials);
+                }
+            }
+        } else if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
             const unsigned int f = (u - u_vis) * TPB + threadIdx.x;
             if (f < n_flags) {
                 const FlagRaw r = D.flags_raw[f];
