@@ -86,6 +86,7 @@ bool Sim::infect(int pid, int time, int source_loc, int strain, bool has_source,
                  uint32_t key_a, uint32_t key_b, uint32_t key_sub) {
     Person& p = people[pid];
     const int a = age[pid], com = comorbid[pid];
+    last_rep_draws = 0;
     // ---- calculate_event_probabilities ----
     const bool crossProtected   = is_cross_protected(p, pid, time, strain, s);
     const bool vaccineProtected = is_vaccine_protected(p, time, strain, s);
@@ -217,6 +218,7 @@ bool Sim::infect(int pid, int time, int source_loc, int strain, bool has_source,
                 if (me < (long) par.run_length) ledger[CABM_C_DET_DEATHS_REPORT][me]++;
             }
         }
+        last_rep_draws = r.s.idx;
     }
 
     // ---- flag future hot locations (:475-486) ----

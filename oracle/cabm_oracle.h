@@ -91,6 +91,7 @@ struct Sim {
     std::vector<cabm_foi_row> foi;
     std::vector<cabm_infection> log;                      // every infection, in creation order
     uint32_t seed_calls = 0;
+    uint32_t last_rep_draws = 0;                          // REPORTING_RNG draws of the last infect() (known-answer tests)
     int pending_infector = -1;                            // infector traced for the exposure being applied (Community.cpp:795-825)
     std::string err;
 

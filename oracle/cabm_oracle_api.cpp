@@ -180,4 +180,52 @@ int cabm_oracle_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n
 }
 int cabm_oracle_device_time_ms(cabm_t*, double* out_ms, uint64_t* out_launches) { if (out_ms) *out_ms = 0; if (out_launches) *out_launches = 0; return CABM_OK; }
 
+
+// ---- known-answer hooks (tests/test_reference_kat.py): scripted person state, one Person::infect call ----
+// hist: n_hist x {infectedBegin, infectiousEnd, symptomEnd (INT_MIN = none), strain}
+int cabm_oracle_kat_set_person(cabm_t* h, uint32_t pid, int n_hist, const int32_t* hist, int n_dose, const int32_t* doses, int naive) {
+    H_OK(h); Sim& S = h->sim; if (pid >= S.n_people) return CABM_E_ARG;
+    cabm_oracle::Person& p = S.people[pid];
+    p = cabm_oracle::Person();
+    for (int k = 0; k < n_hist; ++k) {
+        cabm_oracle::Infection inf;
+        inf.t[cabm_oracle::T_INFECTED] = hist[4 * k]; inf.t[cabm_oracle::T_INFECTIOUS_BEGIN] = hist[4 * k] + 1; inf.t[cabm_oracle::T_INFECTIOUS_END] = hist[4 * k + 1];
+        if (hist[4 * k + 2] != INT_MIN) { inf.t[cabm_oracle::T_SYMPTOM_BEGIN] = hist[4 * k] + 1; inf.t[cabm_oracle::T_SYMPTOM_END] = hist[4 * k + 2]; }
+        inf.strain = hist[4 * k + 3];
+        p.hist.push_back(inf);
+    }
+    for (int k = 0; k < n_dose; ++k) p.vax_days.push_back(doses[k]);
+    p.naive_vax = naive != 0;
+    return CABM_OK;
+}
+// out: ok, t[12], strain, detected_state, report_day, draws_rng, draws_reporting, cumul delta[5], n_flags, then {day, loc} pairs (cap pairs)
+int cabm_oracle_kat_infect(cabm_t* h, uint32_t pid, int strain, int day, int has_source, uint32_t key_a, uint32_t key_b,
+                           int64_t* out, float* out_rel_inf, int32_t* out_flags, size_t cap_flags) {
+    H_OK(h); Sim& S = h->sim; int rc = ready(S, day); if (rc) return rc;
+    if (pid >= S.n_people || !out) return CABM_E_ARG;
+    uint64_t cum0[CABM_N_OUTCOMES]; for (int k = 0; k < CABM_N_OUTCOMES; ++k) cum0[k] = S.cumul[k];
+    for (auto& v : S.hot) v.clear();
+    cabm_oracle::Stream s; s.begin(S.par.seed, (uint32_t) day, CABM_P_SEED, key_a, key_b);
+    S.pending_infector = -1;
+    const bool ok = S.infect((int) pid, day, has_source ? S.home[pid] : -1, strain, has_source != 0, s, CABM_P_SEED, key_a, key_b, 0);
+    cabm_oracle::Infection blank; const cabm_oracle::Infection& I = ok ? S.people[pid].hist.back() : blank;
+    size_t o = 0; out[o++] = ok ? 1 : 0;
+    for (int k = 0; k < cabm_oracle::T_N; ++k) out[o++] = I.t[k];
+    out[o++] = ok ? I.strain : 0; out[o++] = I.detected_state; out[o++] = I.report_day; out[o++] = s.s.idx; out[o++] = S.last_rep_draws;
+    for (int k = 0; k < CABM_N_OUTCOMES; ++k) out[o++] = (int64_t) (S.cumul[k] - cum0[k]);
+    size_t nf = 0;
+    for (size_t d = 0; d < S.hot.size(); ++d) for (const cabm_oracle::HotRec& r : S.hot[d]) { if (nf < cap_flags) { out_flags[2 * nf] = (int32_t) d; out_flags[2 * nf + 1] = r.loc; } nf++; }
+    out[o++] = (int64_t) nf;
+    if (out_rel_inf) *out_rel_inf = ok ? I.rel_inf : 1.0f;
+    return CABM_OK;
+}
+// FNV-style digest + sum of one ledger series, same arithmetic as ref_driver kat's last line
+int cabm_oracle_kat_ledger_digest(cabm_t* h, int counter, uint64_t* out_sum, uint64_t* out_hash) {
+    H_OK(h); Sim& S = h->sim; if (counter < 0 || counter >= CABM_N_COUNTERS) return CABM_E_ARG;
+    uint64_t s = 0, hh = 1469598103934665603ull;
+    for (size_t d = 0; d < S.ledger[counter].size(); ++d) { s += S.ledger[counter][d]; hh = (hh ^ (S.ledger[counter][d] + 0x9E37u * d)) * 1099511628211ull; }
+    *out_sum = s; *out_hash = hh;
+    return CABM_OK;
+}
+
 } // extern "C"

@@ -26,6 +26,7 @@
 #include <sstream>
 #include <iostream>
 #include "simulator.h"
+#include "../include/cabm.h"
 
 using namespace std;
 
