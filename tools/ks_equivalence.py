@@ -1,0 +1,149 @@
+#!/usr/bin/env python3
+"""Statistical equivalence of epidemic curves: this repository's model semantics vs the UNMODIFIED reference.
+
+    python tools/ks_equivalence.py [--agents N] [--days D] [--replicates R] [--impl oracle|cuda] [--out file.json]
+
+BASELINE.json north_star: "daily incidence, hospitalisation and death curves must be statistically equivalent over 100
+replicates by a KS test at p > 0.05". Arm A is the unmodified reference (oracle/_ref/ref_driver run: the reference's own
+Community::tick + seed_epidemic with its three sequential GSL-style streams, seeds 1..R). Arm B is the Philox-keyed
+restatement -- the CPU oracle (default; runs anywhere) or the CUDA path (--impl cuda; bit-identical to the oracle, see
+tests/test_parity_gpu.py) -- with seeds 1001..1000+R. Both run the same synthetic population and parameter set. For
+every replicate the daily series are reduced to summary statistics (cumulative counts at three horizons, peak height and
+peak day of the 7-day mean); each statistic is compared across arms with a two-sample Kolmogorov-Smirnov test.
+The reference arm needs /root/reference at BUILD time only (make -C oracle ref).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tools")); sys.path.insert(0, os.path.join(ROOT, "tests"))
+REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+SERIES = {"incidence": "inf", "hospitalisation": "hosp_inc", "death": "dead", "symptomatic": "symp", "detected_cases": "det_case_report"}
+HEADLINE = ("incidence", "hospitalisation", "death")
+ORACLE_COLS = {"inf": "new_infected", "hosp_inc": "hosp_inc", "dead": "new_dead", "symp": "new_symptomatic", "det_case_report": "det_cases_report"}
+
+
+def summaries(series: np.ndarray, days: int) -> dict:
+    cum = np.cumsum(series)
+    sm = np.convolve(series, np.ones(7) / 7.0, mode="same")
+    return {"total": float(cum[-1]), "cum_at_1/3": float(cum[days // 3]), "cum_at_2/3": float(cum[2 * days // 3]),
+            "peak_7d_mean": float(sm.max()), "peak_day": float(sm.argmax())}
+
+
+def run_reference(pop_dir, P, T, seed, days, cabm):
+    Pr = dict(P); Pr["seed"] = seed
+    pf = os.path.join(pop_dir, f"params{seed}.txt"); out = os.path.join(pop_dir, f"ref{seed}.csv")
+    cabm.params.write_text(Pr, T, pf)
+    subprocess.run([REF_DRIVER, "run", pf, pop_dir, "ks", out, str(days)], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    a = np.genfromtxt(out, delimiter=",", names=True)
+    return {k: np.asarray(a[v], dtype=np.float64) for k, v in SERIES.items()}
+
+
+def run_ours(pop, P, T, seed, days, cabm, impl):
+    Pr = dict(P); Pr["seed"] = seed
+    attrs = cabm.abi.immunity_attributes(int(pop["n_people"]), seed)
+    if impl == "cuda":
+        c = cabm.Community(Pr, pop, T, attrs=attrs)
+    else:
+        import oracle_lib
+        c = oracle_lib.oracle_community(Pr, pop, T, attrs=attrs)
+    c.run_days(days)
+    out = {k: c.ledger(ORACLE_COLS[v]).astype(np.float64)[:days] for k, v in SERIES.items()}
+    c.close()
+    return out
+
+
+def build_case(args, cabm, synthpop):
+    pop = synthpop.generate(args.agents, seed=4242)
+    P = cabm.params.default_params(run_length=args.days, seed=1, T=args.T, prob_daily_exposure=args.pde,
+                                   mutant_intro_dates=("2020-03-11", "2020-04-20", "2030-01-01"))
+    return pop, P, cabm.params.build_tables(P)
+
+
+def reference_arm(args, cabm, synthpop, pop, P, T):
+    """Per-replicate summaries of the unmodified reference, seeds 1..R."""
+    if not os.path.exists(REF_DRIVER):
+        sys.exit("oracle/_ref/ref_driver missing: build it with `make -C oracle ref` where /root/reference exists")
+    tmp = tempfile.mkdtemp(prefix="cabm_ks_")
+    synthpop.write_reference_files(pop, tmp, "ks")
+    with ThreadPoolExecutor(max_workers=args.threads) as ex:
+        ref = list(ex.map(lambda s: run_reference(tmp, P, T, s, args.days, cabm), range(1, args.replicates + 1)))
+    subprocess.run(["rm", "-rf", tmp])
+    return [{name: summaries(r[name], args.days) for name in SERIES} for r in ref]
+
+
+def ours_arm(args, cabm, pop, P, T):
+    """Per-replicate summaries of the Philox-keyed restatement, seeds 1001..1000+R."""
+    seeds = range(1001, 1001 + args.replicates)
+    if args.impl == "cuda":
+        runs = [run_ours(pop, P, T, s, args.days, cabm, "cuda") for s in seeds]
+    else:
+        with ThreadPoolExecutor(max_workers=args.threads) as ex:
+            runs = list(ex.map(lambda s: run_ours(pop, P, T, s, args.days, cabm, "oracle"), seeds))
+    return [{name: summaries(r[name], args.days) for name in SERIES} for r in runs]
+
+
+def compare(A, B):
+    from scipy.stats import ks_2samp
+    tests, worst = {}, 1.0
+    for name in SERIES:
+        for stat in A[0][name]:
+            a = np.array([x[name][stat] for x in A]); b = np.array([x[name][stat] for x in B])
+            ks = ks_2samp(a, b)
+            tests[f"{name}.{stat}"] = {"p": float(ks.pvalue), "D": float(ks.statistic), "ref_mean": float(a.mean()), "ours_mean": float(b.mean())}
+            if name in HEADLINE:
+                worst = min(worst, float(ks.pvalue))
+    return tests, worst
+
+
+def config_of(args, pop):
+    return {"agents": int(pop["n_people"]), "days": args.days, "replicates": args.replicates, "T": args.T, "pde": args.pde}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--agents", type=int, default=20000)
+    ap.add_argument("--days", type=int, default=150)
+    ap.add_argument("--replicates", type=int, default=100)
+    ap.add_argument("--impl", default="oracle", choices=["oracle", "cuda"])
+    ap.add_argument("--T", type=float, default=0.2)
+    ap.add_argument("--pde", type=float, default=2e-4)
+    ap.add_argument("--threads", type=int, default=os.cpu_count() or 1)
+    ap.add_argument("--save-ref", default=None, help="write the reference arm's per-replicate summaries (a golden fixture)")
+    ap.add_argument("--load-ref", default=None, help="read the reference arm from such a fixture instead of running it")
+    ap.add_argument("--out", default=None)
+    args = ap.parse_args()
+    import covid_abm_b200 as cabm
+    import synthpop
+    if args.load_ref:
+        fx = json.load(open(args.load_ref)); c = fx["config"]
+        args.agents, args.days, args.replicates, args.T, args.pde = c["agents_requested"], c["days"], c["replicates"], c["T"], c["pde"]
+    pop, P, T = build_case(args, cabm, synthpop)
+    if args.load_ref:
+        A = fx["summaries"]
+    else:
+        A = reference_arm(args, cabm, synthpop, pop, P, T)
+    if args.save_ref:
+        cfg = config_of(args, pop); cfg["agents_requested"] = args.agents
+        json.dump({"what": "per-replicate curve summaries of the UNMODIFIED reference (oracle/_ref/ref_driver run), made by tools/ks_equivalence.py --save-ref",
+                   "config": cfg, "summaries": A}, open(args.save_ref, "w"))
+    B = ours_arm(args, cabm, pop, P, T)
+    tests, worst = compare(A, B)
+    report = dict(config_of(args, pop), impl=args.impl, tests=tests)
+    report["min_p_incidence_hosp_death"] = worst
+    report["pass_p_gt_0.05"] = bool(worst > 0.05)
+    txt = json.dumps(report, indent=1)
+    if args.out:
+        open(args.out, "w").write(txt + "\n")
+    print(txt)
+
+
+if __name__ == "__main__":
+    main()
