@@ -142,7 +142,8 @@ def bench_ours(args):
     torch.cuda.set_device(0)
     K, W = args.steps, args.warmup
     total_days = (K + W) * DAYS_PER_STEP
-    cabm, pop, P, T = make_workload(total_days, seed=1 + rank)
+    import covid_abm_b200 as _c
+    cabm, pop, P, T = make_workload(total_days, seed=_c.replicates.replicate_seed(1, rank, 0, world))
     n = int(pop["n_people"])
     attrs = cabm.abi.immunity_attributes(n, P["seed"])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -195,11 +196,11 @@ def bench_ours(args):
 
     # ---- reduce over ranks ----
     agent_days = float(n) * K * DAYS_PER_STEP
-    vals = torch.tensor([dev_ms, wall, e2e_wall], dtype=torch.float64, device="cuda")
-    tot = torch.tensor([agent_days], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(vals, op=dist.ReduceOp.MAX); dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    dev_ms_max, wall_max, e2e_max = (float(x) for x in vals.tolist()); agent_days_all = float(tot.item())
+    dev = torch.device("cuda", 0)
+    agent_days_all, dev_s_max, _ = cabm.replicates.job_throughput(dist, dev, agent_days, dev_ms * 1e-3)
+    _, wall_max, _ = cabm.replicates.job_throughput(dist, dev, agent_days, wall)
+    _, e2e_max, _ = cabm.replicates.job_throughput(dist, dev, agent_days, e2e_wall)
+    dev_ms_max = dev_s_max * 1e3
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()

@@ -4,6 +4,7 @@
 #include <cstring>
 #include <new>
 #include "cabm_oracle.h"
+#include "cabm_det_math.h"
 
 using cabm_oracle::Sim;
 struct cabm { Sim sim; };
@@ -228,4 +229,19 @@ int cabm_oracle_kat_ledger_digest(cabm_t* h, int counter, uint64_t* out_sum, uin
     return CABM_OK;
 }
 
+// ---- generator / deterministic-math hooks for tests/test_philox.py and tests/test_det_math.py -------------------------
+void cabm_oracle_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { philox4x32_10_ref(ctr, key, out); }
+
+// the first n words of the event stream keyed (seed; day, purpose, a, b) -- the convention of philox_ref.h
+void cabm_oracle_stream_words(uint64_t seed, uint32_t day, uint32_t purpose, uint32_t a, uint32_t b, uint32_t* out, size_t n) {
+    philox_stream_ref s; philox_stream_begin(&s, seed, day, purpose, a, b);
+    for (size_t i = 0; i < n; ++i) out[i] = philox_stream_next(&s);
+}
+
+// kind 0 = cabm_exp, 1 = cabm_log, 2 = cabm_logistic (include/cabm_det_math.h)
+void cabm_oracle_det_math(int kind, const double* x, double* y, size_t n) {
+    for (size_t i = 0; i < n; ++i) y[i] = kind == 0 ? cabm_exp(x[i]) : kind == 1 ? cabm_log(x[i]) : cabm_logistic(x[i]);
+}
+
 } // extern "C"
+

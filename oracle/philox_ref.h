@@ -2,9 +2,9 @@
  *
  * Plain-C restatement of the Philox4x32-10 counter-based generator
  * (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as 1, 2, 3", SC'11).
- * The product's device implementation lives in covid-abm_b200/csrc/philox.cuh; the two are
- * written independently and cross-checked by tests/test_philox.py against the published
- * known-answer vectors.
+ * The product's device implementation lives in covid-abm_b200/csrc/cabm_device.cuh; the two are
+ * written independently. tests/test_philox.py checks this one against the published known-answer
+ * vectors; the GPU parity tests then require identical draws from the device one.
  *
  * Stream convention shared by oracle, GSL shim tape mode and the CUDA kernels:
  *   key     = (seed_lo, seed_hi)
