@@ -219,6 +219,15 @@ def bench_ours(args):
                      "GBps": round(algorithmic_bytes(work, g[2]) / (group_ms(g) * 1e-3) / 1e9, 1) if group_ms(g) > 0 else None}
               for g in KERNEL_GROUPS}
     total_k_ms = sum(v[0] for v in ktimes.values())
+    traffic = traffic_note = None
+    try:                                  # dram bytes per launch of the dominant group from the committed ncu --set full capture
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            cap = json.load(f)
+        traffic = float(sum(cap["dram_bytes_per_launch"][k] for k in dom_g[1]))
+        cap_alg = algorithmic_bytes(cap["work"], dom_g[2])
+        traffic_note = f"{cap['source']}; algorithmic bytes of that launch {cap_alg:.4g} (traffic/algorithmic {traffic / cap_alg:.2f})"
+    except Exception:
+        pass
     day_bytes = algorithmic_bytes(work)
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -238,7 +247,7 @@ def bench_ours(args):
                 "d2h_bytes_per_step": DAYS_PER_STEP * (cabm.abi.N_COUNTERS * 8 + 4 + 2 * 4), "calls_per_step": DAYS_PER_STEP * 3},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "kernel_avg_us": dom_ms * 1e3 / max(dom_n, 1),
+                     "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note, "kernel_avg_us": dom_ms * 1e3 / max(dom_n, 1),
                      "kernel_share_of_day": dom_ms / total_k_ms if total_k_ms else None,
                      "pipeline_achieved": day_bytes / (dev_ms_max * 1e-3) / 1e9, "pipeline_frac": day_bytes / (dev_ms_max * 1e-3) / 1e9 / peak,
                      "bytes_per_agent_day": day_bytes / (n * K * DAYS_PER_STEP),
