@@ -18,6 +18,9 @@ COUNTERS = ["new_infected", "new_symptomatic", "new_severe", "new_critical", "ne
             "det_hosp", "det_deaths_onset", "det_deaths_report", "new_inf_strain0", "new_inf_strain1",
             "new_inf_strain2", "new_inf_strain3"]
 N_COUNTERS = len(COUNTERS)
+DIAG = ["dose_1", "dose_2", "dose_3", "fully_vaxd", "bt_inf", "bt_dis", "bt_hosp", "bt_death", "bt_reported", "uv_inf", "uv_dis", "uv_hosp",
+        "uv_death", "uv_reported", "infected", "infectious", "symptomatic", "naive", "quarantining", "seropos_all", "seropos_ped", "n_ped"]
+N_DIAG = 24
 WORK = ["agents", "active", "flags", "patrons", "visits", "hot_visits", "hot_locs", "nbr_edges", "trials", "infections"]
 N_WORK = len(WORK)
 
@@ -88,6 +91,8 @@ _PROTOS = {
     "sync_histories": [_vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)], "get_infections": [_vp, C.POINTER(C.c_uint32), C.c_size_t, _vp],
     "snapshot": [_vp, C.POINTER(_vp)], "restore": [_vp, _vp], "snap_free": [_vp],
     "dump_foi": [_vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)], "device_time_ms": [_vp, C.POINTER(d), C.POINTER(C.c_uint64)],
+    "sync_histories_from": [_vp, C.c_size_t, _vp, C.c_size_t, C.POINTER(C.c_size_t)],
+    "diagnostics": [_vp, C.c_int, C.POINTER(C.c_uint64)], "serosurvey": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_uint64)],
 }
 _OPTIONAL = {
     "set_profile": [_vp, C.c_int],

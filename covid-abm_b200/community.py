@@ -206,6 +206,53 @@ class Community:
         self._check(self.fn.get_infections(self._h, ptr, n, out.ctypes.data))
         return out
 
+    # ---- caller-side daily diagnostics (simulator.h:402-410,438), device reductions ----
+    def diagnostics(self, day: int | None = None) -> dict:
+        out = np.zeros(abi.N_DIAG, dtype=np.uint64)
+        self._check(self.fn.diagnostics(self._h, max(self.day - 1, 0) if day is None else int(day), out.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return dict(zip(abi.DIAG, (int(x) for x in out)))
+
+    def calculate_vax_stats(self, day: int) -> dict:
+        """Community::calculate_vax_stats (Community.cpp:1329-1423): same keys, same arithmetic on the device counts."""
+        c = self.diagnostics(day); n = float(self.n_people)
+        full = float(c["fully_vaxd"]); unv = n - full
+
+        def ve(bt, uv):
+            with np.errstate(divide="ignore", invalid="ignore"):
+                return float(1.0 - (np.float64(c[bt]) / np.float64(full)) / (np.float64(c[uv]) / np.float64(unv)))
+        with np.errstate(divide="ignore", invalid="ignore"):
+            brk = float(np.float64(c["bt_reported"]) / np.float64(c["bt_reported"] + c["uv_reported"]))
+        return {"coverage": full / n, "dose_1": c["dose_1"] / n, "dose_2": c["dose_2"] / n, "dose_3": c["dose_3"] / n,
+                "VES": ve("bt_inf", "uv_inf"), "VEP": ve("bt_dis", "uv_dis"), "VEH": ve("bt_hosp", "uv_hosp"), "VED": ve("bt_death", "uv_death"),
+                "breakthruRatio": brk, "vaxInfs": float(c["bt_inf"]), "unvaxInfs": float(c["uv_inf"]), "vaxHosp": float(c["bt_hosp"]),
+                "unvaxHosp": float(c["uv_hosp"])}
+
+    def doSerosurvey(self, pids, day: int) -> float:
+        """Community::doSerosurvey(NATURAL, pop, day) (Community.cpp:1224-1274); pids None = everybody."""
+        out = C.c_uint64(0)
+        if pids is None:
+            n = self.n_people; ptr = None
+        else:
+            p = np.ascontiguousarray(pids, dtype=np.uint32); n = p.size; ptr = p.ctypes.data_as(C.POINTER(C.c_uint32))
+        self._check(self.fn.serosurvey(self._h, int(day), ptr, n, C.byref(out)))
+        return out.value / n if n else float("nan")
+
+    def getNumPeopleQuarantining(self, day: int) -> float:
+        return self.diagnostics(day)["quarantining"] / self.n_people
+
+    def getNumInfected(self, day: int) -> int: return self.diagnostics(day)["infected"]
+    def getNumInfectious(self, day: int) -> int: return self.diagnostics(day)["infectious"]
+    def getNumSymptomatic(self, day: int) -> int: return self.diagnostics(day)["symptomatic"]
+    def getNumNaive(self) -> int: return self.diagnostics(max(self.day - 1, 0))["naive"]
+
+    def infection_histories_from(self, first: int) -> np.ndarray:
+        n = C.c_size_t(0)
+        self._check(self.fn.sync_histories_from(self._h, int(first), None, 0, C.byref(n)))
+        out = np.zeros(n.value, dtype=abi.INFECTION_DTYPE)
+        if n.value:
+            self._check(self.fn.sync_histories_from(self._h, int(first), out.ctypes.data, n.value, C.byref(n)))
+        return out
+
     def foi(self) -> np.ndarray:
         n = C.c_size_t(0)
         self._check(self.fn.dump_foi(self._h, None, 0, C.byref(n)))

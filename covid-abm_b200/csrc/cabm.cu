@@ -33,7 +33,7 @@ struct cabm {
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
     uint64_t launches_per_day = 12;
-    unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr;
+    unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr;
     int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
 };
 
@@ -472,6 +472,49 @@ int cabm_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_
     n = std::min<unsigned long long>(n, h->d.cap_log);
     if (out_n) *out_n = (size_t) n;
     if (out && cap) CK(cudaMemcpy(out, h->d.log, std::min<size_t>(cap, (size_t) n) * sizeof(cabm_infection), cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+
+int cabm_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_t cap, size_t* out_n) {
+    if (!h || !h->have_pop) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    unsigned long long n = 0;
+    CK(cudaMemcpy(&n, &h->d.ctr->n_log, sizeof(n), cudaMemcpyDeviceToHost));
+    n = std::min<unsigned long long>(n, h->d.cap_log);
+    const size_t avail = first < n ? (size_t) n - first : 0;
+    if (out_n) *out_n = avail;
+    if (out && cap && avail) CK(cudaMemcpy(out, h->d.log + first, std::min(cap, avail) * sizeof(cabm_infection), cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+
+int cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]) {
+    if (!h || !out) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    cudaSetDevice(h->device);
+    if (!h->d_diag) { int rc2 = dalloc(h, &h->d_diag, CABM_N_DIAG); if (rc2) return rc2; }
+    CK(cudaMemsetAsync(h->d_diag, 0, CABM_N_DIAG * sizeof(unsigned long long), h->stream));
+    k_diagnostics<<<grid_for(h, h->d.N, 8), 256, 0, h->stream>>>(h->d, sim_day, h->d_diag);
+    CK(cudaMemcpyAsync(out, h->d_diag, CABM_N_DIAG * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return CABM_OK;
+}
+
+int cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos) {
+    if (!h || !out_seropos) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (!pids) n = h->d.N;
+    *out_seropos = 0;
+    if (n == 0) return CABM_OK;
+    if (pids) for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    if (!h->d_diag) { int rc2 = dalloc(h, &h->d_diag, CABM_N_DIAG); if (rc2) return rc2; }
+    unsigned int* d_p = nullptr;
+    if (pids) { CK(cudaMalloc(&d_p, n * sizeof(unsigned int))); CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream)); }
+    CK(cudaMemsetAsync(h->d_diag, 0, sizeof(unsigned long long), h->stream));
+    k_serosurvey<<<grid_for(h, n, 8), TPB, 0, h->stream>>>(h->d, sim_day, d_p, (unsigned int) n, h->d_diag);
+    unsigned long long r = 0;
+    CK(cudaMemcpyAsync(&r, h->d_diag, sizeof(r), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (d_p) cudaFree(d_p);
+    *out_seropos = r;
     return CABM_OK;
 }
 

@@ -349,6 +349,77 @@ __global__ void k_gather_infections(const Dev D, const unsigned int* pids, const
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Caller-side daily diagnostics as one device pass: calculate_vax_stats
+// (Community.cpp:1329-1423), doSerosurvey(NATURAL, ...) (:1224-1274), getNumPeopleQuarantining
+// (Community.h:437), getNumInfected/Infectious/Symptomatic/Naive (:1196-1222).
+// ---------------------------------------------------------------------------------------------
+// N-antibody positivity of one person on `day` (Community.cpp:1232-1252)
+__device__ __forceinline__ bool sero_positive(const Dev& D, const cabm_params* par, const unsigned int p, const int day) {
+    if (D.imm[p] == 0) return false;
+    const Tl0 a = D.tl0[p];
+    const int last_end = max((int) a.infectious_end, (int) a.symptom_end);
+    const int tsl = day - last_end;
+    const bool converted = (double) a.infected >= par->seroconversion_lag;       // latest infection has the largest infectedBegin
+    if (!converted) return false;
+    if (par->immunity_leaky) return remaining_efficacy(par, D.nat_eff[p], (double) tsl) > par->seropositivity_threshold;
+    return tsl < D.nat_dur[p];
+}
+
+__global__ void __launch_bounds__(256) k_diagnostics(const Dev D, const int day, unsigned long long* out) {
+    __shared__ unsigned int s_cnt[CABM_N_DIAG];
+    if (threadIdx.x < CABM_N_DIAG) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const cabm_params* par = D.par;
+    const int lag = par->vaccine_dose_to_protection_lag;
+    const unsigned int lane = threadIdx.x & 31;
+    for (unsigned int base = blockIdx.x * blockDim.x; base < D.N; base += gridDim.x * blockDim.x) {
+        const unsigned int p = base + threadIdx.x;
+        unsigned int bits = 0;                                    // one bit per counter this person adds to
+        if (p < D.N) {
+            const unsigned int v = D.vax[p]; const unsigned int nd = v & 0xFF; const int last_dose = (short) (v >> 16);
+            if (nd >= 1 && nd <= 3) bits |= 1u << CABM_D_DOSE1;   // the reference's switch has no case above 3 doses (:1351-1356)
+            if (nd == 2 || nd == 3) bits |= 1u << CABM_D_DOSE2;
+            if (nd == 3) bits |= 1u << CABM_D_DOSE3;
+            const bool full = nd > 1 && (day - last_dose) >= lag;
+            if (full) bits |= 1u << CABM_D_FULLY_VAXD;
+            const unsigned int imm = D.imm[p];
+            if (imm) {
+                const Tl0 a = D.tl0[p]; const Tl1 b = D.tl1[p];
+                const int o = full ? CABM_D_BT_INF : CABM_D_UV_INF;
+                if (a.infected == day) bits |= 1u << o;
+                if (a.symptom_begin == day) bits |= 1u << (o + 1);
+                if (a.hosp_begin == day) bits |= 1u << (o + 2);
+                if (b.death == day) bits |= 1u << (o + 3);
+                if (b.detected < CABM_N_OUTCOMES && b.report_day == day) bits |= 1u << (o + 4);
+                if (a.infected <= day && day < a.infectious_end) bits |= 1u << CABM_D_INFECTED;
+                if (a.infectious_begin <= day && day < a.infectious_end) bits |= 1u << CABM_D_INFECTIOUS;
+                if (a.symptom_begin <= day && day < a.symptom_end) bits |= 1u << CABM_D_SYMPTOMATIC;
+            } else if (nd == 0) bits |= 1u << CABM_D_NAIVE;
+            const unsigned int q = D.quar[p]; const int qf = (short) (q & 0xFFFF), qu = (short) (q >> 16);
+            if (q != 0 && day >= qf && day < qu) bits |= 1u << CABM_D_QUARANTINING;
+            const bool ped = D.age[p] <= 17;
+            if (ped) bits |= 1u << CABM_D_N_PED;
+            if (imm && sero_positive(D, par, p, day)) bits |= (1u << CABM_D_SEROPOS_ALL) | (ped ? 1u << CABM_D_SEROPOS_PED : 0u);
+        }
+#pragma unroll
+        for (int c = 0; c < CABM_D_N_PED + 1; ++c) {
+            const unsigned int n = __popc(__ballot_sync(0xFFFFFFFFu, (bits >> c) & 1u));
+            if (lane == 0 && n) atomicAdd(&s_cnt[c], n);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < CABM_N_DIAG && s_cnt[threadIdx.x]) atomicAdd(&out[threadIdx.x], (unsigned long long) s_cnt[threadIdx.x]);
+}
+
+__global__ void k_serosurvey(const Dev D, const int day, const unsigned int* pids, const unsigned int n, unsigned long long* out) {
+    unsigned int mine = 0;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        mine += sero_positive(D, D.par, pids ? pids[i] : i, day) ? 1u : 0u;
+    mine = warp_sum(mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(out, (unsigned long long) mine);
+}
+
 __global__ void k_init_state(const Dev D) {
     const unsigned int stride = gridDim.x * blockDim.x;
     for (unsigned int p = blockIdx.x * blockDim.x + threadIdx.x; p < D.N; p += stride) {

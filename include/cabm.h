@@ -175,6 +175,33 @@ typedef struct cabm_population {
     const int32_t*  natural_immunity_duration;
 } cabm_population;
 
+/* Daily diagnostics the caller computes over all people (simulator.h:402-410,438), as one device pass. */
+enum cabm_diag {
+    CABM_D_DOSE1 = 0,        /* people with >= 1, >= 2, >= 3 doses (calculate_vax_stats, Community.cpp:1351-1357) */
+    CABM_D_DOSE2,
+    CABM_D_DOSE3,
+    CABM_D_FULLY_VAXD,       /* > 1 dose and days since last dose >= vaccine_dose_to_protection_lag (:1359) */
+    CABM_D_BT_INF,           /* among those: latest infection began / symptoms began / hospitalised / died / reported today (:1361-1385) */
+    CABM_D_BT_DIS,
+    CABM_D_BT_HOSP,
+    CABM_D_BT_DEATH,
+    CABM_D_BT_REPORTED,
+    CABM_D_UV_INF,           /* the same events among everybody else */
+    CABM_D_UV_DIS,
+    CABM_D_UV_HOSP,
+    CABM_D_UV_DEATH,
+    CABM_D_UV_REPORTED,
+    CABM_D_INFECTED,         /* getNumInfected(day), getNumInfectious(day), getNumSymptomatic(day), getNumNaive() (:1196-1222) */
+    CABM_D_INFECTIOUS,
+    CABM_D_SYMPTOMATIC,
+    CABM_D_NAIVE,
+    CABM_D_QUARANTINING,     /* numerator of getNumPeopleQuarantining(day) (Community.h:437) */
+    CABM_D_SEROPOS_ALL,      /* doSerosurvey(NATURAL, everybody, day) numerator (:1224-1274) */
+    CABM_D_SEROPOS_PED,      /* the same over ages 0-17 (simulator.h:405-410) ... */
+    CABM_D_N_PED,            /* ... and that cohort's size */
+    CABM_N_DIAG = 24
+};
+
 /* One record of Person::infectionHistory, as returned by cabm_sync_histories (Person.h:35-175). */
 typedef struct cabm_infection {
     uint32_t person;
@@ -233,6 +260,8 @@ int  cabm_work_counters(cabm_t* h, uint64_t out[CABM_N_WORK]);
 
 /* lazy D2H of every infection record (Person::getInfectionHistory, Person.h:281) */
 int  cabm_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_n);
+/* the same, starting at record `first` of the append-only infection log (incremental refresh of host-side proxies) */
+int  cabm_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_t cap, size_t* out_n);
 /* current (latest) infection of selected people; pids NULL => all */
 int  cabm_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infection* out);
 
@@ -243,6 +272,12 @@ int  cabm_snap_free(cabm_snap_t* s);
 
 /* parity hook: hazards of the most recent tick */
 int  cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n);
+/* caller-side daily diagnostics as device reductions: calculate_vax_stats (Community.cpp:1329-1423), doSerosurvey (:1224-1274),
+   getNumPeopleQuarantining (Community.h:437), getNumInfected/Infectious/Symptomatic/Naive (Community.cpp:1196-1222) */
+int  cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]);
+/* doSerosurvey(NATURAL, pop, day) for an arbitrary list of people (pids == NULL: everybody); returns the seropositive count */
+int  cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos);
+
 /* device time (ms, CUDA events) spent in the day pipeline since the last call; resets the accumulator */
 int  cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches);
 

@@ -153,6 +153,75 @@ int cabm_oracle_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_
     return CABM_OK;
 }
 
+int cabm_oracle_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_t cap, size_t* out_n) {
+    H_OK(h); Sim& S = h->sim;
+    const size_t avail = first < S.log.size() ? S.log.size() - first : 0;
+    if (out_n) *out_n = avail;
+    if (out && avail) std::memcpy(out, S.log.data() + first, std::min(cap, avail) * sizeof(cabm_infection));
+    return CABM_OK;
+}
+
+// Community::doSerosurvey, NATURAL branch, for one person (Community.cpp:1232-1252)
+static bool oracle_sero_positive(const Sim& S, uint32_t pid, int day) {
+    const cabm_oracle::Person& p = S.people[pid];
+    if (p.hist.empty()) return false;
+    const cabm_oracle::Infection& last = p.hist.back();
+    const int last_end = std::max(last.t[cabm_oracle::T_INFECTIOUS_END], last.t[cabm_oracle::T_SYMPTOM_END]);
+    const int tsl = day - last_end;
+    bool converted = false;
+    for (int i = (int) p.hist.size() - 1; i >= 0; --i) if ((double) p.hist[i].t[cabm_oracle::T_INFECTED] >= S.par.seroconversion_lag) { converted = true; break; }
+    if (!converted) return false;
+    if (S.par.immunity_leaky) return S.remaining_efficacy(S.nat_eff[pid], (double) tsl) > S.par.seropositivity_threshold;
+    return tsl < S.nat_dur[pid];
+}
+
+// calculate_vax_stats (Community.cpp:1329-1423) and the per-day population counts of simulator.h:402-410,438
+int cabm_oracle_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]) {
+    H_OK(h); Sim& S = h->sim; if (!out) return CABM_E_ARG;
+    for (int k = 0; k < CABM_N_DIAG; ++k) out[k] = 0;
+    const int day = sim_day;
+    for (uint32_t pid = 0; pid < S.n_people; ++pid) {
+        const cabm_oracle::Person& p = S.people[pid];
+        switch (p.vax_days.size()) {
+            case 3: out[CABM_D_DOSE3]++; [[fallthrough]];
+            case 2: out[CABM_D_DOSE2]++; [[fallthrough]];
+            case 1: out[CABM_D_DOSE1]++; break;
+            default: break;
+        }
+        const bool full = p.vax_days.size() > 1 && (day - p.vax_days.back()) >= S.par.vaccine_dose_to_protection_lag;
+        if (full) out[CABM_D_FULLY_VAXD]++;
+        if (!p.hist.empty()) {
+            const cabm_oracle::Infection& inf = p.hist.back();
+            const int o = full ? CABM_D_BT_INF : CABM_D_UV_INF;
+            if (inf.t[cabm_oracle::T_INFECTED] == day) out[o]++;
+            if (inf.t[cabm_oracle::T_SYMPTOM_BEGIN] == day) out[o + 1]++;
+            if (inf.t[cabm_oracle::T_HOSP_BEGIN] == day) out[o + 2]++;
+            if (inf.t[cabm_oracle::T_DEATH] == day) out[o + 3]++;
+            if (inf.detected_state < CABM_N_OUTCOMES && inf.report_day == day) out[o + 4]++;
+            if (inf.isInfected(day)) out[CABM_D_INFECTED]++;
+            if (inf.isInfectious(day)) out[CABM_D_INFECTIOUS]++;
+            if (inf.t[cabm_oracle::T_SYMPTOM_BEGIN] <= day && day < inf.t[cabm_oracle::T_SYMPTOM_END]) out[CABM_D_SYMPTOMATIC]++;
+        } else if (p.vax_days.empty()) out[CABM_D_NAIVE]++;
+        if (S.quarantining(p, day)) out[CABM_D_QUARANTINING]++;
+        const bool ped = S.age[pid] <= 17;
+        if (ped) out[CABM_D_N_PED]++;
+        if (oracle_sero_positive(S, pid, day)) { out[CABM_D_SEROPOS_ALL]++; if (ped) out[CABM_D_SEROPOS_PED]++; }
+    }
+    return CABM_OK;
+}
+
+int cabm_oracle_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos) {
+    H_OK(h); Sim& S = h->sim; if (!out_seropos) return CABM_E_ARG;
+    if (!pids) n = S.n_people;
+    uint64_t c = 0;
+    for (size_t i = 0; i < n; ++i) {
+        const uint32_t pid = pids ? pids[i] : (uint32_t) i; if (pid >= S.n_people) return CABM_E_ARG;
+        c += oracle_sero_positive(S, pid, sim_day) ? 1 : 0;
+    }
+    *out_seropos = c;
+    return CABM_OK;
+}
+
 int cabm_oracle_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infection* out) {
     H_OK(h); Sim& S = h->sim;
     for (size_t i = 0; i < n; ++i) {

@@ -228,3 +228,56 @@ def test_ragged_population_edges():
     c.run_days(30)
     w = c.work_counters()
     assert w["patrons"] == 0 and w["visits"] == 0 and w["nbr_edges"] == 0 and w["infections"] > 0
+
+
+def test_daily_diagnostics_against_brute_force():
+    """cabm_diagnostics / cabm_serosurvey (calculate_vax_stats Community.cpp:1329-1423, doSerosurvey :1224-1274,
+    getNumInfected... :1196-1222, getNumPeopleQuarantining Community.h:437) against a numpy restatement on the records."""
+    pop, P, c = community(n=6000, days=90, T=0.2, pde=1e-3, seed=8)
+    n = int(pop["n_people"])
+    doses = np.zeros(n, dtype=np.int64); last = np.full(n, -10**6, dtype=np.int64)
+    rng = np.random.default_rng(1)
+    for dose_day, frac in ((5, 0.7), (26, 0.5), (50, 0.2)):
+        c.run_days(dose_day - c.day)
+        who = np.flatnonzero(rng.random(n) < frac).astype(np.uint32)
+        ok = c.vaccinate(who, dose_day)
+        doses[who[ok]] += 1; last[who[ok]] = dose_day
+    c.quarantine(np.arange(0, n, 5, dtype=np.uint32), 60, 75)
+    c.run_days(70 - c.day)
+    day = 69
+    d = c.diagnostics(day)
+    rec = c.current_infections(); t = rec["t"].astype(np.int64)
+    had = t[:, T_INFECTED] != NEVER
+    assert d["dose_1"] == np.count_nonzero((doses >= 1) & (doses <= 3)) and d["dose_2"] == np.count_nonzero((doses >= 2) & (doses <= 3))
+    assert d["dose_3"] == np.count_nonzero(doses == 3) and d["dose_1"] > d["dose_2"] > d["dose_3"] > 0
+    full = (doses > 1) & (day - last >= P["vaccine_dose_to_protection_lag"])
+    assert d["fully_vaxd"] == full.sum() > 0
+    for key, col in (("inf", T_INFECTED), ("dis", T_SYMPTOM_BEGIN), ("hosp", T_HOSP_BEGIN), ("death", T_DEATH)):
+        ev = had & (t[:, col] == day)
+        assert d["bt_" + key] == np.count_nonzero(ev & full) and d["uv_" + key] == np.count_nonzero(ev & ~full), key
+    rep = had & (rec["report_day"] == day) & (rec["detected_state"] < 5)
+    assert d["bt_reported"] == np.count_nonzero(rep & full) and d["uv_reported"] == np.count_nonzero(rep & ~full)
+    assert d["uv_inf"] + d["bt_inf"] > 0
+    assert d["infected"] == np.count_nonzero(had & (t[:, T_INFECTED] <= day) & (day < t[:, T_INFECTIOUS_END]))
+    assert d["infectious"] == np.count_nonzero(had & (t[:, T_INFECTIOUS_BEGIN] <= day) & (day < t[:, T_INFECTIOUS_END]))
+    assert d["symptomatic"] == np.count_nonzero(had & (t[:, T_SYMPTOM_BEGIN] <= day) & (day < t[:, T_SYMPTOM_END]))
+    assert d["naive"] == np.count_nonzero(~had & (doses == 0))
+    assert d["quarantining"] == len(range(0, n, 5)) and c.diagnostics(59)["quarantining"] == 0 and c.diagnostics(75)["quarantining"] == 0
+    ped = pop["age"] <= 17
+    assert d["n_ped"] == ped.sum()
+    # serosurvey: seroconverted (infected on or after day seroconversion_lag -- the reference's test) and remaining efficacy above threshold
+    last_end = np.maximum(t[:, T_INFECTIOUS_END], np.where(t[:, T_SYMPTOM_END] == -32768, -10**9, t[:, T_SYMPTOM_END]))
+    # with threshold 0 every converted person is positive unless their starting natural efficacy was clamped to 0
+    # (Parameters.h:605: remainingEfficacy(0, .) = logistic(-inf) = 0, and 0 > 0 is false)
+    nat_eff = cabm.abi.immunity_attributes(n, P["seed"])[0]
+    conv = had & (t[:, T_INFECTED] >= P["seroconversion_lag"]) & (nat_eff > 0)
+    assert P["seropositivity_threshold"] == 0.0 and (nat_eff == 0).sum() > 0
+    assert d["seropos_all"] == conv.sum() > 0 and d["seropos_ped"] == (conv & ped).sum()
+    assert abs(c.doSerosurvey(None, day) - conv.mean()) < 1e-15
+    some = np.arange(3, n, 7, dtype=np.uint32)
+    assert abs(c.doSerosurvey(some, day) - conv[some].mean()) < 1e-15
+    vs = c.calculate_vax_stats(day)
+    assert abs(vs["coverage"] - full.mean()) < 1e-15 and abs(vs["dose_2"] - d["dose_2"] / n) < 1e-15
+    # incremental history sync returns the tail of the log
+    allh = c.infection_histories(); tail = c.infection_histories_from(allh.size - 10)
+    assert tail.size == 10 and np.array_equal(tail, allh[-10:]) and c.infection_histories_from(allh.size).size == 0

@@ -97,7 +97,16 @@ def test_multi_variant_vaccination_quarantine():
         g.step(); o.step()
         if d % 15 == 14:
             assert_same_state(g, o, f"day {d}")
+        if d % 7 == 3 or d in (10, 31, 52, 74):   # caller-side daily diagnostics as device reductions (cabm_diagnostics / cabm_serosurvey)
+            dg, do = g.diagnostics(d), o.diagnostics(d)
+            assert dg == do, f"day {d}: {[(k, dg[k], do[k]) for k in dg if dg[k] != do[k]]}"
+            some = rng.choice(n, size=n // 4, replace=False)
+            assert g.doSerosurvey(some, d) == o.doSerosurvey(some, d) and g.doSerosurvey(None, d) == o.doSerosurvey(None, d)
     assert_same_state(g, o, "end")
+    dg = g.diagnostics(74)
+    assert dg["fully_vaxd"] > 0 and dg["seropos_all"] > 0 and dg["quarantining"] == 0 and dg["bt_inf"] + dg["uv_inf"] > 0
+    hg, ho = g.infection_histories(), o.infection_histories()
+    assert np.array_equal(g.infection_histories_from(hg.size - 50), hg[-50:]) and hg.size == ho.size
     strains = g.ledger_table()[:, 16:20].sum(axis=0)
     assert (strains > 0).sum() >= 3, f"variants seen: {strains}"
     assert g.ledger("vaccinated_cases").sum() > 0
