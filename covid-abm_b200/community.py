@@ -167,7 +167,10 @@ class Community:
         return out
 
     def ledger_table(self) -> np.ndarray:
-        return np.stack([self.ledger(i) for i in range(abi.N_COUNTERS)], axis=1)
+        """[run_length][N_COUNTERS], one device read (cabm_ledger_table)."""
+        out = np.zeros((abi.N_COUNTERS, self.run_length), dtype=np.uint64)
+        self._check(self.fn.ledger_table(self._h, out.ctypes.data_as(C.POINTER(C.c_uint64)), out.size))
+        return np.ascontiguousarray(out.T)
 
     def getNumNewlyInfected(self): return self.ledger("new_infected")
     def getNumNewlySymptomatic(self): return self.ledger("new_symptomatic")

@@ -445,6 +445,14 @@ int cabm_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n) {
     for (size_t d = m; d < n; ++d) out[d] = 0;
     return CABM_OK;
 }
+int cabm_ledger_table(cabm_t* h, uint64_t* out, size_t n) {
+    if (!h || !h->have_par || !out) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    const size_t all = (size_t) h->hpar.run_length * CABM_N_COUNTERS, m = std::min(n, all);
+    CK(cudaMemcpy(out, h->d.ledger, m * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    for (size_t i = m; i < n; ++i) out[i] = 0;
+    return CABM_OK;
+}
 int cabm_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]) {
     if (!h || !out) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     cudaSetDevice(h->device);

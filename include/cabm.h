@@ -255,6 +255,8 @@ int  cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, in
 /* replaces the ledger getters (Community.h:353-375) */
 int  cabm_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n);
 int  cabm_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]);
+/* all series at once, counter-major: out[counter * run_length + day] (the 15+4 by-value getters of simulator.h:376-390,450-452) */
+int  cabm_ledger_table(cabm_t* h, uint64_t* out, size_t n);
 int  cabm_cumulative_outcomes(cabm_t* h, uint64_t out[CABM_N_OUTCOMES]);
 int  cabm_work_counters(cabm_t* h, uint64_t out[CABM_N_WORK]);
 

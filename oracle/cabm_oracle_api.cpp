@@ -138,6 +138,12 @@ int cabm_oracle_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n) {
     for (size_t d = 0; d < n; ++d) out[d] = d < S.ledger[counter].size() ? S.ledger[counter][d] : 0;
     return CABM_OK;
 }
+int cabm_oracle_ledger_table(cabm_t* h, uint64_t* out, size_t n) {
+    H_OK(h); Sim& S = h->sim; if (!out) return CABM_E_ARG;
+    const size_t R = (size_t) S.par.run_length;
+    for (size_t i = 0; i < n; ++i) { const size_t c = i / R, d = i % R; out[i] = c < CABM_N_COUNTERS && d < S.ledger[c].size() ? S.ledger[c][d] : 0; }
+    return CABM_OK;
+}
 int cabm_oracle_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]) {
     H_OK(h); Sim& S = h->sim; int rc = ready(S, sim_day); if (rc) return rc;
     for (int c = 0; c < CABM_N_COUNTERS; ++c) out[c] = S.ledger[c][sim_day];

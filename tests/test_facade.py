@@ -1,0 +1,134 @@
+"""The C++ drop-in facade (covid-abm_b200/facade/): the reference's UNMODIFIED simulator.h running on the C ABI.
+
+facade_driver_{cuda,oracle} are built by `make -C covid-abm_b200/facade` from the reference's own simulator.h /
+Parameters / Utility / Vac_Campaign / behavior_tuner sources plus the proxies Community / Person / Location of this
+repository (needs /root/reference at BUILD time only; the binaries travel to the GPU box). The same host code links
+against the CUDA library and, prefix cabm_oracle_, against the CPU oracle:
+
+  CPU : host logic of the facade on the oracle backend (loaders, tables, lazy history mirror, campaign, diagnostics) and
+        coarse agreement of simulate_epidemic-through-the-facade with the unmodified reference;
+  GPU : simulate_epidemic through the facade gives byte-identical output on the CUDA library and on the oracle.
+"""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import covid_abm_b200 as cabm
+import synthpop
+import oracle_lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BUILD = os.path.join(ROOT, "covid-abm_b200", "facade", "_build")
+DRV_ORACLE = os.path.join(BUILD, "facade_driver_oracle")
+DRV_CUDA = os.path.join(BUILD, "facade_driver_cuda")
+MUT = ("2020-03-11", "2020-04-20", "2030-01-01")
+
+needs_oracle_driver = pytest.mark.skipif(not os.path.exists(DRV_ORACLE), reason="facade driver not built (make -C covid-abm_b200/facade needs /root/reference)")
+
+
+def _case(tmp, n=12000, days=90, seed=5, T=0.2, pde=3e-4):
+    pop = synthpop.generate(n, seed=4242)
+    P = cabm.params.default_params(run_length=days, seed=seed, T=T, prob_daily_exposure=pde, mutant_intro_dates=MUT)
+    tab = cabm.params.build_tables(P)
+    synthpop.write_reference_files(pop, str(tmp), "f")
+    return pop, P, tab
+
+
+def _run(driver, tmp, P, tab, seed, campaign, tag):
+    Pr = dict(P); Pr["seed"] = seed
+    pf = os.path.join(str(tmp), f"params_{tag}.txt"); cabm.params.write_text(Pr, tab, pf)
+    prefix = os.path.join(str(tmp), f"out_{tag}")
+    r = subprocess.run([driver, "sim", pf, str(tmp), "f", prefix, str(int(campaign))], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    led = np.genfromtxt(prefix + ".ledger.csv", delimiter=",", names=True)
+    return info, led, open(prefix + ".plot.csv").read(), open(prefix + ".ledger.csv").read(), r.stderr
+
+
+@needs_oracle_driver
+def test_bridge_tables_match_python_tables(tmp_path):
+    """params_bridge.cpp (C++ series for the gamma / binomial / negative-binomial / Poisson CDFs) vs params.py (scipy)."""
+    pop, P, tab = _case(tmp_path, n=2000, days=40)
+    pf = tmp_path / "p.txt"; cabm.params.write_text(P, tab, str(pf))
+    out = tmp_path / "tables.txt"
+    subprocess.check_call([DRV_ORACLE, "tables", str(pf), str(out)])
+    got = {l.split()[0]: np.array(l.split()[1:], dtype=np.float64) for l in open(out)}
+    for key in ("incub_cdf", "onset_cdf", "presev_cdf", "mild_cdf", "severe_only_cdf", "critical_cdf", "icu_death_cdf", "community_death_cdf",
+                "death_lag_cdf", "visit_cdf", "trace_ev_cdf"):
+        want = np.asarray(tab[key], dtype=np.float64).ravel()
+        assert got[key].shape == want.shape, key
+        np.testing.assert_allclose(got[key], want, rtol=0, atol=2e-13, err_msg=key)
+    np.testing.assert_allclose(got["p_high"], [tab["p_high_asym"], tab["p_high_sym"]], rtol=1e-15)
+    s, _keep = cabm.abi.pack_params(P, tab)
+    np.testing.assert_array_equal(got["haz_mult"], np.ctypeslib.as_array(s.haz_mult))
+    np.testing.assert_array_equal(got["VES"], np.ctypeslib.as_array(s.VES).ravel())
+    np.testing.assert_array_equal(got["VEH"], np.ctypeslib.as_array(s.VEH).ravel())
+    np.testing.assert_array_equal(got["prob_icu_death_comorbid"], np.ctypeslib.as_array(s.prob_icu_death)[1].astype(np.float64))
+    np.testing.assert_allclose(got["prob_first_detection"], np.asarray(P["prob_first_detection"]).ravel(), rtol=0, atol=1e-15)
+    np.testing.assert_allclose(got["icu_mortality_reduction"], np.asarray(P["icu_mortality_reduction"]), rtol=0, atol=1e-15)
+
+
+@needs_oracle_driver
+def test_simulate_epidemic_runs_through_the_facade(tmp_path):
+    pop, P, tab = _case(tmp_path)
+    info, led, plot, _, err = _run(DRV_ORACLE, tmp_path, P, tab, 5, campaign=True, tag="a")
+    n, days = int(pop["n_people"]), P["run_length"]
+    assert info["agents"] == n and info["days"] == days
+    assert len(plot.strip().splitlines()) == days + 1                      # header + one plot-log row per simulated day
+    assert "symptomatic infections, total infections" in err                # simulate_epidemic's own end-of-run summary ran
+    assert info["infections"] > 1000 and info["doses"] > 1000 and info["cumul_death"] > 0
+    # host mirror of the device's infection log: one Infection per ledger entry plus the ones made after the daily tally
+    assert info["infections"] >= led["inf"].sum() > 0.8 * info["infections"]
+    assert 0.8 * info["infections"] < info["secondary_links"] < info["infections"]      # every local infection is linked to its infector
+    assert np.array_equal(led["inf"], led["inf_wt"] + led["inf_alpha"] + led["inf_delta"] + led["inf_omicron"])
+    # the plot log carries coverage computed by the device reduction (calculate_vax_stats): monotone, reaching > 10 %
+    rows = [l.split(",") for l in plot.strip().splitlines()[1:]]
+    cov1 = np.array([float(r[25]) for r in rows])
+    assert np.all(np.diff(cov1) >= 0) and cov1[-1] > 0.1 and cov1[15] == 0.0
+    seroprev = np.array([float(r[28]) for r in rows])
+    assert seroprev[-1] > 0.02 and np.all((seroprev >= 0) & (seroprev <= 1))
+    # same seed, same output; another seed, another epidemic
+    info2, _, plot2, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 5, campaign=True, tag="b")
+    assert plot2 == plot
+    _, _, plot3, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 6, campaign=True, tag="c")
+    assert plot3 != plot
+
+
+@needs_oracle_driver
+@pytest.mark.skipif(not os.path.exists(oracle_lib.REF_DRIVER), reason="reference driver not built")
+def test_facade_agrees_with_unmodified_reference_coarsely(tmp_path):
+    """Same simulator.h, same population files, same Parameters: the reference's own classes vs the facade on the C ABI."""
+    pop, P, tab = _case(tmp_path, n=10000, days=100)
+    R = 12
+    tot_f, tot_r, dead_f, dead_r = [], [], [], []
+    for s in range(R):
+        _, led, _, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 100 + s, campaign=False, tag=f"s{s}")
+        tot_f.append(led["inf"].sum()); dead_f.append(led["dead"].sum())
+        Pr = dict(P); Pr["seed"] = 200 + s
+        pf = os.path.join(str(tmp_path), f"ref{s}.txt"); cabm.params.write_text(Pr, tab, pf)
+        out = os.path.join(str(tmp_path), f"ref{s}.csv")
+        subprocess.run([oracle_lib.REF_DRIVER, "run", pf, str(tmp_path), "f", out], check=True, capture_output=True)
+        a = np.genfromtxt(out, delimiter=",", names=True)
+        tot_r.append(a["inf"].sum()); dead_r.append(a["dead"].sum())
+    # ref_driver keeps the parameter file's social-distancing series while simulate_epidemic installs its own anchors
+    # (simulator.h:283-308), so only coarse agreement is asserted here; tools/ks_equivalence.py is the real comparison.
+    for f, r, name in ((tot_f, tot_r, "infections"), (dead_f, dead_r, "deaths")):
+        mf, mr = np.mean(f), np.mean(r)
+        assert mf > 0 and mr > 0 and 0.3 < mf / mr < 3.0, (name, mf, mr)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not (os.path.exists(DRV_CUDA) and os.path.exists(DRV_ORACLE)), reason="facade drivers not built")
+@pytest.mark.parametrize("campaign", [False, True])
+def test_facade_cuda_equals_facade_oracle(tmp_path, campaign):
+    pop, P, tab = _case(tmp_path, n=30000, days=120, T=0.2)
+    ic, _, plot_c, led_c, _ = _run(DRV_CUDA, tmp_path, P, tab, 9, campaign, tag="cuda")
+    io, _, plot_o, led_o, _ = _run(DRV_ORACLE, tmp_path, P, tab, 9, campaign, tag="oracle")
+    assert led_c == led_o, "ledger differs between the CUDA library and the oracle behind the same facade"
+    assert plot_c == plot_o, "simulate_epidemic's plot log differs"
+    for k in ("infections", "secondary_links", "doses", "cumul_death"):
+        assert ic[k] == io[k], k
+    assert ic["infections"] > 3000 and (ic["doses"] > 0) == campaign
