@@ -93,6 +93,7 @@ _PROTOS = {
     "dump_foi": [_vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)], "device_time_ms": [_vp, C.POINTER(d), C.POINTER(C.c_uint64)],
     "sync_histories_from": [_vp, C.c_size_t, _vp, C.c_size_t, C.POINTER(C.c_size_t)],
     "ledger_table": [_vp, C.POINTER(C.c_uint64), C.c_size_t],
+    "detected_today": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_size_t)],
     "diagnostics": [_vp, C.c_int, C.POINTER(C.c_uint64)], "serosurvey": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_uint64)],
 }
 _OPTIONAL = {

@@ -248,6 +248,15 @@ class Community:
     def getNumSymptomatic(self, day: int) -> int: return self.diagnostics(day)["symptomatic"]
     def getNumNaive(self) -> int: return self.diagnostics(max(self.day - 1, 0))["naive"]
 
+    def detected_today(self, day: int) -> np.ndarray:
+        """Primary cases of traceForwardContacts (Community.cpp:1062-1070) before the coverage draw, ascending ids."""
+        n = C.c_size_t(0)
+        self._check(self.fn.detected_today(self._h, int(day), None, 0, C.byref(n)))
+        out = np.zeros(n.value, dtype=np.uint32)
+        if n.value:
+            self._check(self.fn.detected_today(self._h, int(day), out.ctypes.data_as(C.POINTER(C.c_uint32)), n.value, C.byref(n)))
+        return out
+
     def infection_histories_from(self, first: int) -> np.ndarray:
         n = C.c_size_t(0)
         self._check(self.fn.sync_histories_from(self._h, int(first), None, 0, C.byref(n)))

@@ -33,7 +33,7 @@ struct cabm {
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
     uint64_t launches_per_day = 12;
-    unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr;
+    unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
 };
 
@@ -492,6 +492,25 @@ int cabm_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_
     const size_t avail = first < n ? (size_t) n - first : 0;
     if (out_n) *out_n = avail;
     if (out && cap && avail) CK(cudaMemcpy(out, h->d.log + first, std::min(cap, avail) * sizeof(cabm_infection), cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+
+int cabm_detected_today(cabm_t* h, int sim_day, uint32_t* out_pids, size_t cap, size_t* out_n) {
+    if (!h || !out_n) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    cudaSetDevice(h->device);
+    if (!h->d_det) { if ((rc = dalloc(h, &h->d_det, (size_t) h->d.N + 1))) return rc; }       // [0] = count, then ids
+    CK(cudaMemsetAsync(h->d_det, 0, sizeof(unsigned int), h->stream));
+    k_detected_today<<<grid_for(h, h->d.N, 8), TPB, 0, h->stream>>>(h->d, sim_day, h->d_det + 1, h->d.N, h->d_det);
+    unsigned int n = 0;
+    CK(cudaMemcpyAsync(&n, h->d_det, sizeof(n), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *out_n = n;
+    if (out_pids && cap && n) {
+        std::vector<unsigned int> ids(n);
+        CK(cudaMemcpy(ids.data(), h->d_det + 1, (size_t) n * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+        std::sort(ids.begin(), ids.end());
+        std::memcpy(out_pids, ids.data(), std::min<size_t>(cap, n) * sizeof(unsigned int));
+    }
     return CABM_OK;
 }
 

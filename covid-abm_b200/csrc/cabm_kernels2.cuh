@@ -420,6 +420,19 @@ __global__ void k_serosurvey(const Dev D, const int day, const unsigned int* pid
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(out, (unsigned long long) mine);
 }
 
+// primary cases of contact tracing (Community.cpp:1062-1070): alive, latest infection detected and reported today
+__global__ void k_detected_today(const Dev D, const int day, unsigned int* out, unsigned int cap, unsigned int* n_out) {
+    for (unsigned int base = blockIdx.x * blockDim.x; base < D.N; base += gridDim.x * blockDim.x) {
+        const unsigned int p = base + threadIdx.x;
+        bool hit = false;
+        if (p < D.N && D.imm[p]) {
+            const Tl1 b = D.tl1[p];
+            hit = b.detected < CABM_N_OUTCOMES && b.report_day == day && !(b.death <= day);
+        }
+        if (hit) { const unsigned int i = list_reserve(n_out); if (i < cap) out[i] = p; }
+    }
+}
+
 __global__ void k_init_state(const Dev D) {
     const unsigned int stride = gridDim.x * blockDim.x;
     for (unsigned int p = blockIdx.x * blockDim.x + threadIdx.x; p < D.N; p += stride) {

@@ -31,6 +31,7 @@ CABM_DECL(int, tick, cabm_t*, int, int, int); CABM_DECL(int, infect, cabm_t*, ui
 CABM_DECL(int, vaccinate, cabm_t*, int, const uint32_t*, size_t, uint8_t*); CABM_DECL(int, quarantine, cabm_t*, const uint32_t*, size_t, int, int);
 CABM_DECL(int, ledger_table, cabm_t*, uint64_t*, size_t); CABM_DECL(int, cumulative_outcomes, cabm_t*, uint64_t*);
 CABM_DECL(int, sync_histories_from, cabm_t*, size_t, cabm_infection*, size_t, size_t*);
+CABM_DECL(int, detected_today, cabm_t*, int, uint32_t*, size_t, size_t*);
 CABM_DECL(int, diagnostics, cabm_t*, int, uint64_t*); CABM_DECL(int, serosurvey, cabm_t*, int, const uint32_t*, size_t, uint64_t*);
 CABM_DECL(int, snapshot, cabm_t*, cabm_snap_t**); CABM_DECL(int, restore, cabm_t*, const cabm_snap_t*); CABM_DECL(int, snap_free, cabm_snap_t*);
 }
@@ -52,7 +53,7 @@ Community* Person::_community = nullptr;
 // ---------------------------------------------------------------------------------------------------------------------
 Community::Community(const Parameters* parameters, Date* date)
     : _date(date), _day(0), cmty_ledger(nullptr), vac_campaign(nullptr), _h(nullptr), _uploaded(false), _ti_dirty(true), _epoch(1),
-      _ledger_epoch(0), _diag_epoch(0), _diag_day(-1), _log_read(0), _warned_tracing(false) {
+      _ledger_epoch(0), _diag_epoch(0), _diag_day(-1), _log_read(0) {
     _par = parameters;
     cmty_ledger = new CommunityLedger(parameters);
     cmty_ledger->_owner = this;
@@ -306,16 +307,65 @@ void Community::tick() {
     if (rc != 0) fail("cabm_tick", rc);
     device_changed();
 
-    // contact tracing (Community.cpp:1054-1145) is not part of the device path yet: nobody is traced
-    vector<set<Person*, PerPtrComp>> tracedContactsByDepth(_par->contactTracingDepth);
-    if (_day >= _par->beginContactTracing and not _warned_tracing) {
-        cerr << "WARNING: contact tracing is not implemented by the CUDA path; traced sets stay empty" << endl;
-        _warned_tracing = true;
-    }
+    // contact tracing to the configured depth from today's reported cases, then reactive scheduling and the day's doses
+    vector<set<Person*, PerPtrComp>> tracedContactsByDepth = traceForwardContacts();
     if (vac_campaign) {
         vac_campaign->reactive_strategy(_day, tracedContactsByDepth, this);
         vaccinate();
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// contact tracing: Community::traceForwardContacts (Community.cpp:1054-1145). The primary cases come from the device
+// (cabm_detected_today: alive, latest infection reported today, ascending ids -- the order in which the reference walks
+// _people and consumes RNG); the depth-limited search over household / neighbours / day location is the reference's
+// sequential logic on the static proxies; quarantines are written through (Person::scheduleQuarantine -> cabm_quarantine).
+// Difference: a hospital's roster here holds its staff only (admitted patients are device state), so the day-location
+// contacts of hospital staff are drawn among staff.
+// ---------------------------------------------------------------------------------------------------------------------
+static void insert_new_living(set<Person*, PerPtrComp>& into, const vector<Person*>& from, set<Person*, PerPtrComp>& seen, int day) {
+    for (Person* p : from) if (p->isAlive(day) and seen.insert(p).second) into.insert(p);
+}
+
+vector<set<Person*, PerPtrComp>> Community::traceForwardContacts() {
+    vector<set<Person*, PerPtrComp>> traced(_par->contactTracingDepth + 1);
+    if (_day < _par->beginContactTracing) return traced;
+    size_t n = 0;
+    int rc = CABM_FN(detected_today)(handle(), _day, nullptr, 0, &n);
+    if (rc != 0) fail("cabm_detected_today", rc);
+    vector<uint32_t> ids(n);
+    if (n) { rc = CABM_FN(detected_today)(_h, _day, ids.data(), n, &n); if (rc != 0) fail("cabm_detected_today", rc); }
+    set<Person*, PerPtrComp> cases;
+    for (uint32_t id : ids) if (gsl_rng_uniform(RNG) < _par->contactTracingCoverage) cases.insert(_people[id]);
+    traced[0] = cases;
+
+    set<Person*, PerPtrComp> all_traced, all_interviewed;
+    auto pick = [&](vector<Person*> pool, LocationType ev_of) {                  // Poisson(EV) contacts recalled out of `pool`
+        const size_t k = gsl_ran_poisson(RNG, _par->contactTracingEV[ev_of]);
+        return k <= pool.size() ? covid::util::choose_k(RNG, pool, k) : pool;
+    };
+    for (size_t depth = 0; depth < _par->contactTracingDepth; ++depth) {
+        const set<Person*, PerPtrComp> interview = depth == 0 ? cases : traced[depth];
+        for (Person* p : interview) {
+            if (not (p->isAlive(_day) and all_interviewed.insert(p).second)) continue;
+            Location* home = p->getHomeLoc();
+            if (home->getType() == NURSINGHOME) {
+                insert_new_living(traced[depth + 1], pick(home->getPeople(), NURSINGHOME), all_traced, _day);
+            } else {
+                insert_new_living(traced[depth + 1], home->getPeople(), all_traced, _day);
+                vector<Person*> neighbours;
+                for (Location* nb : home->neighbors()) for (Person* q : nb->people()) neighbours.push_back(q);
+                insert_new_living(traced[depth + 1], pick(neighbours, HOUSE), all_traced, _day);
+                vector<Person*> day_contacts;
+                if (p->getDayLoc()) day_contacts = pick(p->getDayLoc()->getPeople(), p->getDayLoc()->getType());
+                insert_new_living(traced[depth + 1], day_contacts, all_traced, _day);
+            }
+        }
+    }
+    for (size_t depth = 0; depth < traced.size(); ++depth)
+        for (Person* p : traced[depth])
+            if (not p->isQuarantining(_day) and gsl_rng_uniform(RNG) < _par->quarantineProbability[depth]) p->scheduleQuarantine(_day, _par->quarantineDuration);
+    return traced;
 }
 
 Infection* Community::infect(int id, StrainType strain) {                        // Community.cpp:550-553

@@ -57,6 +57,7 @@ class Community {
     Infection* infect(int id, StrainType strain);
     void tick();                                          // Community.cpp:1147-1192 -> cabm_tick + host-side campaign
     void vaccinate();                                     // Community.cpp:556-629, on the reference's own Vac_Campaign
+    std::vector<std::set<Person*, PerPtrComp>> traceForwardContacts();   // Community.cpp:1054-1145, primary cases from the device
     double social_distancing(int day);
 
     // daily diagnostics of the caller, served by one device reduction per (day, state) (cabm_diagnostics)
@@ -148,6 +149,5 @@ class Community {
     std::vector<unsigned long long> _ledger_cache, _diag_cache;
     size_t _log_read;                                     // records of the device infection log already mirrored
     std::vector<unsigned int> _pending_doses;
-    bool _warned_tracing;
 };
 #endif

@@ -9,8 +9,8 @@
 //   facade_driver sim <params.txt> <pop_dir> <tag> <out_prefix> [campaign]
 //       writes <out_prefix>.plot.csv (simulate_epidemic's plot log) and <out_prefix>.ledger.csv (same columns as
 //       oracle/ref_driver run) and prints one JSON line with wall-clock timings.
-//   `campaign` = 1 attaches a simple age-prioritised Vac_Campaign (the reference's class) so that Community::vaccinate
-//       and the dose bookkeeping run.
+//   `campaign` = 1 attaches a general Vac_Campaign (the reference's class) so that Community::vaccinate and the dose
+//       bookkeeping run; 2 adds ring vaccination of traced contacts (needs begin_contact_tracing < run_length in the file).
 #include <chrono>
 #include "simulator.h"
 #include "kv_parameters.h"
@@ -18,7 +18,7 @@
 using namespace std;
 using namespace cabm_kv;
 
-static Vac_Campaign* simple_campaign(const Parameters* par, Community* community, int first_day, int doses_per_day) {
+static Vac_Campaign* simple_campaign(Parameters* par, Community* community, int first_day, int doses_per_day, bool ring) {
     // the call sequence of generateVac_Campaign / parseVaccineFile (exp/active-vac/main.cpp:327-460,655-706) with a synthetic,
     // un-pooled standard allocation: `doses_per_day` first doses per day for adults from `first_day` on, boosters as they fall due
     Vac_Campaign* vc = new Vac_Campaign(par);
@@ -28,14 +28,21 @@ static Vac_Campaign* simple_campaign(const Parameters* par, Community* community
     Dose_Vals std_doses(par->runLength, vector<map<int, int>>(par->numVaccineDoses)), urg_doses(par->runLength, vector<map<int, int>>(par->numVaccineDoses));
     for (int d = 0; d < (int) par->runLength; ++d) for (int dose = 0; dose < par->numVaccineDoses; ++dose) for (int bin : vc->get_unique_age_bins()) {
         std_doses[d][dose][bin] = (d >= first_day and bin >= 18) ? doses_per_day : 0;
-        urg_doses[d][dose][bin] = 0;
+        urg_doses[d][dose][bin] = (ring and d >= par->beginContactTracing and dose == 0) ? doses_per_day : 0;
     }
     vc->set_pool_urg_doses(false); vc->set_pool_std_doses(false); vc->set_pool_all_doses(false);
     vc->init_doses_available(urg_doses, std_doses);
     vc->init_eligibility_queue(community);
     vc->set_prioritize_first_doses(false);
     vc->set_flexible_queue_allocation(false);
-    vc->set_reactive_vac_strategy(NO_CAMPAIGN);
+    if (ring) {                                                                           // exp/active-vac/main.cpp:609,658-674
+        par->urgent_vax_dose_threshold = 1;
+        vc->set_reactive_vac_strategy(RING_VACCINATION);
+        vc->set_start_of_campaign(RING_VACCINATION, par->beginContactTracing);
+        vc->set_end_of_campaign(RING_VACCINATION, par->runLength);
+    } else {
+        vc->set_reactive_vac_strategy(NO_CAMPAIGN);
+    }
     vc->set_min_age(vector<int>(par->runLength, 5));
     vc->set_end_of_campaign(GENERAL_CAMPAIGN, par->runLength);
     return vc;
@@ -71,13 +78,13 @@ int main(int argc, char** argv) {
     Parameters* par = make_parameters(kv);
     set_pop_files(par, argv[3], argv[4]);
     const string prefix = argv[5];
-    const bool campaign = argc > 6 and atoi(argv[6]) != 0;
+    const int campaign = argc > 6 ? atoi(argv[6]) : 0;                                  // 0 none, 1 general campaign, 2 + ring vaccination of traced contacts
     gsl_rng_set(RNG, par->randomseed); gsl_rng_set(VAX_RNG, par->randomseed); gsl_rng_set(REPORTING_RNG, par->randomseed);   // main.cpp:536-538
 
     auto t0 = chrono::steady_clock::now();
     Community* community = build_community(par);                                       // simulator.h:63-91
     const double load_s = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
-    if (campaign) community->setVac_Campaign(simple_campaign(par, community, 20, max<int>(1, (int) community->getNumPeople() / 200)));
+    if (campaign) community->setVac_Campaign(simple_campaign(par, community, 20, max<int>(1, (int) community->getNumPeople() / 200), campaign == 2));
     const size_t n = community->getNumPeople();
     const vector<string> mid = kv.count("mutant_intro_dates") ? kv.at("mutant_intro_dates") : vector<string>();
 
@@ -100,14 +107,17 @@ int main(int argc, char** argv) {
     for (size_t d = 0; d < par->runLength; ++d) { out << d; for (const auto& c : cols) out << ',' << c[d]; out << '\n'; }
     out.close();
 
-    size_t n_hist = 0, n_vax = 0, n_secondary = 0;
+    size_t n_hist = 0, n_vax = 0, n_secondary = 0, urg = 0;
+    if (community->getVac_Campaign()) for (size_t d = 0; d < par->runLength; ++d) urg += community->getVac_Campaign()->get_doses_used(d, URGENT_ALLOCATION);
+    double quar_days = 0.0;
+    for (size_t d = 0; d < par->runLength; d += 5) quar_days += community->getNumPeopleQuarantining(d);
     for (Person* p : community->getPeople()) {
         n_hist += p->getNumNaturalInfections(); n_vax += p->getNumVaccinations();
         for (Infection* inf : p->getInfectionHistory()) n_secondary += inf->secondary_infection_tally();
     }
     printf("{\"impl\": \"facade\", \"agents\": %zu, \"days\": %zu, \"load_s\": %.3f, \"simulate_epidemic_s\": %.4f, \"agent_days_per_s\": %.6g, "
-           "\"infections\": %zu, \"secondary_links\": %zu, \"doses\": %zu, \"cumul_death\": %zu}\n",
-           n, (size_t) par->runLength, load_s, sim_s, (double) n * par->runLength / sim_s, n_hist, n_secondary, n_vax,
+           "\"infections\": %zu, \"secondary_links\": %zu, \"doses\": %zu, \"urgent_doses\": %zu, \"quarantine_index\": %.6f, \"cumul_death\": %zu}\n",
+           n, (size_t) par->runLength, load_s, sim_s, (double) n * par->runLength / sim_s, n_hist, n_secondary, n_vax, urg, quar_days,
            community->getCumulIncidenceByOutcome(DEATH));
     delete community;
     return 0;

@@ -274,6 +274,11 @@ int  cabm_snap_free(cabm_snap_t* s);
 
 /* parity hook: hazards of the most recent tick */
 int  cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n);
+/* the primary cases of traceForwardContacts (Community.cpp:1062-1070): living people whose latest infection is reported on
+   sim_day, ascending ids (the reference walks _people in id order). The depth-limited contact search itself is sequential
+   host logic over the static household / neighbour / day-location graph and stays with the caller. */
+int  cabm_detected_today(cabm_t* h, int sim_day, uint32_t* out_pids, size_t cap, size_t* out_n);
+
 /* caller-side daily diagnostics as device reductions: calculate_vax_stats (Community.cpp:1329-1423), doSerosurvey (:1224-1274),
    getNumPeopleQuarantining (Community.h:437), getNumInfected/Infectious/Symptomatic/Naive (Community.cpp:1196-1222) */
 int  cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]);

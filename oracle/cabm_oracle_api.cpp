@@ -181,6 +181,21 @@ static bool oracle_sero_positive(const Sim& S, uint32_t pid, int day) {
     return tsl < S.nat_dur[pid];
 }
 
+// primary cases of traceForwardContacts (Community.cpp:1062-1070) before the coverage draw
+int cabm_oracle_detected_today(cabm_t* h, int sim_day, uint32_t* out_pids, size_t cap, size_t* out_n) {
+    H_OK(h); Sim& S = h->sim; if (!out_n) return CABM_E_ARG;
+    size_t n = 0;
+    for (uint32_t pid = 0; pid < S.n_people; ++pid) {
+        const cabm_oracle::Person& p = S.people[pid];
+        if (p.hist.empty()) continue;
+        const cabm_oracle::Infection& inf = p.hist.back();
+        if (inf.isDead(sim_day)) continue;
+        if (inf.detected_state < CABM_N_OUTCOMES && inf.report_day == sim_day) { if (out_pids && n < cap) out_pids[n] = pid; ++n; }
+    }
+    *out_n = n;
+    return CABM_OK;
+}
+
 // calculate_vax_stats (Community.cpp:1329-1423) and the per-day population counts of simulator.h:402-410,438
 int cabm_oracle_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]) {
     H_OK(h); Sim& S = h->sim; if (!out) return CABM_E_ARG;

@@ -29,9 +29,11 @@ MUT = ("2020-03-11", "2020-04-20", "2030-01-01")
 needs_oracle_driver = pytest.mark.skipif(not os.path.exists(DRV_ORACLE), reason="facade driver not built (make -C covid-abm_b200/facade needs /root/reference)")
 
 
-def _case(tmp, n=12000, days=90, seed=5, T=0.2, pde=3e-4):
+def _case(tmp, n=12000, days=90, seed=5, T=0.2, pde=3e-4, tracing_from=None):
     pop = synthpop.generate(n, seed=4242)
     P = cabm.params.default_params(run_length=days, seed=seed, T=T, prob_daily_exposure=pde, mutant_intro_dates=MUT)
+    if tracing_from is not None:                         # exp/active-vac/main.cpp:101-111,711: tracing + self-quarantine of traced contacts
+        P["begin_contact_tracing"] = tracing_from; P["quarantine_probability"] = [0.9, 0.75, 0.5]
     tab = cabm.params.build_tables(P)
     synthpop.write_reference_files(pop, str(tmp), "f")
     return pop, P, tab
@@ -98,6 +100,24 @@ def test_simulate_epidemic_runs_through_the_facade(tmp_path):
 
 
 @needs_oracle_driver
+def test_contact_tracing_and_ring_vaccination_through_the_facade(tmp_path):
+    """traceForwardContacts (Community.cpp:1054-1145) on the proxies with device-supplied primary cases, quarantines written
+    through, and the reference's own Vac_Campaign::ring_scheduling (Vac_Campaign.cpp:24-48) turning traced sets into urgent doses."""
+    pop, P, tab = _case(tmp_path, tracing_from=30)
+    info, led, plot, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 5, campaign=2, tag="ring")
+    base, _, plot0, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 5, campaign=1, tag="noring")
+    assert info["urgent_doses"] > 100 and base["urgent_doses"] == 0
+    assert info["quarantine_index"] > 0 and base["quarantine_index"] > 0          # tracing quarantines in both (it is a Parameters setting)
+    rows = [l.split(",") for l in plot.strip().splitlines()[1:]]
+    urg = np.array([float(r[24]) for r in rows])                                    # urg_doses per 10k in simulate_epidemic's plot log
+    assert urg[:30].sum() == 0 and urg[30:].sum() > 0
+    # without tracing nobody quarantines
+    pop2, P2, tab2 = _case(tmp_path)
+    none, _, _, _, _ = _run(DRV_ORACLE, tmp_path, P2, tab2, 5, campaign=1, tag="notrace")
+    assert none["quarantine_index"] == 0.0
+
+
+@needs_oracle_driver
 @pytest.mark.skipif(not os.path.exists(oracle_lib.REF_DRIVER), reason="reference driver not built")
 def test_facade_agrees_with_unmodified_reference_coarsely(tmp_path):
     """Same simulator.h, same population files, same Parameters: the reference's own classes vs the facade on the C ABI."""
@@ -122,13 +142,13 @@ def test_facade_agrees_with_unmodified_reference_coarsely(tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.skipif(not (os.path.exists(DRV_CUDA) and os.path.exists(DRV_ORACLE)), reason="facade drivers not built")
-@pytest.mark.parametrize("campaign", [False, True])
+@pytest.mark.parametrize("campaign", [0, 1, 2])
 def test_facade_cuda_equals_facade_oracle(tmp_path, campaign):
-    pop, P, tab = _case(tmp_path, n=30000, days=120, T=0.2)
+    pop, P, tab = _case(tmp_path, n=30000, days=120, T=0.2, tracing_from=40 if campaign == 2 else None)
     ic, _, plot_c, led_c, _ = _run(DRV_CUDA, tmp_path, P, tab, 9, campaign, tag="cuda")
     io, _, plot_o, led_o, _ = _run(DRV_ORACLE, tmp_path, P, tab, 9, campaign, tag="oracle")
     assert led_c == led_o, "ledger differs between the CUDA library and the oracle behind the same facade"
     assert plot_c == plot_o, "simulate_epidemic's plot log differs"
-    for k in ("infections", "secondary_links", "doses", "cumul_death"):
+    for k in ("infections", "secondary_links", "doses", "urgent_doses", "quarantine_index", "cumul_death"):
         assert ic[k] == io[k], k
-    assert ic["infections"] > 3000 and (ic["doses"] > 0) == campaign
+    assert ic["infections"] > 3000 and (ic["doses"] > 0) == (campaign > 0) and (ic["urgent_doses"] > 0) == (campaign == 2)

@@ -100,9 +100,11 @@ def test_multi_variant_vaccination_quarantine():
         if d % 7 == 3 or d in (10, 31, 52, 74):   # caller-side daily diagnostics as device reductions (cabm_diagnostics / cabm_serosurvey)
             dg, do = g.diagnostics(d), o.diagnostics(d)
             assert dg == do, f"day {d}: {[(k, dg[k], do[k]) for k in dg if dg[k] != do[k]]}"
+            assert np.array_equal(g.detected_today(d), o.detected_today(d))
             some = rng.choice(n, size=n // 4, replace=False)
             assert g.doSerosurvey(some, d) == o.doSerosurvey(some, d) and g.doSerosurvey(None, d) == o.doSerosurvey(None, d)
     assert_same_state(g, o, "end")
+    assert sum(g.detected_today(d).size for d in range(40, 75)) > 20
     dg = g.diagnostics(74)
     assert dg["fully_vaxd"] > 0 and dg["seropos_all"] > 0 and dg["quarantining"] == 0 and dg["bt_inf"] + dg["uv_inf"] > 0
     hg, ho = g.infection_histories(), o.infection_histories()
