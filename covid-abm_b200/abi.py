@@ -21,6 +21,7 @@ N_COUNTERS = len(COUNTERS)
 DIAG = ["dose_1", "dose_2", "dose_3", "fully_vaxd", "bt_inf", "bt_dis", "bt_hosp", "bt_death", "bt_reported", "uv_inf", "uv_dis", "uv_hosp",
         "uv_death", "uv_reported", "infected", "infectious", "symptomatic", "naive", "quarantining", "seropos_all", "seropos_ped", "n_ped"]
 N_DIAG = 24
+SHARD_FLAG_BYTES = 24
 WORK = ["agents", "active", "flags", "patrons", "visits", "hot_visits", "hot_locs", "nbr_edges", "trials", "infections"]
 N_WORK = len(WORK)
 
@@ -94,6 +95,10 @@ _PROTOS = {
     "sync_histories_from": [_vp, C.c_size_t, _vp, C.c_size_t, C.POINTER(C.c_size_t)],
     "ledger_table": [_vp, C.POINTER(C.c_uint64), C.c_size_t],
     "detected_today": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_size_t)],
+    "shard_config": [_vp, C.c_int, C.c_int, C.c_uint32, C.c_uint32],
+    "shard_day_part": [_vp, C.c_int, C.c_int, C.c_int, C.c_int, d, C.POINTER(d), C.POINTER(i32)],
+    "shard_flags_out": [_vp, C.POINTER(_vp), C.POINTER(C.c_size_t)], "shard_flags_in": [_vp, _vp, C.c_size_t],
+    "shard_census": [_vp, C.POINTER(_vp), C.POINTER(C.c_size_t)], "shard_patients": [_vp, C.POINTER(_vp), C.POINTER(C.c_size_t)],
     "diagnostics": [_vp, C.c_int, C.POINTER(C.c_uint64)], "serosurvey": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_uint64)],
 }
 _OPTIONAL = {

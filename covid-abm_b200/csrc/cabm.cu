@@ -22,6 +22,7 @@ struct cabm {
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     double acc_ms = 0.0; uint64_t launches = 0;
     int device = 0, sms = 148;
+    int gm[9] = { 8, 8, 8, 4, 8, 1, 2, 2, 4 };   // blocks per SM: active, hazard, trials, gate0, apply+status, hosp+import, gate1, apply1, end (CABM_GRID_MULT overrides: development knob)
     bool have_par = false, have_pop = false;
     cabm_params hpar{};                       // host copy (pointers nulled)
     std::vector<double> h_ti[3];
@@ -32,8 +33,9 @@ struct cabm {
     cudaGraphExec_t day_graph = nullptr;
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
-    uint64_t launches_per_day = 12;
+    uint64_t launches_per_day = 11;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
+    int* d_hosp_ids = nullptr; int* d_pat_save = nullptr; int* d_pat_buf = nullptr; unsigned int n_hosp = 0; unsigned int n_flags_own = 0;   // sharding
     int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
 };
 
@@ -103,7 +105,7 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
 enum { KID_SCAN = 0, KID_ACTIVE, KID_VISIT, KID_HAZARD, KID_TRIALS, KID_GATE0, KID_APPLY_STATUS, KID_HOSP_IMPORT, KID_GATE1, KID_APPLY1,
        KID_END, KID_SMALL, KID_N };
 static const char* const KID_NAMES[KID_N] = { "k_scan", "k_active", "k_visit", "k_hazard", "k_trials", "k_gate(phase0)", "k_apply_status",
-    "k_hosp_import", "k_gate(phase1)", "k_apply(phase1)", "k_end", "k_day_end" };
+    "k_hosp_import", "k_gate(phase1)", "k_apply(phase1)", "k_end", "(unused)" };
 
 // LAUNCH records an event in front of every kernel when per-kernel profiling is on (stream path only, never under graph capture)
 #define LAUNCH(id, ...) do { if (h->profile) prof_mark(h, id); __VA_ARGS__; h->launches++; } while (0)
@@ -128,19 +130,18 @@ static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     const unsigned int gScan = (unsigned int) ((D.N + TPB * 4 - 1) / (TPB * 4)), gSM = h->sms;
     if (tick) {
         LAUNCH(KID_SCAN, k_scan<<<gScan, TPB, 0, st>>>(D));
-        LAUNCH(KID_ACTIVE, k_active<<<gSM * 8, TPB, 0, st>>>(D));
+        LAUNCH(KID_ACTIVE, k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D));
         LAUNCH(KID_VISIT, k_visit<<<std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), gSM * 4), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words));
-        LAUNCH(KID_HAZARD, k_hazard<<<gSM * 8, TPB, 0, st>>>(D));
-        LAUNCH(KID_TRIALS, k_trials<<<gSM * 8, TPB, 0, st>>>(D));
-        LAUNCH(KID_GATE0, k_gate<<<gSM * 4, 128, 0, st>>>(D, 0));
-        LAUNCH(KID_APPLY_STATUS, k_apply_status<<<gSM * 8, 128, 0, st>>>(D, 0, 1));
+        LAUNCH(KID_HAZARD, k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D));
+        LAUNCH(KID_TRIALS, k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D));
+        LAUNCH(KID_GATE0, k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D, 0));
+        LAUNCH(KID_APPLY_STATUS, k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 1));
     }
-    LAUNCH(KID_HOSP_IMPORT, k_hosp_import<<<gSM, TPB, 0, st>>>(D, tick ? 1 : 0, import ? 1 : 0));
-    LAUNCH(KID_GATE1, k_gate<<<gSM * 2, 128, 0, st>>>(D, 1));
-    LAUNCH(KID_APPLY1, k_apply_status<<<gSM * 2, 128, 0, st>>>(D, 1, 0));
+    LAUNCH(KID_HOSP_IMPORT, k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, tick ? 1 : 0, import ? 1 : 0));
+    LAUNCH(KID_GATE1, k_gate<<<gSM * h->gm[6], 128, 0, st>>>(D, 1));
+    LAUNCH(KID_APPLY1, k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0));
     if (!tick && h->d_out_new) cudaMemcpyAsync(h->d_out_new, &D.ctr->n_new[1], sizeof(unsigned int), cudaMemcpyDeviceToDevice, st);
-    LAUNCH(KID_END, k_end<<<gSM * 4, TPB, 0, st>>>(D, tick ? 1 : 0));
-    LAUNCH(KID_SMALL, k_day_end<<<1, 32, 0, st>>>(D, tick ? 1 : 0, advance));
+    LAUNCH(KID_END, k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, tick ? 1 : 0, advance));
     if (h->profile) prof_mark(h, -1);
 }
 
@@ -176,6 +177,7 @@ int cabm_create(cabm_t** out) {
     h->sms = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
     cudaEventCreate(&h->e0); cudaEventCreate(&h->e1);
+    if (const char* e = getenv("CABM_GRID_MULT")) { int k = 0; for (const char* q = e; *q && k < 9; ++k) { h->gm[k] = std::max(1, atoi(q)); while (*q && *q != ',') ++q; if (*q == ',') ++q; } }
     *out = h;
     return CABM_OK;
 }
@@ -248,6 +250,7 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     cudaSetDevice(h->device);
     const uint32_t N = pop->n_people, L = pop->n_loc, NP = pop->n_patron;
     Dev& D = h->d; D.N = N; D.L = L; D.n_patron = std::max<uint32_t>(NP, 1);
+    D.own_lo = 0; D.own_hi = N; D.shard_rank = 0;
     int rc;
     // ---- static agents ----
     std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N), patron((size_t) N * PATRON_ROW, 0);
@@ -295,6 +298,13 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = upload(h, (float**) &D.loc_risk, lrisk)) || (rc = upload(h, (int**) &D.loc_hospital, lhosp)) ||
         (rc = upload(h, (unsigned int**) &D.roster_off, roff)) || (rc = upload(h, (unsigned int**) &D.nbr_off, noff)) ||
         (rc = upload(h, (int**) &D.roster, roster)) || (rc = upload(h, (int**) &D.nbr, nbr))) return rc;
+    {   // hospitals, for the census exchange of a sharded community (cabm_shard_patients)
+        std::vector<int> hosp_ids;
+        for (uint32_t l = 0; l < L; ++l) if (ltype[l] == CABM_HOSPITAL) hosp_ids.push_back((int) l);
+        h->n_hosp = (unsigned int) hosp_ids.size();
+        if (hosp_ids.empty()) hosp_ids.push_back(0);
+        if ((rc = upload(h, &h->d_hosp_ids, hosp_ids)) || (rc = dalloc(h, &h->d_pat_save, hosp_ids.size())) || (rc = dalloc(h, &h->d_pat_buf, hosp_ids.size()))) return rc;
+    }
     // ---- dynamic state ----
     const size_t Q1 = std::max<size_t>(D.Q, 1);
     if ((rc = dalloc(h, &D.win, (size_t) N + 4, true)) || (rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
@@ -492,6 +502,92 @@ int cabm_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_
     const size_t avail = first < n ? (size_t) n - first : 0;
     if (out_n) *out_n = avail;
     if (out && cap && avail) CK(cudaMemcpy(out, h->d.log + first, std::min(cap, avail) * sizeof(cabm_infection), cudaMemcpyDeviceToHost));
+    return CABM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// One community over several handles; see include/cabm.h for the protocol.
+// ---------------------------------------------------------------------------------------------
+int cabm_shard_config(cabm_t* h, int rank, int world, uint32_t pid_lo, uint32_t pid_hi) {
+    if (!h || !h->have_pop || world < 1 || rank < 0 || rank >= world || pid_lo > pid_hi || pid_hi > h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    h->d.own_lo = pid_lo; h->d.own_hi = pid_hi; h->d.shard_rank = rank;
+    if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; }      // the captured graph carries the old range
+    return CABM_OK;
+}
+
+int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is_weekday, double expected_imports,
+                        const double* strain_w, int32_t* out_imported) {
+    if (!h || part < 0 || part > 3 || julian_day < 1 || julian_day > 366) return CABM_E_ARG;
+    int rc = ready(h, sim_day); if (rc) return rc;
+    cudaSetDevice(h->device);
+    const Dev& D = h->d; cudaStream_t st = h->stream; const unsigned int gSM = h->sms;
+    DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
+    fill_ctx(h, c, sim_day, julian_day, is_weekday);
+    CK(cudaEventRecord(h->e0, st));
+    if (part == 0) {
+        CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), st));
+        const unsigned int gScan = (unsigned int) ((D.N + TPB * 4 - 1) / (TPB * 4));
+        k_scan<<<gScan, TPB, 0, st>>>(D);
+        k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D);
+        CK(cudaMemcpyAsync(&h->n_flags_own, &D.ctr->n_flags, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+        h->launches += 2;
+    } else if (part == 1) {
+        k_visit<<<std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), gSM * 4), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
+        h->launches += 1;
+    } else if (part == 2) {
+        if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
+        k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D);
+        k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D);
+        k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D, 0);
+        k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 1);
+        if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 1);
+        h->launches += 6;
+    } else {
+        c.n_imports = (strain_w && expected_imports > 0) ? import_count(h->hpar.seed, sim_day, expected_imports) : 0;
+        if (strain_w) for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
+        CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, st));
+        if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 2);
+        k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, 1, strain_w ? 1 : 0);
+        k_gate<<<gSM * h->gm[6], 128, 0, st>>>(D, 1);
+        k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0);
+        if (h->d_out_new) CK(cudaMemcpyAsync(h->d_out_new, &D.ctr->n_new[1], sizeof(unsigned int), cudaMemcpyDeviceToDevice, st));
+        k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, 1, 0);
+        h->launches += 5;
+    }
+    int32_t n_new = 0;
+    if (part == 3 && h->d_out_new) CK(cudaMemcpyAsync(&n_new, h->d_out_new, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    if ((rc = timed_sync(h))) return rc;
+    if (part == 3 && out_imported) *out_imported = n_new;       // new infections of the hospital pass and the importation on this handle
+    return part == 3 ? check_overflow(h) : CABM_OK;
+}
+
+int cabm_shard_flags_out(cabm_t* h, void** records, size_t* n) {
+    if (!h || !records || !n || !h->have_pop) return CABM_E_ARG;
+    *records = h->d.flags_raw; *n = std::min<size_t>(h->n_flags_own, h->d.cap_flags);
+    return CABM_OK;
+}
+
+int cabm_shard_flags_in(cabm_t* h, const void* records, size_t n) {
+    if (!h || !h->have_pop || (!records && n)) return CABM_E_ARG;
+    if (n == 0) return CABM_OK;
+    cudaSetDevice(h->device);
+    k_flags_in<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, (const FlagRaw*) records, (unsigned int) n);
+    h->launches += 1;
+    CK(cudaStreamSynchronize(h->stream));                        // the caller may reuse `records` after return
+    return CABM_OK;
+}
+
+int cabm_shard_census(cabm_t* h, void** buf, size_t* n_u32) {
+    if (!h || !buf || !n_u32 || !h->have_pop) return CABM_E_ARG;
+    *buf = h->d.nvis; *n_u32 = h->d.Q;
+    return CABM_OK;
+}
+
+int cabm_shard_patients(cabm_t* h, void** buf, size_t* n_i32) {
+    if (!h || !buf || !n_i32 || !h->have_pop) return CABM_E_ARG;
+    *buf = h->d_pat_buf; *n_i32 = h->n_hosp;
     return CABM_OK;
 }
 

@@ -45,7 +45,7 @@ struct DayCtx {                     // per-day scalars, staged by the host for e
 
 // counters living in device memory
 struct Counters {
-    // ---- day-scoped: zeroed by k_day_end ----
+    // ---- day-scoped: zeroed by the last block of k_end ----
     unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;
     unsigned int n_hits[2], n_new[2];                        // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
     unsigned int day_pad[4];
@@ -54,6 +54,7 @@ struct Counters {
     unsigned int overflow;                                   // sticky: a list ran out of capacity
     unsigned int day_idx;                                    // index into the staged DayCtx array
     unsigned int seed_calls;
+    unsigned int end_ticket;                                 // blocks of k_end that have finished (the last one closes the day)
     unsigned long long n_log;
     unsigned long long work[CABM_N_WORK];
     unsigned long long cumul[CABM_N_OUTCOMES];
@@ -63,6 +64,8 @@ struct Counters {
 struct Dev {
     // sizes
     unsigned int N, L, Q, n_patron; int R;
+    // one community over several handles (cabm_shard_config): this handle owns agents [own_lo, own_hi); one handle: [0, N)
+    unsigned int own_lo, own_hi; int shard_rank;
     // static agents
     const int* home; const int* day_loc; const int* patron; const unsigned char* age; const unsigned char* pflags;
     const double* nat_eff; const float* xprot; const int* nat_dur; const float* home_risk;

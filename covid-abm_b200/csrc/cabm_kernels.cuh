@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(TPB) k_scan(const Dev D) {
     __shared__ unsigned int s_warp[TPB / 32], s_base;
     const DayCtx& cx = D.dayctx[D.ctr->day_idx];
     const int day = cx.day;
-    if (blockIdx.x == 0 && threadIdx.x == 0) { *D.today = cx; atomicAdd(&D.ctr->work[CABM_W_AGENTS], (unsigned long long) D.N); }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { *D.today = cx; atomicAdd(&D.ctr->work[CABM_W_AGENTS], (unsigned long long) (D.own_hi - D.own_lo)); }
     const unsigned int p0 = (blockIdx.x * TPB + threadIdx.x) * 4u;
     uint4 w = make_uint4(0x80007FFFu, 0x80007FFFu, 0x80007FFFu, 0x80007FFFu);
     if (p0 + 3 < D.N) w = *reinterpret_cast<const uint4*>(D.win + p0);
@@ -208,7 +208,8 @@ __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned in
     for (unsigned int i = threadIdx.x; i < bitmap_words; i += blockDim.x) s_hot[i] = D.pub_hot[i];
     __syncthreads();
     const unsigned int stride = gridDim.x * blockDim.x * 4u;
-    const unsigned int n_round = (D.N + stride - 1) / stride * stride;
+    const unsigned int t_base = D.own_lo & ~127u;                                   // tiles cover the owned agents only
+    const unsigned int n_round = t_base + (D.own_hi - t_base + stride - 1) / stride * stride;
     const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
     const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
     const double sd = cx.sd;
@@ -217,7 +218,7 @@ __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned in
     unsigned int w_pat = 0, w_v0 = 0, w_v = 0;
     // a warp takes tiles of 128 consecutive agents; in slot a lane l handles agent tile + 32 a + l, so the 32-byte patron
     // rows a load instruction touches are consecutive (8 cache lines per request instead of 32)
-    for (unsigned int t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 128u; t0 < n_round; t0 += stride) {
+    for (unsigned int t0 = t_base + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 128u; t0 < n_round; t0 += stride) {
         unsigned int pb4 = 0;
 #pragma unroll
         for (int a = 0; a < 4; ++a) { const unsigned int p = t0 + a * 32 + lane; if (p < D.N) pb4 |= (unsigned int) D.pbyte[p] << (8 * a); }
@@ -226,7 +227,7 @@ __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned in
         for (int a = 0; a < 4; ++a) {
             const unsigned int pb = (pb4 >> (8 * a)) & 0xFFu, p = t0 + a * 32 + lane;
             const unsigned int npat = pb & PB_NPAT;
-            const bool act = npat && !(pb & PB_INHOSP);
+            const bool act = npat && !(pb & PB_INHOSP) && p >= D.own_lo && p < D.own_hi;     // another handle draws for agents it owns
             // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017); no memory needed
             const uint4 b = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
             unsigned int k = (b.x >= thr0) + (b.x >= thr1) + (b.x >= thr2) + (b.x >= thr3);
@@ -311,6 +312,7 @@ __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1
 // A success is queued for the susceptibility gate (k_gate).
 __device__ __forceinline__ void trial(const Dev& D, const int day, const int phase, const unsigned int pid, const int src, const int purpose,
                                       const unsigned int sub, const double T, unsigned int& trials) {
+    if (pid < D.own_lo || pid >= D.own_hi) return;                                 // the owner of an agent draws its exposures
     if (D.any_quarantine) {
         const unsigned int q = D.quar[pid]; const int qf = (short) (q & 0xFFFF), qu = (short) (q >> 16);
         if (day >= qf && day < qu && src != D.home[pid]) return;
@@ -428,7 +430,7 @@ __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
         if (D.foi_enabled) write_foi(D, i, loc, type, pws, denom, T, Ts);
     }
     edges = warp_sum(edges);
-    if ((threadIdx.x & 31) == 0 && edges) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges);
+    if ((threadIdx.x & 31) == 0 && edges && D.shard_rank == 0) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -9,7 +9,7 @@
 //   k_hosp_import   hospitals/imports: hospital_transmission (Community.cpp:931-941) after the status pass, and
 //                                     the daily importation draws of seed_epidemic (simulator.h:201-223)
 //   k_end           hot locations   : updateHotLocations + clear_public_activity (Community.cpp:999-1003,1042-1046)
-//   k_day_end       1 thread        : counter reset, next day
+//   (k_end's last block)            : counter reset, next day
 #pragma once
 #include "cabm_kernels.cuh"
 
@@ -262,6 +262,7 @@ __global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_h
         for (unsigned int i = tid; i < (unsigned int) cx.n_imports; i += nth) {
             const uint4 b = philox4x32_10(make_uint4(0u, i, 0u, ((unsigned int) day << 8) | CABM_P_IMPORT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
             const unsigned int pid = __umulhi(b.x, D.N);
+            if (pid < D.own_lo || pid >= D.own_hi) continue;                          // every handle draws the same people, the owner exposes them
             const unsigned int h = base + list_reserve(&D.ctr->n_hits[1]);
             if (h < D.cap_hits) { Hit r; r.pid = pid; r.src = i; r.purpose = CABM_P_IMPORT; r.sub = 0; D.hits[h] = r; }
             else atomicOr(&D.ctr->overflow, 256u);
@@ -274,18 +275,20 @@ __global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_h
 // Community::infect(id, strain) (Community.cpp:550-553): one agent, gate and commit in one go
 __global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain, const int day, int* out) {
     if (threadIdx.x || blockIdx.x) return;
-    const unsigned int seq = D.ctr->seed_calls++;
+    const unsigned int seq = D.ctr->seed_calls++;                                  // every handle counts every call, the owner applies it
+    if (pid < D.own_lo || pid >= D.own_hi) { *out = 0; return; }
     Stream s; s.begin(D.seed, (unsigned int) day, CABM_P_SEED, pid, seq);
     InfectCtx c; c.pid = (int) pid; c.time = day; c.source = -1; c.has_source = false; c.strain = strain; c.infector = -1;
     c.purpose = CABM_P_SEED; c.key_a = pid; c.key_b = seq; c.key_sub = 0;
     *out = infect_event(D, s, c, true) ? 1 : 0;
 }
 
-// reset what today's hot set and today's winners touched
-__global__ void __launch_bounds__(TPB) k_end(const Dev D, const int reset_hot) {
+// reset what today's hot set and today's winners touched; the last block to finish then closes the day (day-scoped counters
+// back to zero, next day context): every other block has read the counters it needs before taking its ticket
+__global__ void __launch_bounds__(TPB) k_end(const Dev D, const int tick_done, const int advance) {
     const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-    if (reset_hot) {
-        const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
+    const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
+    if (tick_done) {
         for (unsigned int i = tid; i < n_hot; i += nth) {
             const int loc = D.hot_list[i];
             ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
@@ -297,16 +300,20 @@ __global__ void __launch_bounds__(TPB) k_end(const Dev D, const int reset_hot) {
     }
     const unsigned int n_new = min(D.ctr->n_new[0] + D.ctr->n_new[1], D.cap_new);
     for (unsigned int i = tid; i < n_new; i += nth) D.cand[D.newinf_list[i]] = CABM_CAND_EMPTY;
-}
-
-__global__ void k_day_end(const Dev D, const int tick_done, const int advance) {
-    if (threadIdx.x || blockIdx.x) return;
-    Counters* c = D.ctr;
-    if (tick_done) { c->work[CABM_W_HOT_LOCS] += min(c->n_hot, D.cap_hot); if (D.foi_enabled) *D.n_foi = min(c->n_hot, D.cap_hot); }
-    unsigned int* w = reinterpret_cast<unsigned int*>(c);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        Counters* c = D.ctr;
+        __threadfence();
+        if (atomicAdd(&c->end_ticket, 1u) == gridDim.x - 1) {
+            if (tick_done) { if (D.shard_rank == 0) c->work[CABM_W_HOT_LOCS] += n_hot; if (D.foi_enabled) *D.n_foi = n_hot; }
+            unsigned int* w = reinterpret_cast<unsigned int*>(c);
 #pragma unroll
-    for (int k = 0; k < CABM_DAY_SCOPED_WORDS; ++k) w[k] = 0;
-    if (advance) c->day_idx++;
+            for (int k = 0; k < CABM_DAY_SCOPED_WORDS; ++k) w[k] = 0;
+            if (advance) c->day_idx++;
+            c->end_ticket = 0;
+            __threadfence();
+        }
+    }
 }
 
 // Person::vaccinate (Person.cpp:611-647), leaky model
@@ -430,6 +437,31 @@ __global__ void k_detected_today(const Dev D, const int day, unsigned int* out, 
             hit = b.detected < CABM_N_OUTCOMES && b.report_day == day && !(b.death <= day);
         }
         if (hit) { const unsigned int i = list_reserve(n_out); if (i < cap) out[i] = p; }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// One community over several handles (include/cabm.h cabm_shard_*): flags of the other handles' agents are applied to
+// this handle's replicated location state exactly as k_active applies its own (same pressure sums, own slot numbering);
+// the hospital census is kept global by exchanging the day's admissions minus discharges.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_flags_in(const Dev D, const FlagRaw* __restrict__ in, const unsigned int n) {
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const FlagRaw r = in[i];
+        const int strain = FLAG_STRAIN(r); const unsigned long long c = FLAG_C(r);
+        atomicAdd(&D.press[(size_t) r.loc * CABM_N_STRAINS + strain], c);
+        const unsigned int slot = atomicAdd(&D.loc_cnt[r.loc], 1u);
+        const unsigned int f = list_reserve(&D.ctr->n_flags);
+        flag_location(D, r.loc, strain, c, r.pid, slot, f);
+    }
+}
+// mode 0: remember the census before the status pass; 1: buf = own admissions - discharges; 2: census = remembered + summed buf
+__global__ void k_patients(const Dev D, const int* __restrict__ hosp_ids, const unsigned int n, int* save, int* buf, const int mode) {
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int loc = hosp_ids[i];
+        if (mode == 0) save[i] = (int) D.pat_count[loc];
+        else if (mode == 1) buf[i] = (int) D.pat_count[loc] - save[i];
+        else D.pat_count[loc] = (unsigned int) (save[i] + buf[i]);
     }
 }
 

@@ -285,6 +285,32 @@ int  cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]);
 /* doSerosurvey(NATURAL, pop, day) for an arbitrary list of people (pids == NULL: everybody); returns the seropositive count */
 int  cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos);
 
+/* ---- one community advanced by several handles, one per GPU -------------------------------------
+   Every handle loads the whole population (static arrays and location state are replicated); handle `rank` OWNS the
+   agents [pid_lo, pid_hi) -- it alone scans, exposes, infects and tallies them. Household members must share an owner.
+   The day is advanced in four parts with three exchanges between them, done by the caller (NCCL / torch.distributed /
+   plain copies between handles of one process):
+     part 0  owned infectious agents -> flag records {place, agent, pressure, strain}
+             exchange A: every handle receives every other handle's records (all-gather; cabm_shard_flags_out / _in)
+     part 1  owned agents' visits (Community::public_activity) -> partial visitor census
+             exchange B: the census buffer is summed over handles in place (all-reduce; cabm_shard_census)
+     part 2  exposure passes HOUSE..NURSINGHOME, winners, status pass
+             exchange C: the admissions-minus-discharges buffer is summed over handles in place (cabm_shard_patients)
+     part 3  hospital pass, the day's importation (strain_w == NULL: none), end of day
+   The exposure draw is keyed (seed, day, person, place), so the owner of an agent draws for it wherever the place's
+   infectious people live: no exposure events are exchanged. Results are bit-identical to a single handle.
+   Buffers are in the backend's memory (device memory for the CUDA library). cabm_infect must be called on every handle
+   (each counts the call, the owner applies it); cabm_vaccinate / cabm_quarantine go to the owner of each agent;
+   ledgers, outcome counts, histories and work counters are per handle and add up. */
+int  cabm_shard_config(cabm_t* h, int rank, int world, uint32_t pid_lo, uint32_t pid_hi);
+int  cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is_weekday, double expected_imports,
+                         const double* strain_w, int32_t* out_imported);
+int  cabm_shard_flags_out(cabm_t* h, void** records, size_t* n);          /* CABM_SHARD_FLAG_BYTES each; valid until the next part 0 */
+int  cabm_shard_flags_in(cabm_t* h, const void* records, size_t n);       /* between part 0 and part 1; may be called once per peer */
+int  cabm_shard_census(cabm_t* h, void** buf, size_t* n_u32);
+int  cabm_shard_patients(cabm_t* h, void** buf, size_t* n_i32);
+#define CABM_SHARD_FLAG_BYTES 24
+
 /* device time (ms, CUDA events) spent in the day pipeline since the last call; resets the accumulator */
 int  cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches);
 

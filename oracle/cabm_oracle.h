@@ -95,6 +95,17 @@ struct Sim {
     int pending_infector = -1;                            // infector traced for the exposure being applied (Community.cpp:795-825)
     std::string err;
 
+    // one community over several instances: this one owns agents [own_lo, own_hi)
+    uint32_t own_lo = 0, own_hi = 0; int shard_rank = 0, shard_world = 1;
+    bool owns(uint32_t pid) const { return pid >= own_lo && pid < own_hi; }
+    std::vector<HotRec> flags_out, flags_in;             // today's flag records: produced here / received from the other instances
+    std::vector<uint32_t> census;                        // [n_loc] visitors of the day (summed over instances between part 1 and 2)
+    std::vector<int32_t> hosp_ids, hosp_index, pat_delta, pat_total;   // hospitals; admissions - discharges of the day; patients of all instances
+    std::map<int32_t, LocHot> hotmap[CABM_N_LOCTYPES];    // today's calendar slice by location type, then id (Community.h:133, Location.h:31)
+    std::map<int32_t, std::vector<int32_t>> visitors;     // today's visitors among the owned agents
+    void day_part(int part, int day, int julian_day, int is_weekday);
+    std::map<int32_t, int> draw_visits(int day, uint32_t pid, int num_locs, bool avoiding) const;
+
     // the hot path
     void tick(int day, int julian_day, int is_weekday);
     int  import_day(int day, double expected, const double* strain_w);

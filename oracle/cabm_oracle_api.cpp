@@ -40,6 +40,10 @@ int cabm_oracle_load_population(cabm_t* h, const cabm_population* pop) {
     S.nat_dur.assign(pop->natural_immunity_duration, pop->natural_immunity_duration + N);
     S.people.assign(N, cabm_oracle::Person());
     S.patients.clear(); S.log.clear(); S.seed_calls = 0;
+    S.own_lo = 0; S.own_hi = N; S.shard_rank = 0; S.shard_world = 1;
+    S.census.assign(L, 0u); S.pat_total.assign(L, 0); S.hosp_index.assign(L, -1); S.hosp_ids.clear();
+    for (uint32_t l = 0; l < L; ++l) if (S.loc_type[l] == CABM_HOSPITAL) { S.hosp_index[l] = (int32_t) S.hosp_ids.size(); S.hosp_ids.push_back((int32_t) l); }
+    S.pat_delta.assign(S.hosp_ids.size(), 0);
     S.have_pop = true;
     return CABM_OK;
 }
@@ -92,7 +96,8 @@ int cabm_oracle_import(cabm_t* h, int sim_day, double expected, const double str
 int cabm_oracle_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected) {
     H_OK(h); Sim& S = h->sim; int rc = ready(S, sim_day); if (rc) return rc;
     if (pid >= S.n_people || strain < 0 || strain >= CABM_N_STRAINS) return CABM_E_ARG;
-    const uint32_t seq = S.seed_calls++;
+    const uint32_t seq = S.seed_calls++;                              // every instance counts every call, the owner applies it
+    if (!S.owns(pid)) { if (out_infected) *out_infected = 0; return CABM_OK; }
     cabm_oracle::Stream s; s.begin(S.par.seed, (uint32_t) sim_day, CABM_P_SEED, pid, seq);
     const bool ok = S.infect((int) pid, sim_day, -1, strain, false, s, CABM_P_SEED, pid, seq, 0);
     if (out_infected) *out_infected = ok ? 1 : 0;
@@ -317,6 +322,43 @@ int cabm_oracle_kat_ledger_digest(cabm_t* h, int counter, uint64_t* out_sum, uin
     for (size_t d = 0; d < S.ledger[counter].size(); ++d) { s += S.ledger[counter][d]; hh = (hh ^ (S.ledger[counter][d] + 0x9E37u * d)) * 1099511628211ull; }
     *out_sum = s; *out_hash = hh;
     return CABM_OK;
+}
+
+// ---- one community over several instances (include/cabm.h "shard" entry points) ----
+int cabm_oracle_shard_config(cabm_t* h, int rank, int world, uint32_t pid_lo, uint32_t pid_hi) {
+    H_OK(h); Sim& S = h->sim;
+    if (!S.have_pop || world < 1 || rank < 0 || rank >= world || pid_lo > pid_hi || pid_hi > S.n_people) return CABM_E_ARG;
+    for (uint32_t p = pid_lo; p < pid_hi; ++p) {                      // household members share an owner
+        const int32_t hm = S.home[p];
+        for (int64_t e = S.roster_off[hm]; e < S.roster_off[hm + 1]; ++e)
+            if (S.home[S.roster[e]] == hm && ((uint32_t) S.roster[e] < pid_lo || (uint32_t) S.roster[e] >= pid_hi)) { S.err = "a household is split between shards"; return CABM_E_ARG; }
+    }
+    S.shard_rank = rank; S.shard_world = world; S.own_lo = pid_lo; S.own_hi = pid_hi;
+    return CABM_OK;
+}
+int cabm_oracle_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is_weekday, double expected, const double* strain_w, int32_t* out_imported) {
+    H_OK(h); Sim& S = h->sim; int rc = ready(S, sim_day); if (rc) return rc;
+    if (part < 0 || part > 3 || julian_day < 1 || julian_day > 366) return CABM_E_ARG;
+    S.day_part(part, sim_day, julian_day, is_weekday);
+    if (part == 3) { const int n = strain_w ? S.import_day(sim_day, expected, strain_w) : 0; if (out_imported) *out_imported = n; }
+    return CABM_OK;
+}
+int cabm_oracle_shard_flags_out(cabm_t* h, void** records, size_t* n) {
+    H_OK(h); if (!records || !n) return CABM_E_ARG;
+    *records = h->sim.flags_out.data(); *n = h->sim.flags_out.size(); return CABM_OK;
+}
+int cabm_oracle_shard_flags_in(cabm_t* h, const void* records, size_t n) {
+    H_OK(h); if (!records && n) return CABM_E_ARG;
+    const cabm_oracle::HotRec* r = (const cabm_oracle::HotRec*) records;
+    h->sim.flags_in.insert(h->sim.flags_in.end(), r, r + n); return CABM_OK;
+}
+int cabm_oracle_shard_census(cabm_t* h, void** buf, size_t* n_u32) {
+    H_OK(h); if (!buf || !n_u32) return CABM_E_ARG;
+    *buf = h->sim.census.data(); *n_u32 = h->sim.census.size(); return CABM_OK;
+}
+int cabm_oracle_shard_patients(cabm_t* h, void** buf, size_t* n_i32) {
+    H_OK(h); if (!buf || !n_i32) return CABM_E_ARG;
+    *buf = h->sim.pat_delta.data(); *n_i32 = h->sim.pat_delta.size(); return CABM_OK;
 }
 
 // ---- generator / deterministic-math hooks for tests/test_philox.py and tests/test_det_math.py -------------------------

@@ -1,0 +1,154 @@
+"""One community over several handles: the sharded run is bit-identical to the single-handle run.
+
+CPU: the oracle backend, shards in one process (LocalExchange) and one shard per process over gloo (DistExchange).
+GPU: the CUDA library, several shards on one device (LocalExchange) against the single-handle CUDA run and the oracle;
+the NCCL path is exercised by `bench.py --shard` under torchrun.
+"""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import covid_abm_b200 as cabm
+import synthpop
+import oracle_lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MUT = ("2020-02-25", "2020-03-10", "2020-03-25")
+
+
+def _case(n=9000, days=70, seed=13, T=0.16, pde=2e-3):
+    pop = synthpop.generate(n, seed=21)
+    P = cabm.params.default_params(run_length=days, seed=seed, T=T, prob_daily_exposure=pde, mutant_intro_dates=MUT)
+    tab = cabm.params.build_tables(P)
+    attrs = cabm.abi.immunity_attributes(int(pop["n_people"]), P["seed"])
+    return pop, P, tab, attrs
+
+
+def _script(c, pop, days, check=None):
+    """The same sequence of calls on a single community or a sharded one."""
+    n = int(pop["n_people"]); rng = np.random.default_rng(3)
+    for pid in range(0, 1500, 11):
+        c.infect(pid, 0, 0)
+    for d in range(days):
+        if d in (12, 33):
+            pids = rng.choice(n, size=n // 3, replace=False)
+            c.vaccinate(pids, d)
+        if d == 25:
+            c.quarantine(rng.choice(n, size=n // 8, replace=False), d, d + 12)
+        c.step()
+        if check is not None:
+            check(d)
+
+
+def _sorted_hist(c):
+    h = c.infection_histories()
+    return h[np.lexsort((h["t"][:, 0], h["person"]))]
+
+
+def _assert_same(single, sharded, label):
+    assert np.array_equal(single.ledger_table(), sharded.ledger_table()), f"{label}: ledger"
+    assert np.array_equal(single.getCumulIncidenceByOutcome(), sharded.getCumulIncidenceByOutcome()), f"{label}: outcomes"
+    a, b = single.current_infections(), sharded.current_infections()
+    bad = np.flatnonzero(a != b)
+    assert bad.size == 0, f"{label}: {bad.size} agents differ, first {bad[:3]}"
+
+
+def test_household_cuts_never_split_a_home():
+    pop, P, tab, attrs = _case(n=5000)
+    for world in (2, 3, 8):
+        cuts = cabm.sharded.household_cuts(pop, world)
+        assert cuts[0] == 0 and cuts[-1] == int(pop["n_people"]) and all(a <= b for a, b in zip(cuts, cuts[1:]))
+        for p in cuts[1:-1]:
+            assert pop["home"][p] != pop["home"][p - 1]
+        sizes = np.diff(cuts)
+        assert sizes.max() - sizes.min() < 20
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_oracle_sharded_equals_single(world):
+    pop, P, tab, attrs = _case()
+    single = oracle_lib.oracle_community(P, pop, tab, attrs=attrs)
+    sh = cabm.sharded.local_sharded(P, pop, tab, world, backend=oracle_lib.oracle_backend(), attrs=attrs)
+    single.foi(); [s.foi() for s in sh.shards]
+    _script(single, pop, 70)
+
+    def check(d):
+        if d in (5, 30, 69):
+            f = sh.foi()
+            for s in sh.shards[1:]:
+                assert np.array_equal(f, s.foi()), f"day {d}: shards disagree on the force of infection"
+    _script(sh, pop, 70, check)
+    _assert_same(single, sh, f"world {world}")
+    hs, hh = _sorted_hist(single), _sorted_hist(sh)
+    assert hs.size == hh.size > 1500 and np.array_equal(hs, hh)
+    assert np.array_equal(single.foi(), sh.foi())
+    w1, w2 = single.work_counters(), sh.work_counters()
+    assert w1 == w2, {k: (w1[k], w2[k]) for k in w1 if w1[k] != w2[k]}
+    owned = [int(s.ledger("new_infected").sum()) for s in sh.shards]
+    assert all(o > 0 for o in owned)                        # every shard carried part of the epidemic
+    strains = single.ledger_table()[:, 16:20].sum(axis=0)
+    assert (strains > 0).sum() >= 3
+
+
+def _gloo_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tools")); sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import covid_abm_b200 as cabm2
+    import oracle_lib as ol
+    pop, P, tab, attrs = _case(n=6000, days=45)
+    cuts = cabm2.sharded.household_cuts(pop, world)
+    shard = cabm2.sharded.Shard(P, pop, tab, rank, world, cuts, backend=ol.oracle_backend(), attrs=attrs)
+    c = cabm2.sharded.ShardedCommunity([shard], cabm2.sharded.DistExchange(shard, dist))
+    for pid in range(0, 1500, 11):
+        c.infect(pid, 0, 0)
+    c.run_days(45)
+    led = torch.from_numpy(c.ledger_table().astype(np.int64))
+    dist.all_reduce(led)
+    cur = c.current_infections()
+    gathered = [None] * world
+    dist.all_gather_object(gathered, cur)
+    if rank == 0:
+        q.put((led.numpy().astype(np.uint64), np.concatenate(gathered)))
+    dist.barrier(); dist.destroy_process_group()
+
+
+def test_gloo_two_ranks_equal_single():
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    ctx = mp.get_context("spawn"); q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    led, cur = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=60); assert p.exitcode == 0
+    pop, P, tab, attrs = _case(n=6000, days=45)
+    single = oracle_lib.oracle_community(P, pop, tab, attrs=attrs)
+    for pid in range(0, 1500, 11):
+        single.infect(pid, 0, 0)
+    single.run_days(45)
+    assert np.array_equal(single.ledger_table(), led)
+    assert np.array_equal(single.current_infections(), cur)
+    assert led[:, 0].sum() > 500
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4])
+def test_cuda_sharded_on_one_device_equals_single(world):
+    import torch
+    pop, P, tab, attrs = _case(n=30000, days=70)
+    single = cabm.Community(P, pop, tab, attrs=attrs)
+    oracle = oracle_lib.oracle_community(P, pop, tab, attrs=attrs)
+    sh = cabm.sharded.local_sharded(P, pop, tab, world, attrs=attrs, device=torch.device("cuda", 0))
+    _script(single, pop, 70); _script(oracle, pop, 70); _script(sh, pop, 70)
+    _assert_same(single, sh, f"cuda world {world} vs single")
+    _assert_same(oracle, sh, f"cuda world {world} vs oracle")
+    hs, hh = _sorted_hist(single), _sorted_hist(sh)
+    assert hs.size == hh.size > 3000 and np.array_equal(hs, hh)
