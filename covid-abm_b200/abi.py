@@ -102,6 +102,8 @@ _PROTOS = {
     "diagnostics": [_vp, C.c_int, C.POINTER(C.c_uint64)], "serosurvey": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_uint64)],
 }
 _OPTIONAL = {
+    "shard_nccl_init": [_vp, _vp, C.c_int, C.c_int], "shard_exchange_capacity": [_vp, C.c_size_t], "shard_exchange_mode": [_vp, C.POINTER(C.c_int)],
+    "shard_run_days": [_vp, C.c_int, C.c_int, C.POINTER(i32), C.POINTER(i32), C.POINTER(d), C.POINTER(d)],
     "set_profile": [_vp, C.c_int],
     "kernel_times": [_vp, C.POINTER(d), C.POINTER(C.c_uint64), C.POINTER(C.c_char_p), C.c_size_t, C.POINTER(C.c_size_t)],
 }
@@ -115,7 +117,11 @@ class Bound:
             fn = getattr(lib, prefix + name); fn.argtypes = args; fn.restype = C.c_int
             setattr(self, "import_" if name == "import" else name, fn)
         self.last_error = getattr(lib, prefix + "last_error"); self.last_error.argtypes = [_vp]; self.last_error.restype = C.c_char_p
-        for name, args in _OPTIONAL.items():            # measurement-only entry points (absent from the oracle)
+        fn = getattr(lib, prefix + "shard_nccl_id", None)
+        if fn is not None:
+            fn.argtypes = [_vp]; fn.restype = C.c_int
+        self.shard_nccl_id = fn
+        for name, args in _OPTIONAL.items():            # measurement / NCCL entry points (absent from the oracle)
             fn = getattr(lib, prefix + name, None)
             if fn is not None:
                 fn.argtypes = args; fn.restype = C.c_int

@@ -7,6 +7,9 @@
 #include <new>
 #include <string>
 #include <vector>
+#include <climits>
+#include <dlfcn.h>
+#include <nccl.h>
 #include "cabm_kernels2.cuh"
 
 namespace {
@@ -35,6 +38,8 @@ struct cabm {
     unsigned long long h_n_log_cap = 0;
     uint64_t launches_per_day = 11;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
+    void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
+    const FlagRaw* peer_flags[CABM_MAX_SHARDS] = { nullptr }; int peer_mode = 0;      // exchange A over peer memory (cudaIpc mappings of the other handles' flag lists)
     int* d_hosp_ids = nullptr; int* d_pat_save = nullptr; int* d_pat_buf = nullptr; unsigned int n_hosp = 0; unsigned int n_flags_own = 0;   // sharding
     int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
 };
@@ -103,9 +108,9 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
 
 // kernel ids for per-kernel timing (cabm_kernel_times)
 enum { KID_SCAN = 0, KID_ACTIVE, KID_VISIT, KID_HAZARD, KID_TRIALS, KID_GATE0, KID_APPLY_STATUS, KID_HOSP_IMPORT, KID_GATE1, KID_APPLY1,
-       KID_END, KID_SMALL, KID_N };
+       KID_END, KID_SMALL, KID_XA, KID_XB, KID_XC, KID_N };
 static const char* const KID_NAMES[KID_N] = { "k_scan", "k_active", "k_visit", "k_hazard", "k_trials", "k_gate(phase0)", "k_apply_status",
-    "k_hosp_import", "k_gate(phase1)", "k_apply(phase1)", "k_end", "(unused)" };
+    "k_hosp_import", "k_gate(phase1)", "k_apply(phase1)", "k_end", "(unused)", "exchange A (flags)", "exchange B (census)", "exchange C (patients)" };
 
 // LAUNCH records an event in front of every kernel when per-kernel profiling is on (stream path only, never under graph capture)
 #define LAUNCH(id, ...) do { if (h->profile) prof_mark(h, id); __VA_ARGS__; h->launches++; } while (0)
@@ -125,9 +130,11 @@ static void prof_collect(cabm_t* h) {      // call after the stream has been syn
 // seed_epidemic (simulator.h:201-223). With both set the importation draws share the hospital pass's gate/apply
 // launches: an agent hit by both keeps the hospital exposure (lower order key), exactly what running
 // seed_epidemic after tick() yields.
+// k_scan covers the owned agents only (the whole population on an unsharded handle), in groups of four from own_lo rounded down
+static unsigned int scan_grid(const Dev& D) { return std::max(1u, (unsigned int) ((D.own_hi - (D.own_lo & ~3u) + TPB * 4 - 1) / (TPB * 4))); }
 static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     const Dev& D = h->d; cudaStream_t st = h->stream;
-    const unsigned int gScan = (unsigned int) ((D.N + TPB * 4 - 1) / (TPB * 4)), gSM = h->sms;
+    const unsigned int gScan = scan_grid(D), gSM = h->sms;
     if (tick) {
         LAUNCH(KID_SCAN, k_scan<<<gScan, TPB, 0, st>>>(D));
         LAUNCH(KID_ACTIVE, k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D));
@@ -165,6 +172,36 @@ static int timed_sync(cabm_t* h) {
     return CABM_OK;
 }
 
+// ---- NCCL, resolved at run time so that the library loads where NCCL is absent (CPU-only checks) ----
+namespace {
+struct NcclApi {
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+NcclApi& nccl_api() {
+    static NcclApi a; static bool tried = false;
+    if (tried) return a;
+    tried = true;
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return a;
+    a.GetUniqueId = (decltype(a.GetUniqueId)) dlsym(lib, "ncclGetUniqueId"); a.CommInitRank = (decltype(a.CommInitRank)) dlsym(lib, "ncclCommInitRank");
+    a.CommDestroy = (decltype(a.CommDestroy)) dlsym(lib, "ncclCommDestroy"); a.AllGather = (decltype(a.AllGather)) dlsym(lib, "ncclAllGather");
+    a.AllReduce = (decltype(a.AllReduce)) dlsym(lib, "ncclAllReduce"); a.GetErrorString = (decltype(a.GetErrorString)) dlsym(lib, "ncclGetErrorString");
+    a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllGather && a.AllReduce && a.GetErrorString;
+    return a;
+}
+}
+#define PM(id) do { if (h->profile) prof_mark(h, id); } while (0)
+static const int SHARD_GROUP = 4;      // days enqueued between two host looks at the flag counts (cabm_shard_run_days)
+#define NK(call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) { h->err = std::string(#call) + ": " + nccl_api().GetErrorString(r_); return CABM_E_CUDA; } } while (0)
+
+
 extern "C" {
 
 int cabm_create(cabm_t** out) {
@@ -187,6 +224,10 @@ int cabm_destroy(cabm_t* h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     if (h->day_graph) cudaGraphExecDestroy(h->day_graph);
+    if (h->nccl_comm && nccl_api().ok) nccl_api().CommDestroy((ncclComm_t) h->nccl_comm);
+    for (int r = 0; r < CABM_MAX_SHARDS; ++r) if (h->peer_flags[r] && r != h->d.shard_rank) cudaIpcCloseMemHandle((void*) h->peer_flags[r]);
+    if (h->d_xrecv) cudaFree(h->d_xrecv);
+    if (h->h_xcounts) cudaFreeHost(h->h_xcounts);
     for (void* p : h->allocs) cudaFree(p);
     if (h->h_ctx) cudaFreeHost(h->h_ctx);
     cudaEventDestroy(h->e0); cudaEventDestroy(h->e1); cudaStreamDestroy(h->stream);
@@ -528,7 +569,7 @@ int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is
     if (part == 0) {
         CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, st));
         CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), st));
-        const unsigned int gScan = (unsigned int) ((D.N + TPB * 4 - 1) / (TPB * 4));
+        const unsigned int gScan = scan_grid(D);
         k_scan<<<gScan, TPB, 0, st>>>(D);
         k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D);
         CK(cudaMemcpyAsync(&h->n_flags_own, &D.ctr->n_flags, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
@@ -589,6 +630,147 @@ int cabm_shard_patients(cabm_t* h, void** buf, size_t* n_i32) {
     if (!h || !buf || !n_i32 || !h->have_pop) return CABM_E_ARG;
     *buf = h->d_pat_buf; *n_i32 = h->n_hosp;
     return CABM_OK;
+}
+
+int cabm_shard_nccl_id(void* out_id) {
+    if (!out_id || !nccl_api().ok) return CABM_E_STATE;
+    ncclUniqueId id;
+    if (nccl_api().GetUniqueId(&id) != ncclSuccess) return CABM_E_CUDA;
+    std::memcpy(out_id, &id, CABM_NCCL_ID_BYTES);
+    return CABM_OK;
+}
+
+int cabm_shard_nccl_init(cabm_t* h, const void* id, int rank, int world) {
+    if (!h || !id || world < 1 || world > CABM_MAX_SHARDS || rank < 0 || rank >= world) return CABM_E_ARG;
+    if (!h->have_pop) { h->err = "load the population and call cabm_shard_config first"; return CABM_E_STATE; }
+    if (!nccl_api().ok) { h->err = "libnccl.so.2 not found"; return CABM_E_STATE; }
+    cudaSetDevice(h->device);
+    ncclUniqueId uid; std::memcpy(&uid, id, CABM_NCCL_ID_BYTES);
+    ncclComm_t comm = nullptr;
+    NK(nccl_api().CommInitRank(&comm, world, uid, rank));
+    h->nccl_comm = comm; h->world = world;
+    int rc;
+    if (!h->d_xcounts && (rc = dalloc(h, &h->d_xcounts, CABM_MAX_SHARDS + 16))) return rc;
+    if (!h->h_xcounts) CK(cudaMallocHost(&h->h_xcounts, 16 * sizeof(unsigned int)));
+    // Peer mapping of the flag lists: every rank publishes the IPC handle of its list, opens the others', and the job uses
+    // the peer path only if every rank could map every peer (one all-reduce of a yes/no word).
+    h->peer_mode = 0;
+    const char* env = getenv("CABM_SHARD_PEER");
+    if (world > 1 && !(env && atoi(env) == 0)) {
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+        unsigned char* d_hd = nullptr; std::vector<unsigned char> hd((size_t) 64 * world);
+        cudaIpcMemHandle_t mine; int ok = cudaIpcGetMemHandle(&mine, h->d.flags_raw) == cudaSuccess ? 1 : 0;
+        if (!ok) { cudaGetLastError(); std::memset(&mine, 0, sizeof(mine)); }
+        CK(cudaMalloc(&d_hd, hd.size() + 64));
+        CK(cudaMemcpyAsync(d_hd + hd.size(), &mine, 64, cudaMemcpyHostToDevice, h->stream));
+        NK(nccl_api().AllGather(d_hd + hd.size(), d_hd, 64, ncclUint8, comm, h->stream));
+        CK(cudaMemcpyAsync(hd.data(), d_hd, hd.size(), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        for (int r = 0; r < world && ok; ++r) {
+            if (r == rank) { h->peer_flags[r] = h->d.flags_raw; continue; }
+            cudaIpcMemHandle_t hr; std::memcpy(&hr, hd.data() + (size_t) 64 * r, 64);
+            void* ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&ptr, hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+            h->peer_flags[r] = (const FlagRaw*) ptr;
+        }
+        int* d_ok = (int*) d_hd; CK(cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, h->stream));
+        NK(nccl_api().AllReduce(d_ok, d_ok, 1, ncclInt32, ncclMin, comm, h->stream));
+        CK(cudaMemcpyAsync(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        cudaFree(d_hd);
+        h->peer_mode = ok;
+        if (!ok) for (int r = 0; r < world; ++r) { if (h->peer_flags[r] && r != rank) cudaIpcCloseMemHandle((void*) h->peer_flags[r]); h->peer_flags[r] = nullptr; }
+    }
+    return CABM_OK;
+}
+
+int cabm_shard_exchange_capacity(cabm_t* h, size_t records_per_rank) {
+    if (!h || records_per_rank == 0) return CABM_E_ARG;
+    h->xcap = std::min<size_t>(records_per_rank, h->d.cap_flags);
+    return CABM_OK;
+}
+
+int cabm_shard_exchange_mode(cabm_t* h, int* out_peer_memory) {
+    if (!h || !out_peer_memory) return CABM_E_ARG;
+    *out_peer_memory = h->peer_mode;
+    return CABM_OK;
+}
+
+int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
+                        const double* expected_imports, const double* strain_w) {
+    if (!h || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;
+    if (!h->nccl_comm) { h->err = "cabm_shard_nccl_init first"; return CABM_E_STATE; }
+    int rc = ready(h, first_day); if (rc) return rc; if ((rc = ready(h, first_day + n_days - 1))) return rc;
+    if (n_days > h->ctx_cap) { h->err = "too many days in one batch"; return CABM_E_ARG; }
+    cudaSetDevice(h->device);
+    const Dev& D = h->d; cudaStream_t st = h->stream; const unsigned int gSM = h->sms; ncclComm_t comm = (ncclComm_t) h->nccl_comm; NcclApi& N = nccl_api();
+    for (int i = 0; i < n_days; ++i) {
+        DayCtx& c = h->h_ctx[i]; std::memset(&c, 0, sizeof(c));
+        if (julian_day[i] < 1 || julian_day[i] > 366) return CABM_E_ARG;
+        fill_ctx(h, c, first_day + i, julian_day[i], is_weekday[i]);
+        c.n_imports = expected_imports[i] > 0 ? import_count(h->hpar.seed, first_day + i, expected_imports[i]) : 0;
+        for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[(size_t) i * CABM_N_STRAINS + s];
+    }
+    CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, (size_t) n_days * sizeof(DayCtx), cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), st));
+    const unsigned int gScan = scan_grid(D);
+    // The gather size must be known on the host. Days are enqueued in groups of SHARD_GROUP with no host round trip inside a
+    // group; between groups the host reads the largest per-handle flag count and sizes the next gathers at 8x that (floor 8192
+    // records, or what cabm_shard_exchange_capacity asked for), so the all-gather moves what the epidemic needs, not N/4 records.
+    const int group = h->peer_mode ? (h->profile ? 8 : n_days) : SHARD_GROUP;     // (profiling: the event pool holds eight days of marks)
+    PeerFlags peers; for (int r = 0; r < CABM_MAX_SHARDS; ++r) peers.p[r] = h->peer_flags[r];
+    for (int g0 = 0; g0 < n_days; g0 += group) {
+        size_t want = h->x_seen == UINT_MAX ? std::max<size_t>(65536, (size_t) D.N / (size_t) (4 * h->world)) : std::max<size_t>(8192, (size_t) h->x_seen * 8);
+        want = std::min<size_t>(std::max(want, h->xcap), D.cap_flags);
+        if (!h->peer_mode && want > h->xcap_alloc) {                                  // receive blocks of the flag all-gather
+            CK(cudaStreamSynchronize(st));
+            if (h->d_xrecv) cudaFree(h->d_xrecv);
+            CK(cudaMalloc(&h->d_xrecv, want * (size_t) h->world * sizeof(FlagRaw)));
+            h->xcap_alloc = want;
+        }
+        const unsigned int cap = (unsigned int) want;
+        CK(cudaMemsetAsync(h->d_xcounts + CABM_MAX_SHARDS, 0, sizeof(unsigned int), st));
+        CK(cudaEventRecord(h->e0, st));
+        for (int i = g0; i < std::min(n_days, g0 + group); ++i) {
+            PM(KID_SCAN); k_scan<<<gScan, TPB, 0, st>>>(D);
+            PM(KID_ACTIVE); k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D);
+            // exchange A: counts, then the front `cap` records of every handle's flag list
+            PM(KID_XA);
+            NK(N.AllGather(&D.ctr->n_flags, h->d_xcounts, 1, ncclUint32, comm, st));
+            if (h->peer_mode) k_flags_pull<<<gSM * 2, TPB, 0, st>>>(D, peers, h->d_xcounts, h->world, D.shard_rank);
+            else {
+                NK(N.AllGather(D.flags_raw, h->d_xrecv, (size_t) cap * sizeof(FlagRaw), ncclUint8, comm, st));
+                k_flags_in_all<<<gSM * 2, TPB, 0, st>>>(D, h->d_xrecv, h->d_xcounts, cap, h->world, D.shard_rank);
+            }
+            PM(KID_VISIT); k_visit<<<std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), gSM * 4), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
+            PM(KID_XB); NK(N.AllReduce(D.nvis, D.nvis, D.Q, ncclUint32, ncclSum, comm, st));                    // exchange B
+            if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
+            PM(KID_HAZARD); k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D);
+            PM(KID_TRIALS); k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D);
+            PM(KID_GATE0); k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D, 0);
+            PM(KID_APPLY_STATUS); k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 1);
+            if (h->n_hosp) {
+                PM(KID_XC);
+                k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 1);
+                NK(N.AllReduce(h->d_pat_buf, h->d_pat_buf, h->n_hosp, ncclInt32, ncclSum, comm, st));  // exchange C
+                k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 2);
+            }
+            PM(KID_HOSP_IMPORT); k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, 1, 1);
+            PM(KID_GATE1); k_gate<<<gSM * h->gm[6], 128, 0, st>>>(D, 1);
+            PM(KID_APPLY1); k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0);
+            PM(KID_END); k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, 1, 1);
+            h->launches += 15;
+        }
+        PM(-1);
+        CK(cudaMemcpyAsync(h->h_xcounts, h->d_xcounts + CABM_MAX_SHARDS, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+        if ((rc = timed_sync(h))) return rc;
+        h->x_seen = h->h_xcounts[0];
+        if (!h->peer_mode && h->x_seen > cap) break;                                  // reported below
+    }
+    unsigned int ov = 0;
+    CK(cudaMemcpy(&ov, &h->d.ctr->overflow, sizeof(ov), cudaMemcpyDeviceToHost));
+    if (ov & 512u) { h->err = "flag exchange capacity exceeded: raise it with cabm_shard_exchange_capacity and re-run from a snapshot"; return CABM_E_NOMEM; }
+    return check_overflow(h);
 }
 
 int cabm_detected_today(cabm_t* h, int sim_day, uint32_t* out_pids, size_t cap, size_t* out_n) {
@@ -678,6 +860,7 @@ int cabm_restore(cabm_t* h, const cabm_snap_t* s) {
     for (size_t i = 0; i < s->bufs.size(); ++i) CK(cudaMemcpyAsync(h->dyn[i].first, s->bufs[i].first, s->bufs[i].second, cudaMemcpyDeviceToDevice, h->stream));
     if (s->n_log) CK(cudaMemcpyAsync(h->d.log, s->log, s->n_log * sizeof(cabm_infection), cudaMemcpyDeviceToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    h->x_seen = UINT_MAX;                   // flag counts of the restored day are unknown to the host
     return CABM_OK;
 }
 int cabm_snap_free(cabm_snap_t* s) {
@@ -713,7 +896,7 @@ int cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches) {
 int cabm_set_profile(cabm_t* h, int on) {
     if (!h) return CABM_E_ARG;
     cudaSetDevice(h->device);
-    if (on && h->marks.empty()) { h->marks.resize(64); h->mark_id.resize(64); for (auto& e : h->marks) cudaEventCreate(&e); }
+    if (on && h->marks.empty()) { h->marks.resize(160); h->mark_id.resize(160); for (auto& e : h->marks) cudaEventCreate(&e); }
     h->profile = on ? 1 : 0; h->n_marks = 0;
     return CABM_OK;
 }

@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(TPB) k_scan(const Dev D) {
     const DayCtx& cx = D.dayctx[D.ctr->day_idx];
     const int day = cx.day;
     if (blockIdx.x == 0 && threadIdx.x == 0) { *D.today = cx; atomicAdd(&D.ctr->work[CABM_W_AGENTS], (unsigned long long) (D.own_hi - D.own_lo)); }
-    const unsigned int p0 = (blockIdx.x * TPB + threadIdx.x) * 4u;
+    const unsigned int p0 = (D.own_lo & ~3u) + (blockIdx.x * TPB + threadIdx.x) * 4u;      // agents of other handles are never active here
     uint4 w = make_uint4(0x80007FFFu, 0x80007FFFu, 0x80007FFFu, 0x80007FFFu);
     if (p0 + 3 < D.N) w = *reinterpret_cast<const uint4*>(D.win + p0);
     else { if (p0 < D.N) w.x = D.win[p0]; if (p0 + 1 < D.N) w.y = D.win[p0 + 1]; if (p0 + 2 < D.N) w.z = D.win[p0 + 2]; }

@@ -455,6 +455,49 @@ __global__ void k_flags_in(const Dev D, const FlagRaw* __restrict__ in, const un
         flag_location(D, r.loc, strain, c, r.pid, slot, f);
     }
 }
+// exchange A inside the library: recv holds `world` blocks of cap records (ncclAllGather of the front of every handle's
+// flags_raw), counts[r] the number of valid records of block r; this handle applies everybody's but its own
+__global__ void k_flags_in_all(const Dev D, const FlagRaw* __restrict__ recv, unsigned int* counts, const unsigned int cap,
+                               const int world, const int rank) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {          // counts[CABM_MAX_SHARDS]: largest per-handle count since the host last looked (sizes the next gathers)
+        unsigned int m = 0;
+        for (int r = 0; r < world; ++r) m = max(m, counts[r]);
+        atomicMax(&counts[CABM_MAX_SHARDS], m);
+    }
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) continue;
+        const unsigned int n = counts[r];
+        if (n > cap) { if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&D.ctr->overflow, 512u); }
+        const FlagRaw* in = recv + (size_t) r * cap;
+        for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < min(n, cap); i += gridDim.x * blockDim.x) {
+            const FlagRaw f = in[i];
+            const int strain = FLAG_STRAIN(f); const unsigned long long c = FLAG_C(f);
+            atomicAdd(&D.press[(size_t) f.loc * CABM_N_STRAINS + strain], c);
+            const unsigned int slot = atomicAdd(&D.loc_cnt[f.loc], 1u);
+            flag_location(D, f.loc, strain, c, f.pid, slot, list_reserve(&D.ctr->n_flags));
+        }
+    }
+}
+// Exchange A over peer memory: every handle reads the other handles' flag lists where they lie (NVLink loads through the
+// pointers cudaIpcOpenMemHandle gave), exactly counts[r] records each. Ordering comes from the collectives around it: the
+// count all-gather in front completes only after every peer's k_active has, and a peer cannot start overwriting its list
+// (next day's k_active) before the census all-reduce behind this kernel, which needs this handle's contribution.
+struct PeerFlags { const FlagRaw* p[CABM_MAX_SHARDS]; };
+__global__ void k_flags_pull(const Dev D, const PeerFlags peers, const unsigned int* __restrict__ counts, const int world, const int rank) {
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) continue;
+        const unsigned int n = min(counts[r], D.cap_flags);
+        const unsigned long long* in = reinterpret_cast<const unsigned long long*>(peers.p[r]);
+        for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+            const unsigned long long w0 = __ldcv(in + 3 * (size_t) i), w1 = __ldcv(in + 3 * (size_t) i + 1), c_raw = __ldcv(in + 3 * (size_t) i + 2);
+            FlagRaw f; f.loc = (int) (unsigned int) w0; f.slot = (unsigned int) (w0 >> 32); f.pid = (unsigned int) w1; f.pad = 0; f.c = c_raw;
+            const int strain = FLAG_STRAIN(f); const unsigned long long c = FLAG_C(f);
+            atomicAdd(&D.press[(size_t) f.loc * CABM_N_STRAINS + strain], c);
+            const unsigned int slot = atomicAdd(&D.loc_cnt[f.loc], 1u);
+            flag_location(D, f.loc, strain, c, f.pid, slot, list_reserve(&D.ctr->n_flags));
+        }
+    }
+}
 // mode 0: remember the census before the status pass; 1: buf = own admissions - discharges; 2: census = remembered + summed buf
 __global__ void k_patients(const Dev D, const int* __restrict__ hosp_ids, const unsigned int n, int* save, int* buf, const int mode) {
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {

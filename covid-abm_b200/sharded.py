@@ -80,6 +80,36 @@ class Shard(Community):
         self._check(fn(self._h, C.byref(p), C.byref(n)))
         return _Buf(p.value or 0, n.value, dtype, self.device)
 
+    # ---- the same protocol inside the library over NCCL (cabm_shard_nccl_init / cabm_shard_run_days) ----
+    def nccl_init(self, dist, group=None):
+        """Collective: rank 0 makes the NCCL id, torch.distributed (any backend) hands it round, every rank joins."""
+        if self.fn.shard_nccl_init is None:
+            raise RuntimeError("this backend has no NCCL path")
+        ident = [None]
+        if self.rank == 0:
+            buf = (C.c_uint8 * 128)()
+            self._check(self.fn.shard_nccl_id(C.cast(buf, C.c_void_p)))
+            ident = [bytes(buf)]
+        if self.world > 1:
+            dist.broadcast_object_list(ident, src=0, group=group)
+        buf = (C.c_uint8 * 128).from_buffer_copy(ident[0])
+        self._check(self.fn.shard_nccl_init(self._h, C.cast(buf, C.c_void_p), self.rank, self.world))
+
+    def peer_memory(self) -> bool:
+        m = C.c_int(0); self._check(self.fn.shard_exchange_mode(self._h, C.byref(m)))
+        return bool(m.value)
+
+    def run_days_nccl(self, n_days: int):
+        first = self.day
+        strain_w = np.zeros((n_days, 4)); exp = np.zeros(n_days)
+        for i in range(n_days):
+            self.update_strain_mix(first + i)
+            strain_w[i] = self.strains; exp[i] = self.expected_imports(first + i)
+        jd = np.ascontiguousarray(self.julian_day[first:first + n_days]); wd = np.ascontiguousarray(self.is_weekday[first:first + n_days])
+        self._check(self.fn.shard_run_days(self._h, first, n_days, jd.ctypes.data_as(C.POINTER(C.c_int32)), wd.ctypes.data_as(C.POINTER(C.c_int32)),
+                                           exp.ctypes.data_as(C.POINTER(C.c_double)), strain_w.ctypes.data_as(C.POINTER(C.c_double))))
+        self.day += n_days
+
     def flags_out(self) -> _Buf:
         b = self._buf(self.fn.shard_flags_out, np.uint8)
         b.n *= abi.SHARD_FLAG_BYTES

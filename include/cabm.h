@@ -311,6 +311,25 @@ int  cabm_shard_census(cabm_t* h, void** buf, size_t* n_u32);
 int  cabm_shard_patients(cabm_t* h, void** buf, size_t* n_i32);
 #define CABM_SHARD_FLAG_BYTES 24
 
+/* The same protocol driven inside the library over NCCL (one handle per process and GPU): no host round trip inside a batch
+   of days. Rank 0 creates an id (cabm_shard_nccl_id), the launcher hands it to every rank by any transport, every rank
+   calls cabm_shard_nccl_init (collective) after cabm_shard_config, then cabm_shard_run_days replaces cabm_run_days.
+   Exchange A is an all-gather of the counts plus an all-gather of fixed-capacity record blocks; days are enqueued four at
+   a time and between groups the host sizes the blocks at 8x the largest count it last saw (floor 8192 records, or the floor
+   set with cabm_shard_exchange_capacity). A day that overflows the block fails the call (CABM_E_NOMEM): raise the floor and
+   re-run from a snapshot. B and C are in-place ncclAllReduce.
+   Where the GPUs of the job can map each other's memory (cudaIpc*, same node, all devices visible to every process: do not
+   narrow CUDA_VISIBLE_DEVICES per rank) exchange A is instead one kernel that reads every peer's flag list in place over
+   NVLink, exactly as many records as that peer counted: no capacity, no day groups. CABM_SHARD_PEER=0 forces the gather. NCCL is dlopen()ed (libnccl.so.2) at init; libraries without it return CABM_E_STATE. */
+#define CABM_NCCL_ID_BYTES 128
+#define CABM_MAX_SHARDS 16
+int  cabm_shard_nccl_id(void* out_id);
+int  cabm_shard_nccl_init(cabm_t* h, const void* id, int rank, int world);
+int  cabm_shard_exchange_capacity(cabm_t* h, size_t records_per_rank);
+int  cabm_shard_exchange_mode(cabm_t* h, int* out_peer_memory);     /* 1: exchange A reads peer memory, 0: NCCL gather */
+int  cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
+                         const double* expected_imports, const double* strain_w);
+
 /* device time (ms, CUDA events) spent in the day pipeline since the last call; resets the accumulator */
 int  cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches);
 

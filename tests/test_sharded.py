@@ -2,7 +2,8 @@
 
 CPU: the oracle backend, shards in one process (LocalExchange) and one shard per process over gloo (DistExchange).
 GPU: the CUDA library, several shards on one device (LocalExchange) against the single-handle CUDA run and the oracle;
-the NCCL path is exercised by `bench.py --shard` under torchrun.
+the in-library NCCL loop (cabm_shard_run_days) with a one-rank communicator on any box and, where the box has two GPUs, with
+two ranks under torchrun (tools/shard_run.py) against the single-handle run.
 """
 import os
 import socket
@@ -152,3 +153,41 @@ def test_cuda_sharded_on_one_device_equals_single(world):
     _assert_same(oracle, sh, f"cuda world {world} vs oracle")
     hs, hh = _sorted_hist(single), _sorted_hist(sh)
     assert hs.size == hh.size > 3000 and np.array_equal(hs, hh)
+
+
+@pytest.mark.gpu
+def test_nccl_day_loop_with_one_rank_equals_run_days():
+    """cabm_shard_run_days (NCCL dlopen()ed, collectives on the library's stream, gathers sized between day groups) == cabm_run_days."""
+    import torch
+    pop, P, tab, attrs = _case(n=30000, days=75)
+    single = cabm.Community(P, pop, tab, attrs=attrs)
+    cuts = cabm.sharded.household_cuts(pop, 1)
+    sh = cabm.sharded.Shard(P, pop, tab, 0, 1, cuts, attrs=attrs, device=torch.device("cuda", 0))
+    sh.nccl_init(None)
+    for c in (single, sh):
+        for pid in range(0, 1500, 11):
+            c.infect(pid, 0, 0)
+    single.run_days(30); sh.run_days_nccl(30)
+    pids = np.random.default_rng(3).choice(int(pop["n_people"]), size=9000, replace=False)
+    single.vaccinate(pids, 30); sh.vaccinate(pids, 30)
+    single.run_days(45); sh.run_days_nccl(45)                      # 45 days = 11 groups of four + one
+    assert np.array_equal(single.ledger_table(), sh.ledger_table())
+    assert np.array_equal(single.current_infections(), sh.current_infections())
+    assert single.ledger_table()[:, 0].sum() > 3000
+    single.close(); sh.close()
+
+
+@pytest.mark.gpu
+def test_nccl_day_loop_on_two_gpus_equals_single_handle():
+    import json
+    import subprocess
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU on this box")
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(port), os.path.join(ROOT, "tools", "shard_run.py"), "--agents", "200000", "--days", "40", "--warm", "20"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert out["native_nccl"] and out["equals_single_handle"] and out["infections"] > 0
