@@ -85,6 +85,13 @@ class Community:
         except Exception:
             pass
 
+    def set_params(self, P: dict, tables: dict | None = None):
+        """Push an edited parameter set (drivers edit Parameters between calls, exp/active-vac/main.cpp:598-605); run_length is fixed."""
+        self.P = P
+        self.T = tables if tables is not None else _params.build_tables(P)
+        self._par_struct, self._par_keep = abi.pack_params(P, self.T)
+        self._check(self.fn.set_params(self._h, C.byref(self._par_struct)))
+
     # ---- reference-facing calls ----
     def setTimedIntervention(self, which: int, values):
         """Community::setSocialDistancingTimedIntervention / updateTimedIntervention (Community.h:396-412)."""

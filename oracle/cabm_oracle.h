@@ -9,6 +9,11 @@
 // control flow (Community.cpp:971-996). The CUDA path derives the same quantities in parallel
 // (no calendar, atomicMin winner resolution); tests/ compare the two bit-for-bit.
 //
+// Pinned against the unmodified reference compiled and run in the build container (oracle/_ref): Person::infect bit-exact
+// on 1500 scripted states (tests/test_reference_kat.py), every per-location exposure probability of Community::tick on a
+// scripted 45-day epidemic (tests/test_foi_reference.py, 13 368 values, worst relative difference 3.4e-11), epidemic curves
+// by KS test over 400 replicates (tools/ks_equivalence.py).
+//
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may link or load this.
 //
 // Exported C symbols mirror include/cabm.h with the prefix cabm_oracle_.

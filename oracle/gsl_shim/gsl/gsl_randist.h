@@ -100,7 +100,7 @@ static inline unsigned int gsl_ran_binomial(const gsl_rng* r, double p, unsigned
 }
 
 static inline unsigned int gsl_ran_poisson(const gsl_rng* r, double mu) {
-    if (r->tape) { return gsl_shim_table_draw(gsl_shim_find_table(GSL_SHIM_T_POISSON, mu, 0.0), r); }
+    if (r->tape) { gsl_shim_script_step(r); return gsl_shim_table_draw(gsl_shim_find_table(GSL_SHIM_T_POISSON, mu, 0.0), r); }
     /* Knuth TAOCP 3.4.1: gamma/binomial reduction for large mu, product-of-uniforms below 10 */
     unsigned int k = 0;
     while (mu > 10.0) {

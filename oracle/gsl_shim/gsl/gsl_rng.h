@@ -35,6 +35,12 @@ struct gsl_shim_tape {
     uint64_t draws_total = 0;
 };
 
+/* VISIT SCRIPT (FoI parity tooling, `ref_driver_probe foi`): Community::public_activity draws one Poisson per patron in
+ * id order and then that patron's location indices (Community.cpp:1006-1022). While a script is set, the k-th Poisson call
+ * on a taped generator first re-keys the tape to (day, purpose, pids[k], 0): the visit stream of the restatement. */
+struct gsl_shim_script { const uint32_t* pids = nullptr; size_t n = 0, next = 0; uint32_t day = 0, purpose = 0; bool overrun = false; };
+inline gsl_shim_script gsl_shim_visits;
+
 struct gsl_rng {
     const gsl_rng_type* type;
     uint32_t s1, s2, s3;        /* taus2 */
@@ -121,5 +127,10 @@ static inline unsigned long int gsl_rng_uniform_int(const gsl_rng* r, unsigned l
 static inline void gsl_shim_tape_attach(gsl_rng* r, gsl_shim_tape* t) { r->tape = t; }
 static inline void gsl_shim_tape_begin(gsl_shim_tape* t, uint32_t day, uint32_t purpose, uint32_t a, uint32_t b) {
     philox_stream_begin(&t->stream, t->seed, day, purpose, a, b);
+}
+static inline void gsl_shim_script_step(const gsl_rng* r) {
+    gsl_shim_script& s = gsl_shim_visits;
+    if (!r->tape || !s.pids) return;
+    if (s.next < s.n) gsl_shim_tape_begin(r->tape, s.day, s.purpose, s.pids[s.next++], 0); else s.overrun = true;
 }
 #endif

@@ -15,9 +15,9 @@
 //   kat  <params.txt> <cases.txt> <out.txt>           function-level known-answer generation in
 //        TAPE MODE (see gsl_shim/gsl/gsl_rng.h): Person::infect / isCrossProtected /
 //        isVaccineProtected evaluated on scripted person states with Philox-keyed draws.
-//   foi  <params.txt> <pop_dir> <tag> <day> <out.txt> runs to <day>, then dumps the agent state
-//        and the reference's own hot-location calendar slice _isHot[day] (Community.h:133) so the
-//        oracle's derived per-location infectious pressure can be compared with it.
+//   foi  <params.txt> <pop_dir> <tag> <script.txt> <out.txt>   (binary ref_driver_probe only) per-location force of
+//        infection of Community::tick on a scripted epidemic, read out by compile-time probes (foi_probe.h); see
+//        ref_driver_kat.inc.
 #include <chrono>
 #include <map>
 #include <string>
@@ -26,6 +26,9 @@
 #include <sstream>
 #include <iostream>
 #include "simulator.h"
+#ifdef CABM_FOI_PROBE
+#include "foi_probe_log.h"
+#endif
 #include "../include/cabm.h"
 
 using namespace std;
