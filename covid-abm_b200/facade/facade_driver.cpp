@@ -9,6 +9,11 @@
 //   facade_driver sim <params.txt> <pop_dir> <tag> <out_prefix> [campaign]
 //       writes <out_prefix>.plot.csv (simulate_epidemic's plot log) and <out_prefix>.ledger.csv (same columns as
 //       oracle/ref_driver run) and prints one JSON line with wall-clock timings.
+//   facade_driver cache_restore <params.txt> <pop_dir> <tag> <out_prefix> <cache_day> [campaign]
+//       the reference's cache-and-restore check (tests/cache_and_restore/cache_and_restore_check.sh: equal checksums of the
+//       plot logs written before and after a restore) on the facade: days [0, cache_day) run, the reference's own
+//       SimulationCache (behavior_tuner.h:39-87) is taken, the tail runs to the end, restore_from_cache
+//       (behavior_tuner.h:490-508) rewinds, the tail runs again -- twice. Writes <out_prefix>.pass{1,2,3}.csv; they must be equal.
 //   `campaign` = 1 attaches a general Vac_Campaign (the reference's class) so that Community::vaccinate and the dose
 //       bookkeeping run; 2 adds ring vaccination of traced contacts (needs begin_contact_tracing < run_length in the file).
 #include <chrono>
@@ -71,8 +76,90 @@ static int dump_tables(const char* params, const char* path) {
     return 0;
 }
 
+// the strain urn of simulate_epidemic (simulator.h:341-372), which the function keeps inline
+static void advance_strain_urn(const Date* date, const vector<string>& mid, vector<double>& strains) {
+    if (mid.size() < 3) return;
+    if (*date >= mid[0] and *date < mid[1]) {
+        if (strains[WILDTYPE] > 1) { strains[WILDTYPE]--; strains[ALPHA]++; }
+    } else if (*date >= mid[1] and *date < mid[2]) {
+        if (strains[WILDTYPE] > 1) { strains[WILDTYPE]--; strains[DELTA]++; }
+        if (strains[ALPHA] > 1)    { strains[ALPHA]--;    strains[DELTA]++; }
+    } else if (*date >= mid[2]) {
+        for (int i = 0; i < 5; ++i) for (StrainType st : { WILDTYPE, ALPHA, DELTA }) if (strains[st] > 1) { strains[st]--; strains[OMICRON]++; }
+    }
+}
+
+static int cache_restore(int argc, char** argv) {
+    if (argc < 7) { cerr << "usage: facade_driver cache_restore <params> <pop_dir> <tag> <out_prefix> <cache_day> [campaign]\n"; return 2; }
+    const KV kv = read_kv(argv[2]);
+    Parameters* par = make_parameters(kv);
+    set_pop_files(par, argv[3], argv[4]);
+    const string prefix = argv[5];
+    const size_t cache_day = (size_t) atol(argv[6]);
+    const int campaign = argc > 7 ? atoi(argv[7]) : 1;
+    if (campaign < 1) { cerr << "SimulationCache needs a Vac_Campaign (behavior_tuner.h:56)\n"; return 2; }
+    gsl_rng_set(RNG, par->randomseed); gsl_rng_set(VAX_RNG, par->randomseed); gsl_rng_set(REPORTING_RNG, par->randomseed);
+    Community* community = build_community(par);
+    community->setVac_Campaign(simple_campaign(par, community, 20, max<int>(1, (int) community->getNumPeople() / 200), campaign == 2));
+    const vector<string> mid = kv.count("mutant_intro_dates") ? kv.at("mutant_intro_dates") : vector<string>();
+    vector<TimeSeriesAnchorPoint> sd_anchors = { { Date::to_ymd(0, par), 0.0 }, { Date::to_ymd(par->runLength / 2, par), 0.4 }, { Date::to_ymd(par->runLength - 1, par), 0.2 } };
+    community->setSocialDistancingTimedIntervention(sd_anchors);
+    SimulationLedger* ledger = new SimulationLedger();
+    ledger->strains = { 50.0, 0.0, 0.0, 0.0 };
+    Date* date = community->get_date();
+
+    auto run_to = [&](size_t end_day, ostream* out) {                                      // the hot-path part of simulate_epidemic's loop body
+        for (; date->day() < (signed) end_day; date->increment()) {
+            const size_t d = date->day();
+            if (d == 0) seed_epidemic(par, community, WILDTYPE);
+            community->tick();
+            advance_strain_urn(date, mid, ledger->strains);
+            seed_epidemic(par, community, date, ledger->strains);
+            if (not out) continue;
+            Vac_Campaign* vc = community->getVac_Campaign();
+            *out << d << ',' << community->getNumNewlyInfected()[d] << ',' << community->getNumNewlySymptomatic()[d] << ',' << community->getNumNewlyDead()[d]
+                 << ',' << community->getNumHospPrev()[d] << ',' << community->getNumDetectedCasesReport()[d] << ',' << community->getNumVaccinatedCases()[d]
+                 << ',' << vc->get_doses_used(d, STANDARD_ALLOCATION) << ',' << vc->get_doses_used(d, URGENT_ALLOCATION)
+                 << ',' << community->getNumPeopleQuarantining(d) << ',' << community->getNumInfected(d) << '\n';
+        }
+    };
+    auto tail = [&](int pass) {
+        ofstream out(prefix + ".pass" + to_string(pass) + ".csv");
+        out << "day,inf,symp,dead,hosp_prev,det_case_report,vax_cases,std_doses,urg_doses,quarantining,infected\n";
+        run_to(par->runLength, &out);
+        unsigned long long h = 1469598103934665603ull; size_t n_inf = 0, n_vax = 0;       // every infection and dose of every person
+        for (Person* p : community->getPeople()) {
+            for (Infection* inf : p->getInfectionHistory()) {
+                ++n_inf;
+                for (long v : { (long) p->getID(), (long) inf->getInfectedTime(), (long) inf->getStrain(), (long) inf->getSymptomTime(), (long) inf->getDeathTime(),
+                                (long) (inf->getInfectedBy() ? inf->getInfectedBy()->getID() : -1), (long) inf->secondary_infection_tally() })
+                    h = (h ^ (unsigned long long) v) * 1099511628211ull;
+            }
+            n_vax += p->getNumVaccinations();
+            h = (h ^ (unsigned long long) p->getNumVaccinations()) * 1099511628211ull;
+        }
+        out << "people," << n_inf << ',' << n_vax << ',' << h << ',' << community->getCumulIncidenceByOutcome(DEATH) << '\n';
+        return n_inf;
+    };
+
+    run_to(cache_day, nullptr);
+    SimulationCache* cache = new SimulationCache(community, ledger, RNG, REPORTING_RNG, VAX_RNG);      // behavior_tuner.h:52-64
+    size_t n_inf[3];
+    n_inf[0] = tail(1);
+    for (int pass = 2; pass <= 3; ++pass) {
+        restore_from_cache(community, date, cache, ledger, sd_anchors);                                 // behavior_tuner.h:490-508
+        if ((size_t) date->day() != cache_day) { cerr << "restore did not rewind the date\n"; return 3; }
+        n_inf[pass - 1] = tail(pass);
+    }
+    printf("{\"impl\": \"facade\", \"agents\": %zu, \"days\": %zu, \"cache_day\": %zu, \"infections\": [%zu, %zu, %zu]}\n",
+           (size_t) community->getNumPeople(), (size_t) par->runLength, cache_day, n_inf[0], n_inf[1], n_inf[2]);
+    delete cache; delete community;
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc == 4 and string(argv[1]) == "tables") return dump_tables(argv[2], argv[3]);
+    if (argc >= 2 and string(argv[1]) == "cache_restore") return cache_restore(argc, argv);
     if (argc < 6 or string(argv[1]) != "sim") { cerr << "usage: facade_driver sim <params> <pop_dir> <tag> <out_prefix> [campaign]\n"; return 2; }
     const KV kv = read_kv(argv[2]);
     Parameters* par = make_parameters(kv);

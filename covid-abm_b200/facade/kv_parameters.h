@@ -93,6 +93,15 @@ inline Parameters* make_parameters(const KV& kv) {
     par->define_susceptibility_and_pathogenicity();       // the reference's own tables (Parameters.cpp:128-195)
     par->probDailyExposure = DV(kv, "prob_daily_exposure");
     par->behaviorInputFilename = ""; par->behaviorOutputFilename = "";
+    // optional: the behaviour autotuner of simulate_epidemic (exp/active-vac/main.cpp:93-97,257-262)
+    if (kv.count("behavioral_autotuning") and I(kv, "behavioral_autotuning")) {
+        par->behavioral_autotuning = true;
+        par->tuning_window = I(kv, "tuning_window"); par->num_preview_windows = I(kv, "num_preview_windows");
+        par->rCaseDeathFilename = kv.at("rcasedeath_file").at(0);
+        par->behaviorOutputFilename = kv.at("behavior_output_file").at(0);
+        par->behavior_fitting_data_target = CASES;
+        par->death_tuning_offset = 18;
+    }
     return par;
 }
 

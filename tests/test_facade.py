@@ -140,6 +140,93 @@ def test_facade_agrees_with_unmodified_reference_coarsely(tmp_path):
         assert mf > 0 and mr > 0 and 0.3 < mf / mr < 3.0, (name, mf, mr)
 
 
+def _cache_restore(driver, tmp, P, tab, cache_day, campaign, tag):
+    pf = os.path.join(str(tmp), f"params_{tag}.txt"); cabm.params.write_text(P, tab, pf)
+    prefix = os.path.join(str(tmp), f"cr_{tag}")
+    r = subprocess.run([driver, "cache_restore", pf, str(tmp), "f", prefix, str(cache_day), str(campaign)], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    return info, [open(f"{prefix}.pass{k}.csv").read() for k in (1, 2, 3)]
+
+
+@needs_oracle_driver
+def test_cache_and_restore_check_through_the_facade(tmp_path):
+    """The reference's own regression check (tests/cache_and_restore/: equal checksums of the plot logs before and after a
+    restore) with its own SimulationCache / restore_from_cache (behavior_tuner.h:39-87,490-508): CommunityLedger copy = device
+    snapshot, load_from_cache = device restore + roll-back of the host mirrors, Vac_Campaign::quick_cache, the three generators."""
+    pop, P, tab = _case(tmp_path, n=12000, days=100, tracing_from=35)
+    info, passes = _cache_restore(DRV_ORACLE, tmp_path, P, tab, cache_day=45, campaign=2, tag="a")
+    assert passes[0] == passes[1] == passes[2], "a restored run differs from the run the cache was taken from"
+    rows = passes[0].strip().splitlines()
+    assert len(rows) == 1 + (100 - 45) + 1 and rows[1].startswith("45,")
+    body = np.array([[float(x) for x in r.split(",")] for r in rows[1:-1]])
+    assert body[:, 1].sum() > 300 and body[:, 7].sum() > 1000 and body[:, 8].sum() > 0 and body[:, 9].max() > 0   # infections, doses, ring doses, quarantine
+    assert info["infections"][0] == info["infections"][1] == info["infections"][2] > 1000
+    # the cache matters: with another cache day the tail rows of the shared days are still the same epidemic
+    _, other = _cache_restore(DRV_ORACLE, tmp_path, P, tab, cache_day=70, campaign=2, tag="b")
+    assert other[0] == other[1] == other[2]
+    assert other[0].strip().splitlines()[1:-1] == rows[1 + 25:-1]
+
+
+def _autotuned(driver, tmp, P, tab, cases, tag, n_agents):
+    """simulate_epidemic with par->behavioral_autotuning (exp/active-vac/main.cpp:93-97): the reference's behaviour autotuner
+    (behavior_tuner.h) bisects the social-distancing anchor of every 14-day window against reported cases, re-running each window
+    from its SimulationCache until the fit is good. The 'empirical' series is half of what the untuned run reported, scaled to
+    Florida's population as score_fit expects (behavior_tuner.h:261-265)."""
+    import datetime
+    d0 = datetime.date(2020, 2, 5)
+    csv = os.path.join(str(tmp), f"rcasedeath_{tag}.csv")
+    with open(csv, "w") as f:
+        f.write("Date,rcase,x,y,rdeath\n")
+        for d, c in enumerate(cases):
+            f.write(f"{d0 + datetime.timedelta(days=d)},{int(round(c * 0.5 * 21538187 / n_agents))},0,0,0\n")
+    Pa = dict(P); Pa.update(seed=5, behavioral_autotuning=1, tuning_window=14, num_preview_windows=3, rcasedeath_file=csv,
+                            behavior_output_file=os.path.join(str(tmp), f"anchors_{tag}.csv"))
+    pf = os.path.join(str(tmp), f"params_{tag}.txt"); cabm.params.write_text(Pa, tab, pf)
+    prefix = os.path.join(str(tmp), f"auto_{tag}")
+    r = subprocess.run([driver, "sim", pf, str(tmp), "f", prefix, "1"], capture_output=True, text=True, timeout=1500, cwd=str(tmp))   # gen_simvis writes ./plot_log.csv
+    assert r.returncode == 0, r.stderr[-2000:]
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    return info, open(prefix + ".plot.csv").read(), open(prefix + ".ledger.csv").read(), open(Pa["behavior_output_file"]).read(), r.stderr
+
+
+@needs_oracle_driver
+def test_behaviour_autotuner_runs_on_the_facade(tmp_path):
+    pop, P, tab = _case(tmp_path, n=12000, days=120)
+    base, led, _, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 5, campaign=1, tag="untuned")
+    info, plot, ledger, anchors, err = _autotuned(DRV_ORACLE, tmp_path, P, tab, led["det_case_report"], "a", 12000)
+    rows = anchors.strip().splitlines()
+    assert rows[0] == "date,anchor_val" and len(rows) >= 6
+    vals = [float(r.split(",")[1]) for r in rows[1:]]
+    assert max(vals) > 0.3 and all(0.0 <= v <= 1.0 for v in vals)            # the tuner had to raise distancing to halve the cases
+    assert err.count("Decision made.") >= 4                                   # windows tuned, each after several restores
+    assert info["infections"] < 0.7 * base["infections"]
+    info2, plot2, ledger2, anchors2, _ = _autotuned(DRV_ORACLE, tmp_path, P, tab, led["det_case_report"], "b", 12000)
+    assert (plot2, ledger2, anchors2) == (plot, ledger, anchors)              # restores are exact, so the search is reproducible
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not (os.path.exists(DRV_CUDA) and os.path.exists(DRV_ORACLE)), reason="facade drivers not built")
+def test_behaviour_autotuner_cuda_equals_oracle(tmp_path):
+    pop, P, tab = _case(tmp_path, n=20000, days=120)
+    _, led, _, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 5, campaign=1, tag="untuned")
+    ic, plot_c, led_c, anch_c, _ = _autotuned(DRV_CUDA, tmp_path, P, tab, led["det_case_report"], "cuda", 20000)
+    io, plot_o, led_o, anch_o, _ = _autotuned(DRV_ORACLE, tmp_path, P, tab, led["det_case_report"], "oracle", 20000)
+    assert anch_c == anch_o and led_c == led_o and plot_c == plot_o
+    assert ic["infections"] == io["infections"] > 500
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not (os.path.exists(DRV_CUDA) and os.path.exists(DRV_ORACLE)), reason="facade drivers not built")
+def test_cache_and_restore_check_on_the_cuda_library(tmp_path):
+    pop, P, tab = _case(tmp_path, n=30000, days=110, tracing_from=40)
+    info, passes = _cache_restore(DRV_CUDA, tmp_path, P, tab, cache_day=50, campaign=2, tag="cuda")
+    assert passes[0] == passes[1] == passes[2]
+    _, ref = _cache_restore(DRV_ORACLE, tmp_path, P, tab, cache_day=50, campaign=2, tag="oracle")
+    assert passes[0] == ref[0], "CUDA library and oracle disagree behind the same facade"
+    assert info["infections"][0] > 3000
+
+
 @pytest.mark.gpu
 @pytest.mark.skipif(not (os.path.exists(DRV_CUDA) and os.path.exists(DRV_ORACLE)), reason="facade drivers not built")
 @pytest.mark.parametrize("campaign", [0, 1, 2])
