@@ -627,3 +627,63 @@ void Community::_reviseSocialDistancingTimedIntervention(double val) {
     v.resize(v.size() - _par->tuning_window);
     _extendSocialDistancingTimedIntervention(val);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// post-run analytics: every experiment driver asks for Rt by day of infection (exp/active-vac/main.cpp:482,749). They read
+// the infector links of the device's infection log through the Person / Infection proxies.
+// ---------------------------------------------------------------------------------------------------------------------
+// Community.cpp:631-654: entry d = (infections that began on day d, mean number of infections each of them went on to cause)
+vector<pair<size_t, double>> Community::getMeanNumSecondaryInfections() {
+    vector<size_t> n(_par->runLength, 0), caused(_par->runLength, 0);
+    for (Person* p : getPeople()) for (Infection* inf : p->getInfectionHistory()) {
+        const int onset = inf->getInfectedTime();
+        if (onset < 0 or onset >= (int) _par->runLength) continue;                        // historical infection
+        n[onset]++; caused[onset] += inf->secondary_infection_tally();
+    }
+    vector<pair<size_t, double>> Rt(_par->runLength, { 0, 0.0 });
+    for (size_t d = 0; d < Rt.size(); ++d) if (n[d]) Rt[d] = { n[d], (double) caused[d] / (double) n[d] };
+    return Rt;
+}
+
+// Community.cpp:1425-1441: histogram of the number of secondary infections per infection, at least ten bins
+vector<size_t> Community::generateOffspringDistribution() {
+    vector<size_t> hist(10, 0);
+    for (Person* p : getPeople()) for (Infection* inf : p->getInfectionHistory()) {
+        const size_t k = inf->secondary_infection_tally();
+        if (k >= hist.size()) hist.resize(k + 1, 0);
+        hist[k]++;
+    }
+    return hist;
+}
+
+// Community.cpp:1281-1327: household secondary attack rate of the month two months back, called on the first of a month.
+// An index case is somebody whose latest infection began between the start of the survey month and one survey-month length
+// past today, and whose LAST-listed housemate was not infected in the ten days up to that infection (the reference's loop
+// keeps the verdict of the last housemate it looks at; kept). Each index with at least one household member among the
+// infections it caused contributes (such members) / (household size); the mean of those is returned.
+double Community::getHouseholdSecondaryAttackRate(vector<Person*>& pop) {
+    if (pop.empty()) pop = getPeople();
+    if (not (_date->month() >= 3)) return 0.0;
+    const int today = _date->day();
+    const size_t jm = _date->julianMonth();
+    const size_t survey_m = (int) jm - 2 >= 1 ? jm - 2 : jm + 10, between_m = (int) jm - 1 >= 1 ? jm - 1 : jm + 11;
+    const vector<size_t>& dim = _date->isLeap() ? LEAP_DAYS_IN_MONTH : COMMON_DAYS_IN_MONTH;
+    const int first = today - (int) dim.at(between_m - 1) - (int) dim.at(survey_m - 1), last = today + (int) dim.at(survey_m - 1);
+    assert(first >= 0);
+    vector<double> sar;
+    for (Person* p : pop) {
+        if (not p->hasBeenInfected()) continue;
+        const int t = p->getInfectedTime();
+        if (t < first or t > last) continue;
+        bool index_case = false;
+        for (Person* fam : p->getHomeLoc()->getPeople()) {
+            if (fam == p) continue;
+            index_case = not (fam->hasBeenInfected() and fam->getInfectedTime() >= t - 10 and fam->getInfectedTime() <= t);
+        }
+        if (not index_case) continue;
+        int at_home = 0;
+        for (Infection* sec : p->getInfection()->get_infections_caused()) if (sec->getInfectionOwner()->getHomeLoc() == p->getHomeLoc()) ++at_home;
+        if (at_home > 0) sar.push_back((double) at_home / p->getHomeLoc()->getNumPeople());
+    }
+    return covid::util::mean(sar);
+}

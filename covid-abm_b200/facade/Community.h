@@ -67,6 +67,10 @@ class Community {
     size_t getNumNaive();
     double getNumPeopleQuarantining(int day);
     std::map<std::string, double> calculate_vax_stats(int day);
+    // post-run analytics over the infection records (Community.cpp:631-654,1281-1327,1425-1441), on the host mirror of the device log
+    std::vector<std::pair<size_t, double>> getMeanNumSecondaryInfections();
+    std::vector<size_t> generateOffspringDistribution();
+    double getHouseholdSecondaryAttackRate(std::vector<Person*>& pop);
     double doSerosurvey(const ImmuneStateType ist, const std::vector<Person*>& pop, int time);
 
     void setVac_Campaign(Vac_Campaign* vc) { vac_campaign = vc; }

@@ -202,6 +202,16 @@ int main(int argc, char** argv) {
         n_hist += p->getNumNaturalInfections(); n_vax += p->getNumVaccinations();
         for (Infection* inf : p->getInfectionHistory()) n_secondary += inf->secondary_infection_tally();
     }
+    // Rt by day of infection and the offspring distribution, as every exp/ driver reads them after the run (main.cpp:482,749)
+    const vector<pair<size_t, double>> Rt = community->getMeanNumSecondaryInfections();
+    const vector<size_t> offspring = community->generateOffspringDistribution();
+    ofstream rt(prefix + ".rt.csv");
+    rt << "day,infections,mean_secondary\n";
+    for (size_t d = 0; d < Rt.size(); ++d) rt << d << ',' << Rt[d].first << ',' << Rt[d].second << '\n';
+    rt << "offspring"; for (size_t k : offspring) rt << ',' << k; rt << '\n';
+    vector<Person*> everybody;
+    rt << "hsar," << community->getHouseholdSecondaryAttackRate(everybody) << '\n';
+    rt.close();
     printf("{\"impl\": \"facade\", \"agents\": %zu, \"days\": %zu, \"load_s\": %.3f, \"simulate_epidemic_s\": %.4f, \"agent_days_per_s\": %.6g, "
            "\"infections\": %zu, \"secondary_links\": %zu, \"doses\": %zu, \"urgent_doses\": %zu, \"quarantine_index\": %.6f, \"cumul_death\": %zu}\n",
            n, (size_t) par->runLength, load_s, sim_s, (double) n * par->runLength / sim_s, n_hist, n_secondary, n_vax, urg, quar_days,

@@ -92,6 +92,17 @@ def test_simulate_epidemic_runs_through_the_facade(tmp_path):
     assert np.all(np.diff(cov1) >= 0) and cov1[-1] > 0.1 and cov1[15] == 0.0
     seroprev = np.array([float(r[28]) for r in rows])
     assert seroprev[-1] > 0.02 and np.all((seroprev >= 0) & (seroprev <= 1))
+    # post-run analytics every exp/ driver reads (getMeanNumSecondaryInfections, generateOffspringDistribution, hSAR)
+    rt = open(os.path.join(str(tmp_path), "out_a.rt.csv")).read().strip().splitlines()
+    body = np.array([[float(x) for x in r.split(",")] for r in rt[1:1 + days]])
+    assert body[:, 1].sum() == info["infections"] and round((body[:, 1] * body[:, 2]).sum()) == info["secondary_links"]
+    early = body[5:40]; early = early[early[:, 1] > 0]
+    assert 0.8 < np.average(early[:, 2], weights=early[:, 1]) < 6.0                    # a growing epidemic: Rt above ~1 early on
+    off = np.array([int(x) for x in rt[1 + days].split(",")[1:]])
+    assert rt[1 + days].startswith("offspring") and len(off) >= 10
+    assert off.sum() == info["infections"] and (off * np.arange(len(off))).sum() == info["secondary_links"]
+    hsar = float(rt[2 + days].split(",")[1])
+    assert 0.0 < hsar <= 1.0
     # same seed, same output; another seed, another epidemic
     info2, _, plot2, _, _ = _run(DRV_ORACLE, tmp_path, P, tab, 5, campaign=True, tag="b")
     assert plot2 == plot
@@ -235,6 +246,7 @@ def test_facade_cuda_equals_facade_oracle(tmp_path, campaign):
     ic, _, plot_c, led_c, _ = _run(DRV_CUDA, tmp_path, P, tab, 9, campaign, tag="cuda")
     io, _, plot_o, led_o, _ = _run(DRV_ORACLE, tmp_path, P, tab, 9, campaign, tag="oracle")
     assert led_c == led_o, "ledger differs between the CUDA library and the oracle behind the same facade"
+    assert open(os.path.join(str(tmp_path), "out_cuda.rt.csv")).read() == open(os.path.join(str(tmp_path), "out_oracle.rt.csv")).read(), "Rt / offspring / hSAR differ"
     assert plot_c == plot_o, "simulate_epidemic's plot log differs"
     for k in ("infections", "secondary_links", "doses", "urgent_doses", "quarantine_index", "cumul_death"):
         assert ic[k] == io[k], k
