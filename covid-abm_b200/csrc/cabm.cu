@@ -39,6 +39,7 @@ struct cabm {
     uint64_t launches_per_day = 11;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
+    int* h_pin = nullptr;                        // pinned, device-visible scratch: single-word results are written by the kernel itself (no staged copy)
     const FlagRaw* peer_flags[CABM_MAX_SHARDS] = { nullptr }; int peer_mode = 0;      // exchange A over peer memory (cudaIpc mappings of the other handles' flag lists)
     int* d_hosp_ids = nullptr; int* d_pat_save = nullptr; int* d_pat_buf = nullptr; unsigned int n_hosp = 0; unsigned int n_flags_own = 0;   // sharding
     int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
@@ -228,6 +229,7 @@ int cabm_destroy(cabm_t* h) {
     for (int r = 0; r < CABM_MAX_SHARDS; ++r) if (h->peer_flags[r] && r != h->d.shard_rank) cudaIpcCloseMemHandle((void*) h->peer_flags[r]);
     if (h->d_xrecv) cudaFree(h->d_xrecv);
     if (h->h_xcounts) cudaFreeHost(h->h_xcounts);
+    if (h->h_pin) cudaFreeHost(h->h_pin);
     for (void* p : h->allocs) cudaFree(p);
     if (h->h_ctx) cudaFreeHost(h->h_ctx);
     cudaEventDestroy(h->e0); cudaEventDestroy(h->e1); cudaStreamDestroy(h->stream);
@@ -406,12 +408,11 @@ int cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_i
     if (!h) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (pid >= h->d.N || strain < 0 || strain >= CABM_N_STRAINS) return CABM_E_ARG;
     cudaSetDevice(h->device);
-    k_seed_one<<<1, 32, 0, h->stream>>>(h->d, pid, strain, sim_day, h->d_tmp_int);
-    int res = 0;
-    CK(cudaMemcpyAsync(&res, h->d_tmp_int, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (!h->h_pin) { CK(cudaHostAlloc((void**) &h->h_pin, 16 * sizeof(int), cudaHostAllocMapped)); }
+    k_seed_one<<<1, 32, 0, h->stream>>>(h->d, pid, strain, sim_day, h->h_pin);     // the result lands in pinned host memory over PCIe
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());
-    if (out_infected) *out_infected = res;
+    if (out_infected) *out_infected = h->h_pin[0];
     return CABM_OK;
 }
 

@@ -4,6 +4,7 @@
 // reference's own file formats (Community.cpp:174-524), everything that happens inside a simulated day is one C-ABI
 // call into the CUDA library (include/cabm.h). CABM_FN(x) prepends the library prefix, so the same file links against
 // the product (cabm_) and -- for CPU-only tests of this host logic -- against the oracle (cabm_oracle_).
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -12,6 +13,7 @@
 #include <sstream>
 #include <gsl/gsl_rng.h>
 #include <gsl/gsl_randist.h>
+#include "fast_text.h"
 #include "Community.h"
 #include "Person.h"
 #include "../../include/cabm.h"
@@ -51,6 +53,26 @@ Community* Person::_community = nullptr;
 // ---------------------------------------------------------------------------------------------------------------------
 // lifecycle
 // ---------------------------------------------------------------------------------------------------------------------
+// CABM_FACADE_TIMING=1: wall-clock seconds per facade entry point, one line on stderr when the community is destroyed
+namespace {
+struct FtSlot { const char* name; double s = 0; unsigned long n = 0; };
+FtSlot ft_slots[] = { {"load_locations"}, {"load_population"}, {"upload"}, {"tick_device"}, {"tick_tracing"}, {"tick_vaccinate"}, {"infect"},
+                      {"refresh_people"}, {"ledger_table"}, {"diagnostics"}, {"serosurvey_list"} };
+enum { FT_LOADLOC, FT_LOADPOP, FT_UPLOAD, FT_TICK, FT_TRACE, FT_VAX, FT_INFECT, FT_REFRESH, FT_LEDGER, FT_DIAG, FT_SERO, FT_N };
+const bool ft_on = getenv("CABM_FACADE_TIMING") != nullptr;
+struct Ft {
+    int k; std::chrono::steady_clock::time_point t0;
+    explicit Ft(int k_) : k(k_) { if (ft_on) t0 = std::chrono::steady_clock::now(); }
+    ~Ft() { if (ft_on) { ft_slots[k].s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); ft_slots[k].n++; } }
+};
+void ft_report() {
+    if (!ft_on) return;
+    cerr << "facade_timing {";
+    for (int k = 0; k < FT_N; ++k) cerr << (k ? ", " : "") << '"' << ft_slots[k].name << "\": [" << ft_slots[k].s << ", " << ft_slots[k].n << "]";
+    cerr << "}" << endl;
+}
+}
+
 Community::Community(const Parameters* parameters, Date* date)
     : _date(date), _day(0), cmty_ledger(nullptr), vac_campaign(nullptr), _h(nullptr), _uploaded(false), _ti_dirty(true), _epoch(1),
       _ledger_epoch(0), _diag_epoch(0), _diag_day(-1), _log_read(0) {
@@ -66,6 +88,7 @@ Community::Community(const Parameters* parameters, Date* date)
 }
 
 Community::~Community() {
+    ft_report();
     if (_h) CABM_FN(destroy)(_h);
     if (_date) delete _date;
     if (cmty_ledger) delete cmty_ledger;
@@ -123,6 +146,7 @@ void Community::device_changed() { ++_epoch; Person::_stale = true; }
 // ---------------------------------------------------------------------------------------------------------------------
 cabm* Community::handle() {
     if (_uploaded) return _h;
+    Ft ft(FT_UPLOAD);
     cabm_params par; vector<double> pfd, imr;
     cabm_facade_fill_params(_par, &par, pfd, imr);
     int rc = CABM_FN(set_params)(_h, &par);
@@ -183,15 +207,16 @@ void Community::push_interventions() {
 static double pixel_of(double coord) { return floor(coord / 0.01) * 0.01 + 0.005; }           // Community.cpp:396-398
 
 bool Community::loadLocations(string locationFilename, string networkFilename) {
-    ifstream in(locationFilename);
-    if (!in) { cerr << "ERROR: locations file " << locationFilename << " not found." << endl; return false; }
+    Ft ft(FT_LOADLOC);
+    cabm_text::Table in(locationFilename);
+    if (!in.ok()) { cerr << "ERROR: locations file " << locationFilename << " not found." << endl; return false; }
     _location.clear();
-    map<Location*, int> hospital_of;
-    string row, type_s, ess_s, pub_s;
-    while (getline(in, row)) {
-        istringstream f(row);
+    vector<pair<Location*, int>> hospital_of;
+    while (in.next_row()) {
         int locid, hfid; double x, y, compliance;
-        if (!(f >> locid >> x >> y >> type_s >> ess_s >> hfid)) continue;                   // header or malformed line
+        if (!(in.number(locid) and in.number(x) and in.number(y))) continue;               // header or malformed line
+        const string_view type_s = in.field(), ess_s = in.field();
+        if (type_s.empty() or ess_s.empty() or !in.number(hfid)) continue;
         if (locid != (int) _location.size()) { cerr << "ERROR: Location ID's must be sequential integers starting at 0" << endl; return false; }
         LocationType lt = type_s == "h" ? HOUSE : type_s == "w" ? WORK : type_s == "s" ? SCHOOL : type_s == "hf" ? HOSPITAL : type_s == "n" ? NURSINGHOME
                                                                                                                              : NUM_OF_LOCATION_TYPES;
@@ -202,10 +227,12 @@ bool Community::loadLocations(string locationFilename, string networkFilename) {
         loc->setX(x); loc->setY(y); loc->setType(lt); loc->setEssential(ess_s != "n");
         loc->setPixel(pixel_of(x), pixel_of(y));
         _pixelMap[{ loc->getXPixel(), loc->getYPixel() }].push_back(loc);
-        if ((f >> compliance) and compliance >= 0) loc->setRiskiness(1.0 - compliance);
+        const bool have_compliance = in.number(compliance);                                 // a field that is not a number ends the row, as a failed stream does
+        if (have_compliance and compliance >= 0) loc->setRiskiness(1.0 - compliance);
         else if (lt == HOUSE) loc->setRiskiness(gsl_rng_uniform(RNG));                     // Community.cpp:461-464
         PublicTransmissionType pt = NO_PUBLIC_TRANSMISSION;
-        if ((f >> pub_s) and pub_s != "N") {
+        const string_view pub_s = have_compliance ? in.field() : string_view();
+        if (not pub_s.empty() and pub_s != "N") {
             pt = pub_s == "H" ? HIGH_PUBLIC_TRANSMISSION : pub_s == "L" ? LOW_PUBLIC_TRANSMISSION : NUM_OF_PUBLIC_TRANSMISSION_TYPES;
             if (pt == NUM_OF_PUBLIC_TRANSMISSION_TYPES) { cerr << "ERROR: Unknown value for \"public transmission\" status: " << pub_s << endl; return false; }
             _public_locations.push_back(loc);
@@ -213,18 +240,17 @@ bool Community::loadLocations(string locationFilename, string networkFilename) {
         loc->setPublicTransmissionRisk(pt);
         _location.push_back(loc);
         _location_map[lt].insert(loc);
-        if (hfid >= 0) hospital_of[loc] = hfid;
+        if (hfid >= 0) hospital_of.push_back({ loc, hfid });
     }
-    in.close();
     for (auto& kv : hospital_of) {
         if (kv.second >= (int) _location.size() or _location[kv.second]->getType() != HOSPITAL) { cerr << "ERROR: hospital id " << kv.second << " is not a hospital" << endl; return false; }
         kv.first->setHospital(_location[kv.second]);
     }
-    in.open(networkFilename);
-    if (!in) { cerr << "ERROR: network file " << networkFilename << " not found." << endl; return false; }
-    while (getline(in, row)) {
-        istringstream f(row); int a, b;
-        if (f >> a >> b) {
+    cabm_text::Table net(networkFilename);
+    if (!net.ok()) { cerr << "ERROR: network file " << networkFilename << " not found." << endl; return false; }
+    while (net.next_row()) {
+        int a, b;
+        if (net.number(a) and net.number(b)) {
             assert(a >= 0 and b >= 0 and a < (int) _location.size() and b < (int) _location.size());
             _location[a]->addNeighbor(_location[b]); _location[b]->addNeighbor(_location[a]);
         }
@@ -233,56 +259,57 @@ bool Community::loadLocations(string locationFilename, string networkFilename) {
 }
 
 bool Community::loadPopulation(string populationFilename, string comorbidityFilename, string publicActivityFilename, string immunityFilename) {
-    ifstream in(populationFilename);
-    if (!in) { cerr << "ERROR: " << populationFilename << " not found." << endl; return false; }
-    string row;
-    while (getline(in, row)) {
-        istringstream f(row); int pid, hid, sex, age, did;
-        if (!(f >> pid >> hid >> sex >> age >> did)) continue;
-        if (pid != (int) _people.size()) { cerr << "ERROR: Person ID's must be sequential integers starting at 0" << endl; return false; }
-        assert((int) _location.size() > hid and (int) _location.size() > did);
-        Person* p = new Person();
-        _people.push_back(p);
-        p->setAge(age); p->setSex((SexType) sex);
-        // load-time immunity attributes, drawn exactly as the reference does (Community.cpp:212-215) with its own Parameters methods
-        p->setStartingNaturalEfficacy(_par->sampleStartingNaturalEfficacy(RNG));
-        p->setImmunityQuantile(gsl_rng_uniform(RNG));
-        p->setNaturalImmunityDuration(_par->immunityDuration(p->getImmunityQuantile(), p->getStartingNaturalEfficacy()));
-        p->setCrossProtectionProbability(gsl_rng_uniform(RNG));
-        p->setHomeLoc(_location[hid]); _location[hid]->addPerson(p);
-        if (did >= 0) { p->setDayLoc(_location[did]); _location[did]->addPerson(p); }
-        if (_location[hid]->getType() == NURSINGHOME) p->setLongTermCare(true);
-    }
-    in.close();
-    if (comorbidityFilename.length() > 0) {
-        in.open(comorbidityFilename);
-        if (!in) { cerr << "ERROR: " << comorbidityFilename << " not found." << endl; return false; }
-        while (getline(in, row)) {
-            istringstream f(row); int pid, sex, age; bool com;
-            if ((f >> pid >> sex >> age >> com) and com) getPersonByID(pid)->setComorbidity(COMORBID);
+    Ft ft(FT_LOADPOP);
+    {
+        cabm_text::Table in(populationFilename);
+        if (!in.ok()) { cerr << "ERROR: " << populationFilename << " not found." << endl; return false; }
+        while (in.next_row()) {
+            int pid, hid, sex, age, did;
+            if (!(in.number(pid) and in.number(hid) and in.number(sex) and in.number(age) and in.number(did))) continue;
+            if (pid != (int) _people.size()) { cerr << "ERROR: Person ID's must be sequential integers starting at 0" << endl; return false; }
+            assert((int) _location.size() > hid and (int) _location.size() > did);
+            Person* p = new Person();
+            _people.push_back(p);
+            p->setAge(age); p->setSex((SexType) sex);
+            // load-time immunity attributes, drawn exactly as the reference does (Community.cpp:212-215) with its own Parameters methods
+            p->setStartingNaturalEfficacy(_par->sampleStartingNaturalEfficacy(RNG));
+            p->setImmunityQuantile(gsl_rng_uniform(RNG));
+            p->setNaturalImmunityDuration(_par->immunityDuration(p->getImmunityQuantile(), p->getStartingNaturalEfficacy()));
+            p->setCrossProtectionProbability(gsl_rng_uniform(RNG));
+            p->setHomeLoc(_location[hid]); _location[hid]->addPerson(p);
+            if (did >= 0) { p->setDayLoc(_location[did]); _location[did]->addPerson(p); }
+            if (_location[hid]->getType() == NURSINGHOME) p->setLongTermCare(true);
         }
-        in.close();
+    }
+    if (comorbidityFilename.length() > 0) {
+        cabm_text::Table in(comorbidityFilename);
+        if (!in.ok()) { cerr << "ERROR: " << comorbidityFilename << " not found." << endl; return false; }
+        while (in.next_row()) {
+            int pid, sex, age, com;
+            if (in.number(pid) and in.number(sex) and in.number(age) and in.number(com) and com == 1) getPersonByID(pid)->setComorbidity(COMORBID);
+        }
     }
     if (publicActivityFilename.length() > 0) {
-        in.open(publicActivityFilename);
-        if (!in) { cerr << "ERROR: " << publicActivityFilename << " not found." << endl; return false; }
-        while (getline(in, row)) {
-            istringstream f(row); int pid, locid;
-            if (!(f >> pid)) continue;
+        cabm_text::Table in(publicActivityFilename);
+        if (!in.ok()) { cerr << "ERROR: " << publicActivityFilename << " not found." << endl; return false; }
+        while (in.next_row()) {
+            int pid, locid;
+            if (!in.number(pid)) continue;
             Person* p = getPersonByID(pid);
             if (p->getAge() < 18 or p->getLongTermCare()) continue;                      // Community.cpp:286-288
-            while (f >> locid) {
+            while (in.number(locid)) {
                 assert((int) _location.size() > locid);
                 Location* loc = _location[locid];
                 assert(loc->getPublicTransmissionRisk() == LOW_PUBLIC_TRANSMISSION or loc->getPublicTransmissionRisk() == HIGH_PUBLIC_TRANSMISSION);
                 p->addPatronizedLocation(loc);
             }
         }
-        in.close();
     }
     if (immunityFilename.length() > 0) { cerr << "ERROR: Reading in immunity file not currently supported." << endl; return false; }
     _personAgeCohort.clear(); _personAgeCohort.resize(NUM_AGE_CLASSES);
     for (Person* p : _people) { assert(p->getAge() >= 0 and p->getAge() < NUM_AGE_CLASSES); _personAgeCohort[p->getAge()].push_back(p); }
+    _pediatric.clear();
+    for (int a = 0; a <= 17; ++a) _pediatric.insert(_pediatric.end(), _personAgeCohort[a].begin(), _personAgeCohort[a].end());
     return true;
 }
 
@@ -303,13 +330,16 @@ void Community::tick() {
     cabm* h = handle();
     flush_doses();
     push_interventions();
-    const int rc = CABM_FN(tick)(h, _day, (int) _date->julianDay(), _date->isWeekday() ? 1 : 0);
-    if (rc != 0) fail("cabm_tick", rc);
+    { Ft ft(FT_TICK);
+      const int rc = CABM_FN(tick)(h, _day, (int) _date->julianDay(), _date->isWeekday() ? 1 : 0);
+      if (rc != 0) fail("cabm_tick", rc); }
     device_changed();
 
     // contact tracing to the configured depth from today's reported cases, then reactive scheduling and the day's doses
-    vector<set<Person*, PerPtrComp>> tracedContactsByDepth = traceForwardContacts();
+    vector<set<Person*, PerPtrComp>> tracedContactsByDepth;
+    { Ft ft(FT_TRACE); tracedContactsByDepth = traceForwardContacts(); }
     if (vac_campaign) {
+        Ft ft(FT_VAX);
         vac_campaign->reactive_strategy(_day, tracedContactsByDepth, this);
         vaccinate();
     }
@@ -374,6 +404,7 @@ Infection* Community::infect(int id, StrainType strain) {                       
 
 bool Community::infect_on_device(int pid, StrainType strain, int day) {
     cabm* h = handle();
+    Ft ft(FT_INFECT);
     flush_doses();
     int32_t took = 0;
     const int rc = CABM_FN(infect)(h, (uint32_t) pid, (int) strain, day, &took);
@@ -398,6 +429,7 @@ Infection* Person::infect(Community* community, Person* source, const Date* date
 void Person::refresh() { _stale = false; if (_community) _community->refresh_people(); }
 
 void Community::refresh_people() {
+    Ft ft(FT_REFRESH);
     Person::_stale = false;
     if (not _uploaded) return;
     size_t avail = 0;
@@ -529,6 +561,7 @@ std::vector<size_t> Community::series(int counter) {
     const size_t R = _par->runLength;
     if (not _uploaded) return std::vector<size_t>(R, 0);
     if (_ledger_epoch != _epoch) {
+        Ft ft(FT_LEDGER);
         _ledger_cache.assign(R * CABM_N_COUNTERS, 0);
         const int rc = CABM_FN(ledger_table)(_h, (uint64_t*) _ledger_cache.data(), _ledger_cache.size());
         if (rc != 0) fail("cabm_ledger_table", rc);
@@ -547,6 +580,7 @@ std::vector<size_t> Community::getCumulIncidenceByOutcome() {
 
 const std::vector<unsigned long long>& Community::diagnostics(int day) {
     if (_diag_epoch != _epoch or _diag_day != day) {
+        Ft ft(FT_DIAG);
         flush_doses();
         _diag_cache.assign(CABM_N_DIAG, 0);
         const int rc = CABM_FN(diagnostics)(handle(), day, (uint64_t*) _diag_cache.data());
@@ -582,12 +616,9 @@ std::map<std::string, double> Community::calculate_vax_stats(int day) {
 double Community::doSerosurvey(const ImmuneStateType ist, const std::vector<Person*>& pop, int time) {
     if (ist != NATURAL) { cerr << "ERROR: Community::doSerosurvey() not yet implemented for this immunity type" << endl; exit(1); }
     if (pop.size() == _people.size()) return (double) diagnostics(time)[CABM_D_SEROPOS_ALL] / pop.size();
-    size_t n_ped = 0; for (int a = 0; a <= 17; ++a) n_ped += _personAgeCohort[a].size();
-    if (pop.size() == n_ped and n_ped > 0) {
-        bool all_ped = true;
-        for (Person* p : pop) if (p->getAge() > 17) { all_ped = false; break; }
-        if (all_ped) return (double) diagnostics(time)[CABM_D_SEROPOS_PED] / pop.size();
-    }
+    if (pop.size() == _pediatric.size() and not pop.empty() and std::memcmp(pop.data(), _pediatric.data(), pop.size() * sizeof(Person*)) == 0)
+        return (double) diagnostics(time)[CABM_D_SEROPOS_PED] / pop.size();
+    Ft ft(FT_SERO);
     std::vector<uint32_t> ids(pop.size());
     for (size_t i = 0; i < pop.size(); ++i) ids[i] = (uint32_t) pop[i]->getID();
     uint64_t pos = 0;

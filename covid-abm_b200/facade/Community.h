@@ -49,7 +49,7 @@ class Community {
     bool loadLocations(std::string locationFilename, std::string networkFilename = "");
     size_t getNumPeople() const { return _people.size(); }
     size_t getNumLocations() const { return _location.size(); }
-    std::vector<Person*> getPeople() const { return _people; }
+    const std::vector<Person*>& getPeople() const { return _people; }     // the reference returns a copy (Community.h:330); a reference binds wherever a copy did
     Person* getPersonByID(int id);
     Location* getLocationByID(int id);
     int getDay() { return _day; }
@@ -100,7 +100,7 @@ class Community {
 
     const std::vector<Location*> getLocations() const { return _location; }
     std::set<Location*, Location::LocPtrComp> getLocationsByType(LocationType lt) const { return _location_map.at(lt); }
-    const std::vector<Person*> getAgeCohort(unsigned int age) const { assert(age < _personAgeCohort.size()); return _personAgeCohort[age]; }
+    const std::vector<Person*>& getAgeCohort(unsigned int age) const { assert(age < _personAgeCohort.size()); return _personAgeCohort[age]; }
     std::vector<Location*> locsAtPixel(std::pair<double, double> px) { return _pixelMap[{ px.first, px.second }]; }
     std::vector<Location*> locsAtPixel(double xP, double yP) { return _pixelMap[{ xP, yP }]; }
 
@@ -131,6 +131,7 @@ class Community {
     Date* _date;
     std::vector<Person*> _people;
     std::vector<std::vector<Person*>> _personAgeCohort;
+    std::vector<Person*> _pediatric;                                            // cohorts 0..17 in simulate_epidemic's order (simulator.h:405-409)
     std::vector<Location*> _location;
     std::vector<Location*> _public_locations;
     std::map<LocationType, std::set<Location*, Location::LocPtrComp>> _location_map;

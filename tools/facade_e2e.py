@@ -41,10 +41,14 @@ def main():
     synthpop.write_reference_files(pop, tmp, "e2e")
     cabm.params.write_text(P, T, os.path.join(tmp, "params.txt"))
     write_s = time.time() - t0
-    r = subprocess.run([drv, "sim", os.path.join(tmp, "params.txt"), tmp, "e2e", os.path.join(tmp, "out"), str(args.campaign)], capture_output=True, text=True)
+    r = subprocess.run([drv, "sim", os.path.join(tmp, "params.txt"), tmp, "e2e", os.path.join(tmp, "out"), str(args.campaign)], capture_output=True, text=True,
+                       env=dict(os.environ, CABM_FACADE_TIMING="1"))
     if r.returncode != 0:
         sys.exit(r.stderr[-3000:])
     out = json.loads(r.stdout.strip().splitlines()[-1])
+    for line in r.stderr.splitlines():
+        if line.startswith("facade_timing "):                  # seconds and calls per facade entry point (CABM_FACADE_TIMING)
+            out["facade_timing_s_calls"] = json.loads(line[len("facade_timing "):])
     out.update(backend=args.backend, campaign=args.campaign, write_population_files_s=round(write_s, 2),
                ms_per_day=out["simulate_epidemic_s"] * 1e3 / out["days"])
     subprocess.run(["rm", "-rf", tmp])
