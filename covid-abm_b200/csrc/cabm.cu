@@ -39,6 +39,7 @@ struct cabm {
     uint64_t launches_per_day = 11;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
+    Dev* d_batch = nullptr; size_t batch_cap = 0; cudaGraphExec_t batch_graph = nullptr; size_t batch_graph_n = 0;   // cabm_batch_run_days: the communities of the batch, indexed by blockIdx.y
     int* h_pin = nullptr;                        // pinned, device-visible scratch: single-word results are written by the kernel itself (no staged copy)
     const FlagRaw* peer_flags[CABM_MAX_SHARDS] = { nullptr }; int peer_mode = 0;      // exchange A over peer memory (cudaIpc mappings of the other handles' flag lists)
     int* d_hosp_ids = nullptr; int* d_pat_save = nullptr; int* d_pat_buf = nullptr; unsigned int n_hosp = 0; unsigned int n_flags_own = 0;   // sharding
@@ -230,6 +231,8 @@ int cabm_destroy(cabm_t* h) {
     if (h->d_xrecv) cudaFree(h->d_xrecv);
     if (h->h_xcounts) cudaFreeHost(h->h_xcounts);
     if (h->h_pin) cudaFreeHost(h->h_pin);
+    if (h->batch_graph) cudaGraphExecDestroy(h->batch_graph);
+    if (h->d_batch) cudaFree(h->d_batch);
     for (void* p : h->allocs) cudaFree(p);
     if (h->h_ctx) cudaFreeHost(h->h_ctx);
     cudaEventDestroy(h->e0); cudaEventDestroy(h->e1); cudaStreamDestroy(h->stream);
@@ -453,6 +456,75 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
     for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day; }
     if ((rc = timed_sync(h))) return rc;
     return check_overflow(h);
+}
+
+int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
+                        const double* expected_imports, const double* strain_w) {
+    if (!hs || n == 0 || n > 65535 || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;
+    cabm_t* h = hs[0]; if (!h) return CABM_E_ARG;
+    int rc = ready(h, first_day); if (rc) return rc; if ((rc = ready(h, first_day + n_days - 1))) return rc;
+    for (size_t r = 0; r < n; ++r) {
+        cabm_t* g = hs[r];
+        if (!g || (rc = ready(g, first_day + n_days - 1))) { h->err = "batch: a handle is not ready for these days"; return CABM_E_STATE; }
+        if (g->device != h->device || g->d.N != h->d.N || g->d.L != h->d.L || g->d.Q != h->d.Q || g->bitmap_words != h->bitmap_words ||
+            g->d.own_lo != 0 || g->d.own_hi != g->d.N) { h->err = "batch: handles must hold populations of one shape on one device, unsharded"; return CABM_E_ARG; }
+        for (size_t q = 0; q < r; ++q) if (hs[q] == g) { h->err = "batch: a handle appears twice"; return CABM_E_ARG; }
+    }
+    for (int i = 0; i < n_days; ++i) if (julian_day[i] < 1 || julian_day[i] > 366) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    cudaStream_t st = h->stream;
+    std::vector<Dev> devs(n);
+    for (size_t r = 0; r < n; ++r) {
+        cabm_t* g = hs[r];
+        if (g != h) CK(cudaStreamSynchronize(g->stream));              // earlier work of that handle; from here on everything is on st
+        for (int i = 0; i < n_days; ++i) {
+            DayCtx& c = g->h_ctx[i]; std::memset(&c, 0, sizeof(c));
+            fill_ctx(g, c, first_day + i, julian_day[i], is_weekday[i]);
+            c.n_imports = expected_imports[i] > 0 ? import_count(g->hpar.seed, first_day + i, expected_imports[i]) : 0;
+            for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[(size_t) i * CABM_N_STRAINS + s];
+        }
+        CK(cudaMemcpyAsync(g->d_ctx, g->h_ctx, (size_t) n_days * sizeof(DayCtx), cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(&g->d.ctr->day_idx, 0, sizeof(unsigned int), st));
+        devs[r] = g->d;
+    }
+    if (h->batch_cap < n) {
+        if (h->batch_graph) { cudaGraphExecDestroy(h->batch_graph); h->batch_graph = nullptr; }     // it holds the old table's address
+        if (h->d_batch) cudaFree(h->d_batch);
+        CK(cudaMalloc(&h->d_batch, n * sizeof(Dev))); h->batch_cap = n;
+    }
+    CK(cudaMemcpyAsync(h->d_batch, devs.data(), n * sizeof(Dev), cudaMemcpyHostToDevice, st));
+    const Dev* B = h->d_batch; const Dev& D = h->d;
+    const unsigned int R = (unsigned int) n, gSM = h->sms;
+    auto gx = [&](int k) { return std::max(2u, gSM * (unsigned int) h->gm[k] / R); };             // the SMs are shared by the batch
+    const dim3 gScan(scan_grid(D), R), gVisit(std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), std::max(2u, gSM * 4 / R)), R);
+    auto one_day = [&]() {
+        k_scan_b<<<gScan, TPB, 0, st>>>(B);
+        k_active_b<<<dim3(gx(0), R), TPB, 0, st>>>(B);
+        k_visit_b<<<gVisit, TPB, h->bitmap_words * sizeof(unsigned int), st>>>(B, h->bitmap_words);
+        k_hazard_b<<<dim3(gx(1), R), TPB, 0, st>>>(B);
+        k_trials_b<<<dim3(gx(2), R), TPB, 0, st>>>(B);
+        k_gate_b<<<dim3(gx(3), R), 128, 0, st>>>(B, 0);
+        k_apply_status_b<<<dim3(gx(4), R), 128, 0, st>>>(B, 0, 1);
+        k_hosp_import_b<<<dim3(gx(5), R), TPB, 0, st>>>(B, 1, 1);
+        k_gate_b<<<dim3(gx(6), R), 128, 0, st>>>(B, 1);
+        k_apply_status_b<<<dim3(gx(7), R), 128, 0, st>>>(B, 1, 0);
+        k_end_b<<<dim3(gx(8), R), TPB, 0, st>>>(B, 1, 1);
+    };
+    if (!h->batch_graph || h->batch_graph_n != n) {                 // the day of this batch as one graph (the Dev table is read at run time)
+        if (h->batch_graph) { cudaGraphExecDestroy(h->batch_graph); h->batch_graph = nullptr; }
+        cudaGraph_t g = nullptr;
+        CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        one_day();
+        CK(cudaStreamEndCapture(st, &g));
+        CK(cudaGraphInstantiate(&h->batch_graph, g, 0));
+        cudaGraphDestroy(g);
+        h->batch_graph_n = n;
+    }
+    CK(cudaEventRecord(h->e0, st));
+    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->batch_graph, st)); h->launches += 11; }
+    if ((rc = timed_sync(h))) return rc;
+    for (size_t r = 0; r < n; ++r) if ((rc = check_overflow(hs[r]))) { if (hs[r] != h) h->err = hs[r]->err; return rc; }
+    return CABM_OK;
 }
 
 int cabm_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_ok) {

@@ -62,7 +62,7 @@ __device__ __forceinline__ void block_work_add(const Dev& D, const int* ids, con
 // ---------------------------------------------------------------------------------------------
 // k_scan: active-window scan. Also publishes today's DayCtx for the rest of the pipeline.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB) k_scan(const Dev D) {
+__device__ __forceinline__ void k_scan_body(const Dev& D) {
     __shared__ unsigned int s_warp[TPB / 32], s_base;
     const DayCtx& cx = D.dayctx[D.ctr->day_idx];
     const int day = cx.day;
@@ -93,6 +93,8 @@ __global__ void __launch_bounds__(TPB) k_scan(const Dev D) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) if (mask & (1u << k)) { if (o < D.cap_active) D.active_list[o] = p0 + k; else atomicOr(&D.ctr->overflow, 4u); ++o; }
 }
+__global__ void __launch_bounds__(TPB) k_scan(const Dev D) { k_scan_body(D); }
+__global__ void __launch_bounds__(TPB) k_scan_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_scan_body(D); }   // one launch, replicate = blockIdx.y
 
 // Community::flagInfectedLocation (Community.cpp:788-791) on device, second half: the flag record, and for the first
 // flag of a location the hot-list entry. `slot` is what atomicAdd(&loc_cnt[loc], 1) returned, f the record index.
@@ -143,7 +145,7 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
 // ---------------------------------------------------------------------------------------------
 // k_active: one thread per active agent.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB) k_active(const Dev D) {
+__device__ __forceinline__ void k_active_body(const Dev& D) {
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n = min(D.ctr->n_active, D.cap_active);
     unsigned int nflag = 0;
@@ -193,6 +195,8 @@ __global__ void __launch_bounds__(TPB) k_active(const Dev D) {
     nflag = warp_sum(nflag);
     if ((threadIdx.x & 31) == 0 && nflag) atomicAdd(&D.ctr->work[CABM_W_FLAGS], (unsigned long long) nflag);
 }
+__global__ void __launch_bounds__(TPB) k_active(const Dev D) { k_active_body(D); }
+__global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_active_body(D); }   // one launch, replicate = blockIdx.y
 
 // ---------------------------------------------------------------------------------------------
 // k_visit: every agent with patronised locations that is not in hospital draws its visits.
@@ -202,7 +206,7 @@ __global__ void __launch_bounds__(TPB) k_active(const Dev D) {
 // ceil(Q/32) words); visits that land on a hot location are counted (nvis) and recorded with one warp-aggregated
 // reservation per round. There is no block-level synchronisation in the loop.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned int bitmap_words) {
+__device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bitmap_words) {
     extern __shared__ unsigned int s_hot[];
     const DayCtx& cx = day_ctx(D);
     for (unsigned int i = threadIdx.x; i < bitmap_words; i += blockDim.x) s_hot[i] = D.pub_hot[i];
@@ -305,6 +309,8 @@ __global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned in
     const int ids[3] = { CABM_W_PATRONS, CABM_W_VISITS, CABM_W_HOT_VISITS }; const unsigned int vals[3] = { w_pat, w_v0, w_v };
     block_work_add<3>(D, ids, vals);
 }
+__global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
+__global__ void __launch_bounds__(TPB, 4) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
 
 __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1.0, cabm_exp(-hazard)); }
 
@@ -355,7 +361,7 @@ __device__ __forceinline__ unsigned int list_reserve_n(unsigned int* counter, co
 // Every hot location's dependent chain (hot list -> type -> pressure -> roster/neighbour offsets) runs in its own thread,
 // so the chains of all hot locations overlap; the trials themselves are spread over lanes in k_trials.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
+__device__ __forceinline__ void k_hazard_body(const Dev& D) {
     const DayCtx& cx = day_ctx(D);
     const cabm_params* __restrict__ par = D.par;
     const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
@@ -432,11 +438,13 @@ __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) {
     edges = warp_sum(edges);
     if ((threadIdx.x & 31) == 0 && edges && D.shard_rank == 0) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges);
 }
+__global__ void __launch_bounds__(TPB) k_hazard(const Dev D) { k_hazard_body(D); }
+__global__ void __launch_bounds__(TPB) k_hazard_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_hazard_body(D); }   // one launch, replicate = blockIdx.y
 
 // ---------------------------------------------------------------------------------------------
 // k_trials: block-sized units: the 256-member items of big rosters, the visit records, the flag scatter, the small items.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB) k_trials(const Dev D) {
+__device__ __forceinline__ void k_trials_body(const Dev& D) {
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n_items = min(D.ctr->n_items, D.cap_items), n_vis = min(D.ctr->n_vis, D.cap_vis);
     const unsigned int n_flags = min(D.ctr->n_flags, D.cap_flags);
@@ -478,3 +486,5 @@ __global__ void __launch_bounds__(TPB) k_trials(const Dev D) {
     const int ids[1] = { CABM_W_TRIALS }; const unsigned int vals[1] = { trials };
     block_work_add<1>(D, ids, vals);
 }
+__global__ void __launch_bounds__(TPB) k_trials(const Dev D) { k_trials_body(D); }
+__global__ void __launch_bounds__(TPB) k_trials_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_trials_body(D); }   // one launch, replicate = blockIdx.y

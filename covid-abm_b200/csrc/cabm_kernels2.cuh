@@ -105,7 +105,7 @@ __device__ __forceinline__ unsigned long long order_key(const unsigned int purpo
     return make_key(pass, src, (unsigned int) role);
 }
 
-__global__ void __launch_bounds__(128) k_gate(const Dev D, const int phase) {
+__device__ __forceinline__ void k_gate_body(const Dev& D, const int phase) {
     const DayCtx& cx = day_ctx(D);
     const unsigned int lo = phase ? min(D.ctr->n_hits[0], D.cap_hits) : 0u;
     const unsigned int hi = min(lo + D.ctr->n_hits[phase], D.cap_hits);
@@ -123,6 +123,8 @@ __global__ void __launch_bounds__(128) k_gate(const Dev D, const int phase) {
         }
     }
 }
+__global__ void __launch_bounds__(128) k_gate(const Dev D, const int phase) { k_gate_body(D, phase); }
+__global__ void __launch_bounds__(128) k_gate_b(const Dev* __restrict__ devs, const int phase) { const Dev D = devs[blockIdx.y]; k_gate_body(D, phase); }   // one launch, replicate = blockIdx.y
 
 // Community::updatePersonStatus (Community.cpp:682-741) for one agent; returns the ledger increments as a bit mask
 __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p, int day) {
@@ -167,7 +169,7 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
 // other); lane 0 commits, all lanes help with the infector search -- then warps [n_w, n_w + ceil(n_active/32)) run the
 // status pass (with_status) over the agents active at the start of the day that were not re-infected in phase 0.
 // cand[] keeps the winner keys until k_end so the status half can tell who was re-infected.
-__global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int phase, const int with_status) {
+__device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phase, const int with_status) {
     __shared__ unsigned int sm[CABM_N_COUNTERS];
     if (threadIdx.x < CABM_N_COUNTERS) sm[threadIdx.x] = 0;
     __syncthreads();
@@ -214,6 +216,8 @@ __global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int pha
     __syncthreads();
     if (threadIdx.x < CABM_N_COUNTERS && sm[threadIdx.x]) atomicAdd(&D.ledger[(size_t) threadIdx.x * D.R + day], (unsigned long long) sm[threadIdx.x]);
 }
+__global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int phase, const int with_status) { k_apply_status_body(D, phase, with_status); }
+__global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ devs, const int phase, const int with_status) { const Dev D = devs[blockIdx.y]; k_apply_status_body(D, phase, with_status); }   // one launch, replicate = blockIdx.y
 
 // hospital_transmission (Community.cpp:931-941): census = staff + admitted patients; every consumer computes T itself
 __device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, const int hosp, unsigned int* denom_out, unsigned long long* pws) {
@@ -229,7 +233,7 @@ __device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, con
 
 // do_hosp: warps [0, n_hot_hosp) expose the staff of one hot hospital each, then all threads walk the admitted-patient
 // list; do_import: all threads walk today's importation draws (every draw is a "hit": the person is chosen, not exposed)
-__global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_hosp, const int do_import) {
+__device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_hosp, const int do_import) {
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     const unsigned int lane = threadIdx.x & 31, warp = tid >> 5, n_warps = nth >> 5;
@@ -271,6 +275,8 @@ __global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_h
     trials = warp_sum(trials);
     if (lane == 0 && trials) atomicAdd(&D.ctr->work[CABM_W_TRIALS], (unsigned long long) trials);
 }
+__global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_hosp, const int do_import) { k_hosp_import_body(D, do_hosp, do_import); }
+__global__ void __launch_bounds__(TPB) k_hosp_import_b(const Dev* __restrict__ devs, const int do_hosp, const int do_import) { const Dev D = devs[blockIdx.y]; k_hosp_import_body(D, do_hosp, do_import); }   // one launch, replicate = blockIdx.y
 
 // Community::infect(id, strain) (Community.cpp:550-553): one agent, gate and commit in one go
 __global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain, const int day, int* out) {
@@ -285,7 +291,7 @@ __global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain
 
 // reset what today's hot set and today's winners touched; the last block to finish then closes the day (day-scoped counters
 // back to zero, next day context): every other block has read the counters it needs before taking its ticket
-__global__ void __launch_bounds__(TPB) k_end(const Dev D, const int tick_done, const int advance) {
+__device__ __forceinline__ void k_end_body(const Dev& D, const int tick_done, const int advance) {
     const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
     if (tick_done) {
@@ -315,6 +321,8 @@ __global__ void __launch_bounds__(TPB) k_end(const Dev D, const int tick_done, c
         }
     }
 }
+__global__ void __launch_bounds__(TPB) k_end(const Dev D, const int tick_done, const int advance) { k_end_body(D, tick_done, advance); }
+__global__ void __launch_bounds__(TPB) k_end_b(const Dev* __restrict__ devs, const int tick_done, const int advance) { const Dev D = devs[blockIdx.y]; k_end_body(D, tick_done, advance); }   // one launch, replicate = blockIdx.y
 
 // Person::vaccinate (Person.cpp:611-647), leaky model
 __global__ void k_vaccinate(const Dev D, const unsigned int* pids, const unsigned int n, const int day, unsigned char* ok) {

@@ -55,3 +55,25 @@ def gather_ledgers(dist, device, ledgers: np.ndarray, n_replicates: int):
         idx = replicate_slice(n_replicates, r, world)
         full[idx] = out[r].cpu().numpy()[:len(idx)].astype(np.uint64)
     return full
+
+
+def batch_run_days(comms, n_days: int):
+    """`n_days` of every community in `comms` (same population shape, same calendar position) with ONE launch per kernel for the
+    whole batch (cabm_batch_run_days, include/cabm.h): the calibration-batch form of Community.run_days. Each community keeps
+    its own parameters, seed, state and ledger; results equal run_days on each of them."""
+    import ctypes as C
+    c0 = comms[0]
+    first = c0.day
+    if any(c.day != first or c.n_people != c0.n_people or c.backend is not c0.backend for c in comms):
+        raise ValueError("a batch advances communities of one shape from the same day on one backend")
+    strain_w = np.zeros((n_days, 4)); exp = np.zeros(n_days)
+    for i in range(n_days):
+        for c in comms:
+            c.update_strain_mix(first + i)
+        strain_w[i] = c0.strains; exp[i] = c0.expected_imports(first + i)
+    jd = np.ascontiguousarray(c0.julian_day[first:first + n_days]); wd = np.ascontiguousarray(c0.is_weekday[first:first + n_days])
+    hs = (C.c_void_p * len(comms))(*[c._h for c in comms])
+    c0._check(c0.fn.batch_run_days(hs, len(comms), first, n_days, jd.ctypes.data_as(C.POINTER(C.c_int32)), wd.ctypes.data_as(C.POINTER(C.c_int32)),
+                                   exp.ctypes.data_as(C.POINTER(C.c_double)), strain_w.ctypes.data_as(C.POINTER(C.c_double))))
+    for c in comms:
+        c.day += n_days

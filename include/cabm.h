@@ -247,6 +247,16 @@ int  cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_
 int  cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                    const double* expected_imports, const double* strain_w /* [n_days][4] */);
 
+/* MANY COMMUNITIES, ONE LAUNCH PER KERNEL. Calibration runs thousands of replicates of one small population with different
+   parameters and seeds (exp/abc-*, SLURM arrays; BASELINE configs[4]); a 100k-agent day is eleven launches of a few
+   microseconds each, so replicates on separate streams are bound by the device's launch rate. cabm_batch_run_days advances
+   `n` handles of the same shape (same N, locations and rosters; own parameters, seed, state and ledger) together: each of
+   the day's kernels is ONE launch whose blockIdx.y selects the community. Same arguments as cabm_run_days, shared by all
+   handles; results are bit-identical to calling cabm_run_days on each handle. Handles must live on one device and must not
+   be sharded. */
+int  cabm_batch_run_days(cabm_t* const* handles, size_t n, int first_day, int n_days, const int32_t* julian_day,
+                         const int32_t* is_weekday, const double* expected_imports, const double* strain_w);
+
 /* replaces Person::vaccinate via Vac_Campaign::vaccinate (Person.cpp:611-647, Vac_Campaign.h:550) */
 int  cabm_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_ok);
 /* replaces Person::scheduleQuarantine (Person.cpp:649-651) */

@@ -115,6 +115,18 @@ int cabm_oracle_run_days(cabm_t* h, int first_day, int n_days, const int32_t* ju
 }
 
 // Person::vaccinate (Person.cpp:611-647)
+// the batch form of run_days (include/cabm.h): on the CPU the communities simply run one after the other
+int cabm_oracle_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
+                               const double* expected_imports, const double* strain_w) {
+    if (!hs || n == 0) return CABM_E_ARG;
+    for (size_t r = 0; r < n; ++r) {
+        if (!hs[r] || hs[r]->sim.n_people != hs[0]->sim.n_people) return CABM_E_ARG;
+        const int rc = cabm_oracle_run_days(hs[r], first_day, n_days, julian_day, is_weekday, expected_imports, strain_w);
+        if (rc) return rc;
+    }
+    return CABM_OK;
+}
+
 int cabm_oracle_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_ok) {
     H_OK(h); Sim& S = h->sim; int rc = ready(S, sim_day); if (rc) return rc;
     if (!S.par.immunity_leaky) { S.err = "vaccination requires leaky immunity (Person.cpp:622)"; return CABM_E_STATE; }

@@ -9,6 +9,7 @@ import socket
 import sys
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -80,3 +81,44 @@ def test_replicate_striping():
         assert max(len(o) for o in owned) - min(len(o) for o in owned) <= 1
         seeds = {R.replicate_seed(7, r, k, w) for r in range(w) for k in range(len(owned[r]))}
         assert seeds == {7 + g for g in range(n)}
+
+
+def _batch_case(make, R=3, n=4000, days=40):
+    import covid_abm_b200 as cabm
+    import synthpop
+    pop = synthpop.generate(n, seed=77)
+    comms, solo = [], []
+    for r in range(R):
+        P = cabm.params.default_params(run_length=days, seed=100 + r, T=0.15 + 0.02 * r, prob_daily_exposure=1e-3,
+                                       mutant_intro_dates=("2020-02-20", "2020-03-05", "2020-03-20"))
+        tab = cabm.params.build_tables(P)
+        comms.append(make(P, pop, tab)); solo.append(make(P, pop, tab))
+    cabm.replicates.batch_run_days(comms, 15)
+    pids = np.arange(0, n, 3, dtype=np.uint32)
+    for c, s in zip(comms, solo):
+        s.run_days(15)
+        c.vaccinate(pids, 15); s.vaccinate(pids, 15)
+    cabm.replicates.batch_run_days(comms, days - 15)
+    totals = []
+    for c, s in zip(comms, solo):
+        s.run_days(days - 15)
+        assert c.day == s.day == days
+        assert np.array_equal(c.ledger_table(), s.ledger_table())
+        assert np.array_equal(c.current_infections(), s.current_infections())
+        totals.append(int(c.ledger_table()[:, 0].sum()))
+    assert len(set(totals)) == R and min(totals) > 100          # different parameters and seeds: different epidemics
+    for c in comms + solo:
+        c.close()
+
+
+def test_batched_replicates_wrapper_on_the_oracle():
+    """Host side of cabm_batch_run_days (strain urn, calendar slices, handle array): batch == one community at a time."""
+    import oracle_lib
+    _batch_case(lambda P, pop, tab: oracle_lib.oracle_community(P, pop, tab))
+
+
+@pytest.mark.gpu
+def test_batched_replicates_one_launch_per_kernel_equals_run_days():
+    """CUDA: every kernel of the day launched once for the whole batch (replicate = blockIdx.y) == cabm_run_days per handle."""
+    import covid_abm_b200 as cabm
+    _batch_case(lambda P, pop, tab: cabm.Community(P, pop, tab), R=5, n=30000, days=60)

@@ -24,6 +24,8 @@ def main():
     ap.add_argument("--agents", type=int, default=100_000)
     ap.add_argument("--days", type=int, default=200)
     ap.add_argument("--replicates", default="1,4,16,32")
+    ap.add_argument("--mode", default="streams", choices=["streams", "batched"],
+                    help="streams: one handle, stream and host thread per replicate; batched: cabm_batch_run_days, one launch per kernel for all replicates")
     args = ap.parse_args()
     import numpy as np
     import covid_abm_b200 as cabm
@@ -37,21 +39,29 @@ def main():
             comms.append(cabm.Community(P, pop, cabm.params.build_tables(P) if r == 0 else comms[0].T))
         for c in comms:
             c.run_days(20)                                   # warm-up: graph capture, first touch
-        barrier = threading.Barrier(R + 1)
+        if args.mode == "batched":
+            cabm.replicates.batch_run_days(comms, 5)          # first touch of the batch path
+            for c in comms:
+                c.device_time_ms()
+            t0 = time.perf_counter()
+            cabm.replicates.batch_run_days(comms, args.days - 5)
+            wall = (time.perf_counter() - t0) * args.days / (args.days - 5)
+        else:
+            barrier = threading.Barrier(R + 1)
 
-        def work(c):
-            barrier.wait()
-            c.run_days(args.days)
-        th = [threading.Thread(target=work, args=(c,)) for c in comms]
-        for t in th:
-            t.start()
-        barrier.wait(); t0 = time.perf_counter()
-        for t in th:
-            t.join()
-        wall = time.perf_counter() - t0
+            def work(c):
+                barrier.wait()
+                c.run_days(args.days)
+            th = [threading.Thread(target=work, args=(c,)) for c in comms]
+            for t in th:
+                t.start()
+            barrier.wait(); t0 = time.perf_counter()
+            for t in th:
+                t.join()
+            wall = time.perf_counter() - t0
         dev = [c.device_time_ms()[0] for c in comms]
         inf = [int(c.ledger("new_infected").sum()) for c in comms]
-        print(json.dumps({"replicates": R, "agents": n, "days": args.days, "wall_s": round(wall, 4), "agent_days_per_s": R * n * args.days / wall,
+        print(json.dumps({"mode": args.mode, "replicates": R, "agents": n, "days": args.days, "wall_s": round(wall, 4), "agent_days_per_s": R * n * args.days / wall,
                           "per_replicate_device_ms_max": round(max(dev), 2), "us_per_replicate_day_wall": round(wall * 1e6 / args.days, 1),
                           "infections_min_max": [min(inf), max(inf)]}), flush=True)
         for c in comms:
