@@ -106,6 +106,8 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
     c.day = day; c.julian_day = julian_day; c.is_weekday = is_weekday;
     c.season = h->hpar.seasonality[julian_day - 1];
     c.school_closure = h->h_ti[0][day]; c.business_closure = h->h_ti[1][day]; c.sd = h->h_ti[2][day];
+    float up = (float) c.sd; if ((double) up < c.sd) up = nextafterf(up, INFINITY);
+    c.sd_up = up; c.pad = 0.0f;
 }
 
 // kernel ids for per-kernel timing (cabm_kernel_times)
@@ -133,14 +135,15 @@ static void prof_collect(cabm_t* h) {      // call after the stream has been syn
 // launches: an agent hit by both keeps the hospital exposure (lower order key), exactly what running
 // seed_epidemic after tick() yields.
 // k_scan covers the owned agents only (the whole population on an unsharded handle), in groups of four from own_lo rounded down
-static unsigned int scan_grid(const Dev& D) { return std::max(1u, (unsigned int) ((D.own_hi - (D.own_lo & ~3u) + TPB * 4 - 1) / (TPB * 4))); }
+static unsigned int scan_grid(const Dev& D) { return std::max(1u, (unsigned int) ((D.own_hi - (D.own_lo & ~3u) + TPB * 4 * SCAN_V - 1) / (TPB * 4 * SCAN_V))); }
+static unsigned int visit_grid(const Dev& D, unsigned int sms) { return std::min<unsigned int>((D.N + TPB * VIS_A - 1) / (TPB * VIS_A), sms * VIS_MINB); }
 static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     const Dev& D = h->d; cudaStream_t st = h->stream;
     const unsigned int gScan = scan_grid(D), gSM = h->sms;
     if (tick) {
         LAUNCH(KID_SCAN, k_scan<<<gScan, TPB, 0, st>>>(D));
         LAUNCH(KID_ACTIVE, k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D));
-        LAUNCH(KID_VISIT, k_visit<<<std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), gSM * 4), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words));
+        LAUNCH(KID_VISIT, k_visit<<<visit_grid(D, gSM), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words));
         LAUNCH(KID_HAZARD, k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D));
         LAUNCH(KID_TRIALS, k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D));
         LAUNCH(KID_GATE0, k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D, 0));
@@ -496,7 +499,7 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
     const Dev* B = h->d_batch; const Dev& D = h->d;
     const unsigned int R = (unsigned int) n, gSM = h->sms;
     auto gx = [&](int k) { return std::max(2u, gSM * (unsigned int) h->gm[k] / R); };             // the SMs are shared by the batch
-    const dim3 gScan(scan_grid(D), R), gVisit(std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), std::max(2u, gSM * 4 / R)), R);
+    const dim3 gScan(scan_grid(D), R), gVisit(std::min<unsigned int>(visit_grid(D, gSM), std::max(2u, gSM * VIS_MINB / R)), R);
     auto one_day = [&]() {
         k_scan_b<<<gScan, TPB, 0, st>>>(B);
         k_active_b<<<dim3(gx(0), R), TPB, 0, st>>>(B);
@@ -648,7 +651,7 @@ int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is
         CK(cudaMemcpyAsync(&h->n_flags_own, &D.ctr->n_flags, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
         h->launches += 2;
     } else if (part == 1) {
-        k_visit<<<std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), gSM * 4), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
+        k_visit<<<visit_grid(D, gSM), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
         h->launches += 1;
     } else if (part == 2) {
         if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
@@ -815,7 +818,7 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
                 NK(N.AllGather(D.flags_raw, h->d_xrecv, (size_t) cap * sizeof(FlagRaw), ncclUint8, comm, st));
                 k_flags_in_all<<<gSM * 2, TPB, 0, st>>>(D, h->d_xrecv, h->d_xcounts, cap, h->world, D.shard_rank);
             }
-            PM(KID_VISIT); k_visit<<<std::min<unsigned int>((D.N + TPB * 4 - 1) / (TPB * 4), gSM * 4), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
+            PM(KID_VISIT); k_visit<<<visit_grid(D, gSM), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
             PM(KID_XB); NK(N.AllReduce(D.nvis, D.nvis, D.Q, ncclUint32, ncclSum, comm, st));                    // exchange B
             if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
             PM(KID_HAZARD); k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D);

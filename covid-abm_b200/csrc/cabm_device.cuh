@@ -41,6 +41,7 @@ struct DayCtx {                     // per-day scalars, staged by the host for e
     int day, julian_day, is_weekday, n_imports;
     double strain_w[CABM_N_STRAINS];
     double season, sd, school_closure, business_closure;
+    float sd_up, pad;               // smallest float >= sd: for a float r, (double) r < sd  <=>  r < sd_up
 };
 
 // counters living in device memory

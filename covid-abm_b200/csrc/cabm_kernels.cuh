@@ -41,6 +41,15 @@ __device__ __forceinline__ unsigned int list_reserve(unsigned int* counter) {
     return g.shfl(base, 0) + g.thread_rank();
 }
 
+// reserve n entries (n may differ per thread, 0 allowed) of a device list for every thread of a coalesced group: one atomic
+__device__ __forceinline__ unsigned int group_reserve(const cg::coalesced_group& g, unsigned int* counter, const unsigned int n) {
+    unsigned int incl = n;
+    for (unsigned int o = 1; o < g.size(); o <<= 1) { const unsigned int t = g.shfl_up(incl, o); if (g.thread_rank() >= o) incl += t; }
+    unsigned int base = 0;
+    if (g.thread_rank() == g.size() - 1 && incl) base = atomicAdd(counter, incl);
+    return g.shfl(base, g.size() - 1) + incl - n;
+}
+
 __device__ __forceinline__ unsigned int warp_sum(unsigned int v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -62,20 +71,30 @@ __device__ __forceinline__ void block_work_add(const Dev& D, const int* ids, con
 // ---------------------------------------------------------------------------------------------
 // k_scan: active-window scan. Also publishes today's DayCtx for the rest of the pipeline.
 // ---------------------------------------------------------------------------------------------
+#define SCAN_V 4               // uint4 loads per thread in k_scan: a block covers TPB * 4 * SCAN_V agents
 __device__ __forceinline__ void k_scan_body(const Dev& D) {
     __shared__ unsigned int s_warp[TPB / 32], s_base;
     const DayCtx& cx = D.dayctx[D.ctr->day_idx];
     const int day = cx.day;
     if (blockIdx.x == 0 && threadIdx.x == 0) { *D.today = cx; atomicAdd(&D.ctr->work[CABM_W_AGENTS], (unsigned long long) (D.own_hi - D.own_lo)); }
-    const unsigned int p0 = (D.own_lo & ~3u) + (blockIdx.x * TPB + threadIdx.x) * 4u;      // agents of other handles are never active here
-    uint4 w = make_uint4(0x80007FFFu, 0x80007FFFu, 0x80007FFFu, 0x80007FFFu);
-    if (p0 + 3 < D.N) w = *reinterpret_cast<const uint4*>(D.win + p0);
-    else { if (p0 < D.N) w.x = D.win[p0]; if (p0 + 1 < D.N) w.y = D.win[p0 + 1]; if (p0 + 2 < D.N) w.z = D.win[p0 + 2]; }
-    const unsigned int ww[4] = { w.x, w.y, w.z, w.w };
+    const unsigned int b0 = (D.own_lo & ~3u) + blockIdx.x * (TPB * 4u * SCAN_V);            // agents of other handles are never active here
+    uint4 w[SCAN_V];
+#pragma unroll
+    for (int j = 0; j < SCAN_V; ++j) {                                                       // all loads in flight before the first use
+        const unsigned int p0 = b0 + (j * TPB + threadIdx.x) * 4u;
+        w[j] = make_uint4(0x80007FFFu, 0x80007FFFu, 0x80007FFFu, 0x80007FFFu);
+        if (p0 + 3 < D.N) w[j] = *reinterpret_cast<const uint4*>(D.win + p0);
+        else { if (p0 < D.N) w[j].x = D.win[p0]; if (p0 + 1 < D.N) w[j].y = D.win[p0 + 1]; if (p0 + 2 < D.N) w[j].z = D.win[p0 + 2]; }
+    }
     unsigned int mask = 0;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { const int from = (short) (ww[k] & 0xFFFF), until = (short) (ww[k] >> 16); if (day >= from && day <= until) mask |= 1u << k; }
+    for (int j = 0; j < SCAN_V; ++j) {
+        const unsigned int ww[4] = { w[j].x, w[j].y, w[j].z, w[j].w };
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const int from = (short) (ww[k] & 0xFFFF), until = (short) (ww[k] >> 16); if (day >= from && day <= until) mask |= 1u << (j * 4 + k); }
+    }
     const unsigned int cnt = __popc(mask), lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (__syncthreads_or((int) mask) == 0) return;                                           // most blocks outside an epidemic wave: nothing to append
     unsigned int incl = cnt;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
@@ -85,13 +104,16 @@ __device__ __forceinline__ void k_scan_body(const Dev& D) {
         unsigned int acc = 0;
 #pragma unroll
         for (int k = 0; k < TPB / 32; ++k) { const unsigned int c = s_warp[k]; s_warp[k] = acc; acc += c; }
-        s_base = acc ? atomicAdd(&D.ctr->n_active, acc) : 0;
-        if (acc) atomicAdd(&D.ctr->work[CABM_W_ACTIVE], (unsigned long long) acc);
+        s_base = atomicAdd(&D.ctr->n_active, acc);
+        atomicAdd(&D.ctr->work[CABM_W_ACTIVE], (unsigned long long) acc);
     }
     __syncthreads();
     unsigned int o = s_base + s_warp[wid] + incl - cnt;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) if (mask & (1u << k)) { if (o < D.cap_active) D.active_list[o] = p0 + k; else atomicOr(&D.ctr->overflow, 4u); ++o; }
+    while (mask) {
+        const unsigned int bit = (unsigned int) __ffs(mask) - 1u; mask &= mask - 1u;
+        if (o < D.cap_active) D.active_list[o] = b0 + ((bit >> 2) * TPB + threadIdx.x) * 4u + (bit & 3u); else atomicOr(&D.ctr->overflow, 4u);
+        ++o;
+    }
 }
 __global__ void __launch_bounds__(TPB) k_scan(const Dev D) { k_scan_body(D); }
 __global__ void __launch_bounds__(TPB) k_scan_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_scan_body(D); }   // one launch, replicate = blockIdx.y
@@ -176,20 +198,35 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
             }
         }
         if (nl == 0) continue;
-        // all atomics of the agent are issued back to back so their round trips overlap
-        unsigned int slots[2 + MAXV];
+        // Community::flagInfectedLocation (Community.cpp:788-791) for all places of the agent at once: the static loads, the
+        // pressure REDs, the per-location slot atomics and the flag-list reservation are issued back to back (one round trip),
+        // then one reservation covers the hot-list entries of every location this agent was the first to flag
+        unsigned int slots[2 + MAXV]; int ltype[2 + MAXV], lpub[2 + MAXV];
         cg::coalesced_group g = cg::coalesced_threads();
         const unsigned int mine = (unsigned int) nl;
-        unsigned int incl = mine;                                                  // inclusive scan over the group for one reservation
-        for (unsigned int o = 1; o < g.size(); o <<= 1) { const unsigned int t = g.shfl_up(incl, o); if (g.thread_rank() >= o) incl += t; }
-        unsigned int base = 0;
-        if (g.thread_rank() == g.size() - 1) base = atomicAdd(&D.ctr->n_flags, incl);
-        base = g.shfl(base, g.size() - 1) + incl - mine;
+        for (int k = 0; k < nl; ++k) { ltype[k] = D.loc_type[locs[k]]; lpub[k] = D.loc_pub[locs[k]]; }
         for (int k = 0; k < nl; ++k) {
             atomicAdd(&D.press[(size_t) locs[k] * CABM_N_STRAINS + t1.strain], cs[k]);
             slots[k] = atomicAdd(&D.loc_cnt[locs[k]], 1u);
         }
-        for (int k = 0; k < nl; ++k) flag_location(D, locs[k], t1.strain, cs[k], p, slots[k], base + k);
+        const unsigned int base = group_reserve(g, &D.ctr->n_flags, mine);
+        unsigned int nfirst = 0, nfh = 0;
+        for (int k = 0; k < nl; ++k) if (slots[k] == 0) { nfirst++; nfh += ltype[k] == CABM_HOSPITAL ? 1u : 0u; }
+        unsigned int hbase = group_reserve(g, &D.ctr->n_hot, nfirst);
+        unsigned int hhbase = g.any(nfh != 0) ? group_reserve(g, &D.ctr->n_hot_hosp, nfh) : 0u;
+        for (int k = 0; k < nl; ++k) {
+            const unsigned int f = base + k;
+            if (f < D.cap_flags) { FlagRaw r; r.loc = locs[k]; r.slot = slots[k]; r.pid = p; r.pad = 0; r.c = cs[k] | ((unsigned long long) t1.strain << 56); D.flags_raw[f] = r; }
+            else atomicOr(&D.ctr->overflow, 128u);
+            if (slots[k] == 0) {
+                const unsigned int i = hbase++;
+                if (i < D.cap_hot) {
+                    D.hot_list[i] = locs[k]; D.loc_hot[locs[k]] = (int) i;
+                    if (ltype[k] == CABM_HOSPITAL) { const unsigned int j = hhbase++; if (j < D.cap_hot) D.hot_hosp[j] = (int) i; }
+                } else atomicOr(&D.ctr->overflow, 2u);
+                if (lpub[k] >= 0) atomicOr(&D.pub_hot[lpub[k] >> 5], 1u << (lpub[k] & 31));
+            }
+        }
         nflag += mine;
     }
     nflag = warp_sum(nflag);
@@ -200,117 +237,163 @@ __global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) 
 
 // ---------------------------------------------------------------------------------------------
 // k_visit: every agent with patronised locations that is not in hospital draws its visits.
-// Four agents per thread. Per agent the only memory on the path is the status byte and, when k > 0, the agent's
-// 32-byte patron row (5 public-location indices + the household's riskiness); the Philox block needs no memory.
-// Hotness is tested against a shared-memory bitmap over the Q patronised locations (dynamic shared memory,
-// ceil(Q/32) words); visits that land on a hot location are counted (nvis) and recorded with one warp-aggregated
-// reservation per round. There is no block-level synchronisation in the loop.
+// A warp takes tiles of 128 consecutive agents, four per lane. Per agent the only memory on the path is the status byte
+// and, when k > 0, the agent's 32-byte patron row (5 public-location indices + the household's riskiness); the Philox
+// block needs no memory. Hotness is tested against a shared-memory bitmap over the Q patronised locations (dynamic shared
+// memory, ceil(Q/32) words). Visits that land on a hot location are staged in the warp's shared-memory buffer and flushed
+// once per tile: one reservation, coalesced record stores, one census RED per record. Agents that draw k >= 4 (1.9 %) are
+// queued per warp and handled 32 at a time by the generic loop, so the common path carries no divergent tail.
+// There is no block-level synchronisation in the loop.
 // ---------------------------------------------------------------------------------------------
+#ifndef VIS_A
+#define VIS_A 4               // agents per lane and tile: a warp takes tiles of 32 * VIS_A consecutive agents
+#endif
+#ifndef VIS_MINB
+#define VIS_MINB 4            // resident blocks per SM the register allocation aims at
+#endif
+#define VIS_TILE (32 * VIS_A)
+#define VIS_STAGE (4 * VIS_TILE) // hot-visit records a warp stages before it flushes (a tile adds at most 3 * VIS_TILE)
+#define VIS_SLOWQ 512         // k >= 4 agents a block queues for its final full-warp pass (beyond that: handled in place)
+
+// a 32-bit load that is issued only when `on` is set (0 otherwise): keeps k_visit's body free of branches
+__device__ __forceinline__ unsigned int ldg_if(const int* ptr, unsigned int on) {
+    unsigned int v = 0;
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(ptr), "r"(on));
+    return v;
+}
+
+// the generic public_activity loop for one agent that drew k >= 4 (Community.cpp:1012-1026), one lane per agent
+__device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_hot, const unsigned int p, const unsigned int dp, const uint2 key,
+                                           const float sd_up, unsigned int& w_v0, unsigned int& w_v) {
+    const unsigned int npat = D.pbyte[p] & PB_NPAT;
+    const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
+    uint4 bb = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
+    const unsigned int kk = table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) bb.x * (1.0 / 4294967296.0));
+    const bool avoiding = __int_as_float(row[PATRON_RISK]) < sd_up;
+    unsigned int qs[5]; unsigned int nv = 0;
+    for (unsigned int i = 1; i <= kk; ++i) {
+        if ((i & 3u) == 0) bb = philox4x32_10(make_uint4(i >> 2, p, 0u, dp), key);
+        const unsigned int x = (i & 3u) == 0 ? bb.x : (i & 3u) == 1 ? bb.y : (i & 3u) == 2 ? bb.z : bb.w;
+        const int e = row[__umulhi(x, npat)];
+        if (avoiding && (e & PATRON_HIGH)) continue;
+        const unsigned int q = (unsigned int) (e & 0x3FFFFFFF);
+        bool seen = false;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) if (j < (int) nv && qs[j] == q) seen = true;
+        if (seen) continue;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) if (j == (int) nv) qs[j] = q;
+        nv++; w_v0++;
+        if (s_hot[q >> 5] & (1u << (q & 31))) {
+            atomicAdd(&D.nvis[q], 1u);
+            const unsigned int vi = list_reserve(&D.ctr->n_vis);
+            if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
+            w_v++;
+        }
+    }
+}
+
+// flush a warp's staged records: one reservation, coalesced record stores, one census RED per record
+__device__ __forceinline__ void visit_flush(const Dev& D, const uint2* stage, unsigned int* n_stage, const unsigned int total, const unsigned int lane, unsigned int& w_v) {
+    unsigned int base = 0;
+    if (lane == 0) base = atomicAdd(&D.ctr->n_vis, total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    for (unsigned int i = lane; i < total; i += 32) {
+        const uint2 r = stage[i];
+        atomicAdd(&D.nvis[r.y], 1u);
+        if (base + i < D.cap_vis) D.visit_rec[base + i] = r; else atomicOr(&D.ctr->overflow, 8u);
+    }
+    __syncwarp();
+    if (lane == 0) { *n_stage = 0; w_v += total; }
+    __syncwarp();
+}
+
 __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bitmap_words) {
     extern __shared__ unsigned int s_hot[];
+    __shared__ uint2 s_stage[TPB / 32][VIS_STAGE];
+    __shared__ unsigned int s_slowq[VIS_SLOWQ];
+    __shared__ unsigned int s_nslow, s_nstage[TPB / 32];
     const DayCtx& cx = day_ctx(D);
     for (unsigned int i = threadIdx.x; i < bitmap_words; i += blockDim.x) s_hot[i] = D.pub_hot[i];
+    if (threadIdx.x < TPB / 32) s_nstage[threadIdx.x] = 0;
+    if (threadIdx.x == 0) s_nslow = 0;
     __syncthreads();
-    const unsigned int stride = gridDim.x * blockDim.x * 4u;
-    const unsigned int t_base = D.own_lo & ~127u;                                   // tiles cover the owned agents only
+    const unsigned int stride = gridDim.x * blockDim.x * VIS_A;
+    const unsigned int t_base = D.own_lo & ~(VIS_TILE - 1u);                        // tiles cover the owned agents only
     const unsigned int n_round = t_base + (D.own_hi - t_base + stride - 1) / stride * stride;
     const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
     const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
-    const double sd = cx.sd;
-    const unsigned int lane = threadIdx.x & 31;
+    const float sd_up = cx.sd_up;                                                   // (double) risk < sd  <=>  risk < sd_up (fill_ctx)
+    const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const unsigned int thr0 = D.visit_thr[0], thr1 = D.visit_thr[1], thr2 = D.visit_thr[2], thr3 = D.visit_thr[3];
+    const unsigned int own_lo = D.own_lo, own_n = D.own_hi - D.own_lo, N = D.N;
+    uint2* const stage = s_stage[wid];
     unsigned int w_pat = 0, w_v0 = 0, w_v = 0;
-    // a warp takes tiles of 128 consecutive agents; in slot a lane l handles agent tile + 32 a + l, so the 32-byte patron
-    // rows a load instruction touches are consecutive (8 cache lines per request instead of 32)
-    for (unsigned int t0 = t_base + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 128u; t0 < n_round; t0 += stride) {
-        unsigned int pb4 = 0;
+    // in slot a lane l handles agent tile + 32 a + l, so the 32-byte patron rows a load instruction touches are
+    // consecutive (8 cache lines per request instead of 32)
+    const unsigned int t_first = t_base + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * VIS_TILE;
+    unsigned int pb_next = 0;
 #pragma unroll
-        for (int a = 0; a < 4; ++a) { const unsigned int p = t0 + a * 32 + lane; if (p < D.N) pb4 |= (unsigned int) D.pbyte[p] << (8 * a); }
-        unsigned int recq[12]; unsigned int nrec = 0, recmask = 0, slow = 0;       // hot visits of this lane's four agents (k <= 3)
+    for (int a = 0; a < VIS_A; ++a) { const unsigned int p = t_first + a * 32 + lane; if (p < N) pb_next |= (unsigned int) D.pbyte[p] << (8 * a); }
+    for (unsigned int t0 = t_first; t0 < n_round; t0 += stride) {
+        // the status bytes were loaded one tile ahead (an L2 prefetch of the next tile's patron rows was measured: no gain)
+        const unsigned int pb4 = pb_next;
+        pb_next = 0;
+        if (t0 + stride < n_round) {
 #pragma unroll
-        for (int a = 0; a < 4; ++a) {
+            for (int a = 0; a < VIS_A; ++a) { const unsigned int p = t0 + stride + a * 32 + lane; if (p < N) pb_next |= (unsigned int) D.pbyte[p] << (8 * a); }
+        }
+        unsigned int recq[3 * VIS_A]; unsigned int recmask = 0, slow = 0;          // hot visits of this lane's agents (k <= 3)
+#pragma unroll
+        for (int a = 0; a < VIS_A; ++a) {
+            // written as 0/1 arithmetic: the body has no branch, loads are predicated
             const unsigned int pb = (pb4 >> (8 * a)) & 0xFFu, p = t0 + a * 32 + lane;
             const unsigned int npat = pb & PB_NPAT;
-            const bool act = npat && !(pb & PB_INHOSP) && p >= D.own_lo && p < D.own_hi;     // another handle draws for agents it owns
+            const unsigned int act = (unsigned int) (npat != 0) & (unsigned int) ((pb & PB_INHOSP) == 0) & (unsigned int) ((p - own_lo) < own_n);   // another handle draws for agents it owns
             // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017); no memory needed
             const uint4 b = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
-            unsigned int k = (b.x >= thr0) + (b.x >= thr1) + (b.x >= thr2) + (b.x >= thr3);
-            if (!act) k = 0;
-            w_pat += act ? 1u : 0u;
-            if (k >= 4) { slow |= 1u << a; k = 0; }
+            const unsigned int c3 = act & (unsigned int) (b.x >= thr3);            // k >= 4: generic loop
+            const unsigned int live = act ^ c3;
+            unsigned int v0 = live & (unsigned int) (b.x >= thr0), v1 = live & (unsigned int) (b.x >= thr1), v2 = live & (unsigned int) (b.x >= thr2);
+            slow |= c3 << a;
+            w_pat += act;
             const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
-            int e0 = 0, e1 = 0, e2 = 0; float risk = 0.0f;
-            if (k > 0) { e0 = row[__umulhi(b.y, npat)]; risk = __int_as_float(row[PATRON_RISK]); }
-            if (k > 1) e1 = row[__umulhi(b.z, npat)];
-            if (k > 2) e2 = row[__umulhi(b.w, npat)];
-            const bool avoiding = (double) risk < sd;                              // Community.cpp:1020: compliant households skip high-risk places
-            bool v0 = k > 0, v1 = k > 1, v2 = k > 2;
-            if (avoiding) { v0 = v0 && !(e0 & PATRON_HIGH); v1 = v1 && !(e1 & PATRON_HIGH); v2 = v2 && !(e2 & PATRON_HIGH); }
-            const int q0 = e0 & 0x3FFFFFFF, q1 = e1 & 0x3FFFFFFF, q2 = e2 & 0x3FFFFFFF;
-            v2 = v2 && !(v0 && q2 == q0) && !(v1 && q2 == q1);                     // visit_map (Community.cpp:1014): one entry per distinct place
-            v1 = v1 && !(v0 && q1 == q0);
-            w_v0 += (unsigned int) v0 + (unsigned int) v1 + (unsigned int) v2;
-            const bool h0 = v0 && (s_hot[q0 >> 5] & (1u << (q0 & 31))), h1 = v1 && (s_hot[q1 >> 5] & (1u << (q1 & 31))), h2 = v2 && (s_hot[q2 >> 5] & (1u << (q2 & 31)));
-            recq[a * 3 + 0] = (unsigned int) q0; recq[a * 3 + 1] = (unsigned int) q1; recq[a * 3 + 2] = (unsigned int) q2;
-            recmask |= ((unsigned int) h0 | ((unsigned int) h1 << 1) | ((unsigned int) h2 << 2)) << (a * 3);
-            nrec += (unsigned int) h0 + (unsigned int) h1 + (unsigned int) h2;
+            const unsigned int e0 = ldg_if(row + __umulhi(b.y, npat), v0), e1 = ldg_if(row + __umulhi(b.z, npat), v1), e2 = ldg_if(row + __umulhi(b.w, npat), v2);
+            const unsigned int avoiding = (unsigned int) (__uint_as_float(ldg_if(row + PATRON_RISK, v0)) < sd_up);   // Community.cpp:1020: compliant households skip high-risk places
+            v0 &= (avoiding & (e0 >> 30)) ^ 1u; v1 &= (avoiding & (e1 >> 30)) ^ 1u; v2 &= (avoiding & (e2 >> 30)) ^ 1u;      // bit 30 = PATRON_HIGH
+            const unsigned int q0 = e0 & 0x3FFFFFFFu, q1 = e1 & 0x3FFFFFFFu, q2 = e2 & 0x3FFFFFFFu;
+            v2 &= ((v0 & (unsigned int) (q2 == q0)) | (v1 & (unsigned int) (q2 == q1))) ^ 1u;   // visit_map (Community.cpp:1014): one entry per distinct place
+            v1 &= (v0 & (unsigned int) (q1 == q0)) ^ 1u;
+            w_v0 += v0 + v1 + v2;
+            const unsigned int h0 = v0 & (s_hot[q0 >> 5] >> (q0 & 31)), h1 = v1 & (s_hot[q1 >> 5] >> (q1 & 31)), h2 = v2 & (s_hot[q2 >> 5] >> (q2 & 31));
+            recq[a * 3 + 0] = q0; recq[a * 3 + 1] = q1; recq[a * 3 + 2] = q2;
+            recmask |= (h0 | (h1 << 1) | (h2 << 2)) << (a * 3);
         }
-        // one reservation per warp round for the k <= 3 records
-        unsigned int incl = nrec;
+        // stage the tile's records in the warp buffer (offset from a shared-memory counter); flush when the next tile might not fit
+        const unsigned int nrec = __popc(recmask);
+        unsigned int o = 0;
+        if (nrec) o = atomicAdd(&s_nstage[wid], nrec);
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-        const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
-        if (total) {
-            unsigned int base = 0;
-            if (lane == 31) base = atomicAdd(&D.ctr->n_vis, total);
-            base = __shfl_sync(0xffffffffu, base, 31) + incl - nrec;
-#pragma unroll
-            for (int r = 0; r < 12; ++r) if (recmask & (1u << r)) {
-#ifndef CABM_X_NO_NVIS
-                atomicAdd(&D.nvis[recq[r]], 1u);
-#endif
-#ifndef CABM_X_NO_REC
-                if (base < D.cap_vis) D.visit_rec[base] = make_uint2(t0 + (r / 3) * 32 + lane, recq[r]); else atomicOr(&D.ctr->overflow, 8u);
-#endif
-                ++base;
-            }
-            w_v += nrec;
-        }
-        while (slow) {                                                             // k >= 4: 1.9 % of the drawing agents, generic loop
+        for (int r = 0; r < 3 * VIS_A; ++r) if (recmask & (1u << r)) { stage[o] = make_uint2(t0 + (r / 3) * 32 + lane, recq[r]); ++o; }
+        // k >= 4 (1.9 % of the drawing agents): queued for the block's final pass, so the generic loop runs on full warps
+        while (slow) {
             const unsigned int a = (unsigned int) __ffs(slow) - 1u; slow &= slow - 1u;
-            const unsigned int p = t0 + a * 32 + lane, npat = (pb4 >> (8 * a)) & PB_NPAT;
-            const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
-            uint4 bb = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
-            const unsigned int kk = table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) bb.x * (1.0 / 4294967296.0));
-            const bool avoiding = (double) __int_as_float(row[PATRON_RISK]) < sd;
-            unsigned int qs[5]; unsigned int nv = 0;
-            for (unsigned int i = 1; i <= kk; ++i) {
-                if ((i & 3u) == 0) bb = philox4x32_10(make_uint4(i >> 2, p, 0u, dp), key);
-                const unsigned int x = (i & 3u) == 0 ? bb.x : (i & 3u) == 1 ? bb.y : (i & 3u) == 2 ? bb.z : bb.w;
-                const int e = row[__umulhi(x, npat)];
-                if (avoiding && (e & PATRON_HIGH)) continue;
-                const unsigned int q = (unsigned int) (e & 0x3FFFFFFF);
-                bool seen = false;
-#pragma unroll
-                for (int j = 0; j < 5; ++j) if (j < (int) nv && qs[j] == q) seen = true;
-                if (seen) continue;
-#pragma unroll
-                for (int j = 0; j < 5; ++j) if (j == (int) nv) qs[j] = q;
-                nv++; w_v0++;
-                if (s_hot[q >> 5] & (1u << (q & 31))) {
-                    atomicAdd(&D.nvis[q], 1u);
-                    const unsigned int vi = list_reserve(&D.ctr->n_vis);
-                    if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
-                    w_v++;
-                }
-            }
+            const unsigned int pos = atomicAdd(&s_nslow, 1u), p = t0 + a * 32 + lane;
+            if (pos < VIS_SLOWQ) s_slowq[pos] = p; else visit_slow(D, s_hot, p, dp, key, sd_up, w_v0, w_v);
         }
+        __syncwarp();
+        const unsigned int staged = *(volatile unsigned int*) &s_nstage[wid];
+        if (staged > VIS_STAGE - 3 * VIS_TILE) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v);
     }
+    __syncwarp();
+    { const unsigned int staged = *(volatile unsigned int*) &s_nstage[wid]; if (staged) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v); }
+    __syncthreads();
+    { const unsigned int n = min(s_nslow, (unsigned int) VIS_SLOWQ); for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) visit_slow(D, s_hot, s_slowq[i], dp, key, sd_up, w_v0, w_v); }
     const int ids[3] = { CABM_W_PATRONS, CABM_W_VISITS, CABM_W_HOT_VISITS }; const unsigned int vals[3] = { w_pat, w_v0, w_v };
     block_work_add<3>(D, ids, vals);
 }
-__global__ void __launch_bounds__(TPB, 4) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
-__global__ void __launch_bounds__(TPB, 4) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
+__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
 
 __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1.0, cabm_exp(-hazard)); }
 
@@ -361,6 +444,25 @@ __device__ __forceinline__ unsigned int list_reserve_n(unsigned int* counter, co
 // Every hot location's dependent chain (hot list -> type -> pressure -> roster/neighbour offsets) runs in its own thread,
 // so the chains of all hot locations overlap; the trials themselves are spread over lanes in k_trials.
 // ---------------------------------------------------------------------------------------------
+// three list reservations for every calling thread with one round trip: the scans first, then the (up to three) atomics
+// back to back by the group's last thread, then the broadcasts
+__device__ __forceinline__ void list_reserve3(unsigned int* c0, const unsigned int n0, unsigned int* c1, const unsigned int n1, unsigned int* c2, const unsigned int n2,
+                                              unsigned int& b0, unsigned int& b1, unsigned int& b2) {
+    cg::coalesced_group g = cg::coalesced_threads();
+    unsigned int i0 = n0, i1 = n1, i2 = n2;
+    for (unsigned int o = 1; o < g.size(); o <<= 1) {
+        const unsigned int t0 = g.shfl_up(i0, o), t1 = g.shfl_up(i1, o), t2 = g.shfl_up(i2, o);
+        if (g.thread_rank() >= o) { i0 += t0; i1 += t1; i2 += t2; }
+    }
+    unsigned int a0 = 0, a1 = 0, a2 = 0;
+    if (g.thread_rank() == g.size() - 1) {
+        if (i0) a0 = atomicAdd(c0, i0);
+        if (i1) a1 = atomicAdd(c1, i1);
+        if (i2) a2 = atomicAdd(c2, i2);
+    }
+    b0 = g.shfl(a0, g.size() - 1) + i0 - n0; b1 = g.shfl(a1, g.size() - 1) + i1 - n1; b2 = g.shfl(a2, g.size() - 1) + i2 - n2;
+}
+
 __device__ __forceinline__ void k_hazard_body(const Dev& D) {
     const DayCtx& cx = day_ctx(D);
     const cabm_params* __restrict__ par = D.par;
@@ -368,70 +470,68 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
     unsigned int edges = 0;
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_hot; i += gridDim.x * blockDim.x) {
         const int loc = D.hot_list[i];
+        // everything that depends on `loc` only is loaded in one go (one round trip)
         const int type = D.loc_type[loc];
-        D.hot_off[i] = list_reserve_n(&D.ctr->n_seg, D.loc_cnt[loc]);                // this location's segment of the sorted flag array
-        if (type == CABM_HOSPITAL) continue;
+        const unsigned int cnt = D.loc_cnt[loc];
         const ulonglong2* pw = reinterpret_cast<const ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
         const ulonglong2 pa = pw[0], pb = pw[1];
+        const unsigned int rb = D.roster_off[loc], size = D.roster_off[loc + 1] - rb;
+        const unsigned int nb0 = D.nbr_off[loc], deg = D.nbr_off[loc + 1] - nb0;
+        const float lrisk = D.loc_risk[loc];
+        const unsigned char lf = D.loc_flags[loc];
+        const int q = D.loc_pub[loc];
         const unsigned long long pws[4] = { pa.x, pa.y, pb.x, pb.y };
         const double w = CABM_MUL((double) (pws[0] + pws[1] + pws[2] + pws[3]), 1.0 / 4294967296.0);
-        const unsigned int rb = D.roster_off[loc], size = D.roster_off[loc + 1] - rb;
         double T = 0.0, Ts = 0.0; unsigned int denom = size; int purpose = CABM_P_EXPOSE_HH;
+        unsigned int n_nb = 0;                                // small items for the neighbours (between-household pass)
         if (type == CABM_HOUSE) {
             T = hazard_to_T(CABM_MUL(CABM_MUL(par->haz_mult[CABM_HOUSE], cx.season), w));
-            const unsigned int nb0 = D.nbr_off[loc], deg = D.nbr_off[loc + 1] - nb0;
-            const bool risky = (double) D.loc_risk[loc] > cx.sd;
+            const bool risky = (double) lrisk > cx.sd;
             if (risky) { Ts = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_N_LOCTYPES], cx.season), w), (double) (int) size)); edges += deg; }
-            D.hot_T[2 * i + 1] = Ts;
-            // between_household_transmission (Community.cpp:853-875): one small item per neighbour; count 0 = neighbour below the
-            // social-distancing threshold
-            if (risky && Ts > 0.0 && deg) {
-                const unsigned int base = list_reserve_n(&D.ctr->n_sitems, deg);
-                if (base + deg <= D.cap_sitems) {
-                    for (unsigned int e = 0; e < deg; ++e) {
-                        const int nb = D.nbr[nb0 + e];
-                        const unsigned int b = D.roster_off[nb], c = D.roster_off[nb + 1] - b;
-                        SItem it; it.src = loc; it.begin = (int) b; it.count_purpose = (((double) D.loc_risk[nb] > cx.sd ? c : 0u) << 8) | CABM_P_EXPOSE_NB; it.t_idx = 2 * i + 1;
-                        D.sitems[base + e] = it;
-                    }
-                } else atomicOr(&D.ctr->overflow, 16u);
-            }
+            if (risky && Ts > 0.0) n_nb = deg;
         } else if (type == CABM_WORK) {
-            const unsigned char lf = D.loc_flags[loc];
-            const int q = D.loc_pub[loc];
             denom = size + (q >= 0 ? D.nvis[q] : 0u);
             const bool closed = !(lf & LF_ESSENTIAL) && cx.business_closure != 0.0;
             if (!(denom < 2 || closed) && w > 0.0) {
                 const double f = LF_PUBRISK(lf) == CABM_PT_HIGH ? 4.0 : 0.25;
                 T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(CABM_MUL(par->haz_mult[CABM_WORK], f), cx.season), w), CABM_SUB((double) (int) denom, 1.0)));
             }
-            if (q >= 0) D.pub_T[q] = T;
             purpose = CABM_P_EXPOSE_WORK;
         } else if (type == CABM_SCHOOL) {
             const bool open = cx.is_weekday && cx.school_closure < 1;
             const double coef = CABM_MUL(CABM_MUL(CABM_SUB(1.0, cx.school_closure), par->haz_mult[CABM_SCHOOL]), cx.season);
             if (open && coef != 0.0 && size >= 2) T = hazard_to_T(CABM_DIV(CABM_MUL(coef, w), CABM_SUB((double) (int) size, 1.0)));
             purpose = CABM_P_EXPOSE_SCHOOL;
-        } else {  // NURSINGHOME
+        } else if (type == CABM_NURSINGHOME) {
             if (size >= 2) T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_NURSINGHOME], cx.season), w), CABM_SUB((double) (int) size, 1.0)));
             purpose = CABM_P_EXPOSE_NH;
-        }
+        }                                                     // hospitals are left to k_hosp_import: T stays 0 here, no items
+        const bool own = type != CABM_HOSPITAL && T > 0.0;
+        const unsigned int n_small = n_nb + (own && size <= SMALL_ROSTER ? 1u : 0u);
+        const unsigned int n_big = own && size > SMALL_ROSTER ? (size + CHUNK - 1) / CHUNK : 0u;
+        // this location's segment of the sorted flag array, its small items and its big items: one round trip
+        unsigned int seg, sbase, ibase;
+        list_reserve3(&D.ctr->n_seg, cnt, &D.ctr->n_sitems, n_small, &D.ctr->n_items, n_big, seg, sbase, ibase);
+        D.hot_off[i] = seg;
+        if (type == CABM_HOSPITAL) continue;
         D.hot_T[2 * i] = T;
-        if (T > 0.0) {                                       // the location's own roster
-            if (size <= SMALL_ROSTER) {
-                const unsigned int base = list_reserve_n(&D.ctr->n_sitems, 1u);
-                if (base < D.cap_sitems) { SItem it; it.src = loc; it.begin = (int) rb; it.count_purpose = (size << 8) | (unsigned int) purpose; it.t_idx = 2 * i; D.sitems[base] = it; }
-                else atomicOr(&D.ctr->overflow, 16u);
-            } else {
-                const unsigned int nch = (size + CHUNK - 1) / CHUNK;
-                const unsigned int base = list_reserve_n(&D.ctr->n_items, nch);
-                if (base + nch <= D.cap_items) {
-                    for (unsigned int k = 0; k < nch; ++k) {
-                        Item it; it.src = loc; it.begin = (int) (rb + k * CHUNK); it.count = (int) min((unsigned int) CHUNK, size - k * CHUNK); it.purpose = purpose; it.T = T; it.pad = 0.0;
-                        D.items[base + k] = it;
-                    }
-                } else atomicOr(&D.ctr->overflow, 16u);
-            }
+        if (type == CABM_HOUSE) D.hot_T[2 * i + 1] = Ts;
+        if (type == CABM_WORK && q >= 0) D.pub_T[q] = T;
+        if (n_small) {
+            if (sbase + n_small <= D.cap_sitems) {
+                // between_household_transmission (Community.cpp:853-875): one small item per neighbour, resolved by k_trials
+                // (begin = position in the neighbour array; a neighbour below the social-distancing threshold yields no trials)
+                for (unsigned int e = 0; e < n_nb; ++e) { SItem it; it.src = loc; it.begin = (int) (nb0 + e); it.count_purpose = CABM_P_EXPOSE_NB; it.t_idx = 2 * i + 1; D.sitems[sbase + e] = it; }
+                if (n_small > n_nb) { SItem it; it.src = loc; it.begin = (int) rb; it.count_purpose = (size << 8) | (unsigned int) purpose; it.t_idx = 2 * i; D.sitems[sbase + n_nb] = it; }
+            } else atomicOr(&D.ctr->overflow, 16u);
+        }
+        if (n_big) {
+            if (ibase + n_big <= D.cap_items) {
+                for (unsigned int k = 0; k < n_big; ++k) {
+                    Item it; it.src = loc; it.begin = (int) (rb + k * CHUNK); it.count = (int) min((unsigned int) CHUNK, size - k * CHUNK); it.purpose = purpose; it.T = T; it.pad = 0.0;
+                    D.items[ibase + k] = it;
+                }
+            } else atomicOr(&D.ctr->overflow, 16u);
         }
         if (D.foi_enabled) write_foi(D, i, loc, type, pws, denom, T, Ts);
     }
@@ -458,10 +558,16 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
             const unsigned int si = (u - u_flag) * (TPB / 8) + (threadIdx.x >> 3);
             if (si < n_sitems) {
                 const SItem it = D.sitems[si];
-                const unsigned int cnt = it.count_purpose >> 8;
+                unsigned int cnt = it.count_purpose >> 8; int begin = it.begin;
+                const int purpose = (int) (it.count_purpose & 0xFFu);
+                if (purpose == CABM_P_EXPOSE_NB) {                   // a neighbour household: its roster, unless it keeps its distance today
+                    const int nb = D.nbr[begin];
+                    const unsigned int b = D.roster_off[nb], e = D.roster_off[nb + 1];
+                    cnt = (double) D.loc_risk[nb] > cx.sd ? e - b : 0u; begin = (int) b;
+                }
                 if (cnt) {
                     const double T = D.hot_T[it.t_idx];
-                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[it.begin + m], it.src, (int) (it.count_purpose & 0xFFu), 0, T, trials);
+                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[begin + m], it.src, purpose, 0, T, trials);
                 }
             }
         } else if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
