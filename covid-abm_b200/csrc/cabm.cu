@@ -36,7 +36,7 @@ struct cabm {
     cudaGraphExec_t day_graph = nullptr;
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
-    uint64_t launches_per_day = 11;
+    uint64_t launches_per_day = 10;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
     Dev* d_batch = nullptr; size_t batch_cap = 0; cudaGraphExec_t batch_graph = nullptr; size_t batch_graph_n = 0;   // cabm_batch_run_days: the communities of the batch, indexed by blockIdx.y
@@ -114,7 +114,7 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
 enum { KID_SCAN = 0, KID_ACTIVE, KID_VISIT, KID_HAZARD, KID_TRIALS, KID_GATE0, KID_APPLY_STATUS, KID_HOSP_IMPORT, KID_GATE1, KID_APPLY1,
        KID_END, KID_SMALL, KID_XA, KID_XB, KID_XC, KID_N };
 static const char* const KID_NAMES[KID_N] = { "k_scan", "k_active", "k_visit", "k_hazard", "k_trials", "k_gate(phase0)", "k_apply_status",
-    "k_hosp_import", "k_gate(phase1)", "k_apply(phase1)", "k_end", "(unused)", "exchange A (flags)", "exchange B (census)", "exchange C (patients)" };
+    "k_hosp_import", "(unused)", "k_apply(phase1)", "k_end", "(unused)", "exchange A (flags)", "exchange B (census)", "exchange C (patients)" };
 
 // LAUNCH records an event in front of every kernel when per-kernel profiling is on (stream path only, never under graph capture)
 #define LAUNCH(id, ...) do { if (h->profile) prof_mark(h, id); __VA_ARGS__; h->launches++; } while (0)
@@ -136,6 +136,7 @@ static void prof_collect(cabm_t* h) {      // call after the stream has been syn
 // seed_epidemic after tick() yields.
 // k_scan covers the owned agents only (the whole population on an unsharded handle), in groups of four from own_lo rounded down
 static unsigned int scan_grid(const Dev& D) { return std::max(1u, (unsigned int) ((D.own_hi - (D.own_lo & ~3u) + TPB * 4 * SCAN_V - 1) / (TPB * 4 * SCAN_V))); }
+// one wave: more, smaller blocks were measured slower (55 vs 38 us at 2.7 M agents with 8 waves): every block ends in a latency-bound tail
 static unsigned int visit_grid(const Dev& D, unsigned int sms) { return std::min<unsigned int>((D.N + TPB * VIS_A - 1) / (TPB * VIS_A), sms * VIS_MINB); }
 static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     const Dev& D = h->d; cudaStream_t st = h->stream;
@@ -150,7 +151,6 @@ static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
         LAUNCH(KID_APPLY_STATUS, k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 1));
     }
     LAUNCH(KID_HOSP_IMPORT, k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, tick ? 1 : 0, import ? 1 : 0));
-    LAUNCH(KID_GATE1, k_gate<<<gSM * h->gm[6], 128, 0, st>>>(D, 1));
     LAUNCH(KID_APPLY1, k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0));
     if (!tick && h->d_out_new) cudaMemcpyAsync(h->d_out_new, &D.ctr->n_new[1], sizeof(unsigned int), cudaMemcpyDeviceToDevice, st);
     LAUNCH(KID_END, k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, tick ? 1 : 0, advance));
@@ -322,6 +322,7 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         pbyte[p] = (unsigned char) np;
     }
     D.Q = (unsigned int) pub_loc.size();
+    if (N >= (1u << 29)) { h->err = "more than 2^29 agents: k_visit packs the agent id with its patron count"; return CABM_E_ARG; }
     h->bitmap_words = std::max<unsigned int>(1, (D.Q + 31) / 32);
     if (h->bitmap_words * sizeof(unsigned int) > 160 * 1024) { h->err = "too many patronised locations for the shared-memory hot bitmap"; return CABM_E_ARG; }
     CK(cudaFuncSetAttribute(k_visit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (h->bitmap_words * sizeof(unsigned int))));
@@ -436,8 +437,8 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
     }
     CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, (size_t) n_days * sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
+    CK(cudaEventRecord(h->e0, h->stream));
     if (h->profile) {                // per-kernel timing: plain stream launches, one event in front of every kernel
-        CK(cudaEventRecord(h->e0, h->stream));
         for (int i = 0; i < n_days; ++i) {
             launch_day(h, true, true, 1);
             CK(cudaStreamSynchronize(h->stream)); prof_collect(h);
@@ -455,7 +456,6 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
         CK(cudaGraphInstantiate(&h->day_graph, g, 0));
         cudaGraphDestroy(g);
     }
-    CK(cudaEventRecord(h->e0, h->stream));
     for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day; }
     if ((rc = timed_sync(h))) return rc;
     return check_overflow(h);
@@ -509,7 +509,6 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
         k_gate_b<<<dim3(gx(3), R), 128, 0, st>>>(B, 0);
         k_apply_status_b<<<dim3(gx(4), R), 128, 0, st>>>(B, 0, 1);
         k_hosp_import_b<<<dim3(gx(5), R), TPB, 0, st>>>(B, 1, 1);
-        k_gate_b<<<dim3(gx(6), R), 128, 0, st>>>(B, 1);
         k_apply_status_b<<<dim3(gx(7), R), 128, 0, st>>>(B, 1, 0);
         k_end_b<<<dim3(gx(8), R), TPB, 0, st>>>(B, 1, 1);
     };
@@ -524,7 +523,7 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
         h->batch_graph_n = n;
     }
     CK(cudaEventRecord(h->e0, st));
-    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->batch_graph, st)); h->launches += 11; }
+    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->batch_graph, st)); h->launches += 10; }
     if ((rc = timed_sync(h))) return rc;
     for (size_t r = 0; r < n; ++r) if ((rc = check_overflow(hs[r]))) { if (hs[r] != h) h->err = hs[r]->err; return rc; }
     return CABM_OK;
@@ -667,11 +666,10 @@ int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is
         CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, st));
         if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 2);
         k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, 1, strain_w ? 1 : 0);
-        k_gate<<<gSM * h->gm[6], 128, 0, st>>>(D, 1);
         k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0);
         if (h->d_out_new) CK(cudaMemcpyAsync(h->d_out_new, &D.ctr->n_new[1], sizeof(unsigned int), cudaMemcpyDeviceToDevice, st));
         k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, 1, 0);
-        h->launches += 5;
+        h->launches += 4;
     }
     int32_t n_new = 0;
     if (part == 3 && h->d_out_new) CK(cudaMemcpyAsync(&n_new, h->d_out_new, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
@@ -832,10 +830,9 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
                 k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 2);
             }
             PM(KID_HOSP_IMPORT); k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, 1, 1);
-            PM(KID_GATE1); k_gate<<<gSM * h->gm[6], 128, 0, st>>>(D, 1);
             PM(KID_APPLY1); k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0);
             PM(KID_END); k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, 1, 1);
-            h->launches += 15;
+            h->launches += 14;
         }
         PM(-1);
         CK(cudaMemcpyAsync(h->h_xcounts, h->d_xcounts + CABM_MAX_SHARDS, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));

@@ -252,8 +252,9 @@ __global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) 
 #define VIS_MINB 4            // resident blocks per SM the register allocation aims at
 #endif
 #define VIS_TILE (32 * VIS_A)
-#define VIS_STAGE (4 * VIS_TILE) // hot-visit records a warp stages before it flushes (a tile adds at most 3 * VIS_TILE)
-#define VIS_SLOWQ 512         // k >= 4 agents a block queues for its final full-warp pass (beyond that: handled in place)
+#define VIS_STAGE (4 * VIS_TILE < 512 ? 512 : 4 * VIS_TILE)   // records a warp can stage: a tile adds at most 3 * VIS_TILE, the final k >= 4 pass at most 320
+#define VIS_FLUSH_AT (VIS_STAGE - 3 * VIS_TILE < 128 ? VIS_STAGE - 3 * VIS_TILE : 128)   // flush once more than this is staged after a tile
+#define VIS_SLOWQ (4 * TPB)   // k >= 4 agents a block queues for its final full-warp pass (beyond that: handled in place)
 
 // a 32-bit load that is issued only when `on` is set (0 otherwise): keeps k_visit's body free of branches
 __device__ __forceinline__ unsigned int ldg_if(const int* ptr, unsigned int on) {
@@ -262,35 +263,63 @@ __device__ __forceinline__ unsigned int ldg_if(const int* ptr, unsigned int on) 
     return v;
 }
 
-// the generic public_activity loop for one agent that drew k >= 4 (Community.cpp:1012-1026), one lane per agent
-__device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_hot, const unsigned int p, const unsigned int dp, const uint2 key,
-                                           const float sd_up, unsigned int& w_v0, unsigned int& w_v) {
-    const unsigned int npat = D.pbyte[p] & PB_NPAT;
-    const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
+// the generic public_activity loop for one agent that drew k >= 4 (Community.cpp:1012-1026), one lane per agent.
+// s_thr[j] = ceil(visit_cdf[j] * 2^32): u01 >= cdf  <=>  x >= s_thr (64-bit compare, exact). The whole patron row comes with two
+// 16-byte loads, so the agent's dependent chain is one memory round trip. STAGED: hot visits go to the warp's staging buffer
+// (flushed by the caller); otherwise straight to the global record list.
+template <bool STAGED>
+__device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_hot, const unsigned long long* s_thr, const unsigned int p, const unsigned int npat,
+                                           const unsigned int dp, const uint2 key, const float sd_up, uint2* stage, unsigned int* n_stage, unsigned int& w_v0, unsigned int& w_v) {
+    const uint4* __restrict__ row4 = reinterpret_cast<const uint4*>(D.patron + (size_t) p * PATRON_ROW);
+    const uint4 ra = row4[0], rb = row4[1];
     uint4 bb = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
-    const unsigned int kk = table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) bb.x * (1.0 / 4294967296.0));
-    const bool avoiding = __int_as_float(row[PATRON_RISK]) < sd_up;
+    unsigned int kk = 0;
+    while (kk < CABM_T_POISSON - 1 && (unsigned long long) bb.x >= s_thr[kk]) ++kk;          // table_draw on shared-memory thresholds
+    const bool avoiding = __uint_as_float(rb.y) < sd_up;                                  // row[PATRON_RISK]
     unsigned int qs[5]; unsigned int nv = 0;
     for (unsigned int i = 1; i <= kk; ++i) {
         if ((i & 3u) == 0) bb = philox4x32_10(make_uint4(i >> 2, p, 0u, dp), key);
         const unsigned int x = (i & 3u) == 0 ? bb.x : (i & 3u) == 1 ? bb.y : (i & 3u) == 2 ? bb.z : bb.w;
-        const int e = row[__umulhi(x, npat)];
+        const unsigned int j = __umulhi(x, npat);
+        const unsigned int e = j == 0 ? ra.x : j == 1 ? ra.y : j == 2 ? ra.z : j == 3 ? ra.w : rb.x;
         if (avoiding && (e & PATRON_HIGH)) continue;
-        const unsigned int q = (unsigned int) (e & 0x3FFFFFFF);
+        const unsigned int q = e & 0x3FFFFFFFu;
         bool seen = false;
 #pragma unroll
-        for (int j = 0; j < 5; ++j) if (j < (int) nv && qs[j] == q) seen = true;
+        for (int t = 0; t < 5; ++t) if (t < (int) nv && qs[t] == q) seen = true;
         if (seen) continue;
 #pragma unroll
-        for (int j = 0; j < 5; ++j) if (j == (int) nv) qs[j] = q;
+        for (int t = 0; t < 5; ++t) if (t == (int) nv) qs[t] = q;
         nv++; w_v0++;
         if (s_hot[q >> 5] & (1u << (q & 31))) {
-            atomicAdd(&D.nvis[q], 1u);
-            const unsigned int vi = list_reserve(&D.ctr->n_vis);
-            if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
-            w_v++;
+            if (STAGED) stage[atomicAdd(n_stage, 1u)] = make_uint2(p, q);
+            else {
+                atomicAdd(&D.nvis[q], 1u);
+                const unsigned int vi = list_reserve(&D.ctr->n_vis);
+                if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
+                w_v++;
+            }
         }
     }
+}
+
+// Community::public_activity draws of one agent in 0/1 arithmetic (no branch, predicated loads): k ~ Poisson(1) and the
+// first three picks come from one Philox block (Community.cpp:1013-1017). v0..v2 = pick j is a visit (k > j, not avoided,
+// not a repeat of an earlier pick), q0..q2 = its public-location index, c3 = the agent drew k >= 4 (generic loop instead).
+__device__ __forceinline__ void visit_draw(const Dev& D, const unsigned int p, const unsigned int npat, const unsigned int act, const unsigned int dp, const uint2 key,
+                                           const float sd_up, const unsigned int thr0, const unsigned int thr1, const unsigned int thr2, const unsigned int thr3,
+                                           unsigned int& q0, unsigned int& q1, unsigned int& q2, unsigned int& v0, unsigned int& v1, unsigned int& v2, unsigned int& c3) {
+    const uint4 b = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
+    c3 = act & (unsigned int) (b.x >= thr3);
+    const unsigned int live = act ^ c3;
+    v0 = live & (unsigned int) (b.x >= thr0); v1 = live & (unsigned int) (b.x >= thr1); v2 = live & (unsigned int) (b.x >= thr2);
+    const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
+    const unsigned int e0 = ldg_if(row + __umulhi(b.y, npat), v0), e1 = ldg_if(row + __umulhi(b.z, npat), v1), e2 = ldg_if(row + __umulhi(b.w, npat), v2);
+    const unsigned int avoiding = (unsigned int) (__uint_as_float(ldg_if(row + PATRON_RISK, v0)) < sd_up);   // Community.cpp:1020: compliant households skip high-risk places
+    v0 &= (avoiding & (e0 >> 30)) ^ 1u; v1 &= (avoiding & (e1 >> 30)) ^ 1u; v2 &= (avoiding & (e2 >> 30)) ^ 1u;      // bit 30 = PATRON_HIGH
+    q0 = e0 & 0x3FFFFFFFu; q1 = e1 & 0x3FFFFFFFu; q2 = e2 & 0x3FFFFFFFu;
+    v2 &= ((v0 & (unsigned int) (q2 == q0)) | (v1 & (unsigned int) (q2 == q1))) ^ 1u;   // visit_map (Community.cpp:1014): one entry per distinct place
+    v1 &= (v0 & (unsigned int) (q1 == q0)) ^ 1u;
 }
 
 // flush a warp's staged records: one reservation, coalesced record stores, one census RED per record
@@ -311,12 +340,14 @@ __device__ __forceinline__ void visit_flush(const Dev& D, const uint2* stage, un
 __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bitmap_words) {
     extern __shared__ unsigned int s_hot[];
     __shared__ uint2 s_stage[TPB / 32][VIS_STAGE];
-    __shared__ unsigned int s_slowq[VIS_SLOWQ];
+    __shared__ unsigned int s_slowq[VIS_SLOWQ];                               // agent | patron count << 29
+    __shared__ unsigned long long s_thr[CABM_T_POISSON];
     __shared__ unsigned int s_nslow, s_nstage[TPB / 32];
     const DayCtx& cx = day_ctx(D);
     for (unsigned int i = threadIdx.x; i < bitmap_words; i += blockDim.x) s_hot[i] = D.pub_hot[i];
     if (threadIdx.x < TPB / 32) s_nstage[threadIdx.x] = 0;
     if (threadIdx.x == 0) s_nslow = 0;
+    if (threadIdx.x < CABM_T_POISSON) s_thr[threadIdx.x] = __double2ull_ru(D.par->visit_cdf[threadIdx.x] * 4294967296.0);
     __syncthreads();
     const unsigned int stride = gridDim.x * blockDim.x * VIS_A;
     const unsigned int t_base = D.own_lo & ~(VIS_TILE - 1u);                        // tiles cover the owned agents only
@@ -346,24 +377,13 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
         unsigned int recq[3 * VIS_A]; unsigned int recmask = 0, slow = 0;          // hot visits of this lane's agents (k <= 3)
 #pragma unroll
         for (int a = 0; a < VIS_A; ++a) {
-            // written as 0/1 arithmetic: the body has no branch, loads are predicated
             const unsigned int pb = (pb4 >> (8 * a)) & 0xFFu, p = t0 + a * 32 + lane;
             const unsigned int npat = pb & PB_NPAT;
             const unsigned int act = (unsigned int) (npat != 0) & (unsigned int) ((pb & PB_INHOSP) == 0) & (unsigned int) ((p - own_lo) < own_n);   // another handle draws for agents it owns
-            // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017); no memory needed
-            const uint4 b = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
-            const unsigned int c3 = act & (unsigned int) (b.x >= thr3);            // k >= 4: generic loop
-            const unsigned int live = act ^ c3;
-            unsigned int v0 = live & (unsigned int) (b.x >= thr0), v1 = live & (unsigned int) (b.x >= thr1), v2 = live & (unsigned int) (b.x >= thr2);
+            unsigned int q0, q1, q2, v0, v1, v2, c3;
+            visit_draw(D, p, npat, act, dp, key, sd_up, thr0, thr1, thr2, thr3, q0, q1, q2, v0, v1, v2, c3);
             slow |= c3 << a;
             w_pat += act;
-            const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
-            const unsigned int e0 = ldg_if(row + __umulhi(b.y, npat), v0), e1 = ldg_if(row + __umulhi(b.z, npat), v1), e2 = ldg_if(row + __umulhi(b.w, npat), v2);
-            const unsigned int avoiding = (unsigned int) (__uint_as_float(ldg_if(row + PATRON_RISK, v0)) < sd_up);   // Community.cpp:1020: compliant households skip high-risk places
-            v0 &= (avoiding & (e0 >> 30)) ^ 1u; v1 &= (avoiding & (e1 >> 30)) ^ 1u; v2 &= (avoiding & (e2 >> 30)) ^ 1u;      // bit 30 = PATRON_HIGH
-            const unsigned int q0 = e0 & 0x3FFFFFFFu, q1 = e1 & 0x3FFFFFFFu, q2 = e2 & 0x3FFFFFFFu;
-            v2 &= ((v0 & (unsigned int) (q2 == q0)) | (v1 & (unsigned int) (q2 == q1))) ^ 1u;   // visit_map (Community.cpp:1014): one entry per distinct place
-            v1 &= (v0 & (unsigned int) (q1 == q0)) ^ 1u;
             w_v0 += v0 + v1 + v2;
             const unsigned int h0 = v0 & (s_hot[q0 >> 5] >> (q0 & 31)), h1 = v1 & (s_hot[q1 >> 5] >> (q1 & 31)), h2 = v2 & (s_hot[q2 >> 5] >> (q2 & 31));
             recq[a * 3 + 0] = q0; recq[a * 3 + 1] = q1; recq[a * 3 + 2] = q2;
@@ -378,17 +398,26 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
         // k >= 4 (1.9 % of the drawing agents): queued for the block's final pass, so the generic loop runs on full warps
         while (slow) {
             const unsigned int a = (unsigned int) __ffs(slow) - 1u; slow &= slow - 1u;
-            const unsigned int pos = atomicAdd(&s_nslow, 1u), p = t0 + a * 32 + lane;
-            if (pos < VIS_SLOWQ) s_slowq[pos] = p; else visit_slow(D, s_hot, p, dp, key, sd_up, w_v0, w_v);
+            const unsigned int pos = atomicAdd(&s_nslow, 1u), p = t0 + a * 32 + lane, npat = (pb4 >> (8 * a)) & PB_NPAT;
+            if (pos < VIS_SLOWQ) s_slowq[pos] = p | (npat << 29); else visit_slow<false>(D, s_hot, s_thr, p, npat, dp, key, sd_up, nullptr, nullptr, w_v0, w_v);
         }
         __syncwarp();
-        const unsigned int staged = *(volatile unsigned int*) &s_nstage[wid];
-        if (staged > VIS_STAGE - 3 * VIS_TILE) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v);
+        const unsigned int staged = __shfl_sync(0xffffffffu, *(volatile unsigned int*) &s_nstage[wid], 0);   // one value for the whole warp: the flush is collective
+        if (staged > VIS_FLUSH_AT) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v);
+    }
+    // the block's k >= 4 agents on full warps, their hot visits staged with the warp's leftovers, then one final flush per warp
+    __syncthreads();
+    {
+        const unsigned int n = min(s_nslow, (unsigned int) VIS_SLOWQ);
+        for (unsigned int i0 = wid * 32; i0 < n; i0 += blockDim.x) {                  // warp-uniform trip count; a round stages at most 160 records
+            if (i0 + lane < n) { const unsigned int e = s_slowq[i0 + lane]; visit_slow<true>(D, s_hot, s_thr, e & 0x1FFFFFFFu, e >> 29, dp, key, sd_up, stage, &s_nstage[wid], w_v0, w_v); }
+            __syncwarp();
+            const unsigned int staged = __shfl_sync(0xffffffffu, *(volatile unsigned int*) &s_nstage[wid], 0);
+            if (staged > VIS_FLUSH_AT) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v);
+        }
     }
     __syncwarp();
-    { const unsigned int staged = *(volatile unsigned int*) &s_nstage[wid]; if (staged) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v); }
-    __syncthreads();
-    { const unsigned int n = min(s_nslow, (unsigned int) VIS_SLOWQ); for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) visit_slow(D, s_hot, s_slowq[i], dp, key, sd_up, w_v0, w_v); }
+    { const unsigned int staged = __shfl_sync(0xffffffffu, *(volatile unsigned int*) &s_nstage[wid], 0); if (staged) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v); }
     const int ids[3] = { CABM_W_PATRONS, CABM_W_VISITS, CABM_W_HOT_VISITS }; const unsigned int vals[3] = { w_pat, w_v0, w_v };
     block_work_add<3>(D, ids, vals);
 }
@@ -397,8 +426,11 @@ __global__ void __launch_bounds__(TPB, VIS_MINB) k_visit_b(const Dev* __restrict
 
 __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1.0, cabm_exp(-hazard)); }
 
+// the susceptibility gate of one successful trial (cabm_kernels2.cuh)
+__device__ __forceinline__ void gate_hit(const Dev& D, const int phase, const unsigned int pid, const unsigned int src, const unsigned int purpose, const unsigned int sub);
+
 // one exposure trial: the quarantine skip and `gsl_rng_uniform(RNG) < T` of Community::_transmission (Community.cpp:975-976).
-// A success is queued for the susceptibility gate (k_gate).
+// A success of the house..nursing-home passes is queued for the susceptibility gate (k_gate); the hospital pass gates in place.
 __device__ __forceinline__ void trial(const Dev& D, const int day, const int phase, const unsigned int pid, const int src, const int purpose,
                                       const unsigned int sub, const double T, unsigned int& trials) {
     if (pid < D.own_lo || pid >= D.own_hi) return;                                 // the owner of an agent draws its exposures
@@ -410,8 +442,8 @@ __device__ __forceinline__ void trial(const Dev& D, const int day, const int pha
     const uint4 b = philox4x32_10(make_uint4(sub << 16, pid, (unsigned int) src, ((unsigned int) day << 8) | (unsigned int) purpose),
                                   make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
     if ((double) b.x * (1.0 / 4294967296.0) < T) {
-        const unsigned int base = phase ? min(D.ctr->n_hits[0], D.cap_hits) : 0u;
-        const unsigned int h = base + list_reserve(&D.ctr->n_hits[phase]);
+        if (phase) { gate_hit(D, 1, pid, (unsigned int) src, (unsigned int) purpose, sub); return; }   // hospital pass: a handful of hits, gated in place
+        const unsigned int h = list_reserve(&D.ctr->n_hits[0]);
         if (h < D.cap_hits) { Hit r; r.pid = pid; r.src = (unsigned int) src; r.purpose = (unsigned int) purpose; r.sub = sub; D.hits[h] = r; }
         else atomicOr(&D.ctr->overflow, 256u);
     }

@@ -105,22 +105,29 @@ __device__ __forceinline__ unsigned long long order_key(const unsigned int purpo
     return make_key(pass, src, (unsigned int) role);
 }
 
-__device__ __forceinline__ void k_gate_body(const Dev& D, const int phase) {
+// calculate_event_probabilities + the Person::infect bail-out (Person.cpp:322-326) for one successful trial or import draw,
+// against the start-of-phase state; a survivor races for its agent with atomicMin on the 64-bit order key, and the first
+// survivor of an agent puts it on the phase's winner list
+__device__ __forceinline__ void gate_hit(const Dev& D, const int phase, const unsigned int pid, const unsigned int src, const unsigned int purpose, const unsigned int sub) {
     const DayCtx& cx = day_ctx(D);
-    const unsigned int lo = phase ? min(D.ctr->n_hits[0], D.cap_hits) : 0u;
-    const unsigned int hi = min(lo + D.ctr->n_hits[phase], D.cap_hits);
-    const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
-    for (unsigned int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
-        const Hit h = D.hits[i];
-        Stream s; InfectCtx c; unsigned long long t_res = 0;
-        event_setup(D, cx, h.pid, h.src, h.purpose, h.sub, s, c, t_res);
-        if (infect_event(D, s, c, false)) {
-            const unsigned long long old = atomicMin(&D.cand[h.pid], order_key(h.purpose, h.src, h.sub));
-            if (old == CABM_CAND_EMPTY) {
-                const unsigned int ni = nbase + list_reserve(&D.ctr->n_new[phase]);
-                if (ni < D.cap_new) D.newinf_list[ni] = h.pid; else atomicOr(&D.ctr->overflow, 32u);
-            }
+    Stream s; InfectCtx c; unsigned long long t_res = 0;
+    event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);
+    if (infect_event(D, s, c, false)) {
+        const unsigned long long old = atomicMin(&D.cand[pid], order_key(purpose, src, sub));
+        if (old == CABM_CAND_EMPTY) {
+            const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
+            const unsigned int ni = nbase + list_reserve(&D.ctr->n_new[phase]);
+            if (ni < D.cap_new) D.newinf_list[ni] = pid; else atomicOr(&D.ctr->overflow, 32u);
         }
+    }
+}
+
+// phase 0 only: the hits of the house..nursing-home passes (k_trials); the hospital pass and the importation gate in place
+__device__ __forceinline__ void k_gate_body(const Dev& D, const int phase) {
+    const unsigned int hi = min(D.ctr->n_hits[0], D.cap_hits);
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
+        const Hit h = D.hits[i];
+        gate_hit(D, phase, h.pid, h.src, h.purpose, h.sub);
     }
 }
 __global__ void __launch_bounds__(128) k_gate(const Dev D, const int phase) { k_gate_body(D, phase); }
@@ -262,14 +269,11 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
         }
     }
     if (do_import) {
-        const unsigned int base = min(D.ctr->n_hits[0], D.cap_hits);
         for (unsigned int i = tid; i < (unsigned int) cx.n_imports; i += nth) {
             const uint4 b = philox4x32_10(make_uint4(0u, i, 0u, ((unsigned int) day << 8) | CABM_P_IMPORT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
             const unsigned int pid = __umulhi(b.x, D.N);
             if (pid < D.own_lo || pid >= D.own_hi) continue;                          // every handle draws the same people, the owner exposes them
-            const unsigned int h = base + list_reserve(&D.ctr->n_hits[1]);
-            if (h < D.cap_hits) { Hit r; r.pid = pid; r.src = i; r.purpose = CABM_P_IMPORT; r.sub = 0; D.hits[h] = r; }
-            else atomicOr(&D.ctr->overflow, 256u);
+            gate_hit(D, 1, pid, i, CABM_P_IMPORT, 0);
         }
     }
     trials = warp_sum(trials);
