@@ -156,3 +156,22 @@ def test_edge_cases_empty_and_tiny():
     for d in range(30):
         g.step(); o.step()
     assert_same_state(g, o, "tiny")
+
+
+def test_many_tiles_per_warp_state_and_work_counters():
+    """1.5 M agents: every warp of k_visit walks several tiles, stages and flushes records repeatedly, and every block queues
+    k >= 4 agents; a strong epidemic makes a large share of the visits land on hot locations. State, ledger and every device
+    work counter (patrons, visits, hot visits, flags, trials, hot locations ...) must equal the oracle's."""
+    pop, P, g, o = make_pair(1_500_000, 16, T=0.15, pde=2e-3, seed=71, pop_seed=3)
+    n = int(pop["n_people"])
+    for c in (g, o):
+        for pid in range(0, n, 500):
+            c.infect(pid, 0, 0)
+    g.run_days(16)
+    for _ in range(16):
+        o.step()
+    assert_same_state(g, o, "1.5M agents")
+    wg, wo = g.work_counters(), o.work_counters()
+    wg.pop("active"); wo.pop("active")      # the oracle counts agents whose window has not ended, the device agents inside their window
+    assert wg == wo, {k: (wg[k], wo[k]) for k in wg if wg[k] != wo[k]}
+    assert wg["hot_visits"] > 500_000 and wg["infections"] > 10_000, wg
