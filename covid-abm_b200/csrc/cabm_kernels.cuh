@@ -137,7 +137,8 @@ __device__ __forceinline__ void flag_location(const Dev& D, int loc, int strain,
 // Community::public_activity draws for one agent (Community.cpp:1012-1026): k ~ Poisson(1) from the first word of
 // the agent's Philox block, then k uniform picks among its patronised locations. Returns the number of distinct
 // locations; qs[] holds public-location indices, hours[] the multiplicities.
-__device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsigned int pid, int npat, int* qs, int* hours) {
+// The agent's 32-byte patron row arrives in (ra, rb): the caller loads it together with the rest of the agent's state.
+__device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsigned int pid, int npat, const uint4 ra, const uint4 rb, int* qs, int* hours) {
     uint4 b = philox4x32_10(make_uint4(0u, pid, 0u, ((unsigned int) cx.day << 8) | CABM_P_VISIT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
     int k;
     if (b.x < D.visit_thr[0]) return 0;
@@ -145,21 +146,19 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
     else if (b.x < D.visit_thr[2]) k = 2;
     else if (b.x < D.visit_thr[3]) k = 3;
     else k = (int) table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
-    int nv = 0, avoiding = -1;
-    const int* __restrict__ row = D.patron + (size_t) pid * PATRON_ROW;
+    int nv = 0;
+    const bool avoiding = (double) __uint_as_float(rb.y) < cx.sd;      // row[PATRON_RISK]
     for (int i = 0; i < k; ++i) {
         const unsigned int idx1 = (unsigned int) i + 1u;              // draw index within the stream (0 was the Poisson draw)
         if ((idx1 & 3u) == 0) b = philox4x32_10(make_uint4(idx1 >> 2, pid, 0u, ((unsigned int) cx.day << 8) | CABM_P_VISIT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
         const unsigned int lane = idx1 & 3u;
         const unsigned int x = lane == 0 ? b.x : lane == 1 ? b.y : lane == 2 ? b.z : b.w;
-        const int e = row[__umulhi(x, (unsigned int) npat)];
-        if (e & PATRON_HIGH) {
-            if (avoiding < 0) avoiding = ((double) __int_as_float(row[PATRON_RISK]) < cx.sd) ? 1 : 0;
-            if (avoiding) continue;
-        }
+        const unsigned int j = __umulhi(x, (unsigned int) npat);
+        const int e = (int) (j == 0 ? ra.x : j == 1 ? ra.y : j == 2 ? ra.z : j == 3 ? ra.w : rb.x);
+        if ((e & PATRON_HIGH) && avoiding) continue;
         const int q = e & 0x3FFFFFFF;
-        int j = 0; while (j < nv && qs[j] != q) ++j;
-        if (j == nv) { qs[nv] = q; hours[nv] = 1; ++nv; } else hours[j]++;
+        int t = 0; while (t < nv && qs[t] != q) ++t;
+        if (t == nv) { qs[nv] = q; hours[nv] = 1; ++nv; } else hours[t]++;
     }
     return nv;
 }
@@ -176,6 +175,8 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
         const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
         const unsigned char pb = D.pbyte[p];
         const int hm = D.home[p], dl = D.day_loc[p];
+        const uint4* __restrict__ row4 = reinterpret_cast<const uint4*>(D.patron + (size_t) p * PATRON_ROW);
+        const uint4 ra = row4[0], rb = row4[1];                                    // the patron row, in flight with the rest of the agent's state
         const bool inhosp = tl_in(t0.hosp_begin, t0.severe_end, day);
         const unsigned char npb = (unsigned char) ((pb & ~PB_INHOSP) | (inhosp ? PB_INHOSP : 0));
         if (npb != pb) D.pbyte[p] = npb;
@@ -190,7 +191,7 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
             const int npat = pb & PB_NPAT;
             if (npat) {
                 int qs[MAXV], hours[MAXV];
-                const int nv = gen_visits(D, cx, p, npat, qs, hours);
+                const int nv = gen_visits(D, cx, p, npat, ra, rb, qs, hours);
                 for (int j = 0; j < nv; ++j) {
                     const unsigned long long cv = (unsigned long long) __double2ll_rn(CABM_MUL(CABM_MUL((double) t1.rel_inf, (double) hours[j]), 536870912.0));
                     if (cv) { locs[nl] = D.pub_loc[qs[j]]; cs[nl] = cv; nl++; }
