@@ -33,10 +33,10 @@ struct cabm {
     std::vector<std::pair<void*, size_t>> dyn;    // dynamic state buffers (snapshot set)
     DayCtx* h_ctx = nullptr; DayCtx* d_ctx = nullptr; int ctx_cap = 0;
     int* d_tmp_int = nullptr;
-    cudaGraphExec_t day_graph = nullptr;
+    cudaGraphExec_t day_graph = nullptr, tick_graph = nullptr, import_graph = nullptr;   // run_days (tick + importation), cabm_tick, cabm_import
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
-    uint64_t launches_per_day = 10;
+    uint64_t launches_per_day = 10, launches_tick = 10, launches_import = 3;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
     Dev* d_batch = nullptr; size_t batch_cap = 0; cudaGraphExec_t batch_graph = nullptr; size_t batch_graph_n = 0;   // cabm_batch_run_days: the communities of the batch, indexed by blockIdx.y
@@ -45,6 +45,8 @@ struct cabm {
     int* d_hosp_ids = nullptr; int* d_pat_save = nullptr; int* d_pat_buf = nullptr; unsigned int n_hosp = 0; unsigned int n_flags_own = 0;   // sharding
     int profile = 0, n_marks = 0; std::vector<cudaEvent_t> marks; std::vector<int> mark_id; double ktime[32] = {0}; uint64_t kcount[32] = {0};
 };
+
+static void drop_graphs(cabm_t* h);
 
 struct cabm_snap {
     std::vector<std::pair<void*, size_t>> bufs;   // device copies, same order as cabm::dyn
@@ -152,9 +154,26 @@ static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     }
     LAUNCH(KID_HOSP_IMPORT, k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, tick ? 1 : 0, import ? 1 : 0));
     LAUNCH(KID_APPLY1, k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0));
-    if (!tick && h->d_out_new) cudaMemcpyAsync(h->d_out_new, &D.ctr->n_new[1], sizeof(unsigned int), cudaMemcpyDeviceToDevice, st);
     LAUNCH(KID_END, k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, tick ? 1 : 0, advance));
     if (h->profile) prof_mark(h, -1);
+}
+
+// kernel arguments (the Dev record) are baked into the captured graphs: whatever changes it drops them
+static void drop_graphs(cabm_t* h) {
+    for (cudaGraphExec_t* g : { &h->day_graph, &h->tick_graph, &h->import_graph }) if (*g) { cudaGraphExecDestroy(*g); *g = nullptr; }
+}
+// capture one launch sequence of the day on the handle's stream; the launches it holds are returned through n_launches
+static int capture_day(cabm_t* h, cudaGraphExec_t* out, bool tick, bool import, int advance, uint64_t* n_launches) {
+    cudaGraph_t g = nullptr;
+    CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    const uint64_t l0 = h->launches;
+    launch_day(h, tick, import, advance);
+    if (n_launches) *n_launches = h->launches - l0;
+    h->launches = l0;
+    CK(cudaStreamEndCapture(h->stream, &g));
+    CK(cudaGraphInstantiate(out, g, 0));
+    cudaGraphDestroy(g);
+    return CABM_OK;
 }
 
 static int ready(cabm_t* h, int day) {
@@ -165,6 +184,12 @@ static int ready(cabm_t* h, int day) {
 static int check_overflow(cabm_t* h) {
     unsigned int ov = 0;
     CK(cudaMemcpy(&ov, &h->d.ctr->overflow, sizeof(ov), cudaMemcpyDeviceToHost));
+    if (ov & ~1u) { h->err = "device list capacity exceeded (mask " + std::to_string(ov) + ")"; return CABM_E_NOMEM; }
+    return CABM_OK;
+}
+// after a synchronised launch sequence that ended in k_end: the overflow mask is already in pinned host memory (no copy)
+static int check_overflow_host(cabm_t* h) {
+    const unsigned int ov = h->d.host_status[0];
     if (ov & ~1u) { h->err = "device list capacity exceeded (mask " + std::to_string(ov) + ")"; return CABM_E_NOMEM; }
     return CABM_OK;
 }
@@ -219,6 +244,9 @@ int cabm_create(cabm_t** out) {
     h->sms = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
     cudaEventCreate(&h->e0); cudaEventCreate(&h->e1);
+    if (cudaHostAlloc((void**) &h->h_pin, 16 * sizeof(int), cudaHostAllocMapped) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
+    std::memset(h->h_pin, 0, 16 * sizeof(int));
+    h->d.host_status = reinterpret_cast<unsigned int*>(h->h_pin) + 4;       // written by k_end: [0] overflow mask, [1] new infections of the hospital pass + importation
     if (const char* e = getenv("CABM_GRID_MULT")) { int k = 0; for (const char* q = e; *q && k < 9; ++k) { h->gm[k] = std::max(1, atoi(q)); while (*q && *q != ',') ++q; if (*q == ',') ++q; } }
     *out = h;
     return CABM_OK;
@@ -228,7 +256,7 @@ int cabm_destroy(cabm_t* h) {
     if (!h) return CABM_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    if (h->day_graph) cudaGraphExecDestroy(h->day_graph);
+    drop_graphs(h);
     if (h->nccl_comm && nccl_api().ok) nccl_api().CommDestroy((ncclComm_t) h->nccl_comm);
     for (int r = 0; r < CABM_MAX_SHARDS; ++r) if (h->peer_flags[r] && r != h->d.shard_rank) cudaIpcCloseMemHandle((void*) h->peer_flags[r]);
     if (h->d_xrecv) cudaFree(h->d_xrecv);
@@ -277,7 +305,7 @@ int cabm_set_params(cabm_t* h, const cabm_params* par) {
         const double c = std::ceil(par->visit_cdf[k] * 4294967296.0);
         h->d.visit_thr[k] = c >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned int) c;
     }
-    if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; }    // kernel arguments are baked into the graph
+    drop_graphs(h);    // kernel arguments are baked into the graph
     h->have_par = true;
     return CABM_OK;
 }
@@ -390,9 +418,13 @@ int cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday) {
     CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
     CK(cudaEventRecord(h->e0, h->stream));
-    launch_day(h, true, false, 0);
+    if (h->profile) launch_day(h, true, false, 0);
+    else {
+        if (!h->tick_graph && (rc = capture_day(h, &h->tick_graph, true, false, 0, &h->launches_tick))) return rc;
+        CK(cudaGraphLaunch(h->tick_graph, h->stream)); h->launches += h->launches_tick;
+    }
     if ((rc = timed_sync(h))) return rc;
-    return check_overflow(h);
+    return check_overflow_host(h);
 }
 
 int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[CABM_N_STRAINS], int32_t* out_infected) {
@@ -403,19 +435,20 @@ int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[C
     for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
     CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));   // no k_scan in front: publish the context directly
     CK(cudaEventRecord(h->e0, h->stream));
-    launch_day(h, false, true, 0);
-    int32_t n_new = 0;
-    CK(cudaMemcpyAsync(&n_new, h->d_out_new, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (h->profile) launch_day(h, false, true, 0);
+    else {
+        if (!h->import_graph && (rc = capture_day(h, &h->import_graph, false, true, 0, &h->launches_import))) return rc;
+        CK(cudaGraphLaunch(h->import_graph, h->stream)); h->launches += h->launches_import;
+    }
     if ((rc = timed_sync(h))) return rc;
-    if (out_infected) *out_infected = n_new;
-    return check_overflow(h);
+    if (out_infected) *out_infected = (int32_t) h->d.host_status[1];               // written by k_end before it zeroes the day counters
+    return check_overflow_host(h);
 }
 
 int cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected) {
     if (!h) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (pid >= h->d.N || strain < 0 || strain >= CABM_N_STRAINS) return CABM_E_ARG;
     cudaSetDevice(h->device);
-    if (!h->h_pin) { CK(cudaHostAlloc((void**) &h->h_pin, 16 * sizeof(int), cudaHostAllocMapped)); }
     k_seed_one<<<1, 32, 0, h->stream>>>(h->d, pid, strain, sim_day, h->h_pin);     // the result lands in pinned host memory over PCIe
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());
@@ -446,19 +479,10 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
         if ((rc = timed_sync(h))) return rc;
         return check_overflow(h);
     }
-    if (!h->day_graph) {             // capture one day (tick + importation) once; every day replays the same graph
-        cudaGraph_t g = nullptr;
-        CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-        const uint64_t l0 = h->launches;
-        launch_day(h, true, true, 1);
-        h->launches_per_day = h->launches - l0; h->launches = l0;
-        CK(cudaStreamEndCapture(h->stream, &g));
-        CK(cudaGraphInstantiate(&h->day_graph, g, 0));
-        cudaGraphDestroy(g);
-    }
+    if (!h->day_graph && (rc = capture_day(h, &h->day_graph, true, true, 1, &h->launches_per_day))) return rc;   // one day (tick + importation), captured once, replayed every day
     for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day; }
     if ((rc = timed_sync(h))) return rc;
-    return check_overflow(h);
+    return check_overflow_host(h);
 }
 
 int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
@@ -559,7 +583,7 @@ int cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, int
     k_quarantine<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, d_p, (unsigned int) n, from_day, std::min(until_day, 32766));
     CK(cudaStreamSynchronize(h->stream));
     cudaFree(d_p);
-    if (!h->d.any_quarantine) { h->d.any_quarantine = 1; if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; } }
+    if (!h->d.any_quarantine) { h->d.any_quarantine = 1; drop_graphs(h); }
     return CABM_OK;
 }
 
@@ -628,7 +652,7 @@ int cabm_shard_config(cabm_t* h, int rank, int world, uint32_t pid_lo, uint32_t 
     if (!h || !h->have_pop || world < 1 || rank < 0 || rank >= world || pid_lo > pid_hi || pid_hi > h->d.N) return CABM_E_ARG;
     cudaSetDevice(h->device);
     h->d.own_lo = pid_lo; h->d.own_hi = pid_hi; h->d.shard_rank = rank;
-    if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; }      // the captured graph carries the old range
+    drop_graphs(h);      // the captured graph carries the old range
     return CABM_OK;
 }
 
@@ -948,7 +972,7 @@ int cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n) {
     if (!h || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     if (!h->d.foi_enabled) {       // first call switches the (otherwise skipped) row writes on; rows exist from the next tick
-        h->d.foi_enabled = 1; if (h->day_graph) { cudaGraphExecDestroy(h->day_graph); h->day_graph = nullptr; }
+        h->d.foi_enabled = 1; drop_graphs(h);
         if (out_n) *out_n = 0; return CABM_OK;
     }
     unsigned int n = 0;

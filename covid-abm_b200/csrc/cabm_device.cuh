@@ -89,6 +89,7 @@ struct Dev {
     unsigned long long* ledger;          // [CABM_N_COUNTERS][R]
     cabm_infection* log; cabm_foi_row* foi; unsigned int* n_foi; int foi_enabled;
     Counters* ctr; const DayCtx* dayctx; DayCtx* today;
+    unsigned int* host_status;           // pinned host memory: [0] overflow mask, [1] n_new[1] of the day, stored by the last block of k_end
     // parameters
     const cabm_params* par; const double* pfd; const double* imr; int n_imr;
     int any_quarantine;

@@ -316,6 +316,8 @@ __device__ __forceinline__ void k_end_body(const Dev& D, const int tick_done, co
         __threadfence();
         if (atomicAdd(&c->end_ticket, 1u) == gridDim.x - 1) {
             if (tick_done) { if (D.shard_rank == 0) c->work[CABM_W_HOT_LOCS] += n_hot; if (D.foi_enabled) *D.n_foi = n_hot; }
+            D.host_status[1] = c->n_new[1]; D.host_status[0] = c->overflow;         // over PCIe into pinned memory: the host reads them after its sync, no copy
+            __threadfence_system();
             unsigned int* w = reinterpret_cast<unsigned int*>(c);
 #pragma unroll
             for (int k = 0; k < CABM_DAY_SCOPED_WORDS; ++k) w[k] = 0;
