@@ -345,28 +345,30 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
     __shared__ unsigned long long s_thr[CABM_T_POISSON];
     __shared__ unsigned int s_nslow, s_nstage[TPB / 32];
     const DayCtx& cx = day_ctx(D);
+    const unsigned int stride = gridDim.x * blockDim.x * VIS_A;
+    const unsigned int t_base = D.own_lo & ~(VIS_TILE - 1u);                        // tiles cover the owned agents only
+    const unsigned int n_round = t_base + (D.own_hi - t_base + stride - 1) / stride * stride;
+    const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned int own_lo = D.own_lo, own_n = D.own_hi - D.own_lo, N = D.N;
+    // in slot a lane l handles agent tile + 32 a + l, so the 32-byte patron rows a load instruction touches are
+    // consecutive (8 cache lines per request instead of 32)
+    const unsigned int t_first = t_base + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * VIS_TILE;
+    // the first tile's status bytes and the day's scalars are requested before the block stages the hot bitmap: one memory
+    // round trip for the whole prologue instead of three
+    unsigned int pb_next = 0;
+#pragma unroll
+    for (int a = 0; a < VIS_A; ++a) { const unsigned int p = t_first + a * 32 + lane; if (p < N) pb_next |= (unsigned int) D.pbyte[p] << (8 * a); }
+    const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
+    const float sd_up = cx.sd_up;                                                   // (double) risk < sd  <=>  risk < sd_up (fill_ctx)
     for (unsigned int i = threadIdx.x; i < bitmap_words; i += blockDim.x) s_hot[i] = D.pub_hot[i];
     if (threadIdx.x < TPB / 32) s_nstage[threadIdx.x] = 0;
     if (threadIdx.x == 0) s_nslow = 0;
     if (threadIdx.x < CABM_T_POISSON) s_thr[threadIdx.x] = __double2ull_ru(D.par->visit_cdf[threadIdx.x] * 4294967296.0);
     __syncthreads();
-    const unsigned int stride = gridDim.x * blockDim.x * VIS_A;
-    const unsigned int t_base = D.own_lo & ~(VIS_TILE - 1u);                        // tiles cover the owned agents only
-    const unsigned int n_round = t_base + (D.own_hi - t_base + stride - 1) / stride * stride;
-    const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
     const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
-    const float sd_up = cx.sd_up;                                                   // (double) risk < sd  <=>  risk < sd_up (fill_ctx)
-    const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const unsigned int thr0 = D.visit_thr[0], thr1 = D.visit_thr[1], thr2 = D.visit_thr[2], thr3 = D.visit_thr[3];
-    const unsigned int own_lo = D.own_lo, own_n = D.own_hi - D.own_lo, N = D.N;
     uint2* const stage = s_stage[wid];
     unsigned int w_pat = 0, w_v0 = 0, w_v = 0;
-    // in slot a lane l handles agent tile + 32 a + l, so the 32-byte patron rows a load instruction touches are
-    // consecutive (8 cache lines per request instead of 32)
-    const unsigned int t_first = t_base + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * VIS_TILE;
-    unsigned int pb_next = 0;
-#pragma unroll
-    for (int a = 0; a < VIS_A; ++a) { const unsigned int p = t_first + a * 32 + lane; if (p < N) pb_next |= (unsigned int) D.pbyte[p] << (8 * a); }
     for (unsigned int t0 = t_first; t0 < n_round; t0 += stride) {
         // the status bytes were loaded one tile ahead (an L2 prefetch of the next tile's patron rows was measured: no gain)
         const unsigned int pb4 = pb_next;
