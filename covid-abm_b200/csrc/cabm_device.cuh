@@ -123,6 +123,11 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
     return c;
 }
 
+// Out-of-line copy for the event streams (Person::infect draws ~25 numbers at as many call sites): the kernels that walk a
+// disease course are latency-bound on one warp per SM and half of their stalls were instruction fetch (k_apply_status was
+// 106 KB of code with Philox inlined at every draw). The streaming kernels (k_visit, k_trials) keep the inline version.
+__device__ __noinline__ uint4 philox4x32_10_call(uint4 c, uint2 k) { return philox4x32_10(c, k); }
+
 struct Stream {
     uint2 key; unsigned int a, b, dp, sub, idx; uint4 buf;
     __device__ __forceinline__ void begin(unsigned long long seed, unsigned int day, unsigned int purpose, unsigned int a_, unsigned int b_, unsigned int sub_ = 0) {
@@ -130,7 +135,7 @@ struct Stream {
     }
     __device__ __forceinline__ unsigned int next() {
         const unsigned int lane = idx & 3u;
-        if (lane == 0) buf = philox4x32_10(make_uint4((sub << 16) | (idx >> 2), a, b, dp), key);
+        if (lane == 0) buf = philox4x32_10_call(make_uint4((sub << 16) | (idx >> 2), a, b, dp), key);
         idx++;
         return lane == 0 ? buf.x : lane == 1 ? buf.y : lane == 2 ? buf.z : buf.w;
     }
@@ -138,11 +143,17 @@ struct Stream {
 };
 
 __device__ __forceinline__ unsigned int table_draw(const double* __restrict__ cdf, int n, double u) {
-    int k = 0; while (k < n - 1 && !(u < cdf[k])) ++k; return (unsigned int) k;
+    int k = 0;
+#pragma unroll 1
+    while (k < n - 1 && !(u < cdf[k])) ++k;       // not unrolled: every iteration's load decides the next, and these draws sit in latency-bound code whose size matters
+    return (unsigned int) k;
 }
 // Parameters::sampler (Parameters.h:433-436)
 __device__ __forceinline__ int ref_sampler(const double* __restrict__ cdf, int n, double r) {
-    int i = 0; while (i < n && cdf[i] < r) ++i; return i;
+    int i = 0;
+#pragma unroll 1
+    while (i < n && cdf[i] < r) ++i;
+    return i;
 }
 
 // strain of the traced infector (Community.cpp:795-825, :982): the draw x picks a point t in [0, total pressure) and the
@@ -158,7 +169,7 @@ __device__ __forceinline__ int pick_strain(const unsigned long long* __restrict_
 }
 
 // Parameters::remainingEfficacy (Parameters.h:611-625)
-__device__ __forceinline__ double remaining_efficacy(const cabm_params* __restrict__ par, double start, double time_delta) {
+__device__ __noinline__ double remaining_efficacy(const cabm_params* __restrict__ par, double start, double time_delta) {
     if (!par->immunity_wanes) return start;
     const double slope = 0.2, intcpt = 2.4603816;
     const double month_delta = CABM_DIV(time_delta, 30.0);
