@@ -40,6 +40,7 @@ struct cabm {
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
     Dev* d_batch = nullptr; size_t batch_cap = 0; cudaGraphExec_t batch_graph = nullptr; size_t batch_graph_n = 0;   // cabm_batch_run_days: the communities of the batch, indexed by blockIdx.y
+    int infect_seq = 0;                          // cabm_infect: sequence number the kernel echoes into h_pin[1] after the result
     int* h_pin = nullptr;                        // pinned, device-visible scratch: single-word results are written by the kernel itself (no staged copy)
     const FlagRaw* peer_flags[CABM_MAX_SHARDS] = { nullptr }; int peer_mode = 0;      // exchange A over peer memory (cudaIpc mappings of the other handles' flag lists)
     int* d_hosp_ids = nullptr; int* d_pat_save = nullptr; int* d_pat_buf = nullptr; unsigned int n_hosp = 0; unsigned int n_flags_own = 0;   // sharding
@@ -449,10 +450,16 @@ int cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_i
     if (!h) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (pid >= h->d.N || strain < 0 || strain >= CABM_N_STRAINS) return CABM_E_ARG;
     cudaSetDevice(h->device);
-    k_seed_one<<<1, 32, 0, h->stream>>>(h->d, pid, strain, sim_day, h->h_pin);     // the result lands in pinned host memory over PCIe
-    CK(cudaStreamSynchronize(h->stream));
+    // The result and then a sequence number land in pinned host memory over PCIe; the host watches the sequence word instead of
+    // waiting for the driver to report the stream idle (the drivers call this once per imported case, hundreds of times a day).
+    const int seq = ++h->infect_seq;
+    k_seed_one<<<1, 32, 0, h->stream>>>(h->d, pid, strain, sim_day, h->h_pin, seq);
     CK(cudaGetLastError());
-    if (out_infected) *out_infected = h->h_pin[0];
+    volatile int* pin = h->h_pin;
+    bool seen = false;
+    for (unsigned int spins = 0; spins < (1u << 22); ++spins) if (pin[1] == seq) { seen = true; break; }   // ~10 us normally; a few ms at most
+    if (!seen) { CK(cudaStreamSynchronize(h->stream)); CK(cudaGetLastError()); if (pin[1] != seq) { h->err = "cabm_infect: the kernel did not report"; return CABM_E_CUDA; } }
+    if (out_infected) *out_infected = pin[0];
     return CABM_OK;
 }
 

@@ -283,14 +283,16 @@ __global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_h
 __global__ void __launch_bounds__(TPB) k_hosp_import_b(const Dev* __restrict__ devs, const int do_hosp, const int do_import) { const Dev D = devs[blockIdx.y]; k_hosp_import_body(D, do_hosp, do_import); }   // one launch, replicate = blockIdx.y
 
 // Community::infect(id, strain) (Community.cpp:550-553): one agent, gate and commit in one go
-__global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain, const int day, int* out) {
+__global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain, const int day, int* out, const int echo) {
     if (threadIdx.x || blockIdx.x) return;
     const unsigned int seq = D.ctr->seed_calls++;                                  // every handle counts every call, the owner applies it
-    if (pid < D.own_lo || pid >= D.own_hi) { *out = 0; return; }
+    if (pid < D.own_lo || pid >= D.own_hi) { out[0] = 0; __threadfence_system(); *(volatile int*) (out + 1) = echo; return; }
     Stream s; s.begin(D.seed, (unsigned int) day, CABM_P_SEED, pid, seq);
     InfectCtx c; c.pid = (int) pid; c.time = day; c.source = -1; c.has_source = false; c.strain = strain; c.infector = -1;
     c.purpose = CABM_P_SEED; c.key_a = pid; c.key_b = seq; c.key_sub = 0;
-    *out = infect_event(D, s, c, true) ? 1 : 0;
+    out[0] = infect_event(D, s, c, true) ? 1 : 0;
+    __threadfence_system();
+    *(volatile int*) (out + 1) = echo;                                              // the host spins on this word (cabm_infect)
 }
 
 // reset what today's hot set and today's winners touched; the last block to finish then closes the day (day-scoped counters
