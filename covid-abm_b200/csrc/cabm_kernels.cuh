@@ -1,18 +1,18 @@
 // covid-abm_b200/csrc/cabm_kernels.cuh -- first half of the day pipeline (sm_100a): who is infectious where,
 // public activity, per-location hazard, exposure trials.
 //
-//   k_scan     all agents      : streams the 4-byte active-window word, block-aggregated compaction of today's
-//                                active agents (replaces walking every Person, Community.cpp:684)
+//   k_scan     all agents      : streams the 4-byte active-window word (16 agents per thread), block-aggregated
+//                                compaction of today's active agents (replaces walking every Person, Community.cpp:684)
 //   k_active   active agents   : Person.cpp:475-486 derived from the stored timeline instead of the reference's
 //                                _isHot calendar: pressure at home / day location / hospital / visited locations
 //                                (Community.cpp:1031-1035), per-location flag chains, hot lists, in-hospital bit
-//   k_visit    all agents      : public_activity (Community.cpp:1006-1039): Poisson(1) visits from one Philox block,
-//                                hot test against a shared-memory bitmap of patronised locations, visitor census,
-//                                block-buffered visit records
-//   k_hazard   hot locations   : _tally_infectiousness + the hazard of every pass (Community.cpp:833-969); one warp
-//                                per location runs the household / neighbour / small-roster trials in place and
-//                                splits big rosters into 256-member items
-//   k_trials   items + visits  : _transmission's `U < T` (Community.cpp:976) for big rosters and visitors; also scatters
+//   k_visit    all agents      : public_activity (Community.cpp:1006-1039): Poisson(1) visits from one Philox block
+//                                (branch-free body), hot test against a shared-memory bitmap of patronised locations,
+//                                visitor census, visit records staged per warp; k >= 4 draws on full warps at the end
+//   k_hazard   hot locations   : _tally_infectiousness + the hazard of every pass (Community.cpp:833-969); one thread
+//                                per location turns pressure into T and emits work items: small rosters and
+//                                neighbour households (resolved by k_trials), 256-member chunks of big rosters
+//   k_trials   items + visits  : _transmission's `U < T` (Community.cpp:976) for rosters and visitors; also scatters
 //                                the day's flag records into one contiguous segment per hot location
 //
 // A trial that succeeds is appended to the hit list; the (rare, heavy) susceptibility gate and the state

@@ -1,9 +1,10 @@
 // covid-abm_b200/csrc/cabm_kernels2.cuh -- second half of the day pipeline: susceptibility gate, winner
 // application fused with the status pass, hospital pass + importation, end of day.
 //
-//   k_gate          hits of a phase : calculate_event_probabilities + the Person::infect bail-out (Person.cpp:322-326)
+//   k_gate          hits of phase 0 : calculate_event_probabilities + the Person::infect bail-out (Person.cpp:322-326)
 //                                     against the start-of-phase state; survivors race with atomicMin on the
 //                                     agent's 64-bit order key, so the first exposure in reference order wins
+//                                     (gate_hit; the hospital pass and the importation call it in place)
 //   k_apply_status  winners + active: Person::infect for each winner (disease course, detection, ledger writes) and,
 //                                     for phase 0, Community::updatePersonStatus (Community.cpp:682-741)
 //   k_hosp_import   hospitals/imports: hospital_transmission (Community.cpp:931-941) after the status pass, and
