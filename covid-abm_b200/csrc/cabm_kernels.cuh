@@ -50,6 +50,25 @@ __device__ __forceinline__ unsigned int group_reserve(const cg::coalesced_group&
     return g.shfl(base, g.size() - 1) + incl - n;
 }
 
+// three list reservations for every calling thread with one round trip: the scans first, then the (up to three) atomics
+// back to back by the group's last thread, then the broadcasts
+__device__ __forceinline__ void list_reserve3(unsigned int* c0, const unsigned int n0, unsigned int* c1, const unsigned int n1, unsigned int* c2, const unsigned int n2,
+                                              unsigned int& b0, unsigned int& b1, unsigned int& b2) {
+    cg::coalesced_group g = cg::coalesced_threads();
+    unsigned int i0 = n0, i1 = n1, i2 = n2;
+    for (unsigned int o = 1; o < g.size(); o <<= 1) {
+        const unsigned int t0 = g.shfl_up(i0, o), t1 = g.shfl_up(i1, o), t2 = g.shfl_up(i2, o);
+        if (g.thread_rank() >= o) { i0 += t0; i1 += t1; i2 += t2; }
+    }
+    unsigned int a0 = 0, a1 = 0, a2 = 0;
+    if (g.thread_rank() == g.size() - 1) {
+        if (i0) a0 = atomicAdd(c0, i0);
+        if (i1) a1 = atomicAdd(c1, i1);
+        if (i2) a2 = atomicAdd(c2, i2);
+    }
+    b0 = g.shfl(a0, g.size() - 1) + i0 - n0; b1 = g.shfl(a1, g.size() - 1) + i1 - n1; b2 = g.shfl(a2, g.size() - 1) + i2 - n2;
+}
+
 __device__ __forceinline__ unsigned int warp_sum(unsigned int v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -210,11 +229,12 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
             atomicAdd(&D.press[(size_t) locs[k] * CABM_N_STRAINS + t1.strain], cs[k]);
             slots[k] = atomicAdd(&D.loc_cnt[locs[k]], 1u);
         }
-        const unsigned int base = group_reserve(g, &D.ctr->n_flags, mine);
         unsigned int nfirst = 0, nfh = 0;
         for (int k = 0; k < nl; ++k) if (slots[k] == 0) { nfirst++; nfh += ltype[k] == CABM_HOSPITAL ? 1u : 0u; }
-        unsigned int hbase = group_reserve(g, &D.ctr->n_hot, nfirst);
-        unsigned int hhbase = g.any(nfh != 0) ? group_reserve(g, &D.ctr->n_hot_hosp, nfh) : 0u;
+        // flag records, hot-list entries and hot hospitals reserved together: the three counters are hit by every warp of the
+        // grid, and in a large epidemic their round trips (same-address atomics queue up) were a quarter of the kernel
+        unsigned int base, hbase, hhbase;
+        list_reserve3(&D.ctr->n_flags, mine, &D.ctr->n_hot, nfirst, &D.ctr->n_hot_hosp, nfh, base, hbase, hhbase);
         for (int k = 0; k < nl; ++k) {
             const unsigned int f = base + k;
             if (f < D.cap_flags) { FlagRaw r; r.loc = locs[k]; r.slot = slots[k]; r.pid = p; r.pad = 0; r.c = cs[k] | ((unsigned long long) t1.strain << 56); D.flags_raw[f] = r; }
@@ -479,25 +499,6 @@ __device__ __forceinline__ unsigned int list_reserve_n(unsigned int* counter, co
 // Every hot location's dependent chain (hot list -> type -> pressure -> roster/neighbour offsets) runs in its own thread,
 // so the chains of all hot locations overlap; the trials themselves are spread over lanes in k_trials.
 // ---------------------------------------------------------------------------------------------
-// three list reservations for every calling thread with one round trip: the scans first, then the (up to three) atomics
-// back to back by the group's last thread, then the broadcasts
-__device__ __forceinline__ void list_reserve3(unsigned int* c0, const unsigned int n0, unsigned int* c1, const unsigned int n1, unsigned int* c2, const unsigned int n2,
-                                              unsigned int& b0, unsigned int& b1, unsigned int& b2) {
-    cg::coalesced_group g = cg::coalesced_threads();
-    unsigned int i0 = n0, i1 = n1, i2 = n2;
-    for (unsigned int o = 1; o < g.size(); o <<= 1) {
-        const unsigned int t0 = g.shfl_up(i0, o), t1 = g.shfl_up(i1, o), t2 = g.shfl_up(i2, o);
-        if (g.thread_rank() >= o) { i0 += t0; i1 += t1; i2 += t2; }
-    }
-    unsigned int a0 = 0, a1 = 0, a2 = 0;
-    if (g.thread_rank() == g.size() - 1) {
-        if (i0) a0 = atomicAdd(c0, i0);
-        if (i1) a1 = atomicAdd(c1, i1);
-        if (i2) a2 = atomicAdd(c2, i2);
-    }
-    b0 = g.shfl(a0, g.size() - 1) + i0 - n0; b1 = g.shfl(a1, g.size() - 1) + i1 - n1; b2 = g.shfl(a2, g.size() - 1) + i2 - n2;
-}
-
 __device__ __forceinline__ void k_hazard_body(const Dev& D) {
     const DayCtx& cx = day_ctx(D);
     const cabm_params* __restrict__ par = D.par;
