@@ -172,11 +172,10 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
     return m;
 }
 
-// Warp index space: warps [0, n_w) take one winner of `phase` each -- Person::infect is a long, branchy, latency-bound
-// routine, so winners are NOT packed into the lanes of a warp (32 divergent disease courses would run one after the
-// other); lane 0 commits, all lanes help with the infector search -- then warps [n_w, n_w + ceil(n_active/32)) run the
-// status pass (with_status) over the agents active at the start of the day that were not re-infected in phase 0.
-// cand[] keeps the winner keys until k_end so the status half can tell who was re-infected.
+// Warp index space: the first n_wu warps take W winners of `phase` each (W = 1 unless the winners outnumber the warps, see
+// below); every lane commits its own winner, the whole warp helps with the infector search of long flag segments. Then
+// ceil(n_active/32) warps run the status pass (with_status) over the agents active at the start of the day that were not
+// re-infected in phase 0. cand[] keeps the winner keys until k_end so the status half can tell who was re-infected.
 __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phase, const int with_status) {
     __shared__ unsigned int sm[CABM_N_COUNTERS];
     if (threadIdx.x < CABM_N_COUNTERS) sm[threadIdx.x] = 0;
@@ -185,30 +184,50 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
     const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
     const unsigned int n_w = min(nbase + D.ctr->n_new[phase], D.cap_new) - nbase;
     const unsigned int n_a = with_status ? min(D.ctr->n_active, D.cap_active) : 0u;
-    const unsigned int n_units = n_w + (n_a + 31) / 32;
     const unsigned int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    // Winners per warp: one while there are at least as many warps as winners (Person::infect is a long dependent chain, a
+    // winner alone in its warp finishes soonest), W = ceil(winners / warps) <= 32 lanes of a warp in a large epidemic: the lanes
+    // walk their disease courses together, every branch arm is issued once per warp, and the loads of all W chains overlap.
+    const unsigned int W = min(32u, max(1u, (n_w + n_warps - 1) / n_warps));
+    const unsigned int n_wu = (n_w + W - 1) / W;
+    const unsigned int n_units = n_wu + (n_a + 31) / 32;
     for (unsigned int u = warp; u < n_units; u += n_warps) {
         unsigned int m = 0;
-        if (u < n_w) {
-            const unsigned int pid = D.newinf_list[nbase + u];
-            const unsigned long long key = D.cand[pid];
-            const int pass = (int) (key >> 40); const unsigned int src = (unsigned int) (key >> 8); const unsigned int role = (unsigned int) (key & 0xFF);
-            unsigned int purpose = (unsigned int) pass, sub = 0;
-            if (pass == PASS_WORK) purpose = role ? CABM_P_EXPOSE_WORK : CABM_P_EXPOSE_WORK_VIS;
-            else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
-            Stream s; InfectCtx c; unsigned long long t_res = 0;
-            event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);                 // all lanes: same values
-            if (c.has_source) {
-                const unsigned int seg_n = D.loc_cnt[src]; const Flag* seg = D.flags + D.hot_off[D.loc_hot[src]];
-                if (seg_n <= INFECTOR_THREAD_MAX) { if (lane == 0) c.infector = pick_infector_thread(seg, seg_n, c.strain, t_res); }
-                else c.infector = pick_infector_warp(seg, seg_n, c.strain, t_res);
+        if (u < n_wu) {
+            const unsigned int wi = u * W + lane;
+            const bool have = lane < W && wi < n_w;
+            unsigned int pid = 0; Stream s; InfectCtx c; unsigned long long t_res = 0;
+            unsigned int seg_n = 0, seg_off = 0; bool longseg = false;
+            if (have) {
+                pid = D.newinf_list[nbase + wi];
+                const unsigned long long key = D.cand[pid];
+                const int pass = (int) (key >> 40); const unsigned int src = (unsigned int) (key >> 8); const unsigned int role = (unsigned int) (key & 0xFF);
+                unsigned int purpose = (unsigned int) pass, sub = 0;
+                if (pass == PASS_WORK) purpose = role ? CABM_P_EXPOSE_WORK : CABM_P_EXPOSE_WORK_VIS;
+                else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
+                event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);
+                if (c.has_source) {
+                    seg_n = D.loc_cnt[src]; seg_off = D.hot_off[D.loc_hot[src]];
+                    if (seg_n <= INFECTOR_THREAD_MAX) c.infector = pick_infector_thread(D.flags + seg_off, seg_n, c.strain, t_res);
+                    else longseg = true;
+                }
             }
-            if (lane == 0) {
+            // long flag segments (hospitals, big workplaces and schools at the peak): the whole warp searches for one winner at a time
+            __syncwarp();
+            for (unsigned int todo = __ballot_sync(0xffffffffu, longseg); todo; todo &= todo - 1u) {
+                const int l = __ffs(todo) - 1;
+                const unsigned int n_l = __shfl_sync(0xffffffffu, seg_n, l), off_l = __shfl_sync(0xffffffffu, seg_off, l);
+                const int strain_l = __shfl_sync(0xffffffffu, c.strain, l);
+                const unsigned long long t_l = __shfl_sync(0xffffffffu, t_res, l);
+                const int r = pick_infector_warp(D.flags + off_l, n_l, strain_l, t_l);
+                if ((int) lane == l) c.infector = r;
+            }
+            if (have) {
                 infect_event(D, s, c, true);
                 if (with_status) m = status_one(D, pid, day);
             }
         } else {
-            const unsigned int i = (u - n_w) * 32 + lane;
+            const unsigned int i = (u - n_wu) * 32 + lane;
             if (i < n_a) {
                 const unsigned int p = D.active_list[i];
                 if (D.cand[p] == CABM_CAND_EMPTY) m = status_one(D, p, day);
@@ -224,7 +243,7 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
     __syncthreads();
     if (threadIdx.x < CABM_N_COUNTERS && sm[threadIdx.x]) atomicAdd(&D.ledger[(size_t) threadIdx.x * D.R + day], (unsigned long long) sm[threadIdx.x]);
 }
-__global__ void __launch_bounds__(128) k_apply_status(const Dev D, const int phase, const int with_status) { k_apply_status_body(D, phase, with_status); }
+__global__ void __launch_bounds__(128, 8) k_apply_status(const Dev D, const int phase, const int with_status) { k_apply_status_body(D, phase, with_status); }
 __global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ devs, const int phase, const int with_status) { const Dev D = devs[blockIdx.y]; k_apply_status_body(D, phase, with_status); }   // one launch, replicate = blockIdx.y
 
 // hospital_transmission (Community.cpp:931-941): census = staff + admitted patients; every consumer computes T itself

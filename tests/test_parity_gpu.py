@@ -175,3 +175,21 @@ def test_many_tiles_per_warp_state_and_work_counters():
     wg.pop("active"); wo.pop("active")      # the oracle counts agents whose window has not ended, the device agents inside their window
     assert wg == wo, {k: (wg[k], wo[k]) for k in wg if wg[k] != wo[k]}
     assert wg["hot_visits"] > 500_000 and wg["infections"] > 10_000, wg
+
+
+def test_several_winners_per_warp(monkeypatch):
+    """k_apply_status packs W = ceil(winners / warps) winners into the lanes of a warp once the winners outnumber the warps.
+    A small grid (one block per SM for both apply launches) and a fast epidemic put that path, with thread- and warp-level
+    infector searches, under the same bit-exact comparison as the rest."""
+    monkeypatch.setenv("CABM_GRID_MULT", "8,8,8,4,1,1,2,1,4")
+    pop, P, g, o = make_pair(80000, 40, T=0.35, pde=5e-3, seed=91, pop_seed=17)
+    for c in (g, o):
+        for pid in range(0, 8000, 4):
+            c.infect(pid, 0, 0)
+    for d in range(40):
+        g.step(); o.step()
+        if d % 8 == 7:
+            assert_same_state(g, o, f"day {d}")
+    assert g.getNumNewlyInfected().max() > 1500, g.getNumNewlyInfected().max()      # > 592 warps' worth of winners in a day
+    hg, ho = sorted_hist(g), sorted_hist(o)
+    assert hg.size == ho.size and np.array_equal(hg, ho)
