@@ -185,10 +185,12 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
     const unsigned int n_w = min(nbase + D.ctr->n_new[phase], D.cap_new) - nbase;
     const unsigned int n_a = with_status ? min(D.ctr->n_active, D.cap_active) : 0u;
     const unsigned int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
-    // Winners per warp: one while there are at least as many warps as winners (Person::infect is a long dependent chain, a
-    // winner alone in its warp finishes soonest), W = ceil(winners / warps) <= 32 lanes of a warp in a large epidemic: the lanes
-    // walk their disease courses together, every branch arm is issued once per warp, and the loads of all W chains overlap.
-    const unsigned int W = min(32u, max(1u, (n_w + n_warps - 1) / n_warps));
+    // Winners per warp: one while the winners fit in two rounds of the grid's warps (Person::infect is a long dependent chain, a
+    // winner alone in its warp finishes soonest, and a second round costs less than two divergent courses in one warp);
+    // beyond that W = ceil(winners / (2 * warps)) <= 32 lanes per warp: the lanes walk their disease courses together, every
+    // branch arm is issued once per warp, and the loads of all W chains overlap. Measured on the 365-day 21.5 M-agent run:
+    // W = 1 always 1148 us per day, packing from one round on 1228, from two rounds on 1078 (three: 1079, four: 1082).
+    const unsigned int W = min(32u, max(1u, (n_w + 2 * n_warps - 1) / (2 * n_warps)));
     const unsigned int n_wu = (n_w + W - 1) / W;
     const unsigned int n_units = n_wu + (n_a + 31) / 32;
     for (unsigned int u = warp; u < n_units; u += n_warps) {
