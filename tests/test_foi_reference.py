@@ -13,6 +13,8 @@ What this pins beyond the formulas: the hot-location calendar (who is infectious
 cases staying home), the public-activity visitor census in the workplace denominators (the reference's visit draws are served
 from the per-person Philox streams), hospital census after the status pass, gates (school closure, weekday, social
 distancing vs household riskiness), seasonality, and Person::infect for every scripted case (final records compared).
+The reference's own ledger of the run (20 daily series + cumulative outcome tallies, dumped by the same probe run) must be
+reproduced bit for bit as well: that pins updatePersonStatus and the ledger writers.
 """
 import os
 
@@ -50,12 +52,19 @@ def _run(make):
         rows.append(c.foi().copy())
     hist = c.infection_histories()
     cur = c.current_infections()
+    ledger = c.ledger_table(); cumul = c.getCumulIncidenceByOutcome()
     c.close()
-    return took, rows, hist, cur, pop, P
+    return took, rows, hist, cur, pop, P, ledger, cumul
 
 
-def _compare(took, rows, hist, cur, pop, P):
+def _compare(took, rows, hist, cur, pop, P, ledger, cumul):
     G = np.load(GOLD)
+    # The reference's own CommunityLedger of the same run (Community.h:112-130; the 13 tallies of updatePersonStatus,
+    # Community.cpp:682-741, and the future-dated reportCase / reportDeath writes, :657-679), number for number, every day.
+    bad = np.argwhere(ledger != G["ledger"])
+    assert bad.size == 0, f"ledger differs from the reference's at (day, counter) {bad[:6].tolist()}"
+    assert np.array_equal(cumul, G["cumul"]), (cumul, G["cumul"])
+    assert G["ledger"][:, 0].sum() == G["seeds"][:, 2].sum() and G["ledger"][:, 8].sum() > 100 and G["ledger"][:, 12].sum() > 100
     risk, nbr_off, nbr = np.asarray(pop["loc_risk"]), np.asarray(pop["nbr_off"]), np.asarray(pop["nbr"])
     assert np.array_equal(np.array(took, dtype=np.int32), G["seeds"]), "Person::infect outcome of a scripted case differs"
     assert len(hist) == int(G["seeds"][:, 2].sum()), "somebody was infected outside the script"
