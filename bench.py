@@ -40,16 +40,15 @@ DAYS_PER_STEP = 10
 N_AGENTS = int(os.environ.get("CABM_BENCH_AGENTS", 2_700_000))
 MUTANTS = ("2020-03-21", "2020-05-20", "2030-01-01")          # alpha ~day 40, delta ~day 100 (start 2020-02-10)
 REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
-BYTES = dict(agents=4, active=40, flags=12, patrons=16.6, visits=4, hot_visits=20, hot_locs=28, nbr_edges=8, trials=10, infections=64)
+BYTES = dict(agents=0, active=40, flags=12, patrons=16.6, visits=4, hot_visits=20, hot_locs=28, nbr_edges=8, trials=10, infections=64)
 # kernels of the day pipeline and the byte-model terms each one moves (DESIGN.md "kernels and byte model"); the gate and the
 # two apply launches share the per-infection term
 KERNEL_GROUPS = [
-    ("k_scan", ("k_scan",), ("agents",)),
     ("k_active", ("k_active",), ("active", "flags")),
     ("k_visit", ("k_visit",), ("patrons", "visits", "hot_visits")),
     ("k_hazard", ("k_hazard",), ("hot_locs", "nbr_edges")),
     ("k_trials+k_hosp_import", ("k_trials", "k_hosp_import"), ("trials",)),
-    ("k_gate+k_apply_status", ("k_gate(phase0)", "k_apply_status", "k_apply(phase1)"), ("infections",)),
+    ("k_apply_status", ("k_apply_status", "k_apply(phase1)"), ("infections",)),
 ]
 
 

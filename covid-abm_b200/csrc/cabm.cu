@@ -25,7 +25,11 @@ struct cabm {
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     double acc_ms = 0.0; uint64_t launches = 0;
     int device = 0, sms = 148;
-    int gm[9] = { 8, 8, 8, 4, 8, 1, 2, 2, 4 };   // blocks per SM: active, hazard, trials, gate0, apply+status, hosp+import, gate1, apply1, end (CABM_GRID_MULT overrides: development knob)
+    int gm[9] = { 8, 8, 6, 4, 8, 2, 2, 2, 4 };   // blocks per SM: active, hazard, trials, (unused), apply+status, hosp+import, (unused), apply1, (unused) (CABM_GRID_MULT overrides: development knob)
+    int pdl = 1;                                 // programmatic dependent launch between the kernels of a day (CABM_PDL=0 switches it off)
+    int visit_bps = 2;                           // resident k_visit blocks per SM (from the occupancy calculator, given the hot bitmap's size)
+    std::vector<float> risk_sorted;              // distinct household riskiness values, ascending: DayCtx::sd_rank = how many lie below the day's social distancing
+    void* scratch = nullptr; size_t scratch_bytes = 0;   // handle-owned device scratch of the small entry points (grows, never shrinks)
     bool have_par = false, have_pop = false;
     cabm_params hpar{};                       // host copy (pointers nulled)
     std::vector<double> h_ti[3];
@@ -36,7 +40,7 @@ struct cabm {
     cudaGraphExec_t day_graph = nullptr, tick_graph = nullptr, import_graph = nullptr;   // run_days (tick + importation), cabm_tick, cabm_import
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
-    uint64_t launches_per_day = 10, launches_tick = 10, launches_import = 3;
+    uint64_t launches_per_day = 7, launches_tick = 7, launches_import = 2;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
     Dev* d_batch = nullptr; size_t batch_cap = 0; cudaGraphExec_t batch_graph = nullptr; size_t batch_graph_n = 0;   // cabm_batch_run_days: the communities of the batch, indexed by blockIdx.y
@@ -70,6 +74,28 @@ static int upload(cabm_t* h, T** p, const std::vector<T>& v) {
     int rc = dalloc(h, p, v.size()); if (rc) return rc;
     if (!v.empty()) CK(cudaMemcpyAsync(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    return CABM_OK;
+}
+
+// handle-owned device scratch for the small entry points (dose lists, quarantine lists, gathers): grows, is never freed before
+// cabm_destroy, so a failing call leaks nothing and a daily call allocates nothing
+static int scratch(cabm_t* h, size_t bytes, void** out) {
+    if (bytes > h->scratch_bytes) {
+        if (h->scratch) { cudaStreamSynchronize(h->stream); cudaFree(h->scratch); h->scratch = nullptr; h->scratch_bytes = 0; }
+        const size_t want = std::max<size_t>(bytes + bytes / 2, 1 << 16);
+        CK(cudaMalloc(&h->scratch, want));
+        h->scratch_bytes = want;
+    }
+    *out = h->scratch;
+    return CABM_OK;
+}
+// the infection log is the only record of past infections (Person::infectionHistory): a record that did not fit is an error
+static int log_count(cabm_t* h, unsigned long long* n) {
+    CK(cudaMemcpy(n, &h->d.ctr->n_log, sizeof(*n), cudaMemcpyDeviceToHost));
+    if (*n > h->d.cap_log) {
+        h->err = "infection log capacity exceeded (" + std::to_string(*n) + " records, capacity " + std::to_string(h->d.cap_log) + "): histories are incomplete";
+        return CABM_E_NOMEM;
+    }
     return CABM_OK;
 }
 
@@ -110,14 +136,16 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
     c.season = h->hpar.seasonality[julian_day - 1];
     c.school_closure = h->h_ti[0][day]; c.business_closure = h->h_ti[1][day]; c.sd = h->h_ti[2][day];
     float up = (float) c.sd; if ((double) up < c.sd) up = nextafterf(up, INFINITY);
-    c.sd_up = up; c.pad = 0.0f;
+    c.sd_up = up;
+    // (double) risk < sd for a household  <=>  the rank of its riskiness among the distinct values < sd_rank
+    c.sd_rank = (unsigned int) (std::lower_bound(h->risk_sorted.begin(), h->risk_sorted.end(), c.sd, [](float r, double sd) { return (double) r < sd; }) - h->risk_sorted.begin());
 }
 
 // kernel ids for per-kernel timing (cabm_kernel_times)
 enum { KID_SCAN = 0, KID_ACTIVE, KID_VISIT, KID_HAZARD, KID_TRIALS, KID_GATE0, KID_APPLY_STATUS, KID_HOSP_IMPORT, KID_GATE1, KID_APPLY1,
        KID_END, KID_SMALL, KID_XA, KID_XB, KID_XC, KID_N };
-static const char* const KID_NAMES[KID_N] = { "k_scan", "k_active", "k_visit", "k_hazard", "k_trials", "k_gate(phase0)", "k_apply_status",
-    "k_hosp_import", "(unused)", "k_apply(phase1)", "k_end", "(unused)", "exchange A (flags)", "exchange B (census)", "exchange C (patients)" };
+static const char* const KID_NAMES[KID_N] = { "(unused)", "k_active", "k_visit", "k_hazard", "k_trials", "(unused)", "k_apply_status",
+    "k_hosp_import", "(unused)", "k_apply(phase1)", "(unused)", "(unused)", "exchange A (flags)", "exchange B (census)", "exchange C (patients)" };
 
 // LAUNCH records an event in front of every kernel when per-kernel profiling is on (stream path only, never under graph capture)
 #define LAUNCH(id, ...) do { if (h->profile) prof_mark(h, id); __VA_ARGS__; h->launches++; } while (0)
@@ -133,29 +161,41 @@ static void prof_collect(cabm_t* h) {      // call after the stream has been syn
     h->n_marks = 0;
 }
 
+// One kernel of the day pipeline. With h->pdl the launch carries the programmatic-stream-serialization attribute: the kernel
+// may start while its predecessor in the stream is still running and synchronises with it at its own griddepcontrol.wait
+// (every kernel of the pipeline has one in front of its first dependent access). Captured into a graph this becomes a
+// programmatic dependency edge. Per-kernel profiling (an event between kernels) launches without it.
+template <typename... KArgs, typename... Args>
+static void launch_k(cabm_t* h, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = (h->pdl && !h->profile) ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 // The launch sequence of one day. tick = Community::tick (Community.cpp:1147-1192), import = the daily
 // seed_epidemic (simulator.h:201-223). With both set the importation draws share the hospital pass's gate/apply
 // launches: an agent hit by both keeps the hospital exposure (lower order key), exactly what running
-// seed_epidemic after tick() yields.
-// k_scan covers the owned agents only (the whole population on an unsharded handle), in groups of four from own_lo rounded down
-static unsigned int scan_grid(const Dev& D) { return std::max(1u, (unsigned int) ((D.own_hi - (D.own_lo & ~3u) + TPB * 4 * SCAN_V - 1) / (TPB * 4 * SCAN_V))); }
-// one wave: more, smaller blocks were measured slower (55 vs 38 us at 2.7 M agents with 8 waves): every block ends in a latency-bound tail
-static unsigned int visit_grid(const Dev& D, unsigned int sms) { return std::min<unsigned int>((D.N + TPB * VIS_A - 1) / (TPB * VIS_A), sms * VIS_MINB); }
+// seed_epidemic after tick() yields. Seven launches for tick + importation, two for an importation alone.
+// one wave of resident blocks: more, smaller blocks were measured slower (every block ends in a latency-bound tail)
+static unsigned int visit_grid(const cabm_t* h, const Dev& D) {
+    const unsigned int tiles = (D.own_hi - (D.own_lo & ~(VIS_TILE - 1u)) + VIS_TILE - 1) / VIS_TILE;
+    return std::max(1u, std::min<unsigned int>((tiles + VIS_WARPS - 1) / VIS_WARPS, (unsigned int) (h->sms * h->visit_bps)));
+}
 static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
-    const Dev& D = h->d; cudaStream_t st = h->stream;
-    const unsigned int gScan = scan_grid(D), gSM = h->sms;
+    const Dev& D = h->d;
+    const unsigned int gSM = h->sms;
     if (tick) {
-        LAUNCH(KID_SCAN, k_scan<<<gScan, TPB, 0, st>>>(D));
-        LAUNCH(KID_ACTIVE, k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D));
-        LAUNCH(KID_VISIT, k_visit<<<visit_grid(D, gSM), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words));
-        LAUNCH(KID_HAZARD, k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D));
-        LAUNCH(KID_TRIALS, k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D));
-        LAUNCH(KID_GATE0, k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D, 0));
-        LAUNCH(KID_APPLY_STATUS, k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 1));
+        LAUNCH(KID_ACTIVE, launch_k(h, k_active, dim3(gSM * h->gm[0]), dim3(TPB), 0, D));
+        LAUNCH(KID_VISIT, launch_k(h, k_visit, dim3(visit_grid(h, D)), dim3(TPB), visit_smem_bytes(h->bitmap_words), D, h->bitmap_words));
+        LAUNCH(KID_HAZARD, launch_k(h, k_hazard, dim3(gSM * h->gm[1]), dim3(TPB), 0, D));
+        LAUNCH(KID_TRIALS, launch_k(h, k_trials, dim3(gSM * h->gm[2]), dim3(TPB), 0, D));
+        LAUNCH(KID_APPLY_STATUS, launch_k(h, k_apply_status, dim3(gSM * h->gm[4]), dim3(128), 0, D, 0, 0));
     }
-    LAUNCH(KID_HOSP_IMPORT, k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, tick ? 1 : 0, import ? 1 : 0));
-    LAUNCH(KID_APPLY1, k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0));
-    LAUNCH(KID_END, k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, tick ? 1 : 0, advance));
+    LAUNCH(KID_HOSP_IMPORT, launch_k(h, k_hosp_import, dim3(gSM * h->gm[5]), dim3(TPB), 0, D, tick ? 1 : 0, import ? 1 : 0));
+    LAUNCH(KID_APPLY1, launch_k(h, k_apply_status, dim3(gSM * h->gm[7]), dim3(128), 0, D, 1, (tick ? 1 : 0) | (advance ? 2 : 0)));
     if (h->profile) prof_mark(h, -1);
 }
 
@@ -188,7 +228,7 @@ static int check_overflow(cabm_t* h) {
     if (ov & ~1u) { h->err = "device list capacity exceeded (mask " + std::to_string(ov) + ")"; return CABM_E_NOMEM; }
     return CABM_OK;
 }
-// after a synchronised launch sequence that ended in k_end: the overflow mask is already in pinned host memory (no copy)
+// after a synchronised launch sequence that closed a day (close_day): the overflow mask is already in pinned host memory (no copy)
 static int check_overflow_host(cabm_t* h) {
     const unsigned int ov = h->d.host_status[0];
     if (ov & ~1u) { h->err = "device list capacity exceeded (mask " + std::to_string(ov) + ")"; return CABM_E_NOMEM; }
@@ -247,7 +287,8 @@ int cabm_create(cabm_t** out) {
     cudaEventCreate(&h->e0); cudaEventCreate(&h->e1);
     if (cudaHostAlloc((void**) &h->h_pin, 16 * sizeof(int), cudaHostAllocMapped) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
     std::memset(h->h_pin, 0, 16 * sizeof(int));
-    h->d.host_status = reinterpret_cast<unsigned int*>(h->h_pin) + 4;       // written by k_end: [0] overflow mask, [1] new infections of the hospital pass + importation
+    h->d.host_status = reinterpret_cast<unsigned int*>(h->h_pin) + 4;       // written by close_day: [0] overflow mask, [1] new infections of the hospital pass + importation
+    if (const char* e = getenv("CABM_PDL")) h->pdl = atoi(e) != 0;
     if (const char* e = getenv("CABM_GRID_MULT")) { int k = 0; for (const char* q = e; *q && k < 9; ++k) { h->gm[k] = std::max(1, atoi(q)); while (*q && *q != ',') ++q; if (*q == ',') ++q; } }
     *out = h;
     return CABM_OK;
@@ -263,6 +304,7 @@ int cabm_destroy(cabm_t* h) {
     if (h->d_xrecv) cudaFree(h->d_xrecv);
     if (h->h_xcounts) cudaFreeHost(h->h_xcounts);
     if (h->h_pin) cudaFreeHost(h->h_pin);
+    if (h->scratch) cudaFree(h->scratch);
     if (h->batch_graph) cudaGraphExecDestroy(h->batch_graph);
     if (h->d_batch) cudaFree(h->d_batch);
     for (void* p : h->allocs) cudaFree(p);
@@ -331,37 +373,61 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     D.own_lo = 0; D.own_hi = N; D.shard_rank = 0;
     int rc;
     // ---- static agents ----
-    std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N), patron((size_t) N * PATRON_ROW, 0);
+    std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N);
     std::vector<unsigned char> age(pop->age, pop->age + N), pflags(N), pbyte(N, 0);
-    std::vector<float> home_risk(N);
-    // patronised ("public") locations get a dense index q: the visit pass tests hotness in a shared-memory bitmap over q
-    std::vector<int> loc_pub(L, -1), pub_loc;
-    for (uint32_t p = 0; p < N; ++p) {
+    // patronised ("public") locations get a dense index q: the visit pass tests hotness in a shared-memory bitmap over q.
+    // The riskiness of a household enters public_activity only through `risk < social_distancing[day]` (Community.cpp:1020),
+    // so the patron row carries its RANK among the distinct household values and the day context the matching threshold.
+    for (uint32_t p = 0; p < N; ++p)
         if (home[p] < 0 || (uint32_t) home[p] >= L || dayl[p] >= (int) L) { h->err = "home/day location out of range"; return CABM_E_ARG; }
+    h->risk_sorted.resize(N);
+    for (uint32_t p = 0; p < N; ++p) h->risk_sorted[p] = pop->loc_risk[home[p]];
+    std::sort(h->risk_sorted.begin(), h->risk_sorted.end());
+    h->risk_sorted.erase(std::unique(h->risk_sorted.begin(), h->risk_sorted.end()), h->risk_sorted.end());
+    h->risk_sorted.shrink_to_fit();
+    if (h->risk_sorted.size() >= PROW_MAX_RANK) { h->err = "more than 2^24 distinct household riskiness values: the patron row holds a 24-bit rank"; return CABM_E_ARG; }
+    const size_t n_rows = ((size_t) N + VIS_TILE - 1) / VIS_TILE * VIS_TILE;          // k_visit copies whole tiles: padded with empty rows
+    std::vector<unsigned int> prow(std::max<size_t>(n_rows, VIS_TILE) * PROW_WORDS, 0u);
+    std::vector<int> loc_pub(L, -1), pub_loc;
+    std::vector<unsigned int> home_rank(L, 0xFFFFFFFFu);
+    for (uint32_t p = 0; p < N; ++p) {
         pflags[p] = (pop->comorbid[p] ? PF_COMORBID : 0) | (pop->ltc[p] ? PF_LTC : 0);
-        home_risk[p] = pop->loc_risk[home[p]];
-        std::memcpy(&patron[(size_t) p * PATRON_ROW + PATRON_RISK], &home_risk[p], sizeof(float));
-        unsigned int np = 0;
+        unsigned int e[5] = { 0, 0, 0, 0, 0 }, np = 0;
         for (uint32_t k = 0; k < NP; ++k) {
             const int loc = pop->patron[(size_t) p * NP + k]; if (loc < 0) break;
             if ((uint32_t) loc >= L) { h->err = "patronised location out of range"; return CABM_E_ARG; }
             if (loc_pub[loc] < 0) { loc_pub[loc] = (int) pub_loc.size(); pub_loc.push_back(loc); }
-            patron[(size_t) p * PATRON_ROW + k] = loc_pub[loc] | (pop->loc_pubrisk[loc] == CABM_PT_HIGH ? PATRON_HIGH : 0); np++;
+            if ((unsigned int) loc_pub[loc] >= PROW_MAX_Q) { h->err = "more than 2^19 patronised locations: the patron row holds 19-bit indices"; return CABM_E_ARG; }
+            e[np++] = (unsigned int) loc_pub[loc] | (pop->loc_pubrisk[loc] == CABM_PT_HIGH ? 1u << PROW_HIGH_BIT : 0u);
         }
+        unsigned int& rank = home_rank[home[p]];
+        if (rank == 0xFFFFFFFFu) rank = (unsigned int) (std::lower_bound(h->risk_sorted.begin(), h->risk_sorted.end(), pop->loc_risk[home[p]]) - h->risk_sorted.begin());
+        { const PRow r = prow_pack(e, np, rank); std::memcpy(&prow[(size_t) p * PROW_WORDS], r.w, sizeof(r.w)); }
         pbyte[p] = (unsigned char) np;
     }
     D.Q = (unsigned int) pub_loc.size();
-    if (N >= (1u << 29)) { h->err = "more than 2^29 agents: k_visit packs the agent id with its patron count"; return CABM_E_ARG; }
     h->bitmap_words = std::max<unsigned int>(1, (D.Q + 31) / 32);
-    if (h->bitmap_words * sizeof(unsigned int) > 160 * 1024) { h->err = "too many patronised locations for the shared-memory hot bitmap"; return CABM_E_ARG; }
-    CK(cudaFuncSetAttribute(k_visit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (h->bitmap_words * sizeof(unsigned int))));
+    {   // dynamic shared memory of k_visit / k_visit_b: the attribute is process-wide per kernel, so it only ever grows
+        static size_t smem_set_dev[64] = { 0 };
+        size_t& smem_set = smem_set_dev[h->device & 63];
+        const size_t need = visit_smem_bytes(h->bitmap_words);
+        if (need > 200 * 1024) { h->err = "too many patronised locations for the shared-memory hot bitmap"; return CABM_E_ARG; }
+        if (need > smem_set) {
+            CK(cudaFuncSetAttribute(k_visit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) need));
+            CK(cudaFuncSetAttribute(k_visit_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) need));
+            smem_set = need;
+        }
+        int bps = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_visit, TPB, need));
+        h->visit_bps = std::max(1, bps);
+    }
     if (pub_loc.empty()) pub_loc.push_back(0);
     std::vector<double> nat_eff(pop->starting_natural_efficacy, pop->starting_natural_efficacy + N);
     std::vector<float> xprot(pop->cross_protection_probability, pop->cross_protection_probability + N);
     std::vector<int> nat_dur(pop->natural_immunity_duration, pop->natural_immunity_duration + N);
-    if ((rc = upload(h, (int**) &D.home, home)) || (rc = upload(h, (int**) &D.day_loc, dayl)) || (rc = upload(h, (int**) &D.patron, patron)) ||
+    if ((rc = upload(h, (int**) &D.home, home)) || (rc = upload(h, (int**) &D.day_loc, dayl)) || (rc = upload(h, (unsigned int**) &D.prow, prow)) ||
         (rc = upload(h, (unsigned char**) &D.age, age)) || (rc = upload(h, (unsigned char**) &D.pflags, pflags)) ||
-        (rc = upload(h, (float**) &D.home_risk, home_risk)) || (rc = upload(h, (double**) &D.nat_eff, nat_eff)) ||
+        (rc = upload(h, (double**) &D.nat_eff, nat_eff)) ||
         (rc = upload(h, (float**) &D.xprot, xprot)) || (rc = upload(h, (int**) &D.nat_dur, nat_dur)) ||
         (rc = upload(h, (int**) &D.loc_pub, loc_pub)) || (rc = upload(h, (int**) &D.pub_loc, pub_loc))) return rc;
     // ---- static locations ----
@@ -391,16 +457,18 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = dalloc(h, &D.quar, N, true)) || (rc = dalloc(h, &D.hosp_count, N, true)) || (rc = dalloc(h, &D.pbyte, N, true)) ||
         (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.inf_place, N, true, 0xFF)) || (rc = dalloc(h, &D.inf_by, N, true, 0xFF)) ||
         (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.loc_cnt, L)) || (rc = dalloc(h, &D.loc_hot, L)) || (rc = dalloc(h, &D.pat_count, L, true)) ||
-        (rc = dalloc(h, &D.nvis, Q1)) || (rc = dalloc(h, &D.pub_T, Q1)) || (rc = dalloc(h, &D.pub_hot, h->bitmap_words))) return rc;
+        (rc = dalloc(h, &D.nvis, Q1)) || (rc = dalloc(h, &D.pub_T, Q1)) || (rc = dalloc(h, &D.pub_hot, ((size_t) h->bitmap_words + 3) & ~(size_t) 3)) ||
+        (rc = dalloc(h, &D.inhosp, n_rows / 32 + 4, true)) || (rc = dalloc(h, &D.act[0], (size_t) N, true)) || (rc = dalloc(h, &D.act[1], (size_t) N, true))) return rc;
     CK(cudaMemcpyAsync(D.pbyte, pbyte.data(), N, cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----
-    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
+    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
     D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + roster.size() / SMALL_ROSTER + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
+    if (const char* e = getenv("CABM_LOG_CAP")) D.cap_log = std::max<unsigned long long>(1, strtoull(e, nullptr, 10));   // test knob: force the log-overflow error
     D.cap_sitems = (unsigned int) std::min<size_t>(0x7FFFFFFF, (size_t) L + nbr.size() + 1024);
     if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, (size_t) 2 * D.cap_hot)) || (rc = dalloc(h, &D.sitems, D.cap_sitems)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
-        (rc = dalloc(h, &D.active_list, D.cap_active)) || (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
-        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
+        (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
+        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
         (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||
         (rc = dalloc(h, &D.n_foi, 1))) return rc;
     k_init_state<<<grid_for(h, std::max(N, L), 8), TPB, 0, h->stream>>>(D);
@@ -434,7 +502,7 @@ int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[C
     DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
     c.day = sim_day; c.julian_day = 1; c.n_imports = expected > 0 ? import_count(h->hpar.seed, sim_day, expected) : 0;
     for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
-    CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));   // no k_scan in front: publish the context directly
+    CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));   // no k_active in front: publish the context directly
     CK(cudaEventRecord(h->e0, h->stream));
     if (h->profile) launch_day(h, false, true, 0);
     else {
@@ -442,7 +510,7 @@ int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[C
         CK(cudaGraphLaunch(h->import_graph, h->stream)); h->launches += h->launches_import;
     }
     if ((rc = timed_sync(h))) return rc;
-    if (out_infected) *out_infected = (int32_t) h->d.host_status[1];               // written by k_end before it zeroes the day counters
+    if (out_infected) *out_infected = (int32_t) h->d.host_status[1];               // written by close_day before it zeroes the day counters
     return check_overflow_host(h);
 }
 
@@ -530,18 +598,15 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
     const Dev* B = h->d_batch; const Dev& D = h->d;
     const unsigned int R = (unsigned int) n, gSM = h->sms;
     auto gx = [&](int k) { return std::max(2u, gSM * (unsigned int) h->gm[k] / R); };             // the SMs are shared by the batch
-    const dim3 gScan(scan_grid(D), R), gVisit(std::min<unsigned int>(visit_grid(D, gSM), std::max(2u, gSM * VIS_MINB / R)), R);
+    const dim3 gVisit(std::min<unsigned int>(visit_grid(h, D), std::max(2u, gSM * (unsigned int) h->visit_bps / R)), R);
     auto one_day = [&]() {
-        k_scan_b<<<gScan, TPB, 0, st>>>(B);
-        k_active_b<<<dim3(gx(0), R), TPB, 0, st>>>(B);
-        k_visit_b<<<gVisit, TPB, h->bitmap_words * sizeof(unsigned int), st>>>(B, h->bitmap_words);
-        k_hazard_b<<<dim3(gx(1), R), TPB, 0, st>>>(B);
-        k_trials_b<<<dim3(gx(2), R), TPB, 0, st>>>(B);
-        k_gate_b<<<dim3(gx(3), R), 128, 0, st>>>(B, 0);
-        k_apply_status_b<<<dim3(gx(4), R), 128, 0, st>>>(B, 0, 1);
-        k_hosp_import_b<<<dim3(gx(5), R), TPB, 0, st>>>(B, 1, 1);
-        k_apply_status_b<<<dim3(gx(7), R), 128, 0, st>>>(B, 1, 0);
-        k_end_b<<<dim3(gx(8), R), TPB, 0, st>>>(B, 1, 1);
+        launch_k(h, k_active_b, dim3(gx(0), R), dim3(TPB), 0, B);
+        launch_k(h, k_visit_b, gVisit, dim3(TPB), visit_smem_bytes(h->bitmap_words), B, h->bitmap_words);
+        launch_k(h, k_hazard_b, dim3(gx(1), R), dim3(TPB), 0, B);
+        launch_k(h, k_trials_b, dim3(gx(2), R), dim3(TPB), 0, B);
+        launch_k(h, k_apply_status_b, dim3(gx(4), R), dim3(128), 0, B, 0, 0);
+        launch_k(h, k_hosp_import_b, dim3(gx(5), R), dim3(TPB), 0, B, 1, 1);
+        launch_k(h, k_apply_status_b, dim3(gx(7), R), dim3(128), 0, B, 1, 3);
     };
     if (!h->batch_graph || h->batch_graph_n != n) {                 // the day of this batch as one graph (the Dev table is read at run time)
         if (h->batch_graph) { cudaGraphExecDestroy(h->batch_graph); h->batch_graph = nullptr; }
@@ -554,7 +619,7 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
         h->batch_graph_n = n;
     }
     CK(cudaEventRecord(h->e0, st));
-    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->batch_graph, st)); h->launches += 10; }
+    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->batch_graph, st)); h->launches += 7; }
     if ((rc = timed_sync(h))) return rc;
     for (size_t r = 0; r < n; ++r) if ((rc = check_overflow(hs[r]))) { if (hs[r] != h) h->err = hs[r]->err; return rc; }
     return CABM_OK;
@@ -566,14 +631,13 @@ int cabm_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8
     if (n == 0) return CABM_OK;
     for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
     cudaSetDevice(h->device);
-    unsigned int* d_p = nullptr; unsigned char* d_ok = nullptr;
-    CK(cudaMalloc(&d_p, n * sizeof(unsigned int))); CK(cudaMalloc(&d_ok, n));
+    void* buf = nullptr; int rc2 = scratch(h, n * sizeof(unsigned int) + n, &buf); if (rc2) return rc2;
+    unsigned int* d_p = (unsigned int*) buf; unsigned char* d_ok = (unsigned char*) buf + n * sizeof(unsigned int);
     CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
     k_vaccinate<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, d_p, (unsigned int) n, sim_day, d_ok);
     std::vector<unsigned char> ok(n);
     CK(cudaMemcpyAsync(ok.data(), d_ok, n, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    cudaFree(d_p); cudaFree(d_ok);
     if (out_ok) std::memcpy(out_ok, ok.data(), n);
     return CABM_OK;
 }
@@ -584,12 +648,11 @@ int cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, int
     if (n == 0) return CABM_OK;
     for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
     cudaSetDevice(h->device);
-    unsigned int* d_p = nullptr;
-    CK(cudaMalloc(&d_p, n * sizeof(unsigned int)));
+    void* buf = nullptr; int rc2 = scratch(h, n * sizeof(unsigned int), &buf); if (rc2) return rc2;
+    unsigned int* d_p = (unsigned int*) buf;
     CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
     k_quarantine<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, d_p, (unsigned int) n, from_day, std::min(until_day, 32766));
     CK(cudaStreamSynchronize(h->stream));
-    cudaFree(d_p);
     if (!h->d.any_quarantine) { h->d.any_quarantine = 1; drop_graphs(h); }
     return CABM_OK;
 }
@@ -633,8 +696,7 @@ int cabm_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_
     if (!h || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     unsigned long long n = 0;
-    CK(cudaMemcpy(&n, &h->d.ctr->n_log, sizeof(n), cudaMemcpyDeviceToHost));
-    n = std::min<unsigned long long>(n, h->d.cap_log);
+    { const int rc = log_count(h, &n); if (rc) return rc; }
     if (out_n) *out_n = (size_t) n;
     if (out && cap) CK(cudaMemcpy(out, h->d.log, std::min<size_t>(cap, (size_t) n) * sizeof(cabm_infection), cudaMemcpyDeviceToHost));
     return CABM_OK;
@@ -644,8 +706,7 @@ int cabm_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_
     if (!h || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     unsigned long long n = 0;
-    CK(cudaMemcpy(&n, &h->d.ctr->n_log, sizeof(n), cudaMemcpyDeviceToHost));
-    n = std::min<unsigned long long>(n, h->d.cap_log);
+    { const int rc = log_count(h, &n); if (rc) return rc; }
     const size_t avail = first < n ? (size_t) n - first : 0;
     if (out_n) *out_n = avail;
     if (out && cap && avail) CK(cudaMemcpy(out, h->d.log + first, std::min(cap, avail) * sizeof(cabm_infection), cudaMemcpyDeviceToHost));
@@ -675,37 +736,30 @@ int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is
     if (part == 0) {
         CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, st));
         CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), st));
-        const unsigned int gScan = scan_grid(D);
-        k_scan<<<gScan, TPB, 0, st>>>(D);
         k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D);
         CK(cudaMemcpyAsync(&h->n_flags_own, &D.ctr->n_flags, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
-        h->launches += 2;
+        h->launches += 1;
     } else if (part == 1) {
-        k_visit<<<visit_grid(D, gSM), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
+        k_visit<<<visit_grid(h, D), TPB, visit_smem_bytes(h->bitmap_words), st>>>(D, h->bitmap_words);
         h->launches += 1;
     } else if (part == 2) {
         if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
         k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D);
         k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D);
-        k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D, 0);
-        k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 1);
+        k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 0);
         if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 1);
-        h->launches += 6;
+        h->launches += 5;
     } else {
         c.n_imports = (strain_w && expected_imports > 0) ? import_count(h->hpar.seed, sim_day, expected_imports) : 0;
         if (strain_w) for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
         CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, st));
         if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 2);
         k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, 1, strain_w ? 1 : 0);
-        k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0);
-        if (h->d_out_new) CK(cudaMemcpyAsync(h->d_out_new, &D.ctr->n_new[1], sizeof(unsigned int), cudaMemcpyDeviceToDevice, st));
-        k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, 1, 0);
-        h->launches += 4;
+        k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 1);
+        h->launches += 3;
     }
-    int32_t n_new = 0;
-    if (part == 3 && h->d_out_new) CK(cudaMemcpyAsync(&n_new, h->d_out_new, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     if ((rc = timed_sync(h))) return rc;
-    if (part == 3 && out_imported) *out_imported = n_new;       // new infections of the hospital pass and the importation on this handle
+    if (part == 3 && out_imported) *out_imported = (int32_t) h->d.host_status[1];   // new infections of the hospital pass and the importation on this handle (written by close_day)
     return part == 3 ? check_overflow(h) : CABM_OK;
 }
 
@@ -818,7 +872,6 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
     }
     CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, (size_t) n_days * sizeof(DayCtx), cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), st));
-    const unsigned int gScan = scan_grid(D);
     // The gather size must be known on the host. Days are enqueued in groups of SHARD_GROUP with no host round trip inside a
     // group; between groups the host reads the largest per-handle flag count and sizes the next gathers at 8x that (floor 8192
     // records, or what cabm_shard_exchange_capacity asked for), so the all-gather moves what the epidemic needs, not N/4 records.
@@ -837,7 +890,6 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
         CK(cudaMemsetAsync(h->d_xcounts + CABM_MAX_SHARDS, 0, sizeof(unsigned int), st));
         CK(cudaEventRecord(h->e0, st));
         for (int i = g0; i < std::min(n_days, g0 + group); ++i) {
-            PM(KID_SCAN); k_scan<<<gScan, TPB, 0, st>>>(D);
             PM(KID_ACTIVE); k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D);
             // exchange A: counts, then the front `cap` records of every handle's flag list
             PM(KID_XA);
@@ -847,13 +899,12 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
                 NK(N.AllGather(D.flags_raw, h->d_xrecv, (size_t) cap * sizeof(FlagRaw), ncclUint8, comm, st));
                 k_flags_in_all<<<gSM * 2, TPB, 0, st>>>(D, h->d_xrecv, h->d_xcounts, cap, h->world, D.shard_rank);
             }
-            PM(KID_VISIT); k_visit<<<visit_grid(D, gSM), TPB, h->bitmap_words * sizeof(unsigned int), st>>>(D, h->bitmap_words);
+            PM(KID_VISIT); k_visit<<<visit_grid(h, D), TPB, visit_smem_bytes(h->bitmap_words), st>>>(D, h->bitmap_words);
             PM(KID_XB); NK(N.AllReduce(D.nvis, D.nvis, D.Q, ncclUint32, ncclSum, comm, st));                    // exchange B
             if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
             PM(KID_HAZARD); k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D);
             PM(KID_TRIALS); k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D);
-            PM(KID_GATE0); k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D, 0);
-            PM(KID_APPLY_STATUS); k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 1);
+            PM(KID_APPLY_STATUS); k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 0);
             if (h->n_hosp) {
                 PM(KID_XC);
                 k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 1);
@@ -861,9 +912,8 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
                 k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 2);
             }
             PM(KID_HOSP_IMPORT); k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, 1, 1);
-            PM(KID_APPLY1); k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 0);
-            PM(KID_END); k_end<<<gSM * h->gm[8], TPB, 0, st>>>(D, 1, 1);
-            h->launches += 14;
+            PM(KID_APPLY1); k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 3);
+            h->launches += 11;
         }
         PM(-1);
         CK(cudaMemcpyAsync(h->h_xcounts, h->d_xcounts + CABM_MAX_SHARDS, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
@@ -916,13 +966,16 @@ int cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint
     cudaSetDevice(h->device);
     if (!h->d_diag) { int rc2 = dalloc(h, &h->d_diag, CABM_N_DIAG); if (rc2) return rc2; }
     unsigned int* d_p = nullptr;
-    if (pids) { CK(cudaMalloc(&d_p, n * sizeof(unsigned int))); CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream)); }
+    if (pids) {
+        void* buf = nullptr; int rc2 = scratch(h, n * sizeof(unsigned int), &buf); if (rc2) return rc2;
+        d_p = (unsigned int*) buf;
+        CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    }
     CK(cudaMemsetAsync(h->d_diag, 0, sizeof(unsigned long long), h->stream));
     k_serosurvey<<<grid_for(h, n, 8), TPB, 0, h->stream>>>(h->d, sim_day, d_p, (unsigned int) n, h->d_diag);
     unsigned long long r = 0;
     CK(cudaMemcpyAsync(&r, h->d_diag, sizeof(r), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    if (d_p) cudaFree(d_p);
     *out_seropos = r;
     return CABM_OK;
 }
@@ -932,13 +985,13 @@ int cabm_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infectio
     if (n == 0) return CABM_OK;
     if (pids) { for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG; } else if (n > h->d.N) return CABM_E_ARG;
     cudaSetDevice(h->device);
-    unsigned int* d_p = nullptr; cabm_infection* d_o = nullptr;
-    CK(cudaMalloc(&d_o, n * sizeof(cabm_infection)));
-    if (pids) { CK(cudaMalloc(&d_p, n * sizeof(unsigned int))); CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream)); }
+    const size_t out_bytes = (n * sizeof(cabm_infection) + 15) & ~(size_t) 15;
+    void* buf = nullptr; int rc2 = scratch(h, out_bytes + (pids ? n * sizeof(unsigned int) : 0), &buf); if (rc2) return rc2;
+    cabm_infection* d_o = (cabm_infection*) buf; unsigned int* d_p = pids ? (unsigned int*) ((unsigned char*) buf + out_bytes) : nullptr;
+    if (pids) CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
     k_gather_infections<<<grid_for(h, n, 4), TPB, 0, h->stream>>>(h->d, d_p, (unsigned int) n, d_o);
     CK(cudaMemcpyAsync(out, d_o, n * sizeof(cabm_infection), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    cudaFree(d_o); if (d_p) cudaFree(d_p);
     return CABM_OK;
 }
 
@@ -946,15 +999,20 @@ int cabm_snapshot(cabm_t* h, cabm_snap_t** out) {
     if (!h || !out || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     cabm_snap_t* s = new cabm_snap();
+    auto fail = [&](cudaError_t e, const char* what) { h->err = std::string(what) + ": " + cudaGetErrorString(e); cabm_snap_free(s); return CABM_E_CUDA; };
+    cudaError_t e;
     for (auto& b : h->dyn) {
-        void* p = nullptr; CK(cudaMalloc(&p, b.second));
-        CK(cudaMemcpyAsync(p, b.first, b.second, cudaMemcpyDeviceToDevice, h->stream));
+        void* p = nullptr;
+        if ((e = cudaMalloc(&p, b.second)) != cudaSuccess) return fail(e, "snapshot: cudaMalloc");
         s->bufs.push_back({ p, b.second });
+        if ((e = cudaMemcpyAsync(p, b.first, b.second, cudaMemcpyDeviceToDevice, h->stream)) != cudaSuccess) return fail(e, "snapshot: copy");
     }
-    CK(cudaMemcpy(&s->n_log, &h->d.ctr->n_log, sizeof(s->n_log), cudaMemcpyDeviceToHost));
-    s->n_log = std::min<unsigned long long>(s->n_log, h->d.cap_log);
-    if (s->n_log) { CK(cudaMalloc(&s->log, s->n_log * sizeof(cabm_infection))); CK(cudaMemcpyAsync(s->log, h->d.log, s->n_log * sizeof(cabm_infection), cudaMemcpyDeviceToDevice, h->stream)); }
-    CK(cudaStreamSynchronize(h->stream));
+    { const int rc = log_count(h, &s->n_log); if (rc) { cabm_snap_free(s); return rc; } }
+    if (s->n_log) {
+        if ((e = cudaMalloc(&s->log, s->n_log * sizeof(cabm_infection))) != cudaSuccess) return fail(e, "snapshot: cudaMalloc(log)");
+        if ((e = cudaMemcpyAsync(s->log, h->d.log, s->n_log * sizeof(cabm_infection), cudaMemcpyDeviceToDevice, h->stream)) != cudaSuccess) return fail(e, "snapshot: copy(log)");
+    }
+    if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) return fail(e, "snapshot: sync");
     *out = s;
     return CABM_OK;
 }

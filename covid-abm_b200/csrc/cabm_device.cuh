@@ -4,7 +4,8 @@
 // Layout (all structure-of-arrays in HBM, one element per agent / location):
 //   agents   : win (active window), tl0/tl1 (latest Infection, 2 x 16 B), imm (infections per strain),
 //              vax (doses, last dose day, naive flag), quar, hosp_count, pbyte (patron count | flags),
-//              cand (64-bit winner key of today's exposure resolution)
+//              cand (64-bit winner key of today's exposure resolution), prow (20-byte packed patron row),
+//              inhosp (one bit per agent: in hospital today), act[2] (the persistent list of agents inside an infection window)
 //   locations: press[4] (u64 fixed-point infectious pressure by strain, 2^-32 units), hot_idx, nvis,
 //              pat_count + static type/flags/risk/hospital, roster CSR, neighbour CSR
 // Day-scoped lists (hot locations, active agents, visits landing on hot locations, exposure work
@@ -41,21 +42,29 @@ struct DayCtx {                     // per-day scalars, staged by the host for e
     int day, julian_day, is_weekday, n_imports;
     double strain_w[CABM_N_STRAINS];
     double season, sd, school_closure, business_closure;
-    float sd_up, pad;               // smallest float >= sd: for a float r, (double) r < sd  <=>  r < sd_up
+    float sd_up;                    // smallest float >= sd: for a float r, (double) r < sd  <=>  r < sd_up
+    unsigned int sd_rank;           // number of distinct household riskiness values below sd: a household keeps away from
+                                    // high-risk places today (Community.cpp:1020) <=> its riskiness rank < sd_rank
 };
 
 // counters living in device memory
 struct Counters {
-    // ---- day-scoped: zeroed by the last block of k_end ----
-    unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;
-    unsigned int n_hits[2], n_new[2];                        // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
-    unsigned int day_pad[4];
+    // ---- day-scoped: zeroed by the block that closes the day (k_apply_status, phase 1) ----
+    unsigned int n_today, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;   // n_today: list entries inside their window today
+    unsigned int n_new[2];                                   // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
+    unsigned int day_pad[6];
     // ---- persistent ----
     unsigned int n_pat;                                      // admitted-patient list length (entries are never removed, see k_status)
     unsigned int overflow;                                   // sticky: a list ran out of capacity
     unsigned int day_idx;                                    // index into the staged DayCtx array
     unsigned int seed_calls;
-    unsigned int end_ticket;                                 // blocks of k_end that have finished (the last one closes the day)
+    unsigned int end_ticket;                                 // blocks of the closing kernel that have finished (the last one closes the day)
+    // The persistent active list (replaces a daily scan over all agents). act[act_sel] is the list the day's k_active reads;
+    // it copies the entries that are still inside their window tomorrow to act[act_sel ^ 1], and every infection committed
+    // from then on appends there unless the agent is already on it (old window end >= list_day, the day that list is for).
+    // Closing the day swaps the lists. in_tick: k_active of the current day has run (appends go to act[act_sel ^ 1]).
+    unsigned int act_sel, in_tick; int list_day; unsigned int n_act[2];
+    unsigned int pad2;
     unsigned long long n_log;
     unsigned long long work[CABM_N_WORK];
     unsigned long long cumul[CABM_N_OUTCOMES];
@@ -68,8 +77,8 @@ struct Dev {
     // one community over several handles (cabm_shard_config): this handle owns agents [own_lo, own_hi); one handle: [0, N)
     unsigned int own_lo, own_hi; int shard_rank;
     // static agents
-    const int* home; const int* day_loc; const int* patron; const unsigned char* age; const unsigned char* pflags;
-    const double* nat_eff; const float* xprot; const int* nat_dur; const float* home_risk;
+    const int* home; const int* day_loc; const unsigned int* prow; const unsigned char* age; const unsigned char* pflags;
+    const double* nat_eff; const float* xprot; const int* nat_dur;
     // static locations
     const unsigned char* loc_type; const unsigned char* loc_flags; const float* loc_risk; const int* loc_hospital;
     const unsigned int* roster_off; const int* roster; const unsigned int* nbr_off; const int* nbr;
@@ -78,18 +87,20 @@ struct Dev {
     // dynamic agents
     unsigned int* win; Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
     unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand; int* inf_place; int* inf_by; unsigned int* n_caused;
+    unsigned int* inhosp;                // [ceil(N / 128) * 4] one bit per agent: in hospital today (k_active keeps it, k_visit reads it)
+    unsigned int* act[2];                // persistent active list, double-buffered (see Counters)
     // dynamic locations
     unsigned long long* press; unsigned int* loc_cnt; int* loc_hot; unsigned int* pat_count;   // loc_cnt: flags today (0 = not hot), loc_hot: index in hot_list
     unsigned int* nvis; double* pub_T; unsigned int* pub_hot;     // [Q], [Q], [ceil(Q/32)] public-location visitor census, T, hot bitmap
     // day lists
     int* hot_list; int* hot_hosp; unsigned int* hot_off; double* hot_T; FlagRaw* flags_raw; Flag* flags; SItem* sitems;
-    unsigned int* active_list; uint2* visit_rec; Item* items; Hit* hits; unsigned int* newinf_list; unsigned int* patient_list;
-    unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_sitems, cap_hits, cap_new, cap_pat; unsigned long long cap_log;
+    uint2* visit_rec; Item* items; unsigned int* newinf_list; unsigned int* patient_list;
+    unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_sitems, cap_new, cap_pat; unsigned long long cap_log;
     // outputs
     unsigned long long* ledger;          // [CABM_N_COUNTERS][R]
     cabm_infection* log; cabm_foi_row* foi; unsigned int* n_foi; int foi_enabled;
     Counters* ctr; const DayCtx* dayctx; DayCtx* today;
-    unsigned int* host_status;           // pinned host memory: [0] overflow mask, [1] n_new[1] of the day, stored by the last block of k_end
+    unsigned int* host_status;           // pinned host memory: [0] overflow mask, [1] n_new[1] of the day, stored by the block that closes the day
     // parameters
     const cabm_params* par; const double* pfd; const double* imr; int n_imr;
     int any_quarantine;
@@ -107,7 +118,48 @@ struct Dev {
 // loc_flags: bit0 essential, bits 1-2 public transmission risk
 #define LF_ESSENTIAL 1
 #define LF_PUBRISK(f) (((f) >> 1) & 3)
-#define PATRON_HIGH 0x40000000
+
+// The patron row of an agent (Person::patronizedLocations, Person.h:357, plus what public_activity needs to know about the
+// agent's household, Community.cpp:1020): five 32-bit words, 20 bytes, so a uniform pick among the agent's places is ONE
+// 32-bit load at word j of the row (rows are staged in shared memory by k_visit; stride 5 words = conflict-free banks).
+//   word k, bits 0-19 : entry k = index q of the k-th patronised location among the patronised ("public") locations
+//                       (19 bits) | HIGH-risk bit 19
+//   word 0, bits 20-22: npat = number of patronised places (0..5)
+//   words 1-2, bits 20-31: rank (low, high 12 bits) of the household's riskiness among the distinct household riskiness
+//                       values of the population, compared with DayCtx::sd_rank
+#define PROW_WORDS 5
+#define PROW_ENTRY_MASK 0xFFFFFu
+#define PROW_Q_MASK 0x7FFFFu
+#define PROW_HIGH_BIT 19
+#define PROW_MAX_Q (1u << 19)
+#define PROW_MAX_RANK (1u << 24)
+struct PRow { unsigned int w[PROW_WORDS]; };
+__host__ __device__ __forceinline__ unsigned int prow_npat(const unsigned int w0) { return w0 >> 20; }
+__host__ __device__ __forceinline__ unsigned int prow_rank(const unsigned int w1, const unsigned int w2) { return (w1 >> 20) | ((w2 >> 20) << 12); }
+__host__ __device__ __forceinline__ unsigned int prow_entry(const PRow& r, const unsigned int j) {
+    return (j == 0 ? r.w[0] : j == 1 ? r.w[1] : j == 2 ? r.w[2] : j == 3 ? r.w[3] : r.w[4]) & PROW_ENTRY_MASK;
+}
+__host__ __forceinline__ PRow prow_pack(const unsigned int e[5], const unsigned int npat, const unsigned int rank) {
+    PRow r;
+    r.w[0] = e[0] | (npat << 20);
+    r.w[1] = e[1] | ((rank & 0xFFFu) << 20);
+    r.w[2] = e[2] | ((rank >> 12) << 20);
+    r.w[3] = e[3];
+    r.w[4] = e[4];
+    return r;
+}
+__device__ __forceinline__ PRow prow_load(const unsigned int* __restrict__ rows, const unsigned int p) {
+    PRow r; const unsigned int* q = rows + (size_t) p * PROW_WORDS;
+#pragma unroll
+    for (int k = 0; k < PROW_WORDS; ++k) r.w[k] = q[k];
+    return r;
+}
+
+// Programmatic dependent launch (sm_90+): every kernel of the day pipeline lets its successor start launching at once and
+// waits for its predecessor's memory before it touches anything the predecessor wrote, so launch latency and prologues
+// overlap the predecessor's tail. Both are no-ops when the kernel was launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10, counter = (sub<<16 | block, a, b, day<<8 | purpose), key = seed

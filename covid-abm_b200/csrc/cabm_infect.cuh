@@ -187,7 +187,16 @@ __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const Infe
     if (t_death != CABM_I16_MAX) until = max(until, t_death);
     if (report_day != CABM_I16_MAX) until = max(until, report_day);
     until = min(until, CABM_I16_MAX - 1);
-    D.win[pid] = ((unsigned int) (unsigned short) (short) time) | ((unsigned int) (unsigned short) (short) until << 16);
+    {   // persistent active list (Counters): the agent joins the list the next k_active reads unless its previous window already put it there
+        const int old_until = (short) (D.win[pid] >> 16);
+        D.win[pid] = ((unsigned int) (unsigned short) (short) time) | ((unsigned int) (unsigned short) (short) until << 16);
+        Counters* ctr = D.ctr;
+        if (old_until < ctr->list_day) {
+            const unsigned int tgt = ctr->act_sel ^ ctr->in_tick;
+            const unsigned int ai = atomicAdd(&ctr->n_act[tgt], 1u);
+            if (ai < D.cap_active) D.act[tgt][ai] = (unsigned int) pid; else atomicOr(&ctr->overflow, 4u);
+        }
+    }
     const unsigned int cnt = (imm >> (8 * strain)) & 0xFF;
     if (cnt < 255) D.imm[pid] = imm + (1u << (8 * strain));
     if (par->retroactive_mature_vaccine && n_doses > 0) D.vax[pid] = vax & ~0x100u;

@@ -1,23 +1,27 @@
 // covid-abm_b200/csrc/cabm_kernels.cuh -- first half of the day pipeline (sm_100a): who is infectious where,
 // public activity, per-location hazard, exposure trials.
 //
-//   k_scan     all agents      : streams the 4-byte active-window word (16 agents per thread), block-aggregated
-//                                compaction of today's active agents (replaces walking every Person, Community.cpp:684)
-//   k_active   active agents   : Person.cpp:475-486 derived from the stored timeline instead of the reference's
-//                                _isHot calendar: pressure at home / day location / hospital / visited locations
+//   k_active   active agents   : walks the PERSISTENT list of agents inside an infection window (no daily scan over all
+//                                agents: an agent joins the list when an infection is committed, k_active drops it when the
+//                                window has passed). Person.cpp:475-486 derived from the stored timeline instead of the
+//                                reference's _isHot calendar: pressure at home / day location / hospital / visited locations
 //                                (Community.cpp:1031-1035), per-location flag chains, hot lists, in-hospital bit
-//   k_visit    all agents      : public_activity (Community.cpp:1006-1039): Poisson(1) visits from one Philox block
-//                                (branch-free body), hot test against a shared-memory bitmap of patronised locations,
-//                                visitor census, visit records staged per warp; k >= 4 draws on full warps at the end
+//   k_visit    all agents      : public_activity (Community.cpp:1006-1039): the 16-byte patron rows of a warp's tile arrive in
+//                                shared memory by bulk copy (TMA, double-buffered per warp), Poisson(1) visits from one Philox
+//                                block (branch-free body), hot test against a shared-memory bitmap of patronised locations,
+//                                visitor census, visit records staged per lane; k >= 4 draws on full warps at the end
 //   k_hazard   hot locations   : _tally_infectiousness + the hazard of every pass (Community.cpp:833-969); one thread
 //                                per location turns pressure into T and emits work items: small rosters and
 //                                neighbour households (resolved by k_trials), 256-member chunks of big rosters
 //   k_trials   items + visits  : _transmission's `U < T` (Community.cpp:976) for rosters and visitors; also scatters
-//                                the day's flag records into one contiguous segment per hot location
+//                                the day's flag records into one contiguous segment per hot location. Successful trials
+//                                are queued per block and pass the susceptibility gate at the end of the block
+//                                (gate_hit, cabm_kernels2.cuh), so the streaming loop stays convergent and no separate
+//                                gate launch is needed
 //
-// A trial that succeeds is appended to the hit list; the (rare, heavy) susceptibility gate and the state
-// transition run in k_gate / k_apply (cabm_kernels2.cuh) so the streaming kernels stay convergent.
-// All kernels read their sizes from device-resident counters, so a whole day is one CUDA-graph replay.
+// All kernels read their sizes from device-resident counters, so a whole day is one CUDA-graph replay; every kernel
+// releases its successor at once (programmatic dependent launch) and waits for its predecessor before the first dependent
+// access.
 #pragma once
 #include <cooperative_groups.h>
 #include "cabm_infect.cuh"
@@ -28,8 +32,6 @@ namespace cg = cooperative_groups;
 #define CHUNK 256
 #define SMALL_ROSTER 64
 #define MAXV 8
-#define PATRON_ROW 8          // ints per agent: 5 patronised public-location indices, household riskiness (float bits), 2 pad
-#define PATRON_RISK 5
 
 __device__ __forceinline__ const DayCtx& day_ctx(const Dev& D) { return *D.today; }
 
@@ -87,56 +89,6 @@ __device__ __forceinline__ void block_work_add(const Dev& D, const int* ids, con
     if (threadIdx.x < NC && s_acc[threadIdx.x]) atomicAdd(&D.ctr->work[ids[threadIdx.x]], (unsigned long long) s_acc[threadIdx.x]);
 }
 
-// ---------------------------------------------------------------------------------------------
-// k_scan: active-window scan. Also publishes today's DayCtx for the rest of the pipeline.
-// ---------------------------------------------------------------------------------------------
-#define SCAN_V 4               // uint4 loads per thread in k_scan: a block covers TPB * 4 * SCAN_V agents
-__device__ __forceinline__ void k_scan_body(const Dev& D) {
-    __shared__ unsigned int s_warp[TPB / 32], s_base;
-    const DayCtx& cx = D.dayctx[D.ctr->day_idx];
-    const int day = cx.day;
-    if (blockIdx.x == 0 && threadIdx.x == 0) { *D.today = cx; atomicAdd(&D.ctr->work[CABM_W_AGENTS], (unsigned long long) (D.own_hi - D.own_lo)); }
-    const unsigned int b0 = (D.own_lo & ~3u) + blockIdx.x * (TPB * 4u * SCAN_V);            // agents of other handles are never active here
-    uint4 w[SCAN_V];
-#pragma unroll
-    for (int j = 0; j < SCAN_V; ++j) {                                                       // all loads in flight before the first use
-        const unsigned int p0 = b0 + (j * TPB + threadIdx.x) * 4u;
-        w[j] = make_uint4(0x80007FFFu, 0x80007FFFu, 0x80007FFFu, 0x80007FFFu);
-        if (p0 + 3 < D.N) w[j] = *reinterpret_cast<const uint4*>(D.win + p0);
-        else { if (p0 < D.N) w[j].x = D.win[p0]; if (p0 + 1 < D.N) w[j].y = D.win[p0 + 1]; if (p0 + 2 < D.N) w[j].z = D.win[p0 + 2]; }
-    }
-    unsigned int mask = 0;
-#pragma unroll
-    for (int j = 0; j < SCAN_V; ++j) {
-        const unsigned int ww[4] = { w[j].x, w[j].y, w[j].z, w[j].w };
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { const int from = (short) (ww[k] & 0xFFFF), until = (short) (ww[k] >> 16); if (day >= from && day <= until) mask |= 1u << (j * 4 + k); }
-    }
-    const unsigned int cnt = __popc(mask), lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (__syncthreads_or((int) mask) == 0) return;                                           // most blocks outside an epidemic wave: nothing to append
-    unsigned int incl = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-    if (lane == 31) s_warp[wid] = incl;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned int acc = 0;
-#pragma unroll
-        for (int k = 0; k < TPB / 32; ++k) { const unsigned int c = s_warp[k]; s_warp[k] = acc; acc += c; }
-        s_base = atomicAdd(&D.ctr->n_active, acc);
-        atomicAdd(&D.ctr->work[CABM_W_ACTIVE], (unsigned long long) acc);
-    }
-    __syncthreads();
-    unsigned int o = s_base + s_warp[wid] + incl - cnt;
-    while (mask) {
-        const unsigned int bit = (unsigned int) __ffs(mask) - 1u; mask &= mask - 1u;
-        if (o < D.cap_active) D.active_list[o] = b0 + ((bit >> 2) * TPB + threadIdx.x) * 4u + (bit & 3u); else atomicOr(&D.ctr->overflow, 4u);
-        ++o;
-    }
-}
-__global__ void __launch_bounds__(TPB) k_scan(const Dev D) { k_scan_body(D); }
-__global__ void __launch_bounds__(TPB) k_scan_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_scan_body(D); }   // one launch, replicate = blockIdx.y
-
 // Community::flagInfectedLocation (Community.cpp:788-791) on device, second half: the flag record, and for the first
 // flag of a location the hot-list entry. `slot` is what atomicAdd(&loc_cnt[loc], 1) returned, f the record index.
 __device__ __forceinline__ void flag_location(const Dev& D, int loc, int strain, unsigned long long c, unsigned int pid, unsigned int slot, unsigned int f) {
@@ -155,9 +107,8 @@ __device__ __forceinline__ void flag_location(const Dev& D, int loc, int strain,
 
 // Community::public_activity draws for one agent (Community.cpp:1012-1026): k ~ Poisson(1) from the first word of
 // the agent's Philox block, then k uniform picks among its patronised locations. Returns the number of distinct
-// locations; qs[] holds public-location indices, hours[] the multiplicities.
-// The agent's 32-byte patron row arrives in (ra, rb): the caller loads it together with the rest of the agent's state.
-__device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsigned int pid, int npat, const uint4 ra, const uint4 rb, int* qs, int* hours) {
+// locations; qs[] holds public-location indices, hours[] the multiplicities. `row` is the agent's packed patron row.
+__device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsigned int pid, int npat, const PRow& row, int* qs, int* hours) {
     uint4 b = philox4x32_10(make_uint4(0u, pid, 0u, ((unsigned int) cx.day << 8) | CABM_P_VISIT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
     int k;
     if (b.x < D.visit_thr[0]) return 0;
@@ -166,16 +117,15 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
     else if (b.x < D.visit_thr[3]) k = 3;
     else k = (int) table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
     int nv = 0;
-    const bool avoiding = (double) __uint_as_float(rb.y) < cx.sd;      // row[PATRON_RISK]
+    const bool avoiding = prow_rank(row.w[1], row.w[2]) < cx.sd_rank;
     for (int i = 0; i < k; ++i) {
         const unsigned int idx1 = (unsigned int) i + 1u;              // draw index within the stream (0 was the Poisson draw)
         if ((idx1 & 3u) == 0) b = philox4x32_10(make_uint4(idx1 >> 2, pid, 0u, ((unsigned int) cx.day << 8) | CABM_P_VISIT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
         const unsigned int lane = idx1 & 3u;
         const unsigned int x = lane == 0 ? b.x : lane == 1 ? b.y : lane == 2 ? b.z : b.w;
-        const unsigned int j = __umulhi(x, (unsigned int) npat);
-        const int e = (int) (j == 0 ? ra.x : j == 1 ? ra.y : j == 2 ? ra.z : j == 3 ? ra.w : rb.x);
-        if ((e & PATRON_HIGH) && avoiding) continue;
-        const int q = e & 0x3FFFFFFF;
+        const unsigned int e = prow_entry(row, __umulhi(x, (unsigned int) npat));
+        if (((e >> PROW_HIGH_BIT) & 1u) && avoiding) continue;
+        const int q = (int) (e & PROW_Q_MASK);
         int t = 0; while (t < nv && qs[t] != q) ++t;
         if (t == nv) { qs[nv] = q; hours[nv] = 1; ++nv; } else hours[t]++;
     }
@@ -186,19 +136,38 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
 // k_active: one thread per active agent.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_active_body(const Dev& D) {
-    const DayCtx& cx = day_ctx(D); const int day = cx.day;
-    const unsigned int n = min(D.ctr->n_active, D.cap_active);
-    unsigned int nflag = 0;
+    pdl_launch_dependents();
+    pdl_wait();
+    Counters* const ctr = D.ctr;
+    const DayCtx& cx = D.dayctx[ctr->day_idx]; const int day = cx.day;
+    const unsigned int sel = ctr->act_sel;
+    const unsigned int n = min(ctr->n_act[sel], D.cap_active);
+    const unsigned int* __restrict__ cur = D.act[sel]; unsigned int* __restrict__ nxt = D.act[sel ^ 1];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {           // publish the day for the rest of the pipeline; infections committed from here on join the next list
+        *D.today = cx; ctr->in_tick = 1u; ctr->list_day = day + 1;
+        atomicAdd(&ctr->work[CABM_W_AGENTS], (unsigned long long) (D.own_hi - D.own_lo));
+    }
+    unsigned int nflag = 0, ntoday = 0;
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const unsigned int p = D.active_list[i];
+        const unsigned int p = cur[i];
+        const unsigned int w = D.win[p];
+        const int from = (short) (w & 0xFFFFu), until = (short) (w >> 16);
+        if (until > day) {                                 // still inside its window tomorrow: stays on the list
+            const unsigned int o = list_reserve(&ctr->n_act[sel ^ 1]);
+            if (o < D.cap_active) nxt[o] = p; else atomicOr(&ctr->overflow, 4u);
+        }
+        if (day < from || day > until) continue;
+        ntoday++;
         const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
         const unsigned char pb = D.pbyte[p];
         const int hm = D.home[p], dl = D.day_loc[p];
-        const uint4* __restrict__ row4 = reinterpret_cast<const uint4*>(D.patron + (size_t) p * PATRON_ROW);
-        const uint4 ra = row4[0], rb = row4[1];                                    // the patron row, in flight with the rest of the agent's state
+        const PRow row = prow_load(D.prow, p);                                     // the patron row, in flight with the rest of the agent's state
         const bool inhosp = tl_in(t0.hosp_begin, t0.severe_end, day);
         const unsigned char npb = (unsigned char) ((pb & ~PB_INHOSP) | (inhosp ? PB_INHOSP : 0));
-        if (npb != pb) D.pbyte[p] = npb;
+        if (npb != pb) {                                                           // admissions and discharges: the status byte and the bit k_visit reads
+            D.pbyte[p] = npb;
+            if (inhosp) atomicOr(&D.inhosp[p >> 5], 1u << (p & 31)); else atomicAnd(&D.inhosp[p >> 5], ~(1u << (p & 31)));
+        }
         if (!tl_in(t0.infectious_begin, t0.infectious_end, day)) continue;
         // where this agent is infectious today (Person.cpp:475-486, Community.cpp:1031-1035): up to 2 + MAXV places
         int locs[2 + MAXV]; unsigned long long cs[2 + MAXV]; int nl = 0;
@@ -210,7 +179,7 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
             const int npat = pb & PB_NPAT;
             if (npat) {
                 int qs[MAXV], hours[MAXV];
-                const int nv = gen_visits(D, cx, p, npat, ra, rb, qs, hours);
+                const int nv = gen_visits(D, cx, p, npat, row, qs, hours);
                 for (int j = 0; j < nv; ++j) {
                     const unsigned long long cv = (unsigned long long) __double2ll_rn(CABM_MUL(CABM_MUL((double) t1.rel_inf, (double) hours[j]), 536870912.0));
                     if (cv) { locs[nl] = D.pub_loc[qs[j]]; cs[nl] = cv; nl++; }
@@ -250,61 +219,84 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
         }
         nflag += mine;
     }
-    nflag = warp_sum(nflag);
-    if ((threadIdx.x & 31) == 0 && nflag) atomicAdd(&D.ctr->work[CABM_W_FLAGS], (unsigned long long) nflag);
+    nflag = warp_sum(nflag); ntoday = warp_sum(ntoday);
+    if ((threadIdx.x & 31) == 0) {
+        if (nflag) atomicAdd(&ctr->work[CABM_W_FLAGS], (unsigned long long) nflag);
+        if (ntoday) { atomicAdd(&ctr->work[CABM_W_ACTIVE], (unsigned long long) ntoday); atomicAdd(&ctr->n_today, ntoday); }
+    }
 }
 __global__ void __launch_bounds__(TPB) k_active(const Dev D) { k_active_body(D); }
 __global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_active_body(D); }   // one launch, replicate = blockIdx.y
 
 // ---------------------------------------------------------------------------------------------
-// k_visit: every agent with patronised locations that is not in hospital draws its visits.
-// A warp takes tiles of 128 consecutive agents, four per lane. Per agent the only memory on the path is the status byte
-// and, when k > 0, the agent's 32-byte patron row (5 public-location indices + the household's riskiness); the Philox
-// block needs no memory. Hotness is tested against a shared-memory bitmap over the Q patronised locations (dynamic shared
-// memory, ceil(Q/32) words). Visits that land on a hot location are staged in the warp's shared-memory buffer and flushed
-// once per tile: one reservation, coalesced record stores, one census RED per record. Agents that draw k >= 4 (1.9 %) are
-// queued per warp and handled 32 at a time by the generic loop, so the common path carries no divergent tail.
+// k_visit: every agent with patronised locations that is not in hospital draws its visits (Community.cpp:1006-1039).
+//
+// A warp takes tiles of 128 consecutive agents, four per lane (lane l of slot a handles agent tile + 32 a + l). The only
+// per-agent memory on the path is the agent's 20-byte patron row: the rows of a tile are one contiguous 2.5 KB block that an
+// elected lane fetches into the warp's shared-memory buffer with one bulk copy (cp.async.bulk, completion on an mbarrier),
+// one tile ahead of the tile being processed, so the warp never waits for HBM and spends no instructions on addresses. The
+// in-hospital flags of a tile are four words of a bitmap (one 16-byte load per lane, same address). The Philox block needs
+// no memory. Hotness is tested against a shared-memory bitmap over the Q patronised locations (dynamic shared memory,
+// fetched with one bulk copy per block). A visit that lands on a hot location is stored in the lane's own column of the
+// warp's staging buffer (no atomics, no shuffles in the body); the warp flushes when a column could overflow: one scan, one
+// reservation, one census RED per record. Agents that draw k >= 4 (1.9 %) are queued per block and handled on full warps
+// by the generic loop at the end, so the common path carries no divergent tail.
 // There is no block-level synchronisation in the loop.
 // ---------------------------------------------------------------------------------------------
-#ifndef VIS_A
-#define VIS_A 4               // agents per lane and tile: a warp takes tiles of 32 * VIS_A consecutive agents
-#endif
-#ifndef VIS_MINB
-#define VIS_MINB 4            // resident blocks per SM the register allocation aims at
-#endif
+#define VIS_A 4               // agents per lane and tile
 #define VIS_TILE (32 * VIS_A)
-#define VIS_STAGE (4 * VIS_TILE < 512 ? 512 : 4 * VIS_TILE)   // records a warp can stage: a tile adds at most 3 * VIS_TILE, the final k >= 4 pass at most 320
-#define VIS_FLUSH_AT (VIS_STAGE - 3 * VIS_TILE < 128 ? VIS_STAGE - 3 * VIS_TILE : 128)   // flush once more than this is staged after a tile
+#define VIS_COL 16            // records a lane can stage (a tile adds at most 3 * VIS_A = 12)
+#define VIS_FLUSH_AT (VIS_COL - 3 * VIS_A)   // flush after a tile once some lane holds more than this
 #define VIS_SLOWQ (4 * TPB)   // k >= 4 agents a block queues for its final full-warp pass (beyond that: handled in place)
+#define VIS_WARPS (TPB / 32)
+#define VIS_TILE_BYTES (VIS_TILE * PROW_WORDS * 4u)
 
-// a 32-bit load that is issued only when `on` is set (0 otherwise): keeps k_visit's body free of branches
-__device__ __forceinline__ unsigned int ldg_if(const int* ptr, unsigned int on) {
-    unsigned int v = 0;
-    asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p ld.global.nc.u32 %0, [%1];\n\t}" : "+r"(v) : "l"(ptr), "r"(on));
-    return v;
+struct __align__(16) VisitSmem {
+    unsigned int rows[VIS_WARPS][2][VIS_TILE * PROW_WORDS];  // patron rows of the current and the next tile of every warp (bulk-copy destinations)
+    uint2 stage[VIS_WARPS][VIS_COL][32];                    // hot visits (agent, public index): [slot][lane]
+    unsigned long long thr[CABM_T_POISSON];                 // ceil(visit_cdf[k] * 2^32)
+    unsigned long long bar_rows[VIS_WARPS][2];              // mbarriers of the row buffers
+    unsigned long long bar_hot;                             // mbarrier of the hot-bitmap copy
+    unsigned int slowq[VIS_SLOWQ];                          // agent | patron count << 29
+    unsigned int nslow, pad[3];
+    unsigned int hot[4];                                    // hot bitmap over the patronised locations, bitmap_words rounded up to 4 (dynamic)
+};
+static inline size_t visit_smem_bytes(unsigned int bitmap_words) { return sizeof(VisitSmem) - 16 + (size_t) ((bitmap_words + 3u) & ~3u) * 4u; }
+
+__device__ __forceinline__ unsigned int smem_u32(const void* p) { return (unsigned int) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned int bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned int parity) {
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}"
+                 :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (TMA, 1-D): bytes is a multiple of 16, both addresses 16-byte aligned; completes on `bar`
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned int bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
 // the generic public_activity loop for one agent that drew k >= 4 (Community.cpp:1012-1026), one lane per agent.
-// s_thr[j] = ceil(visit_cdf[j] * 2^32): u01 >= cdf  <=>  x >= s_thr (64-bit compare, exact). The whole patron row comes with two
-// 16-byte loads, so the agent's dependent chain is one memory round trip. STAGED: hot visits go to the warp's staging buffer
-// (flushed by the caller); otherwise straight to the global record list.
-template <bool STAGED>
+// thr[j] = ceil(visit_cdf[j] * 2^32): u01 >= cdf  <=>  x >= thr (64-bit compare, exact). A hot visit goes straight to the
+// global record list (these agents are 1.9 % of the drawing ones and run on full warps at the end of the block).
 __device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_hot, const unsigned long long* s_thr, const unsigned int p, const unsigned int npat,
-                                           const unsigned int dp, const uint2 key, const float sd_up, uint2* stage, unsigned int* n_stage, unsigned int& w_v0, unsigned int& w_v) {
-    const uint4* __restrict__ row4 = reinterpret_cast<const uint4*>(D.patron + (size_t) p * PATRON_ROW);
-    const uint4 ra = row4[0], rb = row4[1];
+                                           const unsigned int dp, const uint2 key, const unsigned int sd_rank, unsigned int& w_v0, unsigned int& w_v) {
+    const PRow row = prow_load(D.prow, p);
     uint4 bb = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
     unsigned int kk = 0;
     while (kk < CABM_T_POISSON - 1 && (unsigned long long) bb.x >= s_thr[kk]) ++kk;          // table_draw on shared-memory thresholds
-    const bool avoiding = __uint_as_float(rb.y) < sd_up;                                  // row[PATRON_RISK]
+    const bool avoiding = prow_rank(row.w[1], row.w[2]) < sd_rank;
     unsigned int qs[5]; unsigned int nv = 0;
     for (unsigned int i = 1; i <= kk; ++i) {
         if ((i & 3u) == 0) bb = philox4x32_10(make_uint4(i >> 2, p, 0u, dp), key);
         const unsigned int x = (i & 3u) == 0 ? bb.x : (i & 3u) == 1 ? bb.y : (i & 3u) == 2 ? bb.z : bb.w;
-        const unsigned int j = __umulhi(x, npat);
-        const unsigned int e = j == 0 ? ra.x : j == 1 ? ra.y : j == 2 ? ra.z : j == 3 ? ra.w : rb.x;
-        if (avoiding && (e & PATRON_HIGH)) continue;
-        const unsigned int q = e & 0x3FFFFFFFu;
+        const unsigned int e = prow_entry(row, __umulhi(x, npat));
+        if (avoiding && ((e >> PROW_HIGH_BIT) & 1u)) continue;
+        const unsigned int q = e & PROW_Q_MASK;
         bool seen = false;
 #pragma unroll
         for (int t = 0; t < 5; ++t) if (t < (int) nv && qs[t] == q) seen = true;
@@ -313,149 +305,143 @@ __device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_h
         for (int t = 0; t < 5; ++t) if (t == (int) nv) qs[t] = q;
         nv++; w_v0++;
         if (s_hot[q >> 5] & (1u << (q & 31))) {
-            if (STAGED) stage[atomicAdd(n_stage, 1u)] = make_uint2(p, q);
-            else {
-                atomicAdd(&D.nvis[q], 1u);
-                const unsigned int vi = list_reserve(&D.ctr->n_vis);
-                if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
-                w_v++;
-            }
+            atomicAdd(&D.nvis[q], 1u);
+            const unsigned int vi = list_reserve(&D.ctr->n_vis);
+            if (vi < D.cap_vis) D.visit_rec[vi] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
+            w_v++;
         }
     }
 }
 
-// Community::public_activity draws of one agent in 0/1 arithmetic (no branch, predicated loads): k ~ Poisson(1) and the
-// first three picks come from one Philox block (Community.cpp:1013-1017). v0..v2 = pick j is a visit (k > j, not avoided,
-// not a repeat of an earlier pick), q0..q2 = its public-location index, c3 = the agent drew k >= 4 (generic loop instead).
-__device__ __forceinline__ void visit_draw(const Dev& D, const unsigned int p, const unsigned int npat, const unsigned int act, const unsigned int dp, const uint2 key,
-                                           const float sd_up, const unsigned int thr0, const unsigned int thr1, const unsigned int thr2, const unsigned int thr3,
-                                           unsigned int& q0, unsigned int& q1, unsigned int& q2, unsigned int& v0, unsigned int& v1, unsigned int& v2, unsigned int& c3) {
-    const uint4 b = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
-    c3 = act & (unsigned int) (b.x >= thr3);
-    const unsigned int live = act ^ c3;
-    v0 = live & (unsigned int) (b.x >= thr0); v1 = live & (unsigned int) (b.x >= thr1); v2 = live & (unsigned int) (b.x >= thr2);
-    const int* __restrict__ row = D.patron + (size_t) p * PATRON_ROW;
-    const unsigned int e0 = ldg_if(row + __umulhi(b.y, npat), v0), e1 = ldg_if(row + __umulhi(b.z, npat), v1), e2 = ldg_if(row + __umulhi(b.w, npat), v2);
-    const unsigned int avoiding = (unsigned int) (__uint_as_float(ldg_if(row + PATRON_RISK, v0)) < sd_up);   // Community.cpp:1020: compliant households skip high-risk places
-    v0 &= (avoiding & (e0 >> 30)) ^ 1u; v1 &= (avoiding & (e1 >> 30)) ^ 1u; v2 &= (avoiding & (e2 >> 30)) ^ 1u;      // bit 30 = PATRON_HIGH
-    q0 = e0 & 0x3FFFFFFFu; q1 = e1 & 0x3FFFFFFFu; q2 = e2 & 0x3FFFFFFFu;
-    v2 &= ((v0 & (unsigned int) (q2 == q0)) | (v1 & (unsigned int) (q2 == q1))) ^ 1u;   // visit_map (Community.cpp:1014): one entry per distinct place
-    v1 &= (v0 & (unsigned int) (q1 == q0)) ^ 1u;
-}
-
-// flush a warp's staged records: one reservation, coalesced record stores, one census RED per record
-__device__ __forceinline__ void visit_flush(const Dev& D, const uint2* stage, unsigned int* n_stage, const unsigned int total, const unsigned int lane, unsigned int& w_v) {
+// flush a warp's staged records (cnt per lane, column layout): one scan, one reservation, then every lane stores its own
+// run of the record list and adds its visits to the census
+__device__ __forceinline__ void visit_flush(const Dev& D, const uint2 (*stage)[32], unsigned int& cnt, const unsigned int lane, unsigned int& w_v) {
+    unsigned int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
+    const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
     unsigned int base = 0;
-    if (lane == 0) base = atomicAdd(&D.ctr->n_vis, total);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    for (unsigned int i = lane; i < total; i += 32) {
-        const uint2 r = stage[i];
+    if (lane == 31) base = atomicAdd(&D.ctr->n_vis, total);
+    base = __shfl_sync(0xffffffffu, base, 31) + incl - cnt;
+    for (unsigned int k = 0; k < cnt; ++k) {
+        const uint2 r = stage[k][lane];
         atomicAdd(&D.nvis[r.y], 1u);
-        if (base + i < D.cap_vis) D.visit_rec[base + i] = r; else atomicOr(&D.ctr->overflow, 8u);
+        if (base + k < D.cap_vis) D.visit_rec[base + k] = r; else atomicOr(&D.ctr->overflow, 8u);
     }
-    __syncwarp();
-    if (lane == 0) { *n_stage = 0; w_v += total; }
-    __syncwarp();
+    w_v += cnt; cnt = 0;
 }
 
 __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bitmap_words) {
-    extern __shared__ unsigned int s_hot[];
-    __shared__ uint2 s_stage[TPB / 32][VIS_STAGE];
-    __shared__ unsigned int s_slowq[VIS_SLOWQ];                               // agent | patron count << 29
-    __shared__ unsigned long long s_thr[CABM_T_POISSON];
-    __shared__ unsigned int s_nslow, s_nstage[TPB / 32];
-    const DayCtx& cx = day_ctx(D);
-    const unsigned int stride = gridDim.x * blockDim.x * VIS_A;
-    const unsigned int t_base = D.own_lo & ~(VIS_TILE - 1u);                        // tiles cover the owned agents only
-    const unsigned int n_round = t_base + (D.own_hi - t_base + stride - 1) / stride * stride;
+    extern __shared__ __align__(16) unsigned char vis_smem_raw[];
+    VisitSmem& S = *reinterpret_cast<VisitSmem*>(vis_smem_raw);
+    pdl_launch_dependents();
     const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const unsigned int own_lo = D.own_lo, own_n = D.own_hi - D.own_lo, N = D.N;
-    // in slot a lane l handles agent tile + 32 a + l, so the 32-byte patron rows a load instruction touches are
-    // consecutive (8 cache lines per request instead of 32)
-    const unsigned int t_first = t_base + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * VIS_TILE;
-    // the first tile's status bytes and the day's scalars are requested before the block stages the hot bitmap: one memory
-    // round trip for the whole prologue instead of three
-    unsigned int pb_next = 0;
-#pragma unroll
-    for (int a = 0; a < VIS_A; ++a) { const unsigned int p = t_first + a * 32 + lane; if (p < N) pb_next |= (unsigned int) D.pbyte[p] << (8 * a); }
-    const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
-    const float sd_up = cx.sd_up;                                                   // (double) risk < sd  <=>  risk < sd_up (fill_ctx)
-    for (unsigned int i = threadIdx.x; i < bitmap_words; i += blockDim.x) s_hot[i] = D.pub_hot[i];
-    if (threadIdx.x < TPB / 32) s_nstage[threadIdx.x] = 0;
-    if (threadIdx.x == 0) s_nslow = 0;
-    if (threadIdx.x < CABM_T_POISSON) s_thr[threadIdx.x] = __double2ull_ru(D.par->visit_cdf[threadIdx.x] * 4294967296.0);
+    const unsigned int own_lo = D.own_lo, own_hi = D.own_hi, own_n = own_hi - own_lo;
+    const unsigned int t_base = own_lo & ~(VIS_TILE - 1u);                          // tiles cover the owned agents only
+    const unsigned int g_warp = blockIdx.x * VIS_WARPS + wid, tile_stride = gridDim.x * VIS_WARPS * VIS_TILE;
+    unsigned int t0 = t_base + g_warp * VIS_TILE;
+    // ---- prologue, before the dependency on k_active: barriers, thresholds, the first tile's rows (static data) ----
+    if (lane == 0) { mbar_init(&S.bar_rows[wid][0], 1); mbar_init(&S.bar_rows[wid][1], 1); }
+    if (threadIdx.x == 0) { mbar_init(&S.bar_hot, 1); S.nslow = 0; }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    if (threadIdx.x < CABM_T_POISSON) S.thr[threadIdx.x] = __double2ull_ru(D.par->visit_cdf[threadIdx.x] * 4294967296.0);
     __syncthreads();
+    if (lane == 0 && t0 < own_hi) { mbar_expect_tx(&S.bar_rows[wid][0], VIS_TILE_BYTES); bulk_g2s(&S.rows[wid][0][0], D.prow + (size_t) t0 * PROW_WORDS, VIS_TILE_BYTES, &S.bar_rows[wid][0]); }
     const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
     const unsigned int thr0 = D.visit_thr[0], thr1 = D.visit_thr[1], thr2 = D.visit_thr[2], thr3 = D.visit_thr[3];
-    uint2* const stage = s_stage[wid];
-    unsigned int w_pat = 0, w_v0 = 0, w_v = 0;
-    for (unsigned int t0 = t_first; t0 < n_round; t0 += stride) {
-        // the status bytes were loaded one tile ahead (an L2 prefetch of the next tile's patron rows was measured: no gain)
-        const unsigned int pb4 = pb_next;
-        pb_next = 0;
-        if (t0 + stride < n_round) {
-#pragma unroll
-            for (int a = 0; a < VIS_A; ++a) { const unsigned int p = t0 + stride + a * 32 + lane; if (p < N) pb_next |= (unsigned int) D.pbyte[p] << (8 * a); }
+    // ---- everything below reads what k_active wrote today ----
+    pdl_wait();
+    const unsigned int hot_bytes = ((bitmap_words + 3u) & ~3u) * 4u;
+    if (threadIdx.x == 0) { mbar_expect_tx(&S.bar_hot, hot_bytes); bulk_g2s(&S.hot[0], D.pub_hot, hot_bytes, &S.bar_hot); }
+    const DayCtx& cx = day_ctx(D);
+    const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
+    const unsigned int sd_rank = cx.sd_rank;
+    const uint4* __restrict__ hosp4 = reinterpret_cast<const uint4*>(D.inhosp);
+    uint4 hw_next = make_uint4(0u, 0u, 0u, 0u);
+    if (t0 < own_hi) hw_next = hosp4[t0 / VIS_TILE];
+    mbar_wait(&S.bar_hot, 0);
+    const unsigned int* __restrict__ s_hot = S.hot;
+    uint2 (*const stage)[32] = S.stage[wid];
+    unsigned int cnt = 0, w_pat = 0, w_v0 = 0, w_v = 0, phase = 0;                 // phase: bit b = parity to wait for on row buffer b
+    for (unsigned int it = 0; t0 < own_hi; ++it, t0 += tile_stride) {
+        const unsigned int b = it & 1u;
+        const uint4 hw = hw_next;
+        const unsigned int t1 = t0 + tile_stride;
+        if (t1 < own_hi) {                                                          // next tile: rows by bulk copy, in-hospital words by load
+            if (lane == 0) { mbar_expect_tx(&S.bar_rows[wid][b ^ 1u], VIS_TILE_BYTES); bulk_g2s(&S.rows[wid][b ^ 1u][0], D.prow + (size_t) t1 * PROW_WORDS, VIS_TILE_BYTES, &S.bar_rows[wid][b ^ 1u]); }
+            hw_next = hosp4[t1 / VIS_TILE];
         }
-        unsigned int recq[3 * VIS_A]; unsigned int recmask = 0, slow = 0;          // hot visits of this lane's agents (k <= 3)
+        mbar_wait(&S.bar_rows[wid][b], (phase >> b) & 1u);
+        phase ^= 1u << b;
+        const unsigned int* __restrict__ rows = S.rows[wid][b];
+        unsigned int slow = 0;
 #pragma unroll
         for (int a = 0; a < VIS_A; ++a) {
-            const unsigned int pb = (pb4 >> (8 * a)) & 0xFFu, p = t0 + a * 32 + lane;
-            const unsigned int npat = pb & PB_NPAT;
-            const unsigned int act = (unsigned int) (npat != 0) & (unsigned int) ((pb & PB_INHOSP) == 0) & (unsigned int) ((p - own_lo) < own_n);   // another handle draws for agents it owns
-            unsigned int q0, q1, q2, v0, v1, v2, c3;
-            visit_draw(D, p, npat, act, dp, key, sd_up, thr0, thr1, thr2, thr3, q0, q1, q2, v0, v1, v2, c3);
+            const unsigned int* __restrict__ rw = rows + (a * 32 + lane) * PROW_WORDS;    // this agent's row: 5 words, bank = (5 lane + j) mod 32
+            const unsigned int p = t0 + a * 32 + lane;
+            const unsigned int hword = a == 0 ? hw.x : a == 1 ? hw.y : a == 2 ? hw.z : hw.w;
+            const unsigned int w0 = rw[0], w1 = rw[1], w2 = rw[2];
+            const unsigned int npat = prow_npat(w0);
+            // drawing today: has patronised places, is not in hospital (Community.cpp:1009), and this handle owns the agent
+            const unsigned int act = (unsigned int) (npat != 0) & (((hword >> lane) & 1u) ^ 1u) & (unsigned int) ((p - own_lo) < own_n);
+            // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017), in 0/1 arithmetic
+            const uint4 x = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
+            const unsigned int c3 = act & (unsigned int) (x.x >= thr3);                // k >= 4: the generic loop at the end of the block
+            const unsigned int live = act ^ c3;
+            unsigned int v0 = live & (unsigned int) (x.x >= thr0), v1 = live & (unsigned int) (x.x >= thr1), v2 = live & (unsigned int) (x.x >= thr2);
+            const unsigned int e0 = rw[__umulhi(x.y, npat)], e1 = rw[__umulhi(x.z, npat)], e2 = rw[__umulhi(x.w, npat)];   // npat == 0: word 0, ignored (act == 0)
+            const unsigned int avoiding = (unsigned int) (prow_rank(w1, w2) < sd_rank);   // Community.cpp:1020: compliant households skip high-risk places
+            v0 &= (avoiding & (e0 >> PROW_HIGH_BIT)) ^ 1u; v1 &= (avoiding & (e1 >> PROW_HIGH_BIT)) ^ 1u; v2 &= (avoiding & (e2 >> PROW_HIGH_BIT)) ^ 1u;
+            const unsigned int q0 = e0 & PROW_Q_MASK, q1 = e1 & PROW_Q_MASK, q2 = e2 & PROW_Q_MASK;
+            v2 &= ((v0 & (unsigned int) (q2 == q0)) | (v1 & (unsigned int) (q2 == q1))) ^ 1u;   // visit_map (Community.cpp:1014): one entry per distinct place
+            v1 &= (v0 & (unsigned int) (q1 == q0)) ^ 1u;
             slow |= c3 << a;
             w_pat += act;
             w_v0 += v0 + v1 + v2;
-            const unsigned int h0 = v0 & (s_hot[q0 >> 5] >> (q0 & 31)), h1 = v1 & (s_hot[q1 >> 5] >> (q1 & 31)), h2 = v2 & (s_hot[q2 >> 5] >> (q2 & 31));
-            recq[a * 3 + 0] = q0; recq[a * 3 + 1] = q1; recq[a * 3 + 2] = q2;
-            recmask |= (h0 | (h1 << 1) | (h2 << 2)) << (a * 3);
+            const unsigned int h0 = v0 & __funnelshift_r(s_hot[q0 >> 5], 0u, q0), h1 = v1 & __funnelshift_r(s_hot[q1 >> 5], 0u, q1), h2 = v2 & __funnelshift_r(s_hot[q2 >> 5], 0u, q2);
+            if (h0) stage[cnt][lane] = make_uint2(p, q0);
+            cnt += h0;
+            if (h1) stage[cnt][lane] = make_uint2(p, q1);
+            cnt += h1;
+            if (h2) stage[cnt][lane] = make_uint2(p, q2);
+            cnt += h2;
         }
-        // stage the tile's records in the warp buffer (offset from a shared-memory counter); flush when the next tile might not fit
-        const unsigned int nrec = __popc(recmask);
-        unsigned int o = 0;
-        if (nrec) o = atomicAdd(&s_nstage[wid], nrec);
-#pragma unroll
-        for (int r = 0; r < 3 * VIS_A; ++r) if (recmask & (1u << r)) { stage[o] = make_uint2(t0 + (r / 3) * 32 + lane, recq[r]); ++o; }
         // k >= 4 (1.9 % of the drawing agents): queued for the block's final pass, so the generic loop runs on full warps
         while (slow) {
             const unsigned int a = (unsigned int) __ffs(slow) - 1u; slow &= slow - 1u;
-            const unsigned int pos = atomicAdd(&s_nslow, 1u), p = t0 + a * 32 + lane, npat = (pb4 >> (8 * a)) & PB_NPAT;
-            if (pos < VIS_SLOWQ) s_slowq[pos] = p | (npat << 29); else visit_slow<false>(D, s_hot, s_thr, p, npat, dp, key, sd_up, nullptr, nullptr, w_v0, w_v);
+            const unsigned int pos = atomicAdd(&S.nslow, 1u), p = t0 + a * 32 + lane, npat = prow_npat(rows[(a * 32 + lane) * PROW_WORDS]);
+            if (pos < VIS_SLOWQ) S.slowq[pos] = p | (npat << 29); else visit_slow(D, s_hot, S.thr, p, npat, dp, key, sd_rank, w_v0, w_v);
         }
-        __syncwarp();
-        const unsigned int staged = __shfl_sync(0xffffffffu, *(volatile unsigned int*) &s_nstage[wid], 0);   // one value for the whole warp: the flush is collective
-        if (staged > VIS_FLUSH_AT) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v);
+        __syncwarp();                                                               // every lane has read its rows: the buffer may be refilled
+        if (__any_sync(0xffffffffu, cnt > VIS_FLUSH_AT)) visit_flush(D, stage, cnt, lane, w_v);
     }
-    // the block's k >= 4 agents on full warps, their hot visits staged with the warp's leftovers, then one final flush per warp
+    if (__any_sync(0xffffffffu, cnt != 0)) visit_flush(D, stage, cnt, lane, w_v);
+    // the block's k >= 4 agents on full warps
     __syncthreads();
     {
-        const unsigned int n = min(s_nslow, (unsigned int) VIS_SLOWQ);
-        for (unsigned int i0 = wid * 32; i0 < n; i0 += blockDim.x) {                  // warp-uniform trip count; a round stages at most 160 records
-            if (i0 + lane < n) { const unsigned int e = s_slowq[i0 + lane]; visit_slow<true>(D, s_hot, s_thr, e & 0x1FFFFFFFu, e >> 29, dp, key, sd_up, stage, &s_nstage[wid], w_v0, w_v); }
-            __syncwarp();
-            const unsigned int staged = __shfl_sync(0xffffffffu, *(volatile unsigned int*) &s_nstage[wid], 0);
-            if (staged > VIS_FLUSH_AT) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v);
-        }
+        const unsigned int n = min(S.nslow, (unsigned int) VIS_SLOWQ);
+        for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) { const unsigned int e = S.slowq[i]; visit_slow(D, s_hot, S.thr, e & 0x1FFFFFFFu, e >> 29, dp, key, sd_rank, w_v0, w_v); }
     }
-    __syncwarp();
-    { const unsigned int staged = __shfl_sync(0xffffffffu, *(volatile unsigned int*) &s_nstage[wid], 0); if (staged) visit_flush(D, stage, &s_nstage[wid], staged, lane, w_v); }
     const int ids[3] = { CABM_W_PATRONS, CABM_W_VISITS, CABM_W_HOT_VISITS }; const unsigned int vals[3] = { w_pat, w_v0, w_v };
     block_work_add<3>(D, ids, vals);
 }
-__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
-__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB, 2) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
+__global__ void __launch_bounds__(TPB, 2) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
 
 __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1.0, cabm_exp(-hazard)); }
 
 // the susceptibility gate of one successful trial (cabm_kernels2.cuh)
 __device__ __forceinline__ void gate_hit(const Dev& D, const int phase, const unsigned int pid, const unsigned int src, const unsigned int purpose, const unsigned int sub);
 
+// the block's queue of successful trials of the house..nursing-home passes (k_trials): gated when the block's loop is over
+#define HITQ 512
+struct HitQueue { Hit q[HITQ]; unsigned int n; };
+
 // one exposure trial: the quarantine skip and `gsl_rng_uniform(RNG) < T` of Community::_transmission (Community.cpp:975-976).
-// A success of the house..nursing-home passes is queued for the susceptibility gate (k_gate); the hospital pass gates in place.
+// A success of the house..nursing-home passes (hq != nullptr) is queued for the susceptibility gate at the end of the block
+// (gated in place when the queue is full); the hospital pass gates in place.
 __device__ __forceinline__ void trial(const Dev& D, const int day, const int phase, const unsigned int pid, const int src, const int purpose,
-                                      const unsigned int sub, const double T, unsigned int& trials) {
+                                      const unsigned int sub, const double T, unsigned int& trials, HitQueue* hq) {
     if (pid < D.own_lo || pid >= D.own_hi) return;                                 // the owner of an agent draws its exposures
     if (D.any_quarantine) {
         const unsigned int q = D.quar[pid]; const int qf = (short) (q & 0xFFFF), qu = (short) (q >> 16);
@@ -465,10 +451,11 @@ __device__ __forceinline__ void trial(const Dev& D, const int day, const int pha
     const uint4 b = philox4x32_10(make_uint4(sub << 16, pid, (unsigned int) src, ((unsigned int) day << 8) | (unsigned int) purpose),
                                   make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
     if ((double) b.x * (1.0 / 4294967296.0) < T) {
-        if (phase) { gate_hit(D, 1, pid, (unsigned int) src, (unsigned int) purpose, sub); return; }   // hospital pass: a handful of hits, gated in place
-        const unsigned int h = list_reserve(&D.ctr->n_hits[0]);
-        if (h < D.cap_hits) { Hit r; r.pid = pid; r.src = (unsigned int) src; r.purpose = (unsigned int) purpose; r.sub = sub; D.hits[h] = r; }
-        else atomicOr(&D.ctr->overflow, 256u);
+        if (hq) {
+            const unsigned int h = atomicAdd(&hq->n, 1u);
+            if (h < HITQ) { Hit r; r.pid = pid; r.src = (unsigned int) src; r.purpose = (unsigned int) purpose; r.sub = sub; hq->q[h] = r; return; }
+        }
+        gate_hit(D, phase, pid, (unsigned int) src, (unsigned int) purpose, sub);
     }
 }
 
@@ -500,6 +487,8 @@ __device__ __forceinline__ unsigned int list_reserve_n(unsigned int* counter, co
 // so the chains of all hot locations overlap; the trials themselves are spread over lanes in k_trials.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_hazard_body(const Dev& D) {
+    pdl_launch_dependents();
+    pdl_wait();
     const DayCtx& cx = day_ctx(D);
     const cabm_params* __restrict__ par = D.par;
     const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
@@ -581,6 +570,11 @@ __global__ void __launch_bounds__(TPB) k_hazard_b(const Dev* __restrict__ devs) 
 // k_trials: block-sized units: the 256-member items of big rosters, the visit records, the flag scatter, the small items.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_trials_body(const Dev& D) {
+    __shared__ HitQueue hq;
+    pdl_launch_dependents();
+    if (threadIdx.x == 0) hq.n = 0;
+    __syncthreads();
+    pdl_wait();
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n_items = min(D.ctr->n_items, D.cap_items), n_vis = min(D.ctr->n_vis, D.cap_vis);
     const unsigned int n_flags = min(D.ctr->n_flags, D.cap_flags);
@@ -603,7 +597,7 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
                 }
                 if (cnt) {
                     const double T = D.hot_T[it.t_idx];
-                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[begin + m], it.src, purpose, 0, T, trials);
+                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[begin + m], it.src, purpose, 0, T, trials, &hq);
                 }
             }
         } else if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
@@ -615,15 +609,22 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
             }
         } else if (u < n_items) {
             const Item it = D.items[u];
-            if ((int) threadIdx.x < it.count) trial(D, day, 0, (unsigned int) D.roster[it.begin + threadIdx.x], it.src, it.purpose, 0, it.T, trials);
+            if ((int) threadIdx.x < it.count) trial(D, day, 0, (unsigned int) D.roster[it.begin + threadIdx.x], it.src, it.purpose, 0, it.T, trials, &hq);
         } else {
             const unsigned int v = (u - n_items) * TPB + threadIdx.x;
             if (v < n_vis) {
                 const uint2 rec = D.visit_rec[v];
                 const double T = D.pub_T[rec.y];
-                if (T > 0.0) trial(D, day, 0, rec.x, D.pub_loc[rec.y], CABM_P_EXPOSE_WORK_VIS, 0, T, trials);
+                if (T > 0.0) trial(D, day, 0, rec.x, D.pub_loc[rec.y], CABM_P_EXPOSE_WORK_VIS, 0, T, trials, &hq);
             }
         }
+    }
+    // the susceptibility gate of the block's successful trials (calculate_event_probabilities + the Person::infect bail-out,
+    // Person.cpp:274-326): rare and divergent, so it runs here on whatever threads there are hits for, after the streaming loop
+    __syncthreads();
+    {
+        const unsigned int nh = min(hq.n, (unsigned int) HITQ);
+        for (unsigned int i = threadIdx.x; i < nh; i += blockDim.x) { const Hit h = hq.q[i]; gate_hit(D, 0, h.pid, h.src, h.purpose, h.sub); }
     }
     const int ids[1] = { CABM_W_TRIALS }; const unsigned int vals[1] = { trials };
     block_work_add<1>(D, ids, vals);

@@ -1,16 +1,19 @@
 // covid-abm_b200/csrc/cabm_kernels2.cuh -- second half of the day pipeline: susceptibility gate, winner
 // application fused with the status pass, hospital pass + importation, end of day.
 //
-//   k_gate          hits of phase 0 : calculate_event_probabilities + the Person::infect bail-out (Person.cpp:322-326)
+//   gate_hit        a successful trial : calculate_event_probabilities + the Person::infect bail-out (Person.cpp:322-326)
 //                                     against the start-of-phase state; survivors race with atomicMin on the
 //                                     agent's 64-bit order key, so the first exposure in reference order wins
-//                                     (gate_hit; the hospital pass and the importation call it in place)
+//                                     (called by k_trials at the end of each block, by the hospital pass and the
+//                                     importation in place)
 //   k_apply_status  winners + active: Person::infect for each winner (disease course, detection, ledger writes) and,
-//                                     for phase 0, Community::updatePersonStatus (Community.cpp:682-741)
+//                                     for phase 0, Community::updatePersonStatus (Community.cpp:682-741) over the day's
+//                                     active list. The phase-1 launch is the last kernel of the day: its last block
+//                                     closes the day (hospital scratch, counters, list swap, next day context)
 //   k_hosp_import   hospitals/imports: hospital_transmission (Community.cpp:931-941) after the status pass, and
-//                                     the daily importation draws of seed_epidemic (simulator.h:201-223)
-//   k_end           hot locations   : updateHotLocations + clear_public_activity (Community.cpp:999-1003,1042-1046)
-//   (k_end's last block)            : counter reset, next day
+//                                     the daily importation draws of seed_epidemic (simulator.h:201-223); beside them
+//                                     updateHotLocations + clear_public_activity (Community.cpp:999-1003,1042-1046) for
+//                                     every hot location that is not a hospital (nothing reads their scratch any more)
 #pragma once
 #include "cabm_kernels.cuh"
 
@@ -123,17 +126,6 @@ __device__ __forceinline__ void gate_hit(const Dev& D, const int phase, const un
     }
 }
 
-// phase 0 only: the hits of the house..nursing-home passes (k_trials); the hospital pass and the importation gate in place
-__device__ __forceinline__ void k_gate_body(const Dev& D, const int phase) {
-    const unsigned int hi = min(D.ctr->n_hits[0], D.cap_hits);
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
-        const Hit h = D.hits[i];
-        gate_hit(D, phase, h.pid, h.src, h.purpose, h.sub);
-    }
-}
-__global__ void __launch_bounds__(128) k_gate(const Dev D, const int phase) { k_gate_body(D, phase); }
-__global__ void __launch_bounds__(128) k_gate_b(const Dev* __restrict__ devs, const int phase) { const Dev D = devs[blockIdx.y]; k_gate_body(D, phase); }   // one launch, replicate = blockIdx.y
-
 // Community::updatePersonStatus (Community.cpp:682-741) for one agent; returns the ledger increments as a bit mask
 __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p, int day) {
     const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
@@ -172,18 +164,62 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
     return m;
 }
 
+// Closing the day: runs in the last block of the day's last kernel (k_apply_status, phase 1) once every other block has
+// finished. tick_done: a whole tick ran (updateHotLocations for the hot hospitals, which the hospital pass and the phase-1
+// winners were still reading; list swap); advance: move on to the next staged day context.
+__device__ __forceinline__ void close_day(const Dev& D, const int tick_done, const int advance) {
+    Counters* c = D.ctr;
+    const unsigned int n_hot = min(c->n_hot, D.cap_hot);
+    if (tick_done) {
+        const unsigned int nh = min(c->n_hot_hosp, D.cap_hot);
+        for (unsigned int j = threadIdx.x; j < nh; j += blockDim.x) {
+            const int loc = D.hot_list[D.hot_hosp[j]];
+            ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
+            pw[0] = make_ulonglong2(0, 0); pw[1] = make_ulonglong2(0, 0);
+            D.loc_cnt[loc] = 0;
+            const int q = D.loc_pub[loc];
+            if (q >= 0) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (tick_done) {
+            if (D.shard_rank == 0) c->work[CABM_W_HOT_LOCS] += n_hot;
+            if (D.foi_enabled) *D.n_foi = n_hot;
+            const unsigned int sel = c->act_sel;           // the list k_active read today is spent; the one it built (plus today's infections) is next
+            c->n_act[sel] = 0; c->act_sel = sel ^ 1u; c->in_tick = 0;
+        }
+        D.host_status[1] = c->n_new[1]; D.host_status[0] = c->overflow;             // over PCIe into pinned memory: the host reads them after its sync, no copy
+        __threadfence_system();
+        unsigned int* w = reinterpret_cast<unsigned int*>(c);
+#pragma unroll
+        for (int k = 0; k < CABM_DAY_SCOPED_WORDS; ++k) w[k] = 0;
+        if (advance) c->day_idx++;
+        c->end_ticket = 0;
+        __threadfence();
+    }
+}
+
 // Warp index space: the first n_wu warps take W winners of `phase` each (W = 1 unless the winners outnumber the warps, see
 // below); every lane commits its own winner, the whole warp helps with the infector search of long flag segments. Then
-// ceil(n_active/32) warps run the status pass (with_status) over the agents active at the start of the day that were not
-// re-infected in phase 0. cand[] keeps the winner keys until k_end so the status half can tell who was re-infected.
-__device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phase, const int with_status) {
+// ceil(n_list/32) warps run the status pass (phase 0) over the day's active list for the agents that were not re-infected
+// in phase 0: cand[] keeps the winner keys of phase 0 until k_hosp_import so the status half can tell who was.
+// Phase 1 (close >= 0 encodes tick_done | advance << 1) is the day's last kernel: winners reset their own candidate word,
+// and the last block to finish closes the day.
+__device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phase, const int close) {
     __shared__ unsigned int sm[CABM_N_COUNTERS];
+    __shared__ unsigned int s_last;
+    pdl_launch_dependents();
     if (threadIdx.x < CABM_N_COUNTERS) sm[threadIdx.x] = 0;
     __syncthreads();
+    pdl_wait();
+    const int with_status = phase == 0;
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
     const unsigned int n_w = min(nbase + D.ctr->n_new[phase], D.cap_new) - nbase;
-    const unsigned int n_a = with_status ? min(D.ctr->n_active, D.cap_active) : 0u;
+    const unsigned int sel = D.ctr->act_sel;
+    const unsigned int n_a = with_status ? min(D.ctr->n_act[sel], D.cap_active) : 0u;
+    const unsigned int* __restrict__ alist = D.act[sel];
     const unsigned int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
     // Winners per warp: one while the winners fit in two rounds of the grid's warps (Person::infect is a long dependent chain, a
     // winner alone in its warp finishes soonest, and a second round costs less than two divergent courses in one warp);
@@ -227,26 +263,36 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
             if (have) {
                 infect_event(D, s, c, true);
                 if (with_status) m = status_one(D, pid, day);
+                else D.cand[pid] = CABM_CAND_EMPTY;                                  // phase 1: nobody reads the key after its winner (phase 0 keys: k_hosp_import)
             }
         } else {
             const unsigned int i = (u - n_wu) * 32 + lane;
             if (i < n_a) {
-                const unsigned int p = D.active_list[i];
+                const unsigned int p = alist[i];
                 if (D.cand[p] == CABM_CAND_EMPTY) m = status_one(D, p, day);
             }
         }
         __syncwarp();
+        if (with_status) {
 #pragma unroll
-        for (int c = 0; c < CABM_N_COUNTERS; ++c) {
-            const unsigned int b = __ballot_sync(0xffffffffu, (m >> c) & 1u);
-            if (b && lane == 0) atomicAdd(&sm[c], __popc(b));
+            for (int c = 0; c < CABM_N_COUNTERS; ++c) {
+                const unsigned int b = __ballot_sync(0xffffffffu, (m >> c) & 1u);
+                if (b && lane == 0) atomicAdd(&sm[c], __popc(b));
+            }
         }
     }
     __syncthreads();
-    if (threadIdx.x < CABM_N_COUNTERS && sm[threadIdx.x]) atomicAdd(&D.ledger[(size_t) threadIdx.x * D.R + day], (unsigned long long) sm[threadIdx.x]);
+    if (with_status) {
+        if (threadIdx.x < CABM_N_COUNTERS && sm[threadIdx.x]) atomicAdd(&D.ledger[(size_t) threadIdx.x * D.R + day], (unsigned long long) sm[threadIdx.x]);
+        return;
+    }
+    // phase 1: the last block to get here closes the day (every other block is done with the day's lists and counters)
+    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&D.ctr->end_ticket, 1u) == gridDim.x - 1 ? 1u : 0u; }
+    __syncthreads();
+    if (s_last) { __threadfence(); close_day(D, close & 1, (close >> 1) & 1); }
 }
-__global__ void __launch_bounds__(128, 8) k_apply_status(const Dev D, const int phase, const int with_status) { k_apply_status_body(D, phase, with_status); }
-__global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ devs, const int phase, const int with_status) { const Dev D = devs[blockIdx.y]; k_apply_status_body(D, phase, with_status); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(128, 8) k_apply_status(const Dev D, const int phase, const int close) { k_apply_status_body(D, phase, close); }
+__global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ devs, const int phase, const int close) { const Dev D = devs[blockIdx.y]; k_apply_status_body(D, phase, close); }   // one launch, replicate = blockIdx.y
 
 // hospital_transmission (Community.cpp:931-941): census = staff + admitted patients; every consumer computes T itself
 __device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, const int hosp, unsigned int* denom_out, unsigned long long* pws) {
@@ -263,11 +309,36 @@ __device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, con
 // do_hosp: warps [0, n_hot_hosp) expose the staff of one hot hospital each, then all threads walk the admitted-patient
 // list; do_import: all threads walk today's importation draws (every draw is a "hit": the person is chosen, not exposed)
 __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_hosp, const int do_import) {
+    pdl_launch_dependents();
+    pdl_wait();
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     const unsigned int lane = threadIdx.x & 31, warp = tid >> 5, n_warps = nth >> 5;
     unsigned int trials = 0;
     if (do_hosp) {
+        // updateHotLocations + clear_public_activity (Community.cpp:999-1003,1042-1046) for today's hot locations other than
+        // hospitals: the passes that read their pressure, flags and census are over (the hospital pass reads hospitals only);
+        // and the winner keys of phase 0, which the status pass has finished reading. Independent stores issued first: they
+        // drain while the dependent chains of the hospital pass wait for memory. Hot hospitals are reset by close_day.
+        const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
+        for (unsigned int i0 = tid; i0 < n_hot; i0 += 4 * nth) {                      // four locations per thread in flight
+            int loc[4], typ[4], q[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const unsigned int i = i0 + k * nth; loc[k] = i < n_hot ? D.hot_list[i] : -1; }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { typ[k] = loc[k] >= 0 ? D.loc_type[loc[k]] : CABM_HOSPITAL; q[k] = loc[k] >= 0 ? D.loc_pub[loc[k]] : -1; }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (typ[k] == CABM_HOSPITAL) continue;
+                ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc[k] * CABM_N_STRAINS]);
+                pw[0] = make_ulonglong2(0, 0); pw[1] = make_ulonglong2(0, 0);
+                D.loc_cnt[loc[k]] = 0;
+                if (q[k] >= 0) { D.nvis[q[k]] = 0; D.pub_T[q[k]] = 0.0; D.pub_hot[q[k] >> 5] = 0; }   // the whole bitmap word: every set bit belongs to a hot location
+            }
+        }
+        const unsigned int n_new0 = min(D.ctr->n_new[0], D.cap_new);
+        for (unsigned int i = tid; i < n_new0; i += nth) D.cand[D.newinf_list[i]] = CABM_CAND_EMPTY;
+
         const unsigned int nh = min(D.ctr->n_hot_hosp, D.cap_hot);
         for (unsigned int j = warp; j < nh; j += n_warps) {
             const unsigned int i = (unsigned int) D.hot_hosp[j];                        // index of the hospital in the hot list
@@ -275,7 +346,7 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
             unsigned int denom; unsigned long long pws[4];
             const double T = hospital_T(D, cx, hosp, &denom, pws);
             const unsigned int rb = D.roster_off[hosp], size = D.roster_off[hosp + 1] - rb;
-            if (T > 0.0) for (unsigned int m = lane; m < size; m += 32) trial(D, day, 1, (unsigned int) D.roster[rb + m], hosp, CABM_P_EXPOSE_HOSP, 0, T, trials);
+            if (T > 0.0) for (unsigned int m = lane; m < size; m += 32) trial(D, day, 1, (unsigned int) D.roster[rb + m], hosp, CABM_P_EXPOSE_HOSP, 0, T, trials, nullptr);
             if (D.foi_enabled && lane == 0) write_foi(D, i, hosp, CABM_HOSPITAL, pws, denom, T, 0.0);
         }
         const unsigned int np = min(D.ctr->n_pat, D.cap_pat);
@@ -287,7 +358,7 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
             if (hosp < 0 || D.loc_cnt[hosp] == 0) continue;
             unsigned int denom; unsigned long long pws[4];
             const double T = hospital_T(D, cx, hosp, &denom, pws);
-            if (T > 0.0) for (unsigned int sub = 0; sub < c; ++sub) trial(D, day, 1, pid, hosp, CABM_P_EXPOSE_HOSP_PAT, sub, T, trials);
+            if (T > 0.0) for (unsigned int sub = 0; sub < c; ++sub) trial(D, day, 1, pid, hosp, CABM_P_EXPOSE_HOSP_PAT, sub, T, trials, nullptr);
         }
     }
     if (do_import) {
@@ -316,43 +387,6 @@ __global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain
     __threadfence_system();
     *(volatile int*) (out + 1) = echo;                                              // the host spins on this word (cabm_infect)
 }
-
-// reset what today's hot set and today's winners touched; the last block to finish then closes the day (day-scoped counters
-// back to zero, next day context): every other block has read the counters it needs before taking its ticket
-__device__ __forceinline__ void k_end_body(const Dev& D, const int tick_done, const int advance) {
-    const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-    const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
-    if (tick_done) {
-        for (unsigned int i = tid; i < n_hot; i += nth) {
-            const int loc = D.hot_list[i];
-            ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
-            pw[0] = make_ulonglong2(0, 0); pw[1] = make_ulonglong2(0, 0);
-            D.loc_cnt[loc] = 0;
-            const int q = D.loc_pub[loc];
-            if (q >= 0) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }      // the whole bitmap word: every set bit belongs to a hot location
-        }
-    }
-    const unsigned int n_new = min(D.ctr->n_new[0] + D.ctr->n_new[1], D.cap_new);
-    for (unsigned int i = tid; i < n_new; i += nth) D.cand[D.newinf_list[i]] = CABM_CAND_EMPTY;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        Counters* c = D.ctr;
-        __threadfence();
-        if (atomicAdd(&c->end_ticket, 1u) == gridDim.x - 1) {
-            if (tick_done) { if (D.shard_rank == 0) c->work[CABM_W_HOT_LOCS] += n_hot; if (D.foi_enabled) *D.n_foi = n_hot; }
-            D.host_status[1] = c->n_new[1]; D.host_status[0] = c->overflow;         // over PCIe into pinned memory: the host reads them after its sync, no copy
-            __threadfence_system();
-            unsigned int* w = reinterpret_cast<unsigned int*>(c);
-#pragma unroll
-            for (int k = 0; k < CABM_DAY_SCOPED_WORDS; ++k) w[k] = 0;
-            if (advance) c->day_idx++;
-            c->end_ticket = 0;
-            __threadfence();
-        }
-    }
-}
-__global__ void __launch_bounds__(TPB) k_end(const Dev D, const int tick_done, const int advance) { k_end_body(D, tick_done, advance); }
-__global__ void __launch_bounds__(TPB) k_end_b(const Dev* __restrict__ devs, const int tick_done, const int advance) { const Dev D = devs[blockIdx.y]; k_end_body(D, tick_done, advance); }   // one launch, replicate = blockIdx.y
 
 // Person::vaccinate (Person.cpp:611-647), leaky model
 __global__ void k_vaccinate(const Dev D, const unsigned int* pids, const unsigned int n, const int day, unsigned char* ok) {

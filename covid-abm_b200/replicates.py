@@ -71,6 +71,12 @@ def batch_run_days(comms, n_days: int):
         for c in comms:
             c.update_strain_mix(first + i)
         strain_w[i] = c0.strains; exp[i] = c0.expected_imports(first + i)
+        # cabm_batch_run_days takes ONE importation schedule and strain urn for the whole batch (include/cabm.h): a sweep that
+        # varies prob_daily_exposure or the variant calendar across replicates must not be batched silently with comms[0]'s
+        for c in comms[1:]:
+            if list(c.strains) != list(c0.strains) or c.expected_imports(first + i) != exp[i]:
+                raise ValueError("cabm_batch_run_days shares the importation schedule and the strain urn: every community of a batch "
+                                 "must have the same prob_daily_exposure, population size and mutant_intro_dates")
     jd = np.ascontiguousarray(c0.julian_day[first:first + n_days]); wd = np.ascontiguousarray(c0.is_weekday[first:first + n_days])
     hs = (C.c_void_p * len(comms))(*[c._h for c in comms])
     c0._check(c0.fn.batch_run_days(hs, len(comms), first, n_days, jd.ctypes.data_as(C.POINTER(C.c_int32)), wd.ctypes.data_as(C.POINTER(C.c_int32)),

@@ -193,3 +193,18 @@ def test_several_winners_per_warp(monkeypatch):
     assert g.getNumNewlyInfected().max() > 1500, g.getNumNewlyInfected().max()      # > 592 warps' worth of winners in a day
     hg, ho = sorted_hist(g), sorted_hist(o)
     assert hg.size == ho.size and np.array_equal(hg, ho)
+
+
+def test_infection_log_overflow_is_an_error(monkeypatch):
+    """The infection log is the only record of past infections: when it is full the history getters and the snapshot fail
+    (CABM_E_NOMEM) instead of returning a truncated history (the capacity is 3 N + 1024 records; CABM_LOG_CAP forces it)."""
+    monkeypatch.setenv("CABM_LOG_CAP", "200")
+    pop, P, g, o = make_pair(8000, 30, T=0.3, pde=2e-3, seed=6)
+    for pid in range(0, 3000, 5):
+        g.infect(pid, 0, 0)
+    with pytest.raises(cabm.community.CabmError, match="infection log capacity"):
+        g.infection_histories()
+    with pytest.raises(cabm.community.CabmError, match="infection log capacity"):
+        g.snapshot()
+    monkeypatch.delenv("CABM_LOG_CAP")
+    g.close()
