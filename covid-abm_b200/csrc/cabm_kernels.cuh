@@ -258,9 +258,10 @@ struct __align__(16) VisitSmem {
     unsigned long long bar_rows[VIS_WARPS][2];              // mbarriers of the row buffers
     unsigned long long bar_hot;                             // mbarrier of the hot-bitmap copy
     unsigned int slowq[VIS_SLOWQ];                          // agent | patron count << 29
-    unsigned int nslow, pad[3];
-    unsigned int hot[4];                                    // hot bitmap over the patronised locations, bitmap_words rounded up to 4 (dynamic)
+    unsigned int nslow;
+    alignas(16) unsigned int hot[4];                        // hot bitmap over the patronised locations, bitmap_words rounded up to 4 (dynamic); 16-byte aligned: bulk-copy destination
 };
+static_assert(offsetof(VisitSmem, hot) % 16 == 0 && offsetof(VisitSmem, rows) % 16 == 0 && offsetof(VisitSmem, bar_rows) % 8 == 0 && sizeof(VisitSmem) == offsetof(VisitSmem, hot) + 16, "VisitSmem layout");
 static inline size_t visit_smem_bytes(unsigned int bitmap_words) { return sizeof(VisitSmem) - 16 + (size_t) ((bitmap_words + 3u) & ~3u) * 4u; }
 
 __device__ __forceinline__ unsigned int smem_u32(const void* p) { return (unsigned int) __cvta_generic_to_shared(p); }
