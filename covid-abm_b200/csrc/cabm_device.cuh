@@ -167,9 +167,8 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        const unsigned int hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
-        const unsigned int hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        const unsigned long long m0 = (unsigned long long) c.x * 0xD2511F53ull, m1 = (unsigned long long) c.z * 0xCD9E8D57ull;   // one IMAD.WIDE each
+        c = make_uint4((unsigned int) (m1 >> 32) ^ c.y ^ k.x, (unsigned int) m1, (unsigned int) (m0 >> 32) ^ c.w ^ k.y, (unsigned int) m0);
         k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
     }
     return c;

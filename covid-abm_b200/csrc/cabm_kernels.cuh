@@ -237,23 +237,25 @@ __global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) 
 // one tile ahead of the tile being processed, so the warp never waits for HBM and spends no instructions on addresses. The
 // in-hospital flags of a tile are four words of a bitmap (one 16-byte load per lane, same address). The Philox block needs
 // no memory. Hotness is tested against a shared-memory bitmap over the Q patronised locations (dynamic shared memory,
-// fetched with one bulk copy per block). A visit that lands on a hot location is stored in the lane's own column of the
-// warp's staging buffer (no atomics, no shuffles in the body); the warp flushes when a column could overflow: one scan, one
-// reservation, one census RED per record. Agents that draw k >= 4 (1.9 %) are queued per block and handled on full warps
+// fetched with one bulk copy per block). A visit that lands on a hot location is stored as one word in the lane's own column
+// of the warp's staging buffer (no atomics, no shuffles in the body); the warp flushes when a column could overflow or after
+// 16 tiles: one scan, one reservation, one census RED per record. Agents that draw k >= 4 (1.9 %) are queued per block and handled on full warps
 // by the generic loop at the end, so the common path carries no divergent tail.
 // There is no block-level synchronisation in the loop.
 // ---------------------------------------------------------------------------------------------
 #define VIS_A 4               // agents per lane and tile
 #define VIS_TILE (32 * VIS_A)
-#define VIS_COL 16            // records a lane can stage (a tile adds at most 3 * VIS_A = 12)
+#define VIS_COL 24            // records a lane can stage (a tile adds at most 3 * VIS_A = 12)
 #define VIS_FLUSH_AT (VIS_COL - 3 * VIS_A)   // flush after a tile once some lane holds more than this
-#define VIS_SLOWQ (4 * TPB)   // k >= 4 agents a block queues for its final full-warp pass (beyond that: handled in place)
+#define VIS_WINDOW 16         // tiles between two flushes at most: a staged record names its tile by 4 bits
+#define VIS_SLOWQ (2 * TPB)   // k >= 4 agents a block queues for its final full-warp pass (beyond that: handled in place)
 #define VIS_WARPS (TPB / 32)
 #define VIS_TILE_BYTES (VIS_TILE * PROW_WORDS * 4u)
+#define VIS_MINB 3            // resident blocks per SM the register allocation aims at
 
 struct __align__(16) VisitSmem {
     unsigned int rows[VIS_WARPS][2][VIS_TILE * PROW_WORDS];  // patron rows of the current and the next tile of every warp (bulk-copy destinations)
-    uint2 stage[VIS_WARPS][VIS_COL][32];                    // hot visits (agent, public index): [slot][lane]
+    unsigned int stage[VIS_WARPS][VIS_COL][32];             // hot visits, [slot][lane]: public index | slot a << 19 | tile of the window << 21 (the lane is the column)
     unsigned long long thr[CABM_T_POISSON];                 // ceil(visit_cdf[k] * 2^32)
     unsigned long long bar_rows[VIS_WARPS][2];              // mbarriers of the row buffers
     unsigned long long bar_hot;                             // mbarrier of the hot-bitmap copy
@@ -315,8 +317,10 @@ __device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_h
 }
 
 // flush a warp's staged records (cnt per lane, column layout): one scan, one reservation, then every lane stores its own
-// run of the record list and adds its visits to the census
-__device__ __forceinline__ void visit_flush(const Dev& D, const uint2 (*stage)[32], unsigned int& cnt, const unsigned int lane, unsigned int& w_v) {
+// run of the record list and adds its visits to the census. A staged word names its agent by (tile of the window, slot a)
+// and the column it sits in: agent = win_t0 + tile * tile_stride + 32 a + lane.
+__device__ __forceinline__ void visit_flush(const Dev& D, const unsigned int (*stage)[32], unsigned int& cnt, const unsigned int lane,
+                                            const unsigned int win_t0, const unsigned int tile_stride, unsigned int& w_v) {
     unsigned int incl = cnt;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
@@ -325,9 +329,10 @@ __device__ __forceinline__ void visit_flush(const Dev& D, const uint2 (*stage)[3
     if (lane == 31) base = atomicAdd(&D.ctr->n_vis, total);
     base = __shfl_sync(0xffffffffu, base, 31) + incl - cnt;
     for (unsigned int k = 0; k < cnt; ++k) {
-        const uint2 r = stage[k][lane];
-        atomicAdd(&D.nvis[r.y], 1u);
-        if (base + k < D.cap_vis) D.visit_rec[base + k] = r; else atomicOr(&D.ctr->overflow, 8u);
+        const unsigned int e = stage[k][lane];
+        const unsigned int q = e & PROW_Q_MASK, p = win_t0 + (e >> 21) * tile_stride + ((e >> 19) & 3u) * 32u + lane;
+        atomicAdd(&D.nvis[q], 1u);
+        if (base + k < D.cap_vis) D.visit_rec[base + k] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
     }
     w_v += cnt; cnt = 0;
 }
@@ -362,8 +367,9 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
     if (t0 < own_hi) hw_next = hosp4[t0 / VIS_TILE];
     mbar_wait(&S.bar_hot, 0);
     const unsigned int* __restrict__ s_hot = S.hot;
-    uint2 (*const stage)[32] = S.stage[wid];
+    unsigned int (*const stage)[32] = S.stage[wid];
     unsigned int cnt = 0, w_pat = 0, w_v0 = 0, w_v = 0, phase = 0;                 // phase: bit b = parity to wait for on row buffer b
+    unsigned int win_t0 = t0, win_n = 0;                                            // first tile and number of tiles of the staging window
     for (unsigned int it = 0; t0 < own_hi; ++it, t0 += tile_stride) {
         const unsigned int b = it & 1u;
         const uint4 hw = hw_next;
@@ -372,9 +378,28 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
             if (lane == 0) { mbar_expect_tx(&S.bar_rows[wid][b ^ 1u], VIS_TILE_BYTES); bulk_g2s(&S.rows[wid][b ^ 1u][0], D.prow + (size_t) t1 * PROW_WORDS, VIS_TILE_BYTES, &S.bar_rows[wid][b ^ 1u]); }
             hw_next = hosp4[t1 / VIS_TILE];
         }
+        // k ~ Poisson(1) and the first three picks of every agent come from one Philox block (Community.cpp:1013-1017). The four
+        // agents of a lane are independent: their Philox rounds are interleaved so a warp always has eight multiplies in flight,
+        // and the whole computation sits in front of the wait for the tile's rows.
+        uint4 x[VIS_A];
+        {
+            uint2 k = key;
+#pragma unroll
+            for (int a = 0; a < VIS_A; ++a) x[a] = make_uint4(0u, t0 + a * 32 + lane, 0u, dp);
+#pragma unroll
+            for (int r = 0; r < 10; ++r) {
+#pragma unroll
+                for (int a = 0; a < VIS_A; ++a) {
+                    const unsigned long long m0 = (unsigned long long) x[a].x * 0xD2511F53ull, m1 = (unsigned long long) x[a].z * 0xCD9E8D57ull;   // one IMAD.WIDE each
+                    x[a] = make_uint4((unsigned int) (m1 >> 32) ^ x[a].y ^ k.x, (unsigned int) m1, (unsigned int) (m0 >> 32) ^ x[a].w ^ k.y, (unsigned int) m0);
+                }
+                k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
+            }
+        }
         mbar_wait(&S.bar_rows[wid][b], (phase >> b) & 1u);
         phase ^= 1u << b;
         const unsigned int* __restrict__ rows = S.rows[wid][b];
+        const unsigned int tag = win_n << 21;
         unsigned int slow = 0;
 #pragma unroll
         for (int a = 0; a < VIS_A; ++a) {
@@ -385,12 +410,10 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
             const unsigned int npat = prow_npat(w0);
             // drawing today: has patronised places, is not in hospital (Community.cpp:1009), and this handle owns the agent
             const unsigned int act = (unsigned int) (npat != 0) & (((hword >> lane) & 1u) ^ 1u) & (unsigned int) ((p - own_lo) < own_n);
-            // k ~ Poisson(1) and the first three picks come from one Philox block (Community.cpp:1013-1017), in 0/1 arithmetic
-            const uint4 x = philox4x32_10(make_uint4(0u, p, 0u, dp), key);
-            const unsigned int c3 = act & (unsigned int) (x.x >= thr3);                // k >= 4: the generic loop at the end of the block
+            const unsigned int c3 = act & (unsigned int) (x[a].x >= thr3);             // k >= 4: the generic loop at the end of the block
             const unsigned int live = act ^ c3;
-            unsigned int v0 = live & (unsigned int) (x.x >= thr0), v1 = live & (unsigned int) (x.x >= thr1), v2 = live & (unsigned int) (x.x >= thr2);
-            const unsigned int e0 = rw[__umulhi(x.y, npat)], e1 = rw[__umulhi(x.z, npat)], e2 = rw[__umulhi(x.w, npat)];   // npat == 0: word 0, ignored (act == 0)
+            unsigned int v0 = live & (unsigned int) (x[a].x >= thr0), v1 = live & (unsigned int) (x[a].x >= thr1), v2 = live & (unsigned int) (x[a].x >= thr2);
+            const unsigned int e0 = rw[__umulhi(x[a].y, npat)], e1 = rw[__umulhi(x[a].z, npat)], e2 = rw[__umulhi(x[a].w, npat)];   // npat == 0: word 0, ignored (act == 0)
             const unsigned int avoiding = (unsigned int) (prow_rank(w1, w2) < sd_rank);   // Community.cpp:1020: compliant households skip high-risk places
             v0 &= (avoiding & (e0 >> PROW_HIGH_BIT)) ^ 1u; v1 &= (avoiding & (e1 >> PROW_HIGH_BIT)) ^ 1u; v2 &= (avoiding & (e2 >> PROW_HIGH_BIT)) ^ 1u;
             const unsigned int q0 = e0 & PROW_Q_MASK, q1 = e1 & PROW_Q_MASK, q2 = e2 & PROW_Q_MASK;
@@ -400,11 +423,12 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
             w_pat += act;
             w_v0 += v0 + v1 + v2;
             const unsigned int h0 = v0 & __funnelshift_r(s_hot[q0 >> 5], 0u, q0), h1 = v1 & __funnelshift_r(s_hot[q1 >> 5], 0u, q1), h2 = v2 & __funnelshift_r(s_hot[q2 >> 5], 0u, q2);
-            if (h0) stage[cnt][lane] = make_uint2(p, q0);
+            const unsigned int ta = tag | ((unsigned int) a << 19);
+            if (h0) stage[cnt][lane] = q0 | ta;
             cnt += h0;
-            if (h1) stage[cnt][lane] = make_uint2(p, q1);
+            if (h1) stage[cnt][lane] = q1 | ta;
             cnt += h1;
-            if (h2) stage[cnt][lane] = make_uint2(p, q2);
+            if (h2) stage[cnt][lane] = q2 | ta;
             cnt += h2;
         }
         // k >= 4 (1.9 % of the drawing agents): queued for the block's final pass, so the generic loop runs on full warps
@@ -414,9 +438,10 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
             if (pos < VIS_SLOWQ) S.slowq[pos] = p | (npat << 29); else visit_slow(D, s_hot, S.thr, p, npat, dp, key, sd_rank, w_v0, w_v);
         }
         __syncwarp();                                                               // every lane has read its rows: the buffer may be refilled
-        if (__any_sync(0xffffffffu, cnt > VIS_FLUSH_AT)) visit_flush(D, stage, cnt, lane, w_v);
+        ++win_n;
+        if (win_n == VIS_WINDOW || __any_sync(0xffffffffu, cnt > VIS_FLUSH_AT)) { visit_flush(D, stage, cnt, lane, win_t0, tile_stride, w_v); win_t0 = t0 + tile_stride; win_n = 0; }
     }
-    if (__any_sync(0xffffffffu, cnt != 0)) visit_flush(D, stage, cnt, lane, w_v);
+    if (__any_sync(0xffffffffu, cnt != 0)) visit_flush(D, stage, cnt, lane, win_t0, tile_stride, w_v);
     // the block's k >= 4 agents on full warps
     __syncthreads();
     {
@@ -426,8 +451,8 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
     const int ids[3] = { CABM_W_PATRONS, CABM_W_VISITS, CABM_W_HOT_VISITS }; const unsigned int vals[3] = { w_pat, w_v0, w_v };
     block_work_add<3>(D, ids, vals);
 }
-__global__ void __launch_bounds__(TPB, 2) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
-__global__ void __launch_bounds__(TPB, 2) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
+__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
 
 __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1.0, cabm_exp(-hazard)); }
 
