@@ -21,6 +21,7 @@ N_COUNTERS = len(COUNTERS)
 DIAG = ["dose_1", "dose_2", "dose_3", "fully_vaxd", "bt_inf", "bt_dis", "bt_hosp", "bt_death", "bt_reported", "uv_inf", "uv_dis", "uv_hosp",
         "uv_death", "uv_reported", "infected", "infectious", "symptomatic", "naive", "quarantining", "seropos_all", "seropos_ped", "n_ped"]
 N_DIAG = 24
+STATIC_MAX_IDS = 1 << 20
 SHARD_FLAG_BYTES = 24
 WORK = ["agents", "active", "flags", "patrons", "visits", "hot_visits", "hot_locs", "nbr_edges", "trials", "infections"]
 N_WORK = len(WORK)
@@ -106,6 +107,7 @@ _OPTIONAL = {
     "shard_nccl_init": [_vp, _vp, C.c_int, C.c_int], "shard_exchange_capacity": [_vp, C.c_size_t], "shard_exchange_mode": [_vp, C.POINTER(C.c_int)],
     "shard_run_days": [_vp, C.c_int, C.c_int, C.POINTER(i32), C.POINTER(i32), C.POINTER(d), C.POINTER(d)],
     "set_profile": [_vp, C.c_int],
+    "serosurvey_static": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_uint64)],   # no-allocation variant (device scratch is a static array)
     "kernel_times": [_vp, C.POINTER(d), C.POINTER(C.c_uint64), C.POINTER(C.c_char_p), C.c_size_t, C.POINTER(C.c_size_t)],
 }
 SYMBOLS = sorted(list(_OPTIONAL) + list(_PROTOS) + ["last_error"])

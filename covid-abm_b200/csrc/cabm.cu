@@ -18,6 +18,29 @@ struct Buf { void** slot; size_t bytes; };
 
 } // namespace
 
+// ---- scratch that needs no allocation (cabm_serosurvey_static, include/cabm.h) -----------------------------------------
+// A file-scope device array: every GPU that loads this library holds CABM_STATIC_SCRATCH_BYTES of it until the process exits.
+// Layout: bytes [0, 256) the 64-bit accumulator of the running call (rest of the block unused), then up to
+// CABM_STATIC_MAX_IDS person ids. In HOST code the name g_static_scratch is only a stand-in for the symbol, not a device
+// address: the address is asked for once per device, with that device current, in cabm_create (cudaGetSymbolAddress) and
+// handed to the kernel as an argument.
+#define CABM_STATIC_HEAD_BYTES 256
+#define CABM_STATIC_SCRATCH_BYTES (CABM_STATIC_HEAD_BYTES + (size_t) CABM_STATIC_MAX_IDS * sizeof(unsigned int))
+static __device__ __align__(256) unsigned char g_static_scratch[CABM_STATIC_SCRATCH_BYTES];
+static void* g_static_scratch_addr[64] = { nullptr };        // per device ordinal, filled by cabm_create
+
+// k_serosurvey on the static scratch: ids (when use_ids) and the accumulator live in `scratch`, nothing else differs
+// (doSerosurvey(NATURAL, pop, day), Community.cpp:1224-1274)
+__global__ void k_serosurvey_static(const Dev D, const int day, unsigned char* scratch, const unsigned int n, const int use_ids) {
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(scratch);
+    const unsigned int* __restrict__ ids = reinterpret_cast<const unsigned int*>(scratch + CABM_STATIC_HEAD_BYTES);
+    unsigned int mine = 0;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        mine += sero_positive(D, D.par, use_ids ? ids[i] : i, day) ? 1u : 0u;
+    mine = warp_sum(mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(out, (unsigned long long) mine);
+}
+
 struct cabm {
     Dev d{};
     std::string err;
@@ -30,6 +53,7 @@ struct cabm {
     int visit_bps = 2;                           // resident k_visit blocks per SM (from the occupancy calculator, given the hot bitmap's size)
     std::vector<float> risk_sorted;              // distinct household riskiness values, ascending: DayCtx::sd_rank = how many lie below the day's social distancing
     void* scratch = nullptr; size_t scratch_bytes = 0;   // handle-owned device scratch of the small entry points (grows, never shrinks)
+    unsigned char* static_scratch = nullptr; std::string static_scratch_err;   // device address of g_static_scratch on this handle's device (cabm_create)
     bool have_par = false, have_pop = false;
     cabm_params hpar{};                       // host copy (pointers nulled)
     std::vector<double> h_ti[3];
@@ -288,6 +312,16 @@ int cabm_create(cabm_t** out) {
     if (cudaHostAlloc((void**) &h->h_pin, 16 * sizeof(int), cudaHostAllocMapped) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
     std::memset(h->h_pin, 0, 16 * sizeof(int));
     h->d.host_status = reinterpret_cast<unsigned int*>(h->h_pin) + 4;       // written by close_day: [0] overflow mask, [1] new infections of the hospital pass + importation
+    {   // device address of the static scratch: once per device, with that device current (it is: cudaGetDevice above)
+        void*& addr = g_static_scratch_addr[h->device & 63];
+        if (!addr) {
+            void* p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+            if (e == cudaSuccess && p) addr = p;
+            else { cudaGetLastError(); h->static_scratch_err = std::string("cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(e); }
+        }
+        h->static_scratch = (unsigned char*) addr;          // nullptr: cabm_serosurvey_static reports static_scratch_err; nothing else uses it
+    }
     if (const char* e = getenv("CABM_PDL")) h->pdl = atoi(e) != 0;
     if (const char* e = getenv("CABM_GRID_MULT")) { int k = 0; for (const char* q = e; *q && k < 9; ++k) { h->gm[k] = std::max(1, atoi(q)); while (*q && *q != ',') ++q; if (*q == ',') ++q; } }
     *out = h;
@@ -977,6 +1011,34 @@ int cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint
     CK(cudaMemcpyAsync(&r, h->d_diag, sizeof(r), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     *out_seropos = r;
+    return CABM_OK;
+}
+
+// cabm_serosurvey without any allocation (include/cabm.h): ids and accumulator in the file-scope device array, the result
+// comes back through the handle's pinned word. No cudaMalloc / cudaFree / allocating library call on this path.
+int cabm_serosurvey_static(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos) {
+    if (!h || !out_seropos) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (!pids) n = h->d.N;
+    *out_seropos = 0;
+    if (pids && n > (size_t) CABM_STATIC_MAX_IDS) {
+        h->err = "cabm_serosurvey_static: " + std::to_string(n) + " ids exceed CABM_STATIC_MAX_IDS (" + std::to_string((size_t) CABM_STATIC_MAX_IDS) +
+                 "): split the list, pass NULL for everybody, or call cabm_serosurvey";
+        return CABM_E_ARG;
+    }
+    if (n == 0) return CABM_OK;
+    if (pids) for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    if (!h->static_scratch) { h->err = h->static_scratch_err.empty() ? "static scratch address unknown" : h->static_scratch_err; return CABM_E_CUDA; }
+    unsigned char* sc = h->static_scratch;
+    // the array keeps the previous call's contents: the accumulator must start at zero, the ids are overwritten
+    CK(cudaMemsetAsync(sc, 0, sizeof(unsigned long long), h->stream));
+    if (pids) CK(cudaMemcpyAsync(sc + CABM_STATIC_HEAD_BYTES, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    k_serosurvey_static<<<grid_for(h, n, 8), TPB, 0, h->stream>>>(h->d, sim_day, sc, (unsigned int) n, pids ? 1 : 0);
+    unsigned long long* pin = reinterpret_cast<unsigned long long*>(h->h_pin + 8);        // pinned at cabm_create; words 8-9 are this call's
+    CK(cudaMemcpyAsync(pin, sc, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    *out_seropos = *pin;
     return CABM_OK;
 }
 

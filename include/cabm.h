@@ -295,6 +295,17 @@ int  cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]);
 /* doSerosurvey(NATURAL, pop, day) for an arbitrary list of people (pids == NULL: everybody); returns the seropositive count */
 int  cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos);
 
+/* cabm_serosurvey for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+   forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same arguments and
+   result as cabm_serosurvey, but the id list and the accumulator live in a file-scope `static __device__` array of the
+   library (4 MiB + 256 B per GPU that loads the library, held until the process exits), so the call makes no cudaMalloc,
+   cudaFree or allocating library call. Limit: n <= CABM_STATIC_MAX_IDS when pids != NULL (more: CABM_E_ARG with a message;
+   pids == NULL, everybody, has no limit). Every call on a device shares the one array: it still holds the previous call's
+   ids (the accumulator is cleared by the call), and two calls that overlap on the same GPU -- from different handles,
+   streams or threads -- race; serialise them. */
+#define CABM_STATIC_MAX_IDS (1u << 20)
+int  cabm_serosurvey_static(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos);
+
 /* ---- one community advanced by several handles, one per GPU -------------------------------------
    Every handle loads the whole population (static arrays and location state are replicated); handle `rank` OWNS the
    agents [pid_lo, pid_hi) -- it alone scans, exposes, infects and tallies them. Household members must share an owner.

@@ -42,6 +42,7 @@ def test_product_library_exports_every_declared_symbol():
 def test_oracle_library_exports_the_same_abi_under_its_prefix():
     lib = oracle_lib.oracle_backend().lib
     skip = {"cabm_set_profile", "cabm_kernel_times",            # device profiling: nothing to mirror on the CPU
+            "cabm_serosurvey_static",                           # where the device scratch lives: nothing to mirror on the CPU
             "cabm_shard_nccl_id", "cabm_shard_nccl_init", "cabm_shard_exchange_capacity", "cabm_shard_exchange_mode", "cabm_shard_run_days"}   # NCCL-driven batch loop
     missing = [n for n in _declared_functions() if n not in skip and not hasattr(lib, n.replace("cabm_", "cabm_oracle_", 1))]
     assert not missing, missing
