@@ -85,6 +85,7 @@ _PROTOS = {
     "set_params": [_vp, C.POINTER(Params)], "set_timed_intervention": [_vp, C.c_int, C.POINTER(d), C.c_size_t],
     "tick": [_vp, C.c_int, C.c_int, C.c_int], "import": [_vp, C.c_int, d, C.POINTER(d), C.POINTER(i32)],
     "infect": [_vp, C.c_uint32, C.c_int, C.c_int, C.POINTER(i32)],
+    "infect_batch": [_vp, C.POINTER(C.c_uint32), C.POINTER(u8), C.c_size_t, C.c_int, C.POINTER(u8)],
     "run_days": [_vp, C.c_int, C.c_int, C.POINTER(i32), C.POINTER(i32), C.POINTER(d), C.POINTER(d)],
     "batch_run_days": [C.POINTER(_vp), C.c_size_t, C.c_int, C.c_int, C.POINTER(i32), C.POINTER(i32), C.POINTER(d), C.POINTER(d)],
     "vaccinate": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(u8)],

@@ -104,6 +104,15 @@ class Community:
         self._check(self.fn.infect(self._h, int(pid), int(strain), self.day if day is None else int(day), C.byref(out)))
         return bool(out.value)
 
+    def infect_many(self, pids, strains, day: int | None = None) -> np.ndarray:
+        """len(pids) consecutive Community::infect(id, strain) calls in one launch (cabm_infect_batch)."""
+        p = np.ascontiguousarray(pids, dtype=np.uint32)
+        st = np.ascontiguousarray(np.broadcast_to(np.asarray(strains, dtype=np.uint8), p.shape))
+        took = np.zeros(p.size, dtype=np.uint8)
+        self._check(self.fn.infect_batch(self._h, p.ctypes.data_as(C.POINTER(C.c_uint32)), st.ctypes.data_as(C.POINTER(C.c_uint8)), p.size,
+                                         self.day if day is None else int(day), took.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return took.astype(bool)
+
     def tick(self, day: int | None = None):
         """Community::tick() (Community.cpp:1147-1192)."""
         dday = self.day if day is None else int(day)

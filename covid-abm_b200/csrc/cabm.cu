@@ -565,6 +565,45 @@ int cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_i
     return CABM_OK;
 }
 
+int cabm_infect_batch(cabm_t* h, const uint32_t* pids, const uint8_t* strains, size_t n, int sim_day, uint8_t* out_infected) {
+    if (!h || ((!pids || !strains) && n)) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (n == 0) return CABM_OK;
+    if (n > 0x7FFFFFFFu || h->d.N >= (1u << 29)) { h->err = "cabm_infect_batch: at most 2^31 calls and 2^29 agents"; return CABM_E_ARG; }
+    for (size_t k = 0; k < n; ++k) if (pids[k] >= h->d.N || strains[k] >= CABM_N_STRAINS) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    // Calls on the same person depend on each other, all others do not: wave w holds the (w+1)-th call of every person, waves
+    // run one after the other (importation draws people uniformly, so there is almost always one wave)
+    std::vector<unsigned int> order(n), wave(n);
+    {
+        std::vector<std::pair<unsigned int, unsigned int>> by_pid(n);
+        for (size_t k = 0; k < n; ++k) by_pid[k] = { pids[k], (unsigned int) k };
+        std::sort(by_pid.begin(), by_pid.end());
+        for (size_t i = 0; i < n; ++i) wave[by_pid[i].second] = (i && by_pid[i].first == by_pid[i - 1].first) ? wave[by_pid[i - 1].second] + 1 : 0u;
+        for (size_t k = 0; k < n; ++k) order[k] = (unsigned int) k;
+        std::stable_sort(order.begin(), order.end(), [&](unsigned int a, unsigned int b) { return wave[a] < wave[b]; });
+    }
+    std::vector<unsigned int> items(n), seq_off(n);
+    for (size_t i = 0; i < n; ++i) { const unsigned int k = order[i]; items[i] = pids[k] | ((unsigned int) strains[k] << 29); seq_off[i] = k; }
+    const size_t out_off = 2 * n * sizeof(unsigned int);
+    void* buf = nullptr; if ((rc = scratch(h, out_off + n, &buf))) return rc;
+    unsigned int* d_items = (unsigned int*) buf; unsigned int* d_seq = d_items + n; unsigned char* d_out = (unsigned char*) buf + out_off;
+    CK(cudaMemcpyAsync(d_items, items.data(), n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_seq, seq_off.data(), n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    for (size_t i0 = 0; i0 < n;) {
+        size_t i1 = i0; while (i1 < n && wave[order[i1]] == wave[order[i0]]) ++i1;
+        k_seed_batch<<<grid_for(h, i1 - i0, 4), TPB, 0, h->stream>>>(h->d, d_items + i0, d_seq + i0, (unsigned int) (i1 - i0), sim_day, d_out);
+        h->launches++;
+        i0 = i1;
+    }
+    k_seed_bump<<<1, 32, 0, h->stream>>>(h->d, (unsigned int) n);
+    std::vector<unsigned char> took(n);
+    CK(cudaMemcpyAsync(took.data(), d_out, n, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    if (out_infected) std::memcpy(out_infected, took.data(), n);
+    return check_overflow(h);
+}
+
 int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                   const double* expected_imports, const double* strain_w) {
     if (!h || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;

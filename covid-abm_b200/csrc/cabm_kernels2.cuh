@@ -388,6 +388,27 @@ __global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain
     *(volatile int*) (out + 1) = echo;                                              // the host spins on this word (cabm_infect)
 }
 
+// n consecutive Community::infect calls (cabm_infect_batch): one thread per call of a WAVE (calls on distinct people, which do
+// not see each other); item = person | strain << 29 (N < 2^29 is checked at load time for this entry point), seq_off = position
+// of the call in the batch. The sequence counter itself is advanced by k_seed_bump after the last wave.
+__global__ void k_seed_batch(const Dev D, const unsigned int* __restrict__ items, const unsigned int* __restrict__ seq_off, const unsigned int n,
+                             const int day, unsigned char* out) {
+    const unsigned int base = D.ctr->seed_calls;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned int pid = items[i] & 0x1FFFFFFFu; const int strain = (int) (items[i] >> 29);
+        const unsigned int k = seq_off[i], seq = base + k;
+        unsigned char took = 0;
+        if (pid >= D.own_lo && pid < D.own_hi) {                                   // every handle counts every call, the owner applies it
+            Stream s; s.begin(D.seed, (unsigned int) day, CABM_P_SEED, pid, seq);
+            InfectCtx c; c.pid = (int) pid; c.time = day; c.source = -1; c.has_source = false; c.strain = strain; c.infector = -1;
+            c.purpose = CABM_P_SEED; c.key_a = pid; c.key_b = seq; c.key_sub = 0;
+            took = infect_event(D, s, c, true) ? 1 : 0;
+        }
+        out[k] = took;
+    }
+}
+__global__ void k_seed_bump(const Dev D, const unsigned int n) { if (threadIdx.x == 0 && blockIdx.x == 0) D.ctr->seed_calls += n; }
+
 // Person::vaccinate (Person.cpp:611-647), leaky model
 __global__ void k_vaccinate(const Dev D, const unsigned int* pids, const unsigned int n, const int day, unsigned char* ok) {
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {

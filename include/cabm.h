@@ -243,6 +243,12 @@ int  cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday);
 int  cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[CABM_N_STRAINS], int32_t* out_infected);
 /* replaces Community::infect(id, strain) (Community.cpp:550-553) */
 int  cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected);
+/* n consecutive Community::infect(id, strain) calls (Community.cpp:550-553) in one launch: the importation loop of
+   seed_epidemic (simulator.h:209-219) and the initial seeding (simulator.h:101-103,113) call Person::infect once per case;
+   a facade queues those calls and resolves them here with one round trip. Same result as calling cabm_infect n times in
+   this order (the k-th call gets the k-th sequence number of the keyed stream; a person listed twice is tried again after
+   its first try has been applied). out_infected[k] = 1 if the k-th call took (may be NULL). */
+int  cabm_infect_batch(cabm_t* h, const uint32_t* pids, const uint8_t* strains, size_t n, int sim_day, uint8_t* out_infected);
 /* run `n_days` of tick+import back to back without returning to the host (CUDA-graph replay) */
 int  cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                    const double* expected_imports, const double* strain_w /* [n_days][4] */);

@@ -104,6 +104,17 @@ int cabm_oracle_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t
     return CABM_OK;
 }
 
+int cabm_oracle_infect_batch(cabm_t* h, const uint32_t* pids, const uint8_t* strains, size_t n, int sim_day, uint8_t* out_infected) {
+    H_OK(h); if ((!pids || !strains) && n) return CABM_E_ARG;
+    for (size_t k = 0; k < n; ++k) if (pids[k] >= h->sim.n_people || strains[k] >= CABM_N_STRAINS) return CABM_E_ARG;
+    for (size_t k = 0; k < n; ++k) {                                  // by definition: the calls one after the other
+        int32_t took = 0;
+        const int rc = cabm_oracle_infect(h, pids[k], (int) strains[k], sim_day, &took); if (rc) return rc;
+        if (out_infected) out_infected[k] = took ? 1 : 0;
+    }
+    return CABM_OK;
+}
+
 int cabm_oracle_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                          const double* expected_imports, const double* strain_w) {
     H_OK(h);

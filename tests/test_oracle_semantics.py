@@ -281,3 +281,22 @@ def test_daily_diagnostics_against_brute_force():
     # incremental history sync returns the tail of the log
     allh = c.infection_histories(); tail = c.infection_histories_from(allh.size - 10)
     assert tail.size == 10 and np.array_equal(tail, allh[-10:]) and c.infection_histories_from(allh.size).size == 0
+
+
+def test_infect_batch_is_the_calls_one_after_the_other():
+    """Host-side contract of cabm_infect_batch on the oracle: same outcomes, sequence numbers and state as single calls."""
+    import numpy as np
+    import synthpop
+    import covid_abm_b200 as cabm
+    import oracle_lib
+    pop = synthpop.generate(5000, seed=3)
+    P = cabm.params.default_params(run_length=10, seed=2, T=0.1)
+    a, b = oracle_lib.oracle_community(P, pop), oracle_lib.oracle_community(P, pop)
+    rng = np.random.default_rng(1)
+    pids = rng.integers(0, 5000, size=600).astype(np.uint32); pids[10:20] = pids[0:10]
+    strains = rng.integers(0, 4, size=600).astype(np.uint8)
+    ta = a.infect_many(pids, strains, 0)
+    tb = np.array([b.infect(int(p), int(s), 0) for p, s in zip(pids, strains)])
+    assert np.array_equal(ta, tb) and ta.sum() > 300 and not ta[10:20].any()
+    a.step(); b.step()
+    assert np.array_equal(a.current_infections(), b.current_infections()) and np.array_equal(a.ledger_table(), b.ledger_table())

@@ -208,3 +208,25 @@ def test_infection_log_overflow_is_an_error(monkeypatch):
         g.snapshot()
     monkeypatch.delenv("CABM_LOG_CAP")
     g.close()
+
+
+def test_infect_batch_equals_consecutive_calls():
+    """cabm_infect_batch = the same calls one after the other: sequence numbers, people listed twice or three times (later tries
+    see the earlier ones applied), mixed strains; on the CUDA library against the oracle's batch, against single CUDA calls."""
+    pop, P, g, o = make_pair(30000, 30, T=0.12, pde=1e-3, seed=15)
+    g1 = cabm.Community(P, pop, g.T, attrs=cabm.abi.immunity_attributes(int(pop["n_people"]), P["seed"]))
+    rng = np.random.default_rng(8)
+    for day in (0, 1, 9):
+        pids = rng.integers(0, 30000, size=4000).astype(np.uint32)
+        pids[100:140] = pids[50:90]; pids[300:310] = pids[50:60]           # repeated people inside one batch
+        strains = rng.integers(0, 4, size=pids.size).astype(np.uint8)
+        tg, to = g.infect_many(pids, strains, day), o.infect_many(pids, strains, day)
+        t1 = np.array([g1.infect(int(p), int(s), day) for p, s in zip(pids, strains)])
+        assert np.array_equal(tg, to) and np.array_equal(tg, t1), f"day {day}: {np.flatnonzero(tg != to)[:5]} {np.flatnonzero(tg != t1)[:5]}"
+        assert tg.sum() > 1000 and not tg[100:140].all()
+        for c in (g, o, g1):
+            for _ in range(3 if day else 1):
+                c.step()
+        assert_same_state(g, o, f"after day {day}")
+    assert np.array_equal(g.ledger_table(), g1.ledger_table()) and np.array_equal(g.current_infections(), g1.current_infections())
+    g1.close()
