@@ -30,6 +30,7 @@ CABM_DECL(int, create, cabm_t**); CABM_DECL(int, destroy, cabm_t*); CABM_DECL(co
 CABM_DECL(int, load_population, cabm_t*, const cabm_population*); CABM_DECL(int, set_params, cabm_t*, const cabm_params*);
 CABM_DECL(int, set_timed_intervention, cabm_t*, int, const double*, size_t);
 CABM_DECL(int, tick, cabm_t*, int, int, int); CABM_DECL(int, infect, cabm_t*, uint32_t, int, int, int32_t*);
+CABM_DECL(int, infect_batch, cabm_t*, const uint32_t*, const uint8_t*, size_t, int, uint8_t*);
 CABM_DECL(int, vaccinate, cabm_t*, int, const uint32_t*, size_t, uint8_t*); CABM_DECL(int, quarantine, cabm_t*, const uint32_t*, size_t, int, int);
 CABM_DECL(int, ledger_table, cabm_t*, uint64_t*, size_t); CABM_DECL(int, cumulative_outcomes, cabm_t*, uint64_t*);
 CABM_DECL(int, sync_histories_from, cabm_t*, size_t, cabm_infection*, size_t, size_t*);
@@ -110,7 +111,7 @@ CommunityLedger::CommunityLedger(const CommunityLedger& o) : _owner(nullptr), _s
 }
 
 std::shared_ptr<cabm_snap> Community::take_snapshot() {
-    flush_doses();
+    flush_pending();
     cabm_snap_t* s = nullptr;
     const int rc = CABM_FN(snapshot)(handle(), &s);
     if (rc != 0) fail("cabm_snapshot", rc);
@@ -134,7 +135,9 @@ void Community::load_from_cache(CommunityLedger* cache_ledger, Date* cache_date,
         while (not p->vaccineHistory.empty() and p->vaccineHistory.back() >= day) p->vaccineHistory.pop_back();
         while (not p->quarantineHistory.empty() and p->quarantineHistory.back().first >= day) p->quarantineHistory.pop_back();
     }
-    _log_read = 0; _pending_doses.clear();
+    _log_read = 0; _pending_doses.clear(); _pending_quar.clear();
+    for (auto& q : _pending_inf) delete q.placeholder;      // (their owners' histories are cleared just above)
+    _pending_inf.clear();
     device_changed();
 }
 
@@ -328,7 +331,7 @@ Location* Community::getLocationByID(int id) {
 void Community::tick() {
     _day = _date->day();
     cabm* h = handle();
-    flush_doses();
+    flush_pending();
     push_interventions();
     { Ft ft(FT_TICK);
       const int rc = CABM_FN(tick)(h, _day, (int) _date->julianDay(), _date->isWeekday() ? 1 : 0);
@@ -402,26 +405,50 @@ Infection* Community::infect(int id, StrainType strain) {                       
     return getPersonByID(id)->infect(this, _date, strain);
 }
 
-bool Community::infect_on_device(int pid, StrainType strain, int day) {
-    cabm* h = handle();
-    Ft ft(FT_INFECT);
-    flush_doses();
-    int32_t took = 0;
-    const int rc = CABM_FN(infect)(h, (uint32_t) pid, (int) strain, day, &took);
-    if (rc != 0) fail("cabm_infect", rc);
-    if (took) device_changed();
-    return took != 0;
+// Community::infect / Person::infect without a source (simulator.h:102,113,126,217) are QUEUED: seed_epidemic calls them once
+// per imported case, hundreds of times a day, and a device round trip per case cost 25 times the day itself. The queue is
+// resolved by one cabm_infect_batch (the same calls, in order, with their own sequence numbers) before anything reads or
+// changes the device state. Until then the returned Infection* is provisional: a call that turns out not to take (the person
+// was protected or already infected) has its placeholder removed again.
+void Community::queue_infect(int pid, StrainType strain, int day, Infection* placeholder) {
+    flush_doses();                                        // doses given before this call must be visible to it
+    flush_quarantines();
+    if (not _pending_inf.empty() and day != _pending_inf_day) flush_infects();
+    _pending_inf_day = day;
+    _pending_inf.push_back({ (unsigned int) pid, (unsigned char) strain, placeholder });
+    device_changed();                                     // mirrors and caches are stale: the next reader resolves the queue
 }
+
+void Community::flush_infects() {
+    if (_pending_inf.empty()) return;
+    Ft ft(FT_INFECT);
+    cabm* h = handle();
+    const size_t n = _pending_inf.size();
+    vector<uint32_t> pids(n); vector<uint8_t> strains(n), took(n, 0);
+    for (size_t k = 0; k < n; ++k) { pids[k] = _pending_inf[k].pid; strains[k] = _pending_inf[k].strain; }
+    const int rc = CABM_FN(infect_batch)(h, pids.data(), strains.data(), n, _pending_inf_day, took.data());
+    if (rc != 0) fail("cabm_infect_batch", rc);
+    for (size_t k = 0; k < n; ++k) {
+        if (took[k]) continue;
+        vector<Infection*>& hist = _people[pids[k]]->infectionHistory;
+        for (size_t i = hist.size(); i-- > 0;) if (hist[i] == _pending_inf[k].placeholder) { hist.erase(hist.begin() + i); break; }
+        delete _pending_inf[k].placeholder;
+    }
+    _pending_inf.clear();
+    device_changed();
+}
+
+void Community::flush_pending() { flush_doses(); flush_infects(); flush_quarantines(); }
 
 // Person::infect(community, source, date, sourceloc, strain) with no source is what seed_epidemic and Community::infect
 // call (simulator.h:102,113,126,217); transmission between people never comes through here -- it happens inside cabm_tick.
 Infection* Person::infect(Community* community, Person* source, const Date* date, Location*, StrainType strain, bool) {
     if (source) { cerr << "ERROR: person-to-person infection is resolved on the device, not through Person::infect" << endl; exit(-1); }
     if (strain == NUM_OF_STRAIN_TYPES) strain = WILDTYPE;
-    if (not community->infect_on_device(getID(), strain, date->day())) return nullptr;
-    Infection* placeholder = new Infection();             // completed from the device log at the next refresh
+    Infection* placeholder = new Infection();             // completed from the device log at the next refresh, or withdrawn if the call does not take
     placeholder->infectedBegin = date->day(); placeholder->strain = strain; placeholder->infectionOwner = this;
     infectionHistory.push_back(placeholder);
+    community->queue_infect(getID(), strain, date->day(), placeholder);
     return placeholder;
 }
 
@@ -429,6 +456,7 @@ Infection* Person::infect(Community* community, Person* source, const Date* date
 void Person::refresh() { _stale = false; if (_community) _community->refresh_people(); }
 
 void Community::refresh_people() {
+    flush_pending();
     Ft ft(FT_REFRESH);
     Person::_stale = false;
     if (not _uploaded) return;
@@ -493,7 +521,7 @@ void Community::vaccinate() {
     }
     for (int bin : bins) for (int dose = 0; dose < _par->numVaccineDoses; ++dose) vac_campaign->rollover_unused_doses(_day, dose, bin);
     vac_campaign->schedule_revaccinations(urg_revax, std_revax);
-    flush_doses();
+    flush_pending();
 }
 
 bool Person::vaccinate(int time) {                                                // Person.cpp:611-647 (leaky immunity only, :622)
@@ -502,7 +530,7 @@ bool Person::vaccinate(int time) {                                              
     _community->queue_dose(getID());
     return true;
 }
-void Community::queue_dose(int pid) { _pending_doses.push_back((unsigned int) pid); }
+void Community::queue_dose(int pid) { flush_infects(); _pending_doses.push_back((unsigned int) pid); }
 
 void Community::flush_doses() {
     if (_pending_doses.empty()) return;
@@ -547,10 +575,18 @@ void Person::scheduleQuarantine(int start, int quarantineDuration) {            
     quarantineHistory.emplace_back(start, start + quarantineDuration);
     _community->push_quarantine(getID(), start, start + quarantineDuration);
 }
+// contact tracing quarantines hundreds to thousands of people a day, all for the same interval (Community.cpp:1135): queued and
+// written to the device in one call per interval
 void Community::push_quarantine(int pid, int from, int until) {
-    const uint32_t p = (uint32_t) pid;
-    const int rc = CABM_FN(quarantine)(handle(), &p, 1, from, until);
+    if (not _pending_quar.empty() and (from != _pq_from or until != _pq_until)) flush_quarantines();
+    _pq_from = from; _pq_until = until;
+    _pending_quar.push_back((unsigned int) pid);             // no epoch bump here: a quarantine changes no infection history, and the readers
+}                                                            // that depend on it (tick, diagnostics, snapshot) flush first
+void Community::flush_quarantines() {
+    if (_pending_quar.empty()) return;
+    const int rc = CABM_FN(quarantine)(handle(), _pending_quar.data(), _pending_quar.size(), _pq_from, _pq_until);
     if (rc != 0) fail("cabm_quarantine", rc);
+    _pending_quar.clear();
     device_changed();
 }
 
@@ -559,6 +595,7 @@ void Community::push_quarantine(int pid, int from, int until) {
 // ---------------------------------------------------------------------------------------------------------------------
 std::vector<size_t> Community::series(int counter) {
     const size_t R = _par->runLength;
+    flush_pending();
     if (not _uploaded) return std::vector<size_t>(R, 0);
     if (_ledger_epoch != _epoch) {
         Ft ft(FT_LEDGER);
@@ -574,14 +611,15 @@ std::vector<size_t> Community::getNumNewInfectionsByLoc(std::string) { return st
 
 std::vector<size_t> Community::getCumulIncidenceByOutcome() {
     uint64_t out[CABM_N_OUTCOMES] = { 0 };
+    flush_pending();
     if (_uploaded) { const int rc = CABM_FN(cumulative_outcomes)(_h, out); if (rc != 0) fail("cabm_cumulative_outcomes", rc); }
     return std::vector<size_t>(out, out + CABM_N_OUTCOMES);
 }
 
 const std::vector<unsigned long long>& Community::diagnostics(int day) {
+    flush_pending();
     if (_diag_epoch != _epoch or _diag_day != day) {
         Ft ft(FT_DIAG);
-        flush_doses();
         _diag_cache.assign(CABM_N_DIAG, 0);
         const int rc = CABM_FN(diagnostics)(handle(), day, (uint64_t*) _diag_cache.data());
         if (rc != 0) fail("cabm_diagnostics", rc);
@@ -622,7 +660,7 @@ double Community::doSerosurvey(const ImmuneStateType ist, const std::vector<Pers
     std::vector<uint32_t> ids(pop.size());
     for (size_t i = 0; i < pop.size(); ++i) ids[i] = (uint32_t) pop[i]->getID();
     uint64_t pos = 0;
-    flush_doses();
+    flush_pending();
     const int rc = CABM_FN(serosurvey)(handle(), time, ids.data(), ids.size(), &pos);
     if (rc != 0) fail("cabm_serosurvey", rc);
     return (double) pos / pop.size();

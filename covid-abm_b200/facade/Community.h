@@ -120,7 +120,7 @@ class Community {
     // ---- facade internals used by Person / CommunityLedger ----
     cabm* handle();                                       // uploads population and parameters on first use
     void device_changed();                                // bumps the state epoch: mirrors and caches are stale
-    bool infect_on_device(int pid, StrainType strain, int day);
+    void queue_infect(int pid, StrainType strain, int day, Infection* placeholder);   // no-source infections are resolved in one batch (cabm_infect_batch)
     void queue_dose(int pid);
     void push_quarantine(int pid, int from, int until);
     void refresh_people();
@@ -144,6 +144,9 @@ class Community {
     std::vector<size_t> series(int counter);
     const std::vector<unsigned long long>& diagnostics(int day);
     void flush_doses();
+    void flush_infects();
+    void flush_quarantines();
+    void flush_pending();                                 // everything queued on the host reaches the device: doses, no-source infections, quarantines
     void push_interventions();
     void fail(const char* what, int rc);
 
@@ -154,5 +157,8 @@ class Community {
     std::vector<unsigned long long> _ledger_cache, _diag_cache;
     size_t _log_read;                                     // records of the device infection log already mirrored
     std::vector<unsigned int> _pending_doses;
+    struct PendingInfect { unsigned int pid; unsigned char strain; Infection* placeholder; };
+    std::vector<PendingInfect> _pending_inf; int _pending_inf_day = 0;
+    std::vector<unsigned int> _pending_quar; int _pq_from = 0, _pq_until = 0;
 };
 #endif

@@ -251,3 +251,20 @@ def test_facade_cuda_equals_facade_oracle(tmp_path, campaign):
     for k in ("infections", "secondary_links", "doses", "urgent_doses", "quarantine_index", "cumul_death"):
         assert ic[k] == io[k], k
     assert ic["infections"] > 3000 and (ic["doses"] > 0) == (campaign > 0) and (ic["urgent_doses"] > 0) == (campaign == 2)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not (os.path.exists(DRV_CUDA) and os.path.exists(DRV_ORACLE)), reason="facade drivers not built")
+def test_ring_vaccination_at_scale_cuda_equals_oracle(tmp_path):
+    """BASELINE configs[3] at a size the oracle arm finishes in about two minutes: 300 k agents, 100 days, general campaign +
+    contact tracing from day 30 with self-quarantine and ring vaccination of the traced contacts (exp/active-vac/main.cpp:
+    101-111,711), the reference's unmodified simulate_epidemic and Vac_Campaign on both backends. Everything the run writes
+    must be byte-identical: ledger, plot log, Rt / offspring / household attack rate, dose and quarantine totals."""
+    pop, P, tab = _case(tmp_path, n=300_000, days=100, T=0.12, pde=2e-4, tracing_from=30)
+    ic, _, plot_c, led_c, _ = _run(DRV_CUDA, tmp_path, P, tab, 3, 2, tag="cuda")
+    io, _, plot_o, led_o, _ = _run(DRV_ORACLE, tmp_path, P, tab, 3, 2, tag="oracle")
+    assert led_c == led_o and plot_c == plot_o
+    assert open(os.path.join(str(tmp_path), "out_cuda.rt.csv")).read() == open(os.path.join(str(tmp_path), "out_oracle.rt.csv")).read()
+    for k in ("infections", "secondary_links", "doses", "urgent_doses", "quarantine_index", "cumul_death"):
+        assert ic[k] == io[k], k
+    assert ic["infections"] > 20_000 and ic["urgent_doses"] > 500 and ic["quarantine_index"] > 0, ic
