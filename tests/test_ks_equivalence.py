@@ -34,12 +34,12 @@ def test_curves_statistically_equivalent_to_reference():
     pop, P, T = ks.build_case(args, cabm, synthpop)
     assert int(pop["n_people"]) == c["agents"]
     B = ks.ours_arm(args, cabm, pop, P, T)
-    tests, worst = ks.compare(fx["summaries"], B)
+    tests, worst, families = ks.compare(fx["summaries"], B)
     # the epidemic must actually have happened in both arms (a KS test on all-zero curves proves nothing)
     assert tests["incidence.total"]["ref_mean"] > 0.5 * c["agents"] and tests["death.total"]["ref_mean"] > 20
-    low = {k: round(v["p"], 4) for k, v in tests.items() if v["p"] <= 0.05 and k.split(".")[0] in ks.HEADLINE}
-    assert not low, f"KS p <= 0.05 on {low}"
-    assert worst > 0.05
+    # the decision rule of tools/ks_equivalence.py: Holm-Bonferroni over the 15 pre-declared headline statistics, family-wise 0.05
+    assert families["headline"]["tests"] == 15 and families["headline"]["pass"], families["headline"]
+    assert ks.holm({"a": 0.01, "b": 0.04, "c": 0.03}) == {"a": 0.03, "c": 0.06, "b": 0.06}
     # means agree to a few percent on every series
     for k, v in tests.items():
         if k.endswith(".total"):
