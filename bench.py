@@ -171,7 +171,8 @@ def dropin_record(pop, P0):
             j = json.loads(r.stdout.strip().splitlines()[-1])
             out[key] = j["simulate_epidemic_s"] * 1e3 / j["days"]
             if campaign == 0:
-                out.update(load_s=j["load_s"], agent_days_per_s=j["agent_days_per_s"], infections=j["infections"])
+                out.update(load_s=j["load_s"], upload_s=j.get("upload_s"), agent_days_per_s=j["agent_days_per_s"], infections=j["infections"],
+                           note="ms_per_day = wall clock of simulate_epidemic / days; text-file load and the one-off device upload are load_s and upload_s")
     except Exception as e:                                  # a record, not the headline: never fail the bench line for it
         out["error"] = repr(e)[:300]
     subprocess.run(["rm", "-rf", tmp])

@@ -414,8 +414,12 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     // so the patron row carries its RANK among the distinct household values and the day context the matching threshold.
     for (uint32_t p = 0; p < N; ++p)
         if (home[p] < 0 || (uint32_t) home[p] >= L || dayl[p] >= (int) L) { h->err = "home/day location out of range"; return CABM_E_ARG; }
-    h->risk_sorted.resize(N);
-    for (uint32_t p = 0; p < N; ++p) h->risk_sorted[p] = pop->loc_risk[home[p]];
+    {   // one value per household, not per person
+        std::vector<unsigned char> is_home(L, 0);
+        for (uint32_t p = 0; p < N; ++p) is_home[home[p]] = 1;
+        h->risk_sorted.clear();
+        for (uint32_t l = 0; l < L; ++l) if (is_home[l]) h->risk_sorted.push_back(pop->loc_risk[l]);
+    }
     std::sort(h->risk_sorted.begin(), h->risk_sorted.end());
     h->risk_sorted.erase(std::unique(h->risk_sorted.begin(), h->risk_sorted.end()), h->risk_sorted.end());
     h->risk_sorted.shrink_to_fit();

@@ -136,7 +136,6 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
 // k_active: one thread per active agent.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_active_body(const Dev& D) {
-    pdl_launch_dependents();
     pdl_wait();
     Counters* const ctr = D.ctr;
     const DayCtx& cx = D.dayctx[ctr->day_idx]; const int day = cx.day;
@@ -219,6 +218,7 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
         }
         nflag += mine;
     }
+    pdl_launch_dependents();                             // the successor may start launching: only this block's counters are left
     nflag = warp_sum(nflag); ntoday = warp_sum(ntoday);
     if ((threadIdx.x & 31) == 0) {
         if (nflag) atomicAdd(&ctr->work[CABM_W_FLAGS], (unsigned long long) nflag);
@@ -340,7 +340,6 @@ __device__ __forceinline__ void visit_flush(const Dev& D, const unsigned int (*s
 __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bitmap_words) {
     extern __shared__ __align__(16) unsigned char vis_smem_raw[];
     VisitSmem& S = *reinterpret_cast<VisitSmem*>(vis_smem_raw);
-    pdl_launch_dependents();
     const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const unsigned int own_lo = D.own_lo, own_hi = D.own_hi, own_n = own_hi - own_lo;
     const unsigned int t_base = own_lo & ~(VIS_TILE - 1u);                          // tiles cover the owned agents only
@@ -442,6 +441,7 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
         if (win_n == VIS_WINDOW || __any_sync(0xffffffffu, cnt > VIS_FLUSH_AT)) { visit_flush(D, stage, cnt, lane, win_t0, tile_stride, w_v); win_t0 = t0 + tile_stride; win_n = 0; }
     }
     if (__any_sync(0xffffffffu, cnt != 0)) visit_flush(D, stage, cnt, lane, win_t0, tile_stride, w_v);
+    pdl_launch_dependents();                             // the tiles are done; the k >= 4 pass and the counters remain
     // the block's k >= 4 agents on full warps
     __syncthreads();
     {
@@ -513,7 +513,6 @@ __device__ __forceinline__ unsigned int list_reserve_n(unsigned int* counter, co
 // so the chains of all hot locations overlap; the trials themselves are spread over lanes in k_trials.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_hazard_body(const Dev& D) {
-    pdl_launch_dependents();
     pdl_wait();
     const DayCtx& cx = day_ctx(D);
     const cabm_params* __restrict__ par = D.par;
@@ -586,6 +585,7 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
         }
         if (D.foi_enabled) write_foi(D, i, loc, type, pws, denom, T, Ts);
     }
+    pdl_launch_dependents();
     edges = warp_sum(edges);
     if ((threadIdx.x & 31) == 0 && edges && D.shard_rank == 0) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges);
 }
@@ -597,7 +597,6 @@ __global__ void __launch_bounds__(TPB) k_hazard_b(const Dev* __restrict__ devs) 
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_trials_body(const Dev& D) {
     __shared__ HitQueue hq;
-    pdl_launch_dependents();
     if (threadIdx.x == 0) hq.n = 0;
     __syncthreads();
     pdl_wait();
@@ -647,6 +646,7 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
     }
     // the susceptibility gate of the block's successful trials (calculate_event_probabilities + the Person::infect bail-out,
     // Person.cpp:274-326): rare and divergent, so it runs here on whatever threads there are hits for, after the streaming loop
+    pdl_launch_dependents();
     __syncthreads();
     {
         const unsigned int nh = min(hq.n, (unsigned int) HITQ);

@@ -209,7 +209,6 @@ __device__ __forceinline__ void close_day(const Dev& D, const int tick_done, con
 __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phase, const int close) {
     __shared__ unsigned int sm[CABM_N_COUNTERS];
     __shared__ unsigned int s_last;
-    pdl_launch_dependents();
     if (threadIdx.x < CABM_N_COUNTERS) sm[threadIdx.x] = 0;
     __syncthreads();
     pdl_wait();
@@ -281,6 +280,7 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
             }
         }
     }
+    pdl_launch_dependents();
     __syncthreads();
     if (with_status) {
         if (threadIdx.x < CABM_N_COUNTERS && sm[threadIdx.x]) atomicAdd(&D.ledger[(size_t) threadIdx.x * D.R + day], (unsigned long long) sm[threadIdx.x]);
@@ -309,7 +309,6 @@ __device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, con
 // do_hosp: warps [0, n_hot_hosp) expose the staff of one hot hospital each, then all threads walk the admitted-patient
 // list; do_import: all threads walk today's importation draws (every draw is a "hit": the person is chosen, not exposed)
 __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_hosp, const int do_import) {
-    pdl_launch_dependents();
     pdl_wait();
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
@@ -369,6 +368,7 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
             gate_hit(D, 1, pid, i, CABM_P_IMPORT, 0);
         }
     }
+    pdl_launch_dependents();
     trials = warp_sum(trials);
     if (lane == 0 && trials) atomicAdd(&D.ctr->work[CABM_W_TRIALS], (unsigned long long) trials);
 }

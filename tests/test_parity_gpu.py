@@ -216,7 +216,8 @@ def test_infect_batch_equals_consecutive_calls():
     pop, P, g, o = make_pair(30000, 30, T=0.12, pde=1e-3, seed=15)
     g1 = cabm.Community(P, pop, g.T, attrs=cabm.abi.immunity_attributes(int(pop["n_people"]), P["seed"]))
     rng = np.random.default_rng(8)
-    for day in (0, 1, 9):
+    for day in (0, 1, 4):                                                  # the day each community stands at (1 + 3 steps below)
+        assert g.day == o.day == g1.day == day
         pids = rng.integers(0, 30000, size=4000).astype(np.uint32)
         pids[100:140] = pids[50:90]; pids[300:310] = pids[50:60]           # repeated people inside one batch
         strains = rng.integers(0, 4, size=pids.size).astype(np.uint8)
