@@ -238,7 +238,7 @@ def batch_record(dist, dev, rank, world):
     n = int(pop["n_people"])
     mine = cabm.replicates.replicate_slice(BATCH_REPLICATES, rank, world)
     rng = np.random.default_rng(2024)
-    Ts = rng.uniform(0.03, 0.07, size=BATCH_REPLICATES)                # exp/abc/abc_covid.json:14-18 sweeps T; wide enough here for an epidemic in 200 days
+    Ts = rng.uniform(0.023, 0.043, size=BATCH_REPLICATES)              # the prior of the ABC sweeps (exp/abc/abc_covid.json:14-18)
     comms = []
     for r in mine:
         P = cabm.params.default_params(run_length=BATCH_DAYS, seed=1 + r, T=float(Ts[r]), mutant_intro_dates=("2020-03-01", "2020-03-21", "2020-04-10"))
@@ -256,7 +256,7 @@ def batch_record(dist, dev, rank, world):
     for c in comms:
         c.close()
     days = BATCH_DAYS - 20
-    return {"workload": f"configs[4]: {BATCH_REPLICATES} communities of {n} agents (seeds 1..{BATCH_REPLICATES}, T ~ U(0.03, 0.07)), {len(mine)} per GPU, days 20-{BATCH_DAYS - 1}",
+    return {"workload": f"configs[4]: {BATCH_REPLICATES} communities of {n} agents (seeds 1..{BATCH_REPLICATES}, T ~ U(0.023, 0.043)), {len(mine)} per GPU, days 20-{BATCH_DAYS - 1}",
             "replicates": BATCH_REPLICATES, "per_gpu": len(mine), "days": days, "seconds": float(tmax[0]), "device_seconds": float(tmax[1]),
             "agent_days_per_s": BATCH_REPLICATES * n * days / float(tmax[0]), "us_per_replicate_day": float(tmax[0]) * 1e6 / (len(mine) * days),
             "infections": int(t[2]), "timing": "wall clock around cabm_batch_run_days between barriers, max over ranks"}
