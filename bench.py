@@ -186,7 +186,7 @@ def sharded_record(dist, dev, rank, world):
     import covid_abm_b200 as cabm
     import synthpop
     pop = synthpop.generate(SHARD_AGENTS)
-    n = int(pop["n_people"]); total = SHARD_WARM + 2 * SHARD_DAYS
+    n = int(pop["n_people"]); total = SHARD_WARM + SHARD_DAYS
     P = cabm.params.default_params(run_length=total, seed=1, mutant_intro_dates=MUTANTS, prob_daily_exposure=2e-4)   # exp/active-vac/main.cpp:248-249 at this scale
     T = cabm.params.build_tables(P)
     attrs = cabm.abi.immunity_attributes(n, P["seed"])
@@ -194,6 +194,7 @@ def sharded_record(dist, dev, rank, world):
     shard = cabm.sharded.Shard(P, pop, T, rank, world, cuts, attrs=attrs, device=dev)
     shard.nccl_init(dist)
     shard.run_days_nccl(SHARD_WARM)
+    snap = shard.snapshot()
     shard.device_time_ms()
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -207,11 +208,14 @@ def sharded_record(dist, dev, rank, world):
            "us_per_day": float(t[0]) * 1e6 / SHARD_DAYS, "us_per_day_device": float(t[1]) * 1e3 / SHARD_DAYS,
            "agent_days_per_s": n * SHARD_DAYS / float(t[0]), "timing": "wall clock around cabm_shard_run_days between barriers, max over ranks",
            "infections": int(led[: SHARD_WARM + SHARD_DAYS, 0].sum())}
-    shard.set_profile(True); shard.kernel_times()                      # per-kernel / per-exchange device time of rank 0, separate untimed pass
+    shard.restore(snap)                                                # per-kernel / per-exchange device time of rank 0: the same days again, untimed
+    shard.set_profile(True); shard.kernel_times()
     shard.run_days_nccl(SHARD_DAYS)
     kt = shard.kernel_times(); shard.set_profile(False)
     out["rank0_us_per_day"] = {k: round(v[0] * 1e3 / SHARD_DAYS, 2) for k, v in kt.items() if v[1]}
-    shard.close()
+    led2 = torch.from_numpy(shard.ledger_table().astype(np.int64)).to(dev); dist.all_reduce(led2)
+    out["profiled_pass_equals_timed_pass"] = bool(torch.equal(led, led2))
+    shard.snap_free(snap); shard.close()
     if rank == 0:
         single = cabm.Community(P, pop, T, attrs=attrs)
         single.run_days(SHARD_WARM); single.device_time_ms()
