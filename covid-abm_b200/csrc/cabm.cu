@@ -250,12 +250,14 @@ static int ready(cabm_t* h, int day) {
 static int check_overflow(cabm_t* h) {
     unsigned int ov = 0;
     CK(cudaMemcpy(&ov, &h->d.ctr->overflow, sizeof(ov), cudaMemcpyDeviceToHost));
+    if (ov & 0x80000000u) { h->err = "checked build: a device-side index check failed (mask " + std::to_string(ov) + ")"; return CABM_E_STATE; }
     if (ov & ~1u) { h->err = "device list capacity exceeded (mask " + std::to_string(ov) + ")"; return CABM_E_NOMEM; }
     return CABM_OK;
 }
 // after a synchronised launch sequence that closed a day (close_day): the overflow mask is already in pinned host memory (no copy)
 static int check_overflow_host(cabm_t* h) {
     const unsigned int ov = h->d.host_status[0];
+    if (ov & 0x80000000u) { h->err = "checked build: a device-side index check failed (mask " + std::to_string(ov) + ")"; return CABM_E_STATE; }
     if (ov & ~1u) { h->err = "device list capacity exceeded (mask " + std::to_string(ov) + ")"; return CABM_E_NOMEM; }
     return CABM_OK;
 }
@@ -510,6 +512,10 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
         (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||
         (rc = dalloc(h, &D.n_foi, 1))) return rc;
+#ifdef CABM_CHECKS
+    if (getenv("CABM_CHECK_SELFTEST")) D.Q = 1;      // checked build only: the device then believes there is one patronised location, so the
+                                                     // first hot visit elsewhere must trip `q < D.Q` (arrays keep their real size: nothing is out of bounds)
+#endif
     k_init_state<<<grid_for(h, std::max(N, L), 8), TPB, 0, h->stream>>>(D);
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());

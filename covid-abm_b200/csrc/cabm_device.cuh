@@ -233,6 +233,16 @@ __device__ __noinline__ double remaining_efficacy(const cabm_params* __restrict_
 
 __device__ __forceinline__ bool tl_in(short b, short e, int now) { return b <= now && now < e; }
 
+// Checked build (nvcc -DCABM_CHECKS, covid-abm_b200/csrc/libcabm_checked.so): every index the pipeline computes on the device
+// is range-checked before it is used; a violation sets bit 31 of the sticky overflow word, which fails the running call with
+// the mask in the error text. Stands in for compute-sanitizer memcheck, which is closed on this GPU pool. No code in the
+// product build.
+#ifdef CABM_CHECKS
+#define CABM_CHECK(D, cond) do { if (!(cond)) atomicOr(&(D).ctr->overflow, 0x80000000u); } while (0)
+#else
+#define CABM_CHECK(D, cond) do { } while (0)
+#endif
+
 __device__ __forceinline__ unsigned long long make_key(int pass, unsigned int src, unsigned int role) {
     return ((unsigned long long) pass << 40) | ((unsigned long long) src << 8) | (unsigned long long) (role & 0xFFu);
 }

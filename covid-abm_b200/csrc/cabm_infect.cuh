@@ -15,6 +15,7 @@ struct InfectCtx { int pid, time, source, strain, infector; bool has_source; uns
 __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const InfectCtx c, const bool commit) {
     const cabm_params* __restrict__ par = D.par;
     const int pid = c.pid, time = c.time, strain = c.strain;
+    CABM_CHECK(D, pid >= 0 && (unsigned int) pid < D.N && strain >= 0 && strain < CABM_N_STRAINS && time >= 0 && time < D.R);
     const int a = D.age[pid]; const unsigned int pf = D.pflags[pid]; const int com = (pf & PF_COMORBID) ? 1 : 0;
     const unsigned int imm = D.imm[pid];
     const int n_inf = (int) ((imm & 0xFF) + ((imm >> 8) & 0xFF) + ((imm >> 16) & 0xFF) + (imm >> 24));
@@ -86,6 +87,7 @@ __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const Infe
     int t_critical_begin = CABM_I16_MAX, t_critical_end = CABM_I16_MIN, t_icu_begin = CABM_I16_MAX, t_death = CABM_I16_MAX;
     unsigned long long tally = 1;                                    // bit o set => tallyOutcome(o)
     const int incubation = 1 + (int) table_draw(par->incub_cdf[strain], CABM_INCUB_MAX, s.u01());
+    CABM_CHECK(D, incubation >= 1 && incubation <= CABM_INCUB_MAX);
     const int onset = 1 + (int) table_draw(par->onset_cdf[incubation - 1], CABM_INCUB_MAX + 1, s.u01());
     t_infectious_begin = time + onset;
     t_infectious_end = time + incubation + par->strain_infectious_period[c.has_source ? strain : 0];

@@ -149,6 +149,7 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
     unsigned int nflag = 0, ntoday = 0;
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned int p = cur[i];
+        CABM_CHECK(D, p < D.N && p >= D.own_lo && p < D.own_hi);
         const unsigned int w = D.win[p];
         const int from = (short) (w & 0xFFFFu), until = (short) (w >> 16);
         if (until > day) {                                 // still inside its window tomorrow: stays on the list
@@ -186,6 +187,8 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
             }
         }
         if (nl == 0) continue;
+        for (int k = 0; k < nl; ++k) CABM_CHECK(D, locs[k] >= 0 && (unsigned int) locs[k] < D.L);
+        CABM_CHECK(D, t1.strain < CABM_N_STRAINS && nl <= 2 + MAXV);
         // Community::flagInfectedLocation (Community.cpp:788-791) for all places of the agent at once: the static loads, the
         // pressure REDs, the per-location slot atomics and the flag-list reservation are issued back to back (one round trip),
         // then one reservation covers the hot-list entries of every location this agent was the first to flag
@@ -331,6 +334,7 @@ __device__ __forceinline__ void visit_flush(const Dev& D, const unsigned int (*s
     for (unsigned int k = 0; k < cnt; ++k) {
         const unsigned int e = stage[k][lane];
         const unsigned int q = e & PROW_Q_MASK, p = win_t0 + (e >> 21) * tile_stride + ((e >> 19) & 3u) * 32u + lane;
+        CABM_CHECK(D, q < D.Q && p >= D.own_lo && p < D.own_hi && k < VIS_COL);
         atomicAdd(&D.nvis[q], 1u);
         if (base + k < D.cap_vis) D.visit_rec[base + k] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
     }
@@ -468,6 +472,7 @@ struct HitQueue { Hit q[HITQ]; unsigned int n; };
 // (gated in place when the queue is full); the hospital pass gates in place.
 __device__ __forceinline__ void trial(const Dev& D, const int day, const int phase, const unsigned int pid, const int src, const int purpose,
                                       const unsigned int sub, const double T, unsigned int& trials, HitQueue* hq) {
+    CABM_CHECK(D, pid < D.N && src >= 0 && (unsigned int) src < D.L);
     if (pid < D.own_lo || pid >= D.own_hi) return;                                 // the owner of an agent draws its exposures
     if (D.any_quarantine) {
         const unsigned int q = D.quar[pid]; const int qf = (short) (q & 0xFFFF), qu = (short) (q >> 16);
@@ -520,6 +525,7 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
     unsigned int edges = 0;
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_hot; i += gridDim.x * blockDim.x) {
         const int loc = D.hot_list[i];
+        CABM_CHECK(D, loc >= 0 && (unsigned int) loc < D.L && D.loc_hot[loc] == (int) i);
         // everything that depends on `loc` only is loaded in one go (one round trip)
         const int type = D.loc_type[loc];
         const unsigned int cnt = D.loc_cnt[loc];
@@ -563,6 +569,7 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
         unsigned int seg, sbase, ibase;
         list_reserve3(&D.ctr->n_seg, cnt, &D.ctr->n_sitems, n_small, &D.ctr->n_items, n_big, seg, sbase, ibase);
         D.hot_off[i] = seg;
+        CABM_CHECK(D, cnt >= 1 && (unsigned long long) seg + cnt <= D.cap_flags && (q < 0 || (unsigned int) q < D.Q));
         if (type == CABM_HOSPITAL) continue;
         D.hot_T[2 * i] = T;
         if (type == CABM_HOUSE) D.hot_T[2 * i + 1] = Ts;
@@ -616,11 +623,14 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
                 unsigned int cnt = it.count_purpose >> 8; int begin = it.begin;
                 const int purpose = (int) (it.count_purpose & 0xFFu);
                 if (purpose == CABM_P_EXPOSE_NB) {                   // a neighbour household: its roster, unless it keeps its distance today
+                    CABM_CHECK(D, begin >= 0 && (unsigned int) begin < D.nbr_off[D.L]);
                     const int nb = D.nbr[begin];
+                    CABM_CHECK(D, nb >= 0 && (unsigned int) nb < D.L);
                     const unsigned int b = D.roster_off[nb], e = D.roster_off[nb + 1];
                     cnt = (double) D.loc_risk[nb] > cx.sd ? e - b : 0u; begin = (int) b;
                 }
                 if (cnt) {
+                    CABM_CHECK(D, it.t_idx < 2u * D.cap_hot && (unsigned int) begin + cnt <= D.roster_off[D.L] && (unsigned int) it.src < D.L);
                     const double T = D.hot_T[it.t_idx];
                     for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[begin + m], it.src, purpose, 0, T, trials, &hq);
                 }
@@ -629,16 +639,20 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
             const unsigned int f = (u - u_vis) * TPB + threadIdx.x;
             if (f < n_flags) {
                 const FlagRaw r = D.flags_raw[f];
+                CABM_CHECK(D, r.loc >= 0 && (unsigned int) r.loc < D.L && r.pid < D.N && (unsigned int) D.loc_hot[r.loc] < min(D.ctr->n_hot, D.cap_hot) &&
+                              r.slot < D.loc_cnt[r.loc] && (unsigned long long) D.hot_off[D.loc_hot[r.loc]] + r.slot < D.cap_flags);
                 Flag o; o.pid = r.pid; o.pad = 0; o.c = r.c;
                 D.flags[D.hot_off[D.loc_hot[r.loc]] + r.slot] = o;
             }
         } else if (u < n_items) {
             const Item it = D.items[u];
+            CABM_CHECK(D, it.count >= 1 && it.count <= CHUNK && (unsigned int) it.begin + (unsigned int) it.count <= D.roster_off[D.L] && (unsigned int) it.src < D.L);
             if ((int) threadIdx.x < it.count) trial(D, day, 0, (unsigned int) D.roster[it.begin + threadIdx.x], it.src, it.purpose, 0, it.T, trials, &hq);
         } else {
             const unsigned int v = (u - n_items) * TPB + threadIdx.x;
             if (v < n_vis) {
                 const uint2 rec = D.visit_rec[v];
+                CABM_CHECK(D, rec.x < D.N && rec.y < D.Q);
                 const double T = D.pub_T[rec.y];
                 if (T > 0.0) trial(D, day, 0, rec.x, D.pub_loc[rec.y], CABM_P_EXPOSE_WORK_VIS, 0, T, trials, &hq);
             }

@@ -237,6 +237,7 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
             unsigned int seg_n = 0, seg_off = 0; bool longseg = false;
             if (have) {
                 pid = D.newinf_list[nbase + wi];
+                CABM_CHECK(D, pid < D.N && D.cand[pid] != CABM_CAND_EMPTY);
                 const unsigned long long key = D.cand[pid];
                 const int pass = (int) (key >> 40); const unsigned int src = (unsigned int) (key >> 8); const unsigned int role = (unsigned int) (key & 0xFF);
                 unsigned int purpose = (unsigned int) pass, sub = 0;
@@ -244,7 +245,9 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
                 else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
                 event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);
                 if (c.has_source) {
+                    CABM_CHECK(D, src < D.L && D.loc_cnt[src] >= 1 && (unsigned int) D.loc_hot[src] < min(D.ctr->n_hot, D.cap_hot));
                     seg_n = D.loc_cnt[src]; seg_off = D.hot_off[D.loc_hot[src]];
+                    CABM_CHECK(D, (unsigned long long) seg_off + seg_n <= D.cap_flags);
                     if (seg_n <= INFECTOR_THREAD_MAX) c.infector = pick_infector_thread(D.flags + seg_off, seg_n, c.strain, t_res);
                     else longseg = true;
                 }
@@ -268,6 +271,7 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
             const unsigned int i = (u - n_wu) * 32 + lane;
             if (i < n_a) {
                 const unsigned int p = alist[i];
+                CABM_CHECK(D, p < D.N);
                 if (D.cand[p] == CABM_CAND_EMPTY) m = status_one(D, p, day);
             }
         }
@@ -341,7 +345,9 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
         const unsigned int nh = min(D.ctr->n_hot_hosp, D.cap_hot);
         for (unsigned int j = warp; j < nh; j += n_warps) {
             const unsigned int i = (unsigned int) D.hot_hosp[j];                        // index of the hospital in the hot list
+            CABM_CHECK(D, i < min(D.ctr->n_hot, D.cap_hot));
             const int hosp = D.hot_list[i];
+            CABM_CHECK(D, hosp >= 0 && (unsigned int) hosp < D.L && D.loc_type[hosp] == CABM_HOSPITAL);
             unsigned int denom; unsigned long long pws[4];
             const double T = hospital_T(D, cx, hosp, &denom, pws);
             const unsigned int rb = D.roster_off[hosp], size = D.roster_off[hosp + 1] - rb;
@@ -351,6 +357,7 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
         const unsigned int np = min(D.ctr->n_pat, D.cap_pat);
         for (unsigned int i = tid; i < np; i += nth) {
             const unsigned int pid = D.patient_list[i];
+            CABM_CHECK(D, pid < D.N);
             const unsigned int c = D.hosp_count[pid];
             if (c == 0) continue;
             const int hosp = D.loc_hospital[D.home[pid]];
