@@ -55,11 +55,11 @@ BYTES = dict(agents=0, active=40, flags=12, patrons=16.6, visits=4, hot_visits=2
 # kernels of the day pipeline and the byte-model terms each one moves (DESIGN.md "kernels and byte model"); the gate and the
 # two apply launches share the per-infection term
 KERNEL_GROUPS = [
-    ("k_active", ("k_active",), ("active", "flags")),
+    ("k_scan+k_active", ("k_scan", "k_active"), ("active", "flags")),
     ("k_visit", ("k_visit",), ("patrons", "visits", "hot_visits")),
     ("k_hazard", ("k_hazard",), ("hot_locs", "nbr_edges")),
     ("k_trials+k_hosp_import", ("k_trials", "k_hosp_import"), ("trials",)),
-    ("k_apply_status", ("k_apply_status", "k_apply(phase1)"), ("infections",)),
+    ("k_gate+k_apply_status", ("k_gate", "k_apply_status", "k_apply(phase1)"), ("infections",)),
 ]
 
 

@@ -48,7 +48,7 @@ struct cabm {
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     double acc_ms = 0.0; uint64_t launches = 0;
     int device = 0, sms = 148;
-    int gm[9] = { 8, 8, 6, 4, 8, 2, 2, 2, 4 };   // blocks per SM: active, hazard, trials, (unused), apply+status, hosp+import, (unused), apply1, (unused) (CABM_GRID_MULT overrides: development knob)
+    int gm[9] = { 8, 8, 8, 4, 8, 2, 2, 2, 4 };   // blocks per SM: active, hazard, trials, gate, apply+status, hosp+import, (unused), apply1, (unused) (CABM_GRID_MULT overrides: development knob)
     int pdl = 0;                                 // programmatic dependent launch, one bit per kernel of the day (bit k: kernel k may start before its predecessor
                                                  // has drained): CABM_PDL=<mask>. Measured at 2.7 M agents, graph replay: every edge on 151 us per day, none 141.
     int visit_bps = 2;                           // resident k_visit blocks per SM (from the occupancy calculator, given the hot bitmap's size)
@@ -65,7 +65,7 @@ struct cabm {
     cudaGraphExec_t day_graph = nullptr, tick_graph = nullptr, import_graph = nullptr;   // run_days (tick + importation), cabm_tick, cabm_import
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
-    uint64_t launches_per_day = 7, launches_tick = 7, launches_import = 2;
+    uint64_t launches_per_day = 9, launches_tick = 9, launches_import = 2;
     unsigned int bitmap_words = 1; unsigned int* d_out_new = nullptr; DayCtx* d_today = nullptr; unsigned long long* d_diag = nullptr; unsigned int* d_det = nullptr;
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
     Dev* d_batch = nullptr; size_t batch_cap = 0; cudaGraphExec_t batch_graph = nullptr; size_t batch_graph_n = 0;   // cabm_batch_run_days: the communities of the batch, indexed by blockIdx.y
@@ -169,7 +169,7 @@ static void fill_ctx(const cabm_t* h, DayCtx& c, int day, int julian_day, int is
 // kernel ids for per-kernel timing (cabm_kernel_times)
 enum { KID_SCAN = 0, KID_ACTIVE, KID_VISIT, KID_HAZARD, KID_TRIALS, KID_GATE0, KID_APPLY_STATUS, KID_HOSP_IMPORT, KID_GATE1, KID_APPLY1,
        KID_END, KID_SMALL, KID_XA, KID_XB, KID_XC, KID_N };
-static const char* const KID_NAMES[KID_N] = { "(unused)", "k_active", "k_visit", "k_hazard", "k_trials", "(unused)", "k_apply_status",
+static const char* const KID_NAMES[KID_N] = { "k_scan", "k_active", "k_visit", "k_hazard", "k_trials", "k_gate", "k_apply_status",
     "k_hosp_import", "(unused)", "k_apply(phase1)", "(unused)", "(unused)", "exchange A (flags)", "exchange B (census)", "exchange C (patients)" };
 
 // LAUNCH records an event in front of every kernel when per-kernel profiling is on (stream path only, never under graph capture)
@@ -203,20 +203,27 @@ static void launch_k(cabm_t* h, int edge, void (*kern)(KArgs...), dim3 grid, dim
 // The launch sequence of one day. tick = Community::tick (Community.cpp:1147-1192), import = the daily
 // seed_epidemic (simulator.h:201-223). With both set the importation draws share the hospital pass's gate/apply
 // launches: an agent hit by both keeps the hospital exposure (lower order key), exactly what running
-// seed_epidemic after tick() yields. Seven launches for tick + importation, two for an importation alone.
+// seed_epidemic after tick() yields. Nine launches for tick + importation, two for an importation alone.
 // one wave of resident blocks: more, smaller blocks were measured slower (every block ends in a latency-bound tail)
 static unsigned int visit_grid(const cabm_t* h, const Dev& D) {
     const unsigned int tiles = (D.own_hi - (D.own_lo & ~(VIS_TILE - 1u)) + VIS_TILE - 1) / VIS_TILE;
     return std::max(1u, std::min<unsigned int>((tiles + VIS_WARPS - 1) / VIS_WARPS, (unsigned int) (h->sms * h->visit_bps)));
 }
+// k_scan: one thread per 128 agents (four bitmap words) of the owned range
+static unsigned int scan_grid(const Dev& D) {
+    const unsigned int w_lo = (D.own_lo >> 5) & ~3u, w_hi = (D.own_hi + 31u) >> 5;
+    return std::max(1u, (w_hi - w_lo + TPB * 4 - 1) / (TPB * 4));
+}
 static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     const Dev& D = h->d;
     const unsigned int gSM = h->sms;
     if (tick) {
+        LAUNCH(KID_SCAN, launch_k(h, 8, k_scan, dim3(scan_grid(D)), dim3(TPB), 0, D));
         LAUNCH(KID_ACTIVE, launch_k(h, 0, k_active, dim3(gSM * h->gm[0]), dim3(TPB), 0, D));
         LAUNCH(KID_VISIT, launch_k(h, 1, k_visit, dim3(visit_grid(h, D)), dim3(TPB), visit_smem_bytes(h->bitmap_words), D, h->bitmap_words));
         LAUNCH(KID_HAZARD, launch_k(h, 2, k_hazard, dim3(gSM * h->gm[1]), dim3(TPB), 0, D));
         LAUNCH(KID_TRIALS, launch_k(h, 3, k_trials, dim3(gSM * h->gm[2]), dim3(TPB), 0, D));
+        LAUNCH(KID_GATE0, launch_k(h, 7, k_gate, dim3(gSM * h->gm[3]), dim3(128), 0, D));
         LAUNCH(KID_APPLY_STATUS, launch_k(h, 4, k_apply_status, dim3(gSM * h->gm[4]), dim3(128), 0, D, 0, 0));
     }
     LAUNCH(KID_HOSP_IMPORT, launch_k(h, 5, k_hosp_import, dim3(gSM * h->gm[5]), dim3(TPB), 0, D, tick ? 1 : 0, import ? 1 : 0));
@@ -493,23 +500,23 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     }
     // ---- dynamic state ----
     const size_t Q1 = std::max<size_t>(D.Q, 1);
-    if ((rc = dalloc(h, &D.win, (size_t) N + 4, true)) || (rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
+    if ((rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
         (rc = dalloc(h, &D.imm, N, true)) || (rc = dalloc(h, &D.vax, N, true)) || (rc = dalloc(h, &D.vax_days, (size_t) N * CABM_MAX_DOSES, true)) ||
         (rc = dalloc(h, &D.quar, N, true)) || (rc = dalloc(h, &D.hosp_count, N, true)) || (rc = dalloc(h, &D.pbyte, N, true)) ||
         (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.inf_place, N, true, 0xFF)) || (rc = dalloc(h, &D.inf_by, N, true, 0xFF)) ||
         (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.loc_cnt, L)) || (rc = dalloc(h, &D.loc_hot, L)) || (rc = dalloc(h, &D.pat_count, L, true)) ||
         (rc = dalloc(h, &D.nvis, Q1)) || (rc = dalloc(h, &D.pub_T, Q1)) || (rc = dalloc(h, &D.pub_hot, ((size_t) h->bitmap_words + 3) & ~(size_t) 3)) ||
-        (rc = dalloc(h, &D.inhosp, n_rows / 32 + 4, true)) || (rc = dalloc(h, &D.act[0], (size_t) N, true)) || (rc = dalloc(h, &D.act[1], (size_t) N, true))) return rc;
+        (rc = dalloc(h, &D.inhosp, n_rows / 32 + 4, true)) || (rc = dalloc(h, &D.actbits, ((size_t) N + 1023) / 1024 * 32, true)) || (rc = dalloc(h, &D.active_list, (size_t) N))) return rc;
     CK(cudaMemcpyAsync(D.pbyte, pbyte.data(), N, cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----
-    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
+    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
     D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + roster.size() / SMALL_ROSTER + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
     if (const char* e = getenv("CABM_LOG_CAP")) D.cap_log = std::max<unsigned long long>(1, strtoull(e, nullptr, 10));   // test knob: force the log-overflow error
     D.cap_sitems = (unsigned int) std::min<size_t>(0x7FFFFFFF, (size_t) L + nbr.size() + 1024);
     if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, (size_t) 2 * D.cap_hot)) || (rc = dalloc(h, &D.sitems, D.cap_sitems)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
         (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
-        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
+        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
         (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||
         (rc = dalloc(h, &D.n_foi, 1))) return rc;
 #ifdef CABM_CHECKS
@@ -684,10 +691,12 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
     auto gx = [&](int k) { return std::max(2u, gSM * (unsigned int) h->gm[k] / R); };             // the SMs are shared by the batch
     const dim3 gVisit(std::min<unsigned int>(visit_grid(h, D), std::max(2u, gSM * (unsigned int) h->visit_bps / R)), R);
     auto one_day = [&]() {
+        launch_k(h, 8, k_scan_b, dim3(scan_grid(D), R), dim3(TPB), 0, B);
         launch_k(h, 0, k_active_b, dim3(gx(0), R), dim3(TPB), 0, B);
         launch_k(h, 1, k_visit_b, gVisit, dim3(TPB), visit_smem_bytes(h->bitmap_words), B, h->bitmap_words);
         launch_k(h, 2, k_hazard_b, dim3(gx(1), R), dim3(TPB), 0, B);
         launch_k(h, 3, k_trials_b, dim3(gx(2), R), dim3(TPB), 0, B);
+        launch_k(h, 7, k_gate_b, dim3(gx(3), R), dim3(128), 0, B);
         launch_k(h, 4, k_apply_status_b, dim3(gx(4), R), dim3(128), 0, B, 0, 0);
         launch_k(h, 5, k_hosp_import_b, dim3(gx(5), R), dim3(TPB), 0, B, 1, 1);
         launch_k(h, 6, k_apply_status_b, dim3(gx(7), R), dim3(128), 0, B, 1, 3);
@@ -703,7 +712,7 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
         h->batch_graph_n = n;
     }
     CK(cudaEventRecord(h->e0, st));
-    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->batch_graph, st)); h->launches += 7; }
+    for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->batch_graph, st)); h->launches += 9; }
     if ((rc = timed_sync(h))) return rc;
     for (size_t r = 0; r < n; ++r) if ((rc = check_overflow(hs[r]))) { if (hs[r] != h) h->err = hs[r]->err; return rc; }
     return CABM_OK;
@@ -820,9 +829,10 @@ int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is
     if (part == 0) {
         CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, st));
         CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), st));
+        k_scan<<<scan_grid(D), TPB, 0, st>>>(D);
         k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D);
         CK(cudaMemcpyAsync(&h->n_flags_own, &D.ctr->n_flags, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
-        h->launches += 1;
+        h->launches += 2;
     } else if (part == 1) {
         k_visit<<<visit_grid(h, D), TPB, visit_smem_bytes(h->bitmap_words), st>>>(D, h->bitmap_words);
         h->launches += 1;
@@ -830,9 +840,10 @@ int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is
         if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
         k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D);
         k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D);
+        k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D);
         k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 0);
         if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 1);
-        h->launches += 5;
+        h->launches += 6;
     } else {
         c.n_imports = (strain_w && expected_imports > 0) ? import_count(h->hpar.seed, sim_day, expected_imports) : 0;
         if (strain_w) for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
@@ -974,6 +985,7 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
         CK(cudaMemsetAsync(h->d_xcounts + CABM_MAX_SHARDS, 0, sizeof(unsigned int), st));
         CK(cudaEventRecord(h->e0, st));
         for (int i = g0; i < std::min(n_days, g0 + group); ++i) {
+            PM(KID_SCAN); k_scan<<<scan_grid(D), TPB, 0, st>>>(D);
             PM(KID_ACTIVE); k_active<<<gSM * h->gm[0], TPB, 0, st>>>(D);
             // exchange A: counts, then the front `cap` records of every handle's flag list
             PM(KID_XA);
@@ -988,6 +1000,7 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
             if (h->n_hosp) k_patients<<<1, 256, 0, st>>>(D, h->d_hosp_ids, h->n_hosp, h->d_pat_save, h->d_pat_buf, 0);
             PM(KID_HAZARD); k_hazard<<<gSM * h->gm[1], TPB, 0, st>>>(D);
             PM(KID_TRIALS); k_trials<<<gSM * h->gm[2], TPB, 0, st>>>(D);
+            PM(KID_GATE0); k_gate<<<gSM * h->gm[3], 128, 0, st>>>(D);
             PM(KID_APPLY_STATUS); k_apply_status<<<gSM * h->gm[4], 128, 0, st>>>(D, 0, 0);
             if (h->n_hosp) {
                 PM(KID_XC);
@@ -997,7 +1010,7 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
             }
             PM(KID_HOSP_IMPORT); k_hosp_import<<<gSM * h->gm[5], TPB, 0, st>>>(D, 1, 1);
             PM(KID_APPLY1); k_apply_status<<<gSM * h->gm[7], 128, 0, st>>>(D, 1, 3);
-            h->launches += 11;
+            h->launches += 13;
         }
         PM(-1);
         CK(cudaMemcpyAsync(h->h_xcounts, h->d_xcounts + CABM_MAX_SHARDS, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));

@@ -2,10 +2,10 @@
 // per-exposure state-transition sampler (Person::infect, Person.cpp:320-494) for sm_100a.
 //
 // Layout (all structure-of-arrays in HBM, one element per agent / location):
-//   agents   : win (active window), tl0/tl1 (latest Infection, 2 x 16 B), imm (infections per strain),
+//   agents   : tl0/tl1 (latest Infection, 2 x 16 B), imm (infections per strain),
 //              vax (doses, last dose day, naive flag), quar, hosp_count, pbyte (patron count | flags),
 //              cand (64-bit winner key of today's exposure resolution), prow (20-byte packed patron row),
-//              inhosp (one bit per agent: in hospital today), act[2] (the persistent list of agents inside an infection window)
+//              inhosp (one bit per agent: in hospital today), actbits (one bit per agent: inside an infection window)
 //   locations: press[4] (u64 fixed-point infectious pressure by strain, 2^-32 units), hot_idx, nvis,
 //              pat_count + static type/flags/risk/hospital, roster CSR, neighbour CSR
 // Day-scoped lists (hot locations, active agents, visits landing on hot locations, exposure work
@@ -50,21 +50,17 @@ struct DayCtx {                     // per-day scalars, staged by the host for e
 // counters living in device memory
 struct Counters {
     // ---- day-scoped: zeroed by the block that closes the day (k_apply_status, phase 1) ----
-    unsigned int n_today, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;   // n_today: list entries inside their window today
+    unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;  // n_active: agents inside an infection window today (length of active_list)
     unsigned int n_new[2];                                   // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
-    unsigned int day_pad[6];
+    unsigned int n_hits;                                     // successful trials of the house..nursing-home passes waiting for the gate (k_gate)
+    unsigned int day_pad[5];
     // ---- persistent ----
     unsigned int n_pat;                                      // admitted-patient list length (entries are never removed, see k_status)
     unsigned int overflow;                                   // sticky: a list ran out of capacity
     unsigned int day_idx;                                    // index into the staged DayCtx array
     unsigned int seed_calls;
     unsigned int end_ticket;                                 // blocks of the closing kernel that have finished (the last one closes the day)
-    // The persistent active list (replaces a daily scan over all agents). act[act_sel] is the list the day's k_active reads;
-    // it copies the entries that are still inside their window tomorrow to act[act_sel ^ 1], and every infection committed
-    // from then on appends there unless the agent is already on it (old window end >= list_day, the day that list is for).
-    // Closing the day swaps the lists. in_tick: k_active of the current day has run (appends go to act[act_sel ^ 1]).
-    unsigned int act_sel, in_tick; int list_day; unsigned int n_act[2];
-    unsigned int pad2;
+    unsigned int pad2[5];
     unsigned long long n_log;
     unsigned long long work[CABM_N_WORK];
     unsigned long long cumul[CABM_N_OUTCOMES];
@@ -85,17 +81,23 @@ struct Dev {
     const int* loc_pub;                  // location -> index among patronised ("public") locations, or -1
     const int* pub_loc;                  // [Q] inverse
     // dynamic agents
-    unsigned int* win; Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
+    Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
     unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand; int* inf_place; int* inf_by; unsigned int* n_caused;
     unsigned int* inhosp;                // [ceil(N / 128) * 4] one bit per agent: in hospital today (k_active keeps it, k_visit reads it)
-    unsigned int* act[2];                // persistent active list, double-buffered (see Counters)
+    // The active set: one bit per agent, set when an infection is committed (infect_event), cleared by k_active on the last day
+    // of the agent's activity window. k_active scans it every day (N / 8 bytes: 0.34 MB at 2.7 M agents, 2.7 MB at 21.5 M, i.e.
+    // L2-resident; the per-agent window words a scan used to read were 32 times that) and so meets the active agents in id
+    // order: their state gathers walk memory in one direction. (A persistent list kept in infection order made every gather of
+    // k_active and of the status pass random over a multi-GB footprint: +130 and +107 us per day at 21.5 M agents.)
+    unsigned int* actbits;               // [ceil(N / 1024) * 32]
+    unsigned int* active_list;           // today's active agents, written by k_active in chunks of ascending ids, read by the status pass
     // dynamic locations
     unsigned long long* press; unsigned int* loc_cnt; int* loc_hot; unsigned int* pat_count;   // loc_cnt: flags today (0 = not hot), loc_hot: index in hot_list
     unsigned int* nvis; double* pub_T; unsigned int* pub_hot;     // [Q], [Q], [ceil(Q/32)] public-location visitor census, T, hot bitmap
     // day lists
     int* hot_list; int* hot_hosp; unsigned int* hot_off; double* hot_T; FlagRaw* flags_raw; Flag* flags; SItem* sitems;
-    uint2* visit_rec; Item* items; unsigned int* newinf_list; unsigned int* patient_list;
-    unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_sitems, cap_new, cap_pat; unsigned long long cap_log;
+    uint2* visit_rec; Item* items; Hit* hits; unsigned int* newinf_list; unsigned int* patient_list;
+    unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_sitems, cap_hits, cap_new, cap_pat; unsigned long long cap_log;
     // outputs
     unsigned long long* ledger;          // [CABM_N_COUNTERS][R]
     cabm_infection* log; cabm_foi_row* foi; unsigned int* n_foi; int foi_enabled;
@@ -169,8 +171,11 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        const unsigned long long m0 = (unsigned long long) c.x * 0xD2511F53ull, m1 = (unsigned long long) c.z * 0xCD9E8D57ull;   // one IMAD.WIDE each
-        c = make_uint4((unsigned int) (m1 >> 32) ^ c.y ^ k.x, (unsigned int) m1, (unsigned int) (m0 >> 32) ^ c.w ^ k.y, (unsigned int) m0);
+        // separate high and low products: written as one 64-bit multiply the trial kernel ran 45 % slower (64.5 vs 44.4 us per day
+        // at 2.7 M agents, day 250)
+        const unsigned int hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const unsigned int hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
         k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
     }
     return c;
@@ -232,6 +237,14 @@ __device__ __noinline__ double remaining_efficacy(const cabm_params* __restrict_
 }
 
 __device__ __forceinline__ bool tl_in(short b, short e, int now) { return b <= now && now < e; }
+// last day on which an agent with this infection record needs per-day work (running infection, pending report): the agent's
+// activity window is [infected, tl_until]; win[] holds the same two numbers (written by infect_event)
+__device__ __forceinline__ int tl_until(const Tl0& t0, const Tl1& t1) {
+    int until = max(max((int) t0.infectious_end, (int) t0.symptom_end), max((int) t0.severe_end, (int) t1.critical_end));
+    if (t1.death != CABM_I16_MAX) until = max(until, (int) t1.death);
+    if (t1.report_day != CABM_I16_MAX) until = max(until, (int) t1.report_day);
+    return min(until, CABM_I16_MAX - 1);
+}
 
 // Checked build (nvcc -DCABM_CHECKS, covid-abm_b200/csrc/libcabm_checked.so): every index the pipeline computes on the device
 // is range-checked before it is used; a violation sets bit 31 of the sticky overflow word, which fails the running call with

@@ -185,20 +185,9 @@ __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const Infe
     n1.rel_inf = rel_inf;
     D.tl0[pid] = n0; D.tl1[pid] = n1;
     D.inf_place[pid] = c.has_source ? c.source : -1; D.inf_by[pid] = c.infector;
-    int until = max(max(t_infectious_end, t_symptom_end), max(t_severe_end, t_critical_end));
-    if (t_death != CABM_I16_MAX) until = max(until, t_death);
-    if (report_day != CABM_I16_MAX) until = max(until, report_day);
-    until = min(until, CABM_I16_MAX - 1);
-    {   // persistent active list (Counters): the agent joins the list the next k_active reads unless its previous window already put it there
-        const int old_until = (short) (D.win[pid] >> 16);
-        D.win[pid] = ((unsigned int) (unsigned short) (short) time) | ((unsigned int) (unsigned short) (short) until << 16);
-        Counters* ctr = D.ctr;
-        if (old_until < ctr->list_day) {
-            const unsigned int tgt = ctr->act_sel ^ ctr->in_tick;
-            const unsigned int ai = atomicAdd(&ctr->n_act[tgt], 1u);
-            if (ai < D.cap_active) D.act[tgt][ai] = (unsigned int) pid; else atomicOr(&ctr->overflow, 4u);
-        }
-    }
+    const int until = tl_until(n0, n1);
+    (void) until;
+    atomicOr(&D.actbits[(unsigned int) pid >> 5], 1u << (pid & 31));      // joins the active set (k_active takes it out after day tl_until)
     const unsigned int cnt = (imm >> (8 * strain)) & 0xFF;
     if (cnt < 255) D.imm[pid] = imm + (1u << (8 * strain));
     if (par->retroactive_mature_vaccine && n_doses > 0) D.vax[pid] = vax & ~0x100u;

@@ -1,9 +1,9 @@
 // covid-abm_b200/csrc/cabm_kernels.cuh -- first half of the day pipeline (sm_100a): who is infectious where,
 // public activity, per-location hazard, exposure trials.
 //
-//   k_active   active agents   : walks the PERSISTENT list of agents inside an infection window (no daily scan over all
-//                                agents: an agent joins the list when an infection is committed, k_active drops it when the
-//                                window has passed). Person.cpp:475-486 derived from the stored timeline instead of the
+//   k_scan     active bitmap   : one bit per agent (set when an infection is committed, cleared on the last day of its window;
+//                                N / 8 bytes, L2-resident) -> today's active agents as a list in id order
+//   k_active   active agents   : one thread per list entry. Person.cpp:475-486 derived from the stored timeline instead of the
 //                                reference's _isHot calendar: pressure at home / day location / hospital / visited locations
 //                                (Community.cpp:1031-1035), per-location flag chains, hot lists, in-hospital bit
 //   k_visit    all agents      : public_activity (Community.cpp:1006-1039): the 16-byte patron rows of a warp's tile arrive in
@@ -15,9 +15,8 @@
 //                                neighbour households (resolved by k_trials), 256-member chunks of big rosters
 //   k_trials   items + visits  : _transmission's `U < T` (Community.cpp:976) for rosters and visitors; also scatters
 //                                the day's flag records into one contiguous segment per hot location. Successful trials
-//                                are queued per block and pass the susceptibility gate at the end of the block
-//                                (gate_hit, cabm_kernels2.cuh), so the streaming loop stays convergent and no separate
-//                                gate launch is needed
+//                                go to the hit list; the susceptibility gate runs in k_gate (cabm_kernels2.cuh), so this
+//                                streaming kernel stays at 32 registers
 //
 // All kernels read their sizes from device-resident counters, so a whole day is one CUDA-graph replay; every kernel
 // releases its successor at once (programmatic dependent launch) and waits for its predecessor before the first dependent
@@ -135,31 +134,76 @@ __device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsign
 // ---------------------------------------------------------------------------------------------
 // k_active: one thread per active agent.
 // ---------------------------------------------------------------------------------------------
+// ---------------------------------------------------------------------------------------------
+// k_scan: the active bitmap -> today's list of active agents in ascending id order (a block's run is contiguous, blocks append
+// in any order). 128 agents (one uint4 of the bitmap) per thread; blocks without an active agent return after one
+// __syncthreads_or. Also publishes today's DayCtx for the rest of the pipeline.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void k_scan_body(const Dev& D) {
+    __shared__ unsigned int s_warp[TPB / 32], s_base;
+    pdl_wait();
+    Counters* const ctr = D.ctr;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *D.today = D.dayctx[ctr->day_idx];
+        atomicAdd(&ctr->work[CABM_W_AGENTS], (unsigned long long) (D.own_hi - D.own_lo));
+    }
+    const unsigned int w_lo = (D.own_lo >> 5) & ~3u, w_hi = (D.own_hi + 31u) >> 5;       // bitmap words that hold owned agents (from a uint4 boundary)
+    const unsigned int wb = w_lo + (blockIdx.x * TPB + threadIdx.x) * 4u;
+    unsigned int w[4] = { 0u, 0u, 0u, 0u };
+    if (wb < w_hi) { const uint4 v = *reinterpret_cast<const uint4*>(D.actbits + wb); w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
+    unsigned int cnt = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {                                                       // agents of other handles are not this handle's to walk
+        const unsigned int a0 = (wb + k) * 32u;
+        if (a0 < D.own_lo) w[k] &= (D.own_lo - a0 >= 32u) ? 0u : (0xFFFFFFFFu << (D.own_lo - a0));
+        if (a0 + 32u > D.own_hi) w[k] &= (a0 >= D.own_hi) ? 0u : (0xFFFFFFFFu >> (a0 + 32u - D.own_hi));
+        cnt += __popc(w[k]);
+    }
+    pdl_launch_dependents();
+    if (__syncthreads_or((int) cnt) == 0) return;
+    const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
+    if (lane == 31) s_warp[wid] = incl;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int acc = 0;
+#pragma unroll
+        for (int k = 0; k < TPB / 32; ++k) { const unsigned int c = s_warp[k]; s_warp[k] = acc; acc += c; }
+        s_base = atomicAdd(&ctr->n_active, acc);
+    }
+    __syncthreads();
+    unsigned int o = s_base + s_warp[wid] + incl - cnt;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        for (unsigned int m = w[k]; m; m &= m - 1u, ++o) {
+            if (o < D.cap_active) D.active_list[o] = (wb + k) * 32u + (unsigned int) __ffs(m) - 1u; else atomicOr(&ctr->overflow, 4u);
+        }
+}
+__global__ void __launch_bounds__(TPB) k_scan(const Dev D) { k_scan_body(D); }
+__global__ void __launch_bounds__(TPB) k_scan_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_scan_body(D); }   // one launch, replicate = blockIdx.y
+
+// ---------------------------------------------------------------------------------------------
+// k_active: one thread per active agent, in the id order k_scan left them in.
+// ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_active_body(const Dev& D) {
     pdl_wait();
     Counters* const ctr = D.ctr;
-    const DayCtx& cx = D.dayctx[ctr->day_idx]; const int day = cx.day;
-    const unsigned int sel = ctr->act_sel;
-    const unsigned int n = min(ctr->n_act[sel], D.cap_active);
-    const unsigned int* __restrict__ cur = D.act[sel]; unsigned int* __restrict__ nxt = D.act[sel ^ 1];
-    if (blockIdx.x == 0 && threadIdx.x == 0) {           // publish the day for the rest of the pipeline; infections committed from here on join the next list
-        *D.today = cx; ctr->in_tick = 1u; ctr->list_day = day + 1;
-        atomicAdd(&ctr->work[CABM_W_AGENTS], (unsigned long long) (D.own_hi - D.own_lo));
-    }
+    const DayCtx& cx = day_ctx(D); const int day = cx.day;
+    const unsigned int n = min(ctr->n_active, D.cap_active);
     unsigned int nflag = 0, ntoday = 0;
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const unsigned int p = cur[i];
+        const unsigned int p = D.active_list[i];
         CABM_CHECK(D, p < D.N && p >= D.own_lo && p < D.own_hi);
-        const unsigned int w = D.win[p];
-        const int from = (short) (w & 0xFFFFu), until = (short) (w >> 16);
-        if (until > day) {                                 // still inside its window tomorrow: stays on the list
-            const unsigned int o = list_reserve(&ctr->n_act[sel ^ 1]);
-            if (o < D.cap_active) nxt[o] = p; else atomicOr(&ctr->overflow, 4u);
-        }
-        if (day < from || day > until) continue;
-        ntoday++;
+        // everything of the agent is requested at once; its activity window is a function of the timeline (tl_until)
         const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
         const unsigned char pb = D.pbyte[p];
+        const int from = t0.infected, until = tl_until(t0, t1);
+        CABM_CHECK(D, from <= day && day <= until && D.imm[p] != 0);                       // a set bit means: inside the window today
+        if (until <= day) atomicAnd(&D.actbits[p >> 5], ~(1u << (p & 31)));                 // last day of the window: out of the set from tomorrow on
+        if (day < from || day > until) continue;                                            // (days were skipped by the caller: nothing to do any more)
+        ntoday++;
         const int hm = D.home[p], dl = D.day_loc[p];
         const PRow row = prow_load(D.prow, p);                                     // the patron row, in flight with the rest of the agent's state
         const bool inhosp = tl_in(t0.hosp_begin, t0.severe_end, day);
@@ -225,7 +269,7 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
     nflag = warp_sum(nflag); ntoday = warp_sum(ntoday);
     if ((threadIdx.x & 31) == 0) {
         if (nflag) atomicAdd(&ctr->work[CABM_W_FLAGS], (unsigned long long) nflag);
-        if (ntoday) { atomicAdd(&ctr->work[CABM_W_ACTIVE], (unsigned long long) ntoday); atomicAdd(&ctr->n_today, ntoday); }
+        if (ntoday) atomicAdd(&ctr->work[CABM_W_ACTIVE], (unsigned long long) ntoday);
     }
 }
 __global__ void __launch_bounds__(TPB) k_active(const Dev D) { k_active_body(D); }
@@ -319,24 +363,30 @@ __device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_h
     }
 }
 
-// flush a warp's staged records (cnt per lane, column layout): one scan, one reservation, then every lane stores its own
-// run of the record list and adds its visits to the census. A staged word names its agent by (tile of the window, slot a)
-// and the column it sits in: agent = win_t0 + tile * tile_stride + 32 a + lane.
+// flush a warp's staged records (cnt per lane, column layout): one reservation for the warp, then row k of the staging buffer
+// goes out as one contiguous run of the record list (positions by ballot + popc, so the 8-byte stores of a row coalesce; with
+// every lane writing its own run the stores were scattered and the kernel lost 100 us per day at 21.5 M agents once most visits
+// were hot), one census RED per record. A staged word names its agent by (tile of the window, slot a) and the column it sits
+// in: agent = win_t0 + tile * tile_stride + 32 a + lane.
 __device__ __forceinline__ void visit_flush(const Dev& D, const unsigned int (*stage)[32], unsigned int& cnt, const unsigned int lane,
                                             const unsigned int win_t0, const unsigned int tile_stride, unsigned int& w_v) {
-    unsigned int incl = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
-    const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
+    const unsigned int total = __reduce_add_sync(0xffffffffu, cnt), rows = __reduce_max_sync(0xffffffffu, cnt);
     unsigned int base = 0;
-    if (lane == 31) base = atomicAdd(&D.ctr->n_vis, total);
-    base = __shfl_sync(0xffffffffu, base, 31) + incl - cnt;
-    for (unsigned int k = 0; k < cnt; ++k) {
-        const unsigned int e = stage[k][lane];
-        const unsigned int q = e & PROW_Q_MASK, p = win_t0 + (e >> 21) * tile_stride + ((e >> 19) & 3u) * 32u + lane;
-        CABM_CHECK(D, q < D.Q && p >= D.own_lo && p < D.own_hi && k < VIS_COL);
-        atomicAdd(&D.nvis[q], 1u);
-        if (base + k < D.cap_vis) D.visit_rec[base + k] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
+    if (lane == 0) base = atomicAdd(&D.ctr->n_vis, total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    const unsigned int lt = (1u << lane) - 1u;
+    for (unsigned int k = 0; k < rows; ++k) {
+        const bool have = k < cnt;
+        const unsigned int m = __ballot_sync(0xffffffffu, have);
+        if (have) {
+            const unsigned int e = stage[k][lane];
+            const unsigned int q = e & PROW_Q_MASK, p = win_t0 + (e >> 21) * tile_stride + ((e >> 19) & 3u) * 32u + lane;
+            CABM_CHECK(D, q < D.Q && p >= D.own_lo && p < D.own_hi && k < VIS_COL);
+            const unsigned int pos = base + __popc(m & lt);
+            atomicAdd(&D.nvis[q], 1u);
+            if (pos < D.cap_vis) D.visit_rec[pos] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
+        }
+        base += __popc(m);
     }
     w_v += cnt; cnt = 0;
 }
@@ -393,8 +443,9 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
             for (int r = 0; r < 10; ++r) {
 #pragma unroll
                 for (int a = 0; a < VIS_A; ++a) {
-                    const unsigned long long m0 = (unsigned long long) x[a].x * 0xD2511F53ull, m1 = (unsigned long long) x[a].z * 0xCD9E8D57ull;   // one IMAD.WIDE each
-                    x[a] = make_uint4((unsigned int) (m1 >> 32) ^ x[a].y ^ k.x, (unsigned int) m1, (unsigned int) (m0 >> 32) ^ x[a].w ^ k.y, (unsigned int) m0);
+                    const unsigned int hi0 = __umulhi(0xD2511F53u, x[a].x), lo0 = 0xD2511F53u * x[a].x;
+                    const unsigned int hi1 = __umulhi(0xCD9E8D57u, x[a].z), lo1 = 0xCD9E8D57u * x[a].z;
+                    x[a] = make_uint4(hi1 ^ x[a].y ^ k.x, lo1, hi0 ^ x[a].w ^ k.y, lo0);
                 }
                 k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
             }
@@ -463,15 +514,13 @@ __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1
 // the susceptibility gate of one successful trial (cabm_kernels2.cuh)
 __device__ __forceinline__ void gate_hit(const Dev& D, const int phase, const unsigned int pid, const unsigned int src, const unsigned int purpose, const unsigned int sub);
 
-// the block's queue of successful trials of the house..nursing-home passes (k_trials): gated when the block's loop is over
-#define HITQ 512
-struct HitQueue { Hit q[HITQ]; unsigned int n; };
-
 // one exposure trial: the quarantine skip and `gsl_rng_uniform(RNG) < T` of Community::_transmission (Community.cpp:975-976).
-// A success of the house..nursing-home passes (hq != nullptr) is queued for the susceptibility gate at the end of the block
-// (gated in place when the queue is full); the hospital pass gates in place.
+// A success of the house..nursing-home passes (phase 0) is appended to the hit list for the susceptibility gate (k_gate): the
+// gate is rare, divergent and register-hungry (Person::infect's front half), and kept out of this kernel so that the streaming
+// loop runs at 32 registers and full occupancy (fused in, k_trials needed 70 registers and took 575 instead of 336 us per day
+// in the heavy-epidemic regime at 21.5 M agents). The hospital pass (phase 1: a handful of hits) gates in place.
 __device__ __forceinline__ void trial(const Dev& D, const int day, const int phase, const unsigned int pid, const int src, const int purpose,
-                                      const unsigned int sub, const double T, unsigned int& trials, HitQueue* hq) {
+                                      const unsigned int sub, const double T, unsigned int& trials) {
     CABM_CHECK(D, pid < D.N && src >= 0 && (unsigned int) src < D.L);
     if (pid < D.own_lo || pid >= D.own_hi) return;                                 // the owner of an agent draws its exposures
     if (D.any_quarantine) {
@@ -482,11 +531,10 @@ __device__ __forceinline__ void trial(const Dev& D, const int day, const int pha
     const uint4 b = philox4x32_10(make_uint4(sub << 16, pid, (unsigned int) src, ((unsigned int) day << 8) | (unsigned int) purpose),
                                   make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
     if ((double) b.x * (1.0 / 4294967296.0) < T) {
-        if (hq) {
-            const unsigned int h = atomicAdd(&hq->n, 1u);
-            if (h < HITQ) { Hit r; r.pid = pid; r.src = (unsigned int) src; r.purpose = (unsigned int) purpose; r.sub = sub; hq->q[h] = r; return; }
-        }
-        gate_hit(D, phase, pid, (unsigned int) src, (unsigned int) purpose, sub);
+        if (phase) { gate_hit(D, 1, pid, (unsigned int) src, (unsigned int) purpose, sub); return; }
+        const unsigned int h = list_reserve(&D.ctr->n_hits);
+        if (h < D.cap_hits) { Hit r; r.pid = pid; r.src = (unsigned int) src; r.purpose = (unsigned int) purpose; r.sub = sub; D.hits[h] = r; }
+        else atomicOr(&D.ctr->overflow, 256u);
     }
 }
 
@@ -603,9 +651,6 @@ __global__ void __launch_bounds__(TPB) k_hazard_b(const Dev* __restrict__ devs) 
 // k_trials: block-sized units: the 256-member items of big rosters, the visit records, the flag scatter, the small items.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_trials_body(const Dev& D) {
-    __shared__ HitQueue hq;
-    if (threadIdx.x == 0) hq.n = 0;
-    __syncthreads();
     pdl_wait();
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n_items = min(D.ctr->n_items, D.cap_items), n_vis = min(D.ctr->n_vis, D.cap_vis);
@@ -632,7 +677,7 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
                 if (cnt) {
                     CABM_CHECK(D, it.t_idx < 2u * D.cap_hot && (unsigned int) begin + cnt <= D.roster_off[D.L] && (unsigned int) it.src < D.L);
                     const double T = D.hot_T[it.t_idx];
-                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[begin + m], it.src, purpose, 0, T, trials, &hq);
+                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[begin + m], it.src, purpose, 0, T, trials);
                 }
             }
         } else if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
@@ -647,25 +692,18 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
         } else if (u < n_items) {
             const Item it = D.items[u];
             CABM_CHECK(D, it.count >= 1 && it.count <= CHUNK && (unsigned int) it.begin + (unsigned int) it.count <= D.roster_off[D.L] && (unsigned int) it.src < D.L);
-            if ((int) threadIdx.x < it.count) trial(D, day, 0, (unsigned int) D.roster[it.begin + threadIdx.x], it.src, it.purpose, 0, it.T, trials, &hq);
+            if ((int) threadIdx.x < it.count) trial(D, day, 0, (unsigned int) D.roster[it.begin + threadIdx.x], it.src, it.purpose, 0, it.T, trials);
         } else {
             const unsigned int v = (u - n_items) * TPB + threadIdx.x;
             if (v < n_vis) {
                 const uint2 rec = D.visit_rec[v];
                 CABM_CHECK(D, rec.x < D.N && rec.y < D.Q);
                 const double T = D.pub_T[rec.y];
-                if (T > 0.0) trial(D, day, 0, rec.x, D.pub_loc[rec.y], CABM_P_EXPOSE_WORK_VIS, 0, T, trials, &hq);
+                if (T > 0.0) trial(D, day, 0, rec.x, D.pub_loc[rec.y], CABM_P_EXPOSE_WORK_VIS, 0, T, trials);
             }
         }
     }
-    // the susceptibility gate of the block's successful trials (calculate_event_probabilities + the Person::infect bail-out,
-    // Person.cpp:274-326): rare and divergent, so it runs here on whatever threads there are hits for, after the streaming loop
     pdl_launch_dependents();
-    __syncthreads();
-    {
-        const unsigned int nh = min(hq.n, (unsigned int) HITQ);
-        for (unsigned int i = threadIdx.x; i < nh; i += blockDim.x) { const Hit h = hq.q[i]; gate_hit(D, 0, h.pid, h.src, h.purpose, h.sub); }
-    }
     const int ids[1] = { CABM_W_TRIALS }; const unsigned int vals[1] = { trials };
     block_work_add<1>(D, ids, vals);
 }

@@ -126,6 +126,19 @@ __device__ __forceinline__ void gate_hit(const Dev& D, const int phase, const un
     }
 }
 
+// k_gate: the hits of the house..nursing-home passes (k_trials) pass the susceptibility gate, one thread per hit
+__device__ __forceinline__ void k_gate_body(const Dev& D) {
+    pdl_wait();
+    const unsigned int n = min(D.ctr->n_hits, D.cap_hits);
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const Hit h = D.hits[i];
+        gate_hit(D, 0, h.pid, h.src, h.purpose, h.sub);
+    }
+    pdl_launch_dependents();
+}
+__global__ void __launch_bounds__(128) k_gate(const Dev D) { k_gate_body(D); }
+__global__ void __launch_bounds__(128) k_gate_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_gate_body(D); }   // one launch, replicate = blockIdx.y
+
 // Community::updatePersonStatus (Community.cpp:682-741) for one agent; returns the ledger increments as a bit mask
 __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p, int day) {
     const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
@@ -186,8 +199,6 @@ __device__ __forceinline__ void close_day(const Dev& D, const int tick_done, con
         if (tick_done) {
             if (D.shard_rank == 0) c->work[CABM_W_HOT_LOCS] += n_hot;
             if (D.foi_enabled) *D.n_foi = n_hot;
-            const unsigned int sel = c->act_sel;           // the list k_active read today is spent; the one it built (plus today's infections) is next
-            c->n_act[sel] = 0; c->act_sel = sel ^ 1u; c->in_tick = 0;
         }
         D.host_status[1] = c->n_new[1]; D.host_status[0] = c->overflow;             // over PCIe into pinned memory: the host reads them after its sync, no copy
         __threadfence_system();
@@ -216,9 +227,8 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int nbase = phase ? min(D.ctr->n_new[0], D.cap_new) : 0u;
     const unsigned int n_w = min(nbase + D.ctr->n_new[phase], D.cap_new) - nbase;
-    const unsigned int sel = D.ctr->act_sel;
-    const unsigned int n_a = with_status ? min(D.ctr->n_act[sel], D.cap_active) : 0u;
-    const unsigned int* __restrict__ alist = D.act[sel];
+    const unsigned int n_a = with_status ? min(D.ctr->n_active, D.cap_active) : 0u;
+    const unsigned int* __restrict__ alist = D.active_list;
     const unsigned int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
     // Winners per warp: one while the winners fit in two rounds of the grid's warps (Person::infect is a long dependent chain, a
     // winner alone in its warp finishes soonest, and a second round costs less than two divergent courses in one warp);
@@ -351,7 +361,7 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
             unsigned int denom; unsigned long long pws[4];
             const double T = hospital_T(D, cx, hosp, &denom, pws);
             const unsigned int rb = D.roster_off[hosp], size = D.roster_off[hosp + 1] - rb;
-            if (T > 0.0) for (unsigned int m = lane; m < size; m += 32) trial(D, day, 1, (unsigned int) D.roster[rb + m], hosp, CABM_P_EXPOSE_HOSP, 0, T, trials, nullptr);
+            if (T > 0.0) for (unsigned int m = lane; m < size; m += 32) trial(D, day, 1, (unsigned int) D.roster[rb + m], hosp, CABM_P_EXPOSE_HOSP, 0, T, trials);
             if (D.foi_enabled && lane == 0) write_foi(D, i, hosp, CABM_HOSPITAL, pws, denom, T, 0.0);
         }
         const unsigned int np = min(D.ctr->n_pat, D.cap_pat);
@@ -364,7 +374,7 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
             if (hosp < 0 || D.loc_cnt[hosp] == 0) continue;
             unsigned int denom; unsigned long long pws[4];
             const double T = hospital_T(D, cx, hosp, &denom, pws);
-            if (T > 0.0) for (unsigned int sub = 0; sub < c; ++sub) trial(D, day, 1, pid, hosp, CABM_P_EXPOSE_HOSP_PAT, sub, T, trials, nullptr);
+            if (T > 0.0) for (unsigned int sub = 0; sub < c; ++sub) trial(D, day, 1, pid, hosp, CABM_P_EXPOSE_HOSP_PAT, sub, T, trials);
         }
     }
     if (do_import) {
@@ -611,7 +621,6 @@ __global__ void k_patients(const Dev D, const int* __restrict__ hosp_ids, const 
 __global__ void k_init_state(const Dev D) {
     const unsigned int stride = gridDim.x * blockDim.x;
     for (unsigned int p = blockIdx.x * blockDim.x + threadIdx.x; p < D.N; p += stride) {
-        D.win[p] = 0x80007FFFu;                       // from = 32767, until = -32768: never active
         D.cand[p] = CABM_CAND_EMPTY;
     }
 }

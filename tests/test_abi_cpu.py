@@ -57,7 +57,7 @@ def test_product_library_is_device_code_for_sm_100a():
     assert "sm_100a" in out, out
     res = subprocess.run([cuobjdump, "-res-usage", cabm.community.LIB_PATH], capture_output=True, text=True)
     text = res.stdout + res.stderr
-    for k in ("k_active", "k_visit", "k_hazard", "k_trials", "k_apply_status", "k_hosp_import"):
+    for k in ("k_scan", "k_active", "k_visit", "k_hazard", "k_trials", "k_gate", "k_apply_status", "k_hosp_import"):
         assert k in text, f"kernel {k} not found in libcabm.so"
     # k_visit stages its rows and the hot bitmap with bulk copies completing on mbarriers (TMA; SASS UBLKCP / SYNCS)
     sass = subprocess.run([cuobjdump, "-sass", "-fun", "_Z7k_visit3Devj", cabm.community.LIB_PATH], capture_output=True, text=True).stdout
