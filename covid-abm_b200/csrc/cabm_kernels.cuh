@@ -284,17 +284,17 @@ __global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) 
 // one tile ahead of the tile being processed, so the warp never waits for HBM and spends no instructions on addresses. The
 // in-hospital flags of a tile are four words of a bitmap (one 16-byte load per lane, same address). The Philox block needs
 // no memory. Hotness is tested against a shared-memory bitmap over the Q patronised locations (dynamic shared memory,
-// fetched with one bulk copy per block). A visit that lands on a hot location is stored as one word in the lane's own column
-// of the warp's staging buffer (no atomics, no shuffles in the body); the warp flushes when a column could overflow or after
-// 16 tiles: one scan, one reservation, one census RED per record. Agents that draw k >= 4 (1.9 %) are queued per block and handled on full warps
+// fetched with one bulk copy per block). A visit that lands on a hot location becomes one word of the warp's dense staging
+// buffer (positions from a warp scan per tile, no atomics); the warp flushes when the next tile might not fit or after 64
+// tiles: one reservation, coalesced record stores, one census RED per record. Agents that draw k >= 4 (1.9 %) are queued per block and handled on full warps
 // by the generic loop at the end, so the common path carries no divergent tail.
 // There is no block-level synchronisation in the loop.
 // ---------------------------------------------------------------------------------------------
 #define VIS_A 4               // agents per lane and tile
 #define VIS_TILE (32 * VIS_A)
-#define VIS_COL 24            // records a lane can stage (a tile adds at most 3 * VIS_A = 12)
-#define VIS_FLUSH_AT (VIS_COL - 3 * VIS_A)   // flush after a tile once some lane holds more than this
-#define VIS_WINDOW 16         // tiles between two flushes at most: a staged record names its tile by 4 bits
+#define VIS_STAGE 768         // records a warp can stage (a tile adds at most 3 * VIS_TILE = 384)
+#define VIS_FLUSH_AT (VIS_STAGE - 3 * VIS_TILE)   // flush after a tile once more than this is staged
+#define VIS_WINDOW 64         // tiles between two flushes at most: a staged record names its tile by 6 bits
 #define VIS_SLOWQ (2 * TPB)   // k >= 4 agents a block queues for its final full-warp pass (beyond that: handled in place)
 #define VIS_WARPS (TPB / 32)
 #define VIS_TILE_BYTES (VIS_TILE * PROW_WORDS * 4u)
@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) 
 
 struct __align__(16) VisitSmem {
     unsigned int rows[VIS_WARPS][2][VIS_TILE * PROW_WORDS];  // patron rows of the current and the next tile of every warp (bulk-copy destinations)
-    unsigned int stage[VIS_WARPS][VIS_COL][32];             // hot visits, [slot][lane]: public index | slot a << 19 | tile of the window << 21 (the lane is the column)
+    unsigned int stage[VIS_WARPS][VIS_STAGE];               // hot visits, dense per warp: public index | slot a << 19 | lane << 21 | tile of the window << 26
     unsigned long long thr[CABM_T_POISSON];                 // ceil(visit_cdf[k] * 2^32)
     unsigned long long bar_rows[VIS_WARPS][2];              // mbarriers of the row buffers
     unsigned long long bar_hot;                             // mbarrier of the hot-bitmap copy
@@ -363,32 +363,24 @@ __device__ __forceinline__ void visit_slow(const Dev& D, const unsigned int* s_h
     }
 }
 
-// flush a warp's staged records (cnt per lane, column layout): one reservation for the warp, then row k of the staging buffer
-// goes out as one contiguous run of the record list (positions by ballot + popc, so the 8-byte stores of a row coalesce; with
-// every lane writing its own run the stores were scattered and the kernel lost 100 us per day at 21.5 M agents once most visits
-// were hot), one census RED per record. A staged word names its agent by (tile of the window, slot a) and the column it sits
-// in: agent = win_t0 + tile * tile_stride + 32 a + lane.
-__device__ __forceinline__ void visit_flush(const Dev& D, const unsigned int (*stage)[32], unsigned int& cnt, const unsigned int lane,
+// flush a warp's staged records: one reservation, then the dense buffer goes out 32 records at a time (coalesced 8-byte
+// stores, one census RED per record). A staged word names its agent by (tile of the window, slot a, lane):
+// agent = win_t0 + tile * tile_stride + 32 a + lane.
+__device__ __forceinline__ void visit_flush(const Dev& D, const unsigned int* stage, unsigned int& staged, const unsigned int lane,
                                             const unsigned int win_t0, const unsigned int tile_stride, unsigned int& w_v) {
-    const unsigned int total = __reduce_add_sync(0xffffffffu, cnt), rows = __reduce_max_sync(0xffffffffu, cnt);
     unsigned int base = 0;
-    if (lane == 0) base = atomicAdd(&D.ctr->n_vis, total);
+    if (lane == 0) base = atomicAdd(&D.ctr->n_vis, staged);
     base = __shfl_sync(0xffffffffu, base, 0);
-    const unsigned int lt = (1u << lane) - 1u;
-    for (unsigned int k = 0; k < rows; ++k) {
-        const bool have = k < cnt;
-        const unsigned int m = __ballot_sync(0xffffffffu, have);
-        if (have) {
-            const unsigned int e = stage[k][lane];
-            const unsigned int q = e & PROW_Q_MASK, p = win_t0 + (e >> 21) * tile_stride + ((e >> 19) & 3u) * 32u + lane;
-            CABM_CHECK(D, q < D.Q && p >= D.own_lo && p < D.own_hi && k < VIS_COL);
-            const unsigned int pos = base + __popc(m & lt);
-            atomicAdd(&D.nvis[q], 1u);
-            if (pos < D.cap_vis) D.visit_rec[pos] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
-        }
-        base += __popc(m);
+    for (unsigned int i = lane; i < staged; i += 32) {
+        const unsigned int e = stage[i];
+        const unsigned int q = e & PROW_Q_MASK, p = win_t0 + (e >> 26) * tile_stride + ((e >> 19) & 3u) * 32u + ((e >> 21) & 31u);
+        CABM_CHECK(D, q < D.Q && p >= D.own_lo && p < D.own_hi && staged <= VIS_STAGE);
+        atomicAdd(&D.nvis[q], 1u);
+        if (base + i < D.cap_vis) D.visit_rec[base + i] = make_uint2(p, q); else atomicOr(&D.ctr->overflow, 8u);
     }
-    w_v += cnt; cnt = 0;
+    __syncwarp();                                          // the buffer is written again by the next tile
+    if (lane == 0) w_v += staged;
+    staged = 0;
 }
 
 __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bitmap_words) {
@@ -420,8 +412,8 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
     if (t0 < own_hi) hw_next = hosp4[t0 / VIS_TILE];
     mbar_wait(&S.bar_hot, 0);
     const unsigned int* __restrict__ s_hot = S.hot;
-    unsigned int (*const stage)[32] = S.stage[wid];
-    unsigned int cnt = 0, w_pat = 0, w_v0 = 0, w_v = 0, phase = 0;                 // phase: bit b = parity to wait for on row buffer b
+    unsigned int* const stage = S.stage[wid];
+    unsigned int staged = 0, w_pat = 0, w_v0 = 0, w_v = 0, phase = 0;              // staged: records in the warp's buffer (same in every lane); phase: bit b = parity to wait for on row buffer b
     unsigned int win_t0 = t0, win_n = 0;                                            // first tile and number of tiles of the staging window
     for (unsigned int it = 0; t0 < own_hi; ++it, t0 += tile_stride) {
         const unsigned int b = it & 1u;
@@ -453,8 +445,7 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
         mbar_wait(&S.bar_rows[wid][b], (phase >> b) & 1u);
         phase ^= 1u << b;
         const unsigned int* __restrict__ rows = S.rows[wid][b];
-        const unsigned int tag = win_n << 21;
-        unsigned int slow = 0;
+        unsigned int recq[3 * VIS_A]; unsigned int recmask = 0, slow = 0;          // this lane's hot visits of the tile (k <= 3)
 #pragma unroll
         for (int a = 0; a < VIS_A; ++a) {
             const unsigned int* __restrict__ rw = rows + (a * 32 + lane) * PROW_WORDS;    // this agent's row: 5 words, bank = (5 lane + j) mod 32
@@ -477,13 +468,20 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
             w_pat += act;
             w_v0 += v0 + v1 + v2;
             const unsigned int h0 = v0 & __funnelshift_r(s_hot[q0 >> 5], 0u, q0), h1 = v1 & __funnelshift_r(s_hot[q1 >> 5], 0u, q1), h2 = v2 & __funnelshift_r(s_hot[q2 >> 5], 0u, q2);
-            const unsigned int ta = tag | ((unsigned int) a << 19);
-            if (h0) stage[cnt][lane] = q0 | ta;
-            cnt += h0;
-            if (h1) stage[cnt][lane] = q1 | ta;
-            cnt += h1;
-            if (h2) stage[cnt][lane] = q2 | ta;
-            cnt += h2;
+            recq[a * 3 + 0] = q0; recq[a * 3 + 1] = q1; recq[a * 3 + 2] = q2;
+            recmask |= (h0 | (h1 << 1) | (h2 << 2)) << (a * 3);
+        }
+        // the tile's records go to the warp's dense buffer: positions from a warp scan of the per-lane counts
+        if (__any_sync(0xffffffffu, recmask != 0u)) {
+            const unsigned int nrec = __popc(recmask);
+            unsigned int incl = nrec;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
+            unsigned int o = staged + incl - nrec;
+            const unsigned int tag = (lane << 21) | (win_n << 26);
+#pragma unroll
+            for (int r = 0; r < 3 * VIS_A; ++r) if (recmask & (1u << r)) { stage[o] = recq[r] | ((unsigned int) (r / 3) << 19) | tag; ++o; }
+            staged += __shfl_sync(0xffffffffu, incl, 31);
         }
         // k >= 4 (1.9 % of the drawing agents): queued for the block's final pass, so the generic loop runs on full warps
         while (slow) {
@@ -493,9 +491,9 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
         }
         __syncwarp();                                                               // every lane has read its rows: the buffer may be refilled
         ++win_n;
-        if (win_n == VIS_WINDOW || __any_sync(0xffffffffu, cnt > VIS_FLUSH_AT)) { visit_flush(D, stage, cnt, lane, win_t0, tile_stride, w_v); win_t0 = t0 + tile_stride; win_n = 0; }
+        if (win_n == VIS_WINDOW || staged > VIS_FLUSH_AT) { visit_flush(D, stage, staged, lane, win_t0, tile_stride, w_v); win_t0 = t0 + tile_stride; win_n = 0; }
     }
-    if (__any_sync(0xffffffffu, cnt != 0)) visit_flush(D, stage, cnt, lane, win_t0, tile_stride, w_v);
+    if (staged) visit_flush(D, stage, staged, lane, win_t0, tile_stride, w_v);
     pdl_launch_dependents();                             // the tiles are done; the k >= 4 pass and the counters remain
     // the block's k >= 4 agents on full warps
     __syncthreads();
