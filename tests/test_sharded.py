@@ -178,16 +178,19 @@ def test_nccl_day_loop_with_one_rank_equals_run_days():
 
 
 @pytest.mark.gpu
-def test_nccl_day_loop_on_two_gpus_equals_single_handle():
+@pytest.mark.parametrize("world", [2, 4])
+def test_nccl_day_loop_on_several_gpus_equals_single_handle(world):
+    """One rank per GPU under torchrun (tools/shard_run.py): NCCL + peer-memory exchanges inside the library, summed ledger equal
+    to one handle's. Runs with 2 ranks wherever the box has two GPUs and with 4 wherever it has four."""
     import json
     import subprocess
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("one GPU on this box")
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"{torch.cuda.device_count()} GPU(s) on this box")
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
                         "--master-port", str(port), os.path.join(ROOT, "tools", "shard_run.py"), "--agents", "200000", "--days", "40", "--warm", "20"],
-                       capture_output=True, text=True, timeout=600)
+                       capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stderr[-2000:]
     out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
-    assert out["native_nccl"] and out["equals_single_handle"] and out["infections"] > 0
+    assert out["world"] == world and out["native_nccl"] and out["equals_single_handle"] and out["infections"] > 0
