@@ -21,6 +21,8 @@ N_COUNTERS = len(COUNTERS)
 DIAG = ["dose_1", "dose_2", "dose_3", "fully_vaxd", "bt_inf", "bt_dis", "bt_hosp", "bt_death", "bt_reported", "uv_inf", "uv_dis", "uv_hosp",
         "uv_death", "uv_reported", "infected", "infectious", "symptomatic", "naive", "quarantining", "seropos_all", "seropos_ped", "n_ped"]
 N_DIAG = 24
+EL_ALIVE, EL_EVER_INFECTED, EL_VACCINATED, EL_PRIOR_CASE, EL_DOSES_SHIFT, EL_INFECTED_NOW = 1, 2, 4, 8, 4, 128
+REDUCE = ["seropositive", "quarantining", "infected", "infectious", "symptomatic", "naive", "fully_vaxd", "alive"]
 STATIC_MAX_IDS = 1 << 20
 SHARD_FLAG_BYTES = 24
 WORK = ["agents", "active", "flags", "patrons", "visits", "hot_visits", "hot_locs", "nbr_edges", "trials", "infections"]
@@ -102,6 +104,8 @@ _PROTOS = {
     "shard_day_part": [_vp, C.c_int, C.c_int, C.c_int, C.c_int, d, C.POINTER(d), C.POINTER(i32)],
     "shard_flags_out": [_vp, C.POINTER(_vp), C.POINTER(C.c_size_t)], "shard_flags_in": [_vp, _vp, C.c_size_t],
     "shard_census": [_vp, C.POINTER(_vp), C.POINTER(C.c_size_t)], "shard_patients": [_vp, C.POINTER(_vp), C.POINTER(C.c_size_t)],
+    "eligibility": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(u8)],
+    "reduce": [_vp, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(d)],
     "diagnostics": [_vp, C.c_int, C.POINTER(C.c_uint64)], "serosurvey": [_vp, C.c_int, C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_uint64)],
 }
 _OPTIONAL = {

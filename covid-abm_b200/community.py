@@ -256,6 +256,27 @@ class Community:
         self._check(self.fn.serosurvey(self._h, int(day), ptr, n, C.byref(out)))
         return out.value / n if n else float("nan")
 
+    def eligibility(self, pids, day: int) -> np.ndarray:
+        """CABM_EL_* byte per person (Person::isAlive / isSeroEligible / isInfEligible inputs, Person.cpp:562-608); pids None = everybody."""
+        if pids is None:
+            n = self.n_people; ptr = None
+        else:
+            p = np.ascontiguousarray(pids, dtype=np.uint32); n = p.size; ptr = p.ctypes.data_as(C.POINTER(C.c_uint32))
+        out = np.zeros(n, dtype=np.uint8)
+        self._check(self.fn.eligibility(self._h, int(day), ptr, n, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
+    def reduce(self, what, pids, day: int) -> int:
+        """Count of one per-person predicate (abi.REDUCE) over a cohort; pids None = everybody (cabm_reduce)."""
+        w = abi.REDUCE.index(what) if isinstance(what, str) else int(what)
+        if pids is None:
+            n = self.n_people; ptr = None
+        else:
+            p = np.ascontiguousarray(pids, dtype=np.uint32); n = p.size; ptr = p.ctypes.data_as(C.POINTER(C.c_uint32))
+        out = C.c_double(0)
+        self._check(self.fn.reduce(self._h, w, int(day), ptr, n, C.byref(out)))
+        return int(out.value)
+
     def getNumPeopleQuarantining(self, day: int) -> float:
         return self.diagnostics(day)["quarantining"] / self.n_people
 

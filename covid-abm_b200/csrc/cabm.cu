@@ -1077,6 +1077,45 @@ int cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint
     return CABM_OK;
 }
 
+int cabm_eligibility(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_flags) {
+    if (!h || !out_flags) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (!pids) n = h->d.N;
+    if (n == 0) return CABM_OK;
+    if (pids) for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    const size_t out_bytes = (n + 15) & ~(size_t) 15;
+    void* buf = nullptr; if ((rc = scratch(h, out_bytes + (pids ? n * sizeof(unsigned int) : 0), &buf))) return rc;
+    unsigned char* d_o = (unsigned char*) buf; unsigned int* d_p = pids ? (unsigned int*) ((unsigned char*) buf + out_bytes) : nullptr;
+    if (pids) CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    k_eligibility<<<grid_for(h, n, 8), TPB, 0, h->stream>>>(h->d, sim_day, d_p, (unsigned int) n, d_o);
+    CK(cudaMemcpyAsync(out_flags, d_o, n, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return CABM_OK;
+}
+
+int cabm_reduce(cabm_t* h, int what, int sim_day, const uint32_t* pids, size_t n, double* out_count) {
+    if (!h || !out_count || what < 0 || what >= CABM_N_REDUCE) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (!pids) n = h->d.N;
+    *out_count = 0.0;
+    if (n == 0) return CABM_OK;
+    if (pids) for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG;
+    cudaSetDevice(h->device);
+    if (!h->d_diag) { int rc2 = dalloc(h, &h->d_diag, CABM_N_DIAG); if (rc2) return rc2; }
+    unsigned int* d_p = nullptr;
+    if (pids) {
+        void* buf = nullptr; if ((rc = scratch(h, n * sizeof(unsigned int), &buf))) return rc;
+        d_p = (unsigned int*) buf;
+        CK(cudaMemcpyAsync(d_p, pids, n * sizeof(unsigned int), cudaMemcpyHostToDevice, h->stream));
+    }
+    CK(cudaMemsetAsync(h->d_diag, 0, sizeof(unsigned long long), h->stream));
+    k_reduce<<<grid_for(h, n, 8), TPB, 0, h->stream>>>(h->d, what, sim_day, d_p, (unsigned int) n, h->d_diag);
+    unsigned long long r = 0;
+    CK(cudaMemcpyAsync(&r, h->d_diag, sizeof(r), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *out_count = (double) r;
+    return CABM_OK;
+}
+
 // cabm_serosurvey without any allocation (include/cabm.h): ids and accumulator in the file-scope device array, the result
 // comes back through the handle's pinned word. No cudaMalloc / cudaFree / allocating library call on this path.
 int cabm_serosurvey_static(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos) {

@@ -537,6 +537,40 @@ __global__ void k_serosurvey(const Dev D, const int day, const unsigned int* pid
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(out, (unsigned long long) mine);
 }
 
+// one person's predicates on `day`: bits 0-7 as CABM_EL_*, bits 8.. = 1 << (8 + CABM_R_*)
+__device__ __forceinline__ unsigned int person_bits(const Dev& D, const cabm_params* par, const unsigned int p, const int day) {
+    const unsigned int imm = D.imm[p], v = D.vax[p], nd = v & 0xFF; const int last_dose = (short) (v >> 16);
+    unsigned int b = 0; bool alive = true;
+    if (imm) {
+        const Tl0 a = D.tl0[p]; const Tl1 t = D.tl1[p];
+        alive = !(t.death <= day);
+        b |= CABM_EL_EVER_INFECTED;
+        if (t.detected < CABM_N_OUTCOMES && t.report_day <= day) b |= CABM_EL_PRIOR_CASE;
+        if (a.infected <= day && day < a.infectious_end) b |= CABM_EL_INFECTED_NOW | (1u << (8 + CABM_R_INFECTED));
+        if (a.infectious_begin <= day && day < a.infectious_end) b |= 1u << (8 + CABM_R_INFECTIOUS);
+        if (a.symptom_begin <= day && day < a.symptom_end) b |= 1u << (8 + CABM_R_SYMPTOMATIC);
+        if (sero_positive(D, par, p, day)) b |= 1u << (8 + CABM_R_SEROPOSITIVE);
+    } else if (nd == 0) b |= 1u << (8 + CABM_R_NAIVE);
+    if (alive) b |= CABM_EL_ALIVE | (1u << (8 + CABM_R_ALIVE));
+    if (nd) b |= CABM_EL_VACCINATED;
+    b |= min(nd, 7u) << CABM_EL_DOSES_SHIFT;
+    if (nd > 1 && (day - last_dose) >= par->vaccine_dose_to_protection_lag) b |= 1u << (8 + CABM_R_FULLY_VAXD);
+    const unsigned int q = D.quar[p]; const int qf = (short) (q & 0xFFFF), qu = (short) (q >> 16);
+    if (q != 0 && day >= qf && day < qu) b |= 1u << (8 + CABM_R_QUARANTINING);
+    return b;
+}
+__global__ void k_eligibility(const Dev D, const int day, const unsigned int* pids, const unsigned int n, unsigned char* out) {
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        out[i] = (unsigned char) (person_bits(D, D.par, pids ? pids[i] : i, day) & 0xFFu);
+}
+__global__ void k_reduce(const Dev D, const int what, const int day, const unsigned int* pids, const unsigned int n, unsigned long long* out) {
+    unsigned int mine = 0;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        mine += (person_bits(D, D.par, pids ? pids[i] : i, day) >> (8 + what)) & 1u;
+    mine = warp_sum(mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(out, (unsigned long long) mine);
+}
+
 // primary cases of contact tracing (Community.cpp:1062-1070): alive, latest infection detected and reported today
 __global__ void k_detected_today(const Dev D, const int day, unsigned int* out, unsigned int cap, unsigned int* n_out) {
     for (unsigned int base = blockIdx.x * blockDim.x; base < D.N; base += gridDim.x * blockDim.x) {

@@ -301,6 +301,19 @@ int  cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]);
 /* doSerosurvey(NATURAL, pop, day) for an arbitrary list of people (pids == NULL: everybody); returns the seropositive count */
 int  cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos);
 
+/* What Vac_Campaign asks of a person before scheduling a dose (Person::isAlive, isSeroEligible Person.cpp:562-583, isInfEligible
+   :586-608, getNumVaccinations, Vac_Campaign.h:505-548), one byte per listed person (pids == NULL: everybody, n = n_people):
+   CABM_EL_* bits. PRIOR_CASE looks at the person's latest infection (the device keeps one record per person; earlier ones are
+   in the infection log, cabm_sync_histories). */
+enum { CABM_EL_ALIVE = 1, CABM_EL_EVER_INFECTED = 2, CABM_EL_VACCINATED = 4, CABM_EL_PRIOR_CASE = 8,
+       CABM_EL_DOSES_SHIFT = 4 /* bits 4-6: doses received, saturating at 7 */, CABM_EL_INFECTED_NOW = 128 };
+int  cabm_eligibility(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_flags);
+/* Counts over a list of people (pids == NULL: everybody) of one per-person predicate on sim_day: the population reductions of
+   Community.cpp:1196-1274,1329-1423 and Community.h:437 for an arbitrary cohort (cabm_diagnostics gives them for everybody). */
+enum cabm_reduce_what { CABM_R_SEROPOSITIVE = 0, CABM_R_QUARANTINING, CABM_R_INFECTED, CABM_R_INFECTIOUS, CABM_R_SYMPTOMATIC, CABM_R_NAIVE,
+                        CABM_R_FULLY_VAXD, CABM_R_ALIVE, CABM_N_REDUCE };
+int  cabm_reduce(cabm_t* h, int what, int sim_day, const uint32_t* pids, size_t n, double* out_count);
+
 /* cabm_serosurvey for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
    forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same arguments and
    result as cabm_serosurvey, but the id list and the accumulator live in a file-scope `static __device__` array of the

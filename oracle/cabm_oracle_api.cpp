@@ -271,6 +271,49 @@ int cabm_oracle_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t 
     return CABM_OK;
 }
 
+// per-person predicates behind cabm_eligibility / cabm_reduce (include/cabm.h): bits 0-7 CABM_EL_*, bit 8 + k = CABM_R_k
+static unsigned oracle_person_bits(const Sim& S, uint32_t pid, int day) {
+    const cabm_oracle::Person& p = S.people[pid];
+    unsigned b = 0; bool alive = true;
+    const unsigned nd = (unsigned) p.vax_days.size();
+    if (!p.hist.empty()) {
+        const cabm_oracle::Infection& inf = p.hist.back();
+        alive = !inf.isDead(day);
+        b |= CABM_EL_EVER_INFECTED;
+        if (inf.detected_state < CABM_N_OUTCOMES && inf.report_day <= day) b |= CABM_EL_PRIOR_CASE;
+        if (inf.isInfected(day)) b |= CABM_EL_INFECTED_NOW | (1u << (8 + CABM_R_INFECTED));
+        if (inf.isInfectious(day)) b |= 1u << (8 + CABM_R_INFECTIOUS);
+        if (inf.t[cabm_oracle::T_SYMPTOM_BEGIN] <= day && day < inf.t[cabm_oracle::T_SYMPTOM_END]) b |= 1u << (8 + CABM_R_SYMPTOMATIC);
+        if (oracle_sero_positive(S, pid, day)) b |= 1u << (8 + CABM_R_SEROPOSITIVE);
+    } else if (nd == 0) b |= 1u << (8 + CABM_R_NAIVE);
+    if (alive) b |= CABM_EL_ALIVE | (1u << (8 + CABM_R_ALIVE));
+    if (nd) b |= CABM_EL_VACCINATED;
+    b |= std::min(nd, 7u) << CABM_EL_DOSES_SHIFT;
+    if (nd > 1 && (day - p.vax_days.back()) >= S.par.vaccine_dose_to_protection_lag) b |= 1u << (8 + CABM_R_FULLY_VAXD);
+    if (S.quarantining(p, day)) b |= 1u << (8 + CABM_R_QUARANTINING);
+    return b;
+}
+int cabm_oracle_eligibility(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_flags) {
+    H_OK(h); Sim& S = h->sim; if (!out_flags) return CABM_E_ARG;
+    if (!pids) n = S.n_people;
+    for (size_t i = 0; i < n; ++i) {
+        const uint32_t pid = pids ? pids[i] : (uint32_t) i; if (pid >= S.n_people) return CABM_E_ARG;
+        out_flags[i] = (uint8_t) (oracle_person_bits(S, pid, sim_day) & 0xFFu);
+    }
+    return CABM_OK;
+}
+int cabm_oracle_reduce(cabm_t* h, int what, int sim_day, const uint32_t* pids, size_t n, double* out_count) {
+    H_OK(h); Sim& S = h->sim; if (!out_count || what < 0 || what >= CABM_N_REDUCE) return CABM_E_ARG;
+    if (!pids) n = S.n_people;
+    uint64_t c = 0;
+    for (size_t i = 0; i < n; ++i) {
+        const uint32_t pid = pids ? pids[i] : (uint32_t) i; if (pid >= S.n_people) return CABM_E_ARG;
+        c += (oracle_person_bits(S, pid, sim_day) >> (8 + what)) & 1u;
+    }
+    *out_count = (double) c;
+    return CABM_OK;
+}
+
 int cabm_oracle_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infection* out) {
     H_OK(h); Sim& S = h->sim;
     for (size_t i = 0; i < n; ++i) {

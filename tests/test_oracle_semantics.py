@@ -300,3 +300,44 @@ def test_infect_batch_is_the_calls_one_after_the_other():
     assert np.array_equal(ta, tb) and ta.sum() > 300 and not ta[10:20].any()
     a.step(); b.step()
     assert np.array_equal(a.current_infections(), b.current_infections()) and np.array_equal(a.ledger_table(), b.ledger_table())
+
+
+def test_eligibility_and_reduce_follow_the_person_records():
+    """cabm_eligibility / cabm_reduce on the oracle against the same predicates evaluated with numpy on the records the ABI returns."""
+    import numpy as np
+    import synthpop
+    import covid_abm_b200 as cabm
+    import oracle_lib
+    pop = synthpop.generate(6000, seed=8)
+    P = cabm.params.default_params(run_length=40, seed=4, T=0.25, prob_daily_exposure=2e-3)
+    c = oracle_lib.oracle_community(P, pop)
+    n = int(pop["n_people"]); rng = np.random.default_rng(2)
+    for pid in range(0, 900, 3):
+        c.infect(pid, 0, 0)
+    dosed = rng.choice(n, size=n // 2, replace=False)
+    for d in range(35):
+        if d in (5, 30):
+            c.vaccinate(dosed, d)
+        if d == 20:
+            c.quarantine(rng.choice(n, size=n // 5, replace=False), d, d + 30)
+        c.step()
+    day = 34
+    el = c.eligibility(None, day)
+    rec = c.current_infections()
+    ever = rec["t"][:, 0] != 32767
+    alive = ~(ever & (rec["t"][:, 11] <= day))
+    assert np.array_equal((el & cabm.abi.EL_EVER_INFECTED) != 0, ever) and np.array_equal((el & cabm.abi.EL_ALIVE) != 0, alive)
+    is_dosed = np.zeros(n, bool); is_dosed[dosed] = True
+    doses = (el >> cabm.abi.EL_DOSES_SHIFT) & 7
+    assert np.array_equal((el & cabm.abi.EL_VACCINATED) != 0, doses > 0) and set(np.unique(doses[is_dosed])) <= {1, 2} and (doses[~is_dosed] == 0).all()
+    prior = ever & (rec["detected_state"] < 5) & (rec["report_day"] <= day)
+    assert np.array_equal((el & cabm.abi.EL_PRIOR_CASE) != 0, prior) and prior.sum() > 10
+    inf_now = ever & (rec["t"][:, 0] <= day) & (day < rec["t"][:, 2])
+    assert np.array_equal((el & cabm.abi.EL_INFECTED_NOW) != 0, inf_now)
+    diag = c.diagnostics(day)
+    assert c.reduce("infected", None, day) == inf_now.sum() == diag["infected"]
+    assert c.reduce("alive", None, day) == alive.sum() and c.reduce("quarantining", None, day) == diag["quarantining"] > 0
+    assert c.reduce("fully_vaxd", None, day) == diag["fully_vaxd"] and c.reduce("naive", None, day) == diag["naive"]
+    cohort = rng.choice(n, size=700, replace=False)
+    assert c.reduce("infectious", cohort, day) == (ever & (rec["t"][:, 1] <= day) & (day < rec["t"][:, 2]))[cohort].sum()
+    assert np.array_equal(c.eligibility(cohort, day), el[cohort])

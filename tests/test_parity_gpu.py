@@ -103,6 +103,14 @@ def test_multi_variant_vaccination_quarantine():
             assert np.array_equal(g.detected_today(d), o.detected_today(d))
             some = rng.choice(n, size=n // 4, replace=False)
             assert g.doSerosurvey(some, d) == o.doSerosurvey(some, d) and g.doSerosurvey(None, d) == o.doSerosurvey(None, d)
+            # cabm_eligibility / cabm_reduce: per-person predicates for a cohort and for everybody
+            assert np.array_equal(g.eligibility(some, d), o.eligibility(some, d)) and np.array_equal(g.eligibility(None, d), o.eligibility(None, d))
+            for what in cabm.abi.REDUCE:
+                assert g.reduce(what, some, d) == o.reduce(what, some, d), what
+                assert g.reduce(what, None, d) == o.reduce(what, None, d), what
+            for what, key in (("infected", "infected"), ("infectious", "infectious"), ("symptomatic", "symptomatic"), ("naive", "naive"),
+                              ("quarantining", "quarantining"), ("fully_vaxd", "fully_vaxd"), ("seropositive", "seropos_all")):
+                assert g.reduce(what, None, d) == dg[key], (what, g.reduce(what, None, d), dg[key])
     assert_same_state(g, o, "end")
     assert sum(g.detected_today(d).size for d in range(40, 75)) > 20
     dg = g.diagnostics(74)
