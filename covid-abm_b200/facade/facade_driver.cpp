@@ -17,6 +17,7 @@
 //   `campaign` = 1 attaches a general Vac_Campaign (the reference's class) so that Community::vaccinate and the dose
 //       bookkeeping run; 2 adds ring vaccination of traced contacts (needs begin_contact_tracing < run_length in the file).
 #include <chrono>
+#include <unistd.h>
 #include "simulator.h"
 #include "kv_parameters.h"
 
@@ -200,6 +201,18 @@ int main(int argc, char** argv) {
         community->getNumNewInfections(DELTA), community->getNumNewInfections(OMICRON) };
     for (size_t d = 0; d < par->runLength; ++d) { out << d; for (const auto& c : cols) out << ',' << c[d]; out << '\n'; }
     out.close();
+
+    // The reference's sim-data dump (generate_sim_data_db, simulator.h:642-761; exp/active-vac/main.cpp:814-824), unmodified: it
+    // walks getPeople() -> getInfectionHistory() / get_infections_caused() / getDetection() / getVaccinationHistory(), i.e. the
+    // proxies the facade fills from the device's infection log (cabm_sync_histories_from), writes seven CSV tables into the
+    // working directory and hands them to the sqlite3 command. CABM_SIM_DB=<dir>: run it there (needs a campaign: it reads the
+    // dose ledgers of the Vac_Campaign).
+    if (const char* dbdir = getenv("CABM_SIM_DB")) {
+        if (!community->getVac_Campaign()) { cerr << "CABM_SIM_DB needs campaign >= 1" << endl; return 2; }
+        if (chdir(dbdir) != 0) { cerr << "cannot chdir to " << dbdir << endl; return 2; }
+        generate_sim_data_db(par, community, (unsigned long) par->randomseed, { "infection_history", "secondary_infections", "infection_detection",
+                                                                                 "vaccination_history", "age_bins", "doses_available", "doses_used" });
+    }
 
     size_t n_hist = 0, n_vax = 0, n_secondary = 0, urg = 0;
     if (community->getVac_Campaign()) for (size_t d = 0; d < par->runLength; ++d) urg += community->getVac_Campaign()->get_doses_used(d, URGENT_ALLOCATION);
