@@ -34,6 +34,19 @@ namespace cg = cooperative_groups;
 
 __device__ __forceinline__ const DayCtx& day_ctx(const Dev& D) { return *D.today; }
 
+// A batch kernel (one launch, community = blockIdx.y) keeps its community's Dev in shared memory: copied into registers
+// (`const Dev D = devs[blockIdx.y]`) it cost up to twice the registers of the single-community kernel, whose Dev is a kernel
+// parameter in the constant bank (k_trials 78 against 32, k_active 116 against 60).
+#define BATCH_DEV(D, devs)                                                                                                    \
+    __shared__ Dev s_dev_;                                                                                                    \
+    {                                                                                                                         \
+        const unsigned int* src_ = reinterpret_cast<const unsigned int*>(devs + blockIdx.y);                                  \
+        unsigned int* dst_ = reinterpret_cast<unsigned int*>(&s_dev_);                                                        \
+        for (unsigned int i_ = threadIdx.x; i_ < sizeof(Dev) / 4; i_ += blockDim.x) dst_[i_] = src_[i_];                      \
+    }                                                                                                                         \
+    __syncthreads();                                                                                                          \
+    const Dev& D = s_dev_;
+
 // append n entries to a device list whose length lives at `counter`; one atomic per coalesced group of callers
 __device__ __forceinline__ unsigned int list_reserve(unsigned int* counter) {
     cg::coalesced_group g = cg::coalesced_threads();
@@ -182,88 +195,150 @@ __device__ __forceinline__ void k_scan_body(const Dev& D) {
         }
 }
 __global__ void __launch_bounds__(TPB) k_scan(const Dev D) { k_scan_body(D); }
-__global__ void __launch_bounds__(TPB) k_scan_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_scan_body(D); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB) k_scan_b(const Dev* __restrict__ devs) { BATCH_DEV(D, devs) k_scan_body(D); }   // one launch, replicate = blockIdx.y
 
 // ---------------------------------------------------------------------------------------------
-// k_active: one thread per active agent, in the id order k_scan left them in.
+// k_active: today's active agents in the id order k_scan left them in, a block takes 256 of them at a time, in two halves.
+//   agents : one thread per agent: timeline, status byte, home, day location and patron row requested at once; the activity
+//            window, admissions / discharges, and where the agent is infectious today (Person.cpp:475-486,
+//            Community.cpp:1031-1035): home or hospital, day location, up to five distinct patronised places. Every place
+//            becomes one 16-byte entry of the block's shared-memory list (position from a shared-memory counter).
+//   places : one thread per entry: Community::flagInfectedLocation (Community.cpp:788-791). The location's static words, the
+//            pressure RED, the slot atomic and the flag-record reservation are issued back to back (one round trip); only a
+//            location's first flag of the day needs a second one (hot list, hot hospitals).
+// An agent's places used to be walked by its own thread through arrays in local memory: every slot atomic had to return before
+// the next place could be issued (the store of the result waited for it), a dependent chain of up to 2 x 7 round trips per
+// thread and 23 % of the kernel's stall samples in a large epidemic (profiles/r2_v6_*). Here every place is its own thread and
+// nothing is kept in an indexed array.
 // ---------------------------------------------------------------------------------------------
+#define ACT_MAXL 7            // home or hospital, day location, five distinct patronised places (Community.cpp:279-288)
+struct __align__(16) ActEntry { int loc; unsigned int pid; unsigned long long c; };   // loc < 0: ~(public index); c = pressure | strain << 56
+
+// Community::public_activity draws of one agent as gen_visits makes them, kept in registers: the distinct places in qs[0..4]
+// in order of first appearance, their multiplicities six bits each in `hours` (k <= 31). Returns the number of distinct places.
+__device__ __forceinline__ int gen_visits_r(const Dev& D, const DayCtx& cx, const unsigned int pid, const int npat, const PRow& row, unsigned int (&qs)[5], unsigned int& hours) {
+    const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
+    const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
+    uint4 b = philox4x32_10(make_uint4(0u, pid, 0u, dp), key);
+    hours = 0u;
+    int k;
+    if (b.x < D.visit_thr[0]) return 0;
+    else if (b.x < D.visit_thr[1]) k = 1;
+    else if (b.x < D.visit_thr[2]) k = 2;
+    else if (b.x < D.visit_thr[3]) k = 3;
+    else k = (int) table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
+    int nv = 0;
+    const bool avoiding = prow_rank(row.w[1], row.w[2]) < cx.sd_rank;
+    for (int i = 0; i < k; ++i) {
+        const unsigned int idx1 = (unsigned int) i + 1u;              // draw index within the stream (0 was the Poisson draw)
+        if ((idx1 & 3u) == 0) b = philox4x32_10(make_uint4(idx1 >> 2, pid, 0u, dp), key);
+        const unsigned int w = idx1 & 3u;
+        const unsigned int x = w == 0 ? b.x : w == 1 ? b.y : w == 2 ? b.z : b.w;
+        const unsigned int e = prow_entry(row, __umulhi(x, (unsigned int) npat));
+        if (((e >> PROW_HIGH_BIT) & 1u) && avoiding) continue;
+        const unsigned int q = e & PROW_Q_MASK;
+        int t = nv;
+#pragma unroll
+        for (int u = 4; u >= 0; --u) if (u < nv && qs[u] == q) t = u;
+        if (t == nv) {
+#pragma unroll
+            for (int u = 0; u < 5; ++u) if (u == nv) qs[u] = q;
+            ++nv;
+        }
+        hours += 1u << (6 * t);
+    }
+    return nv;
+}
+
+__device__ __forceinline__ void act_emit(ActEntry* s_e, unsigned int* s_n, const int loc, const unsigned int pid, const unsigned long long c) {
+    const unsigned int k = atomicAdd(s_n, 1u);
+    ActEntry e; e.loc = loc; e.pid = pid; e.c = c;
+    s_e[k] = e;
+}
+
 __device__ __forceinline__ void k_active_body(const Dev& D) {
+    __shared__ ActEntry s_e[ACT_MAXL * TPB];
+    __shared__ unsigned int s_n[2];                        // entries of the current round / of the next one (reset while idle)
     pdl_wait();
     Counters* const ctr = D.ctr;
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n = min(ctr->n_active, D.cap_active);
-    unsigned int nflag = 0, ntoday = 0;
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const unsigned int p = D.active_list[i];
-        CABM_CHECK(D, p < D.N && p >= D.own_lo && p < D.own_hi);
-        // everything of the agent is requested at once; its activity window is a function of the timeline (tl_until)
-        const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
-        const unsigned char pb = D.pbyte[p];
-        const int from = t0.infected, until = tl_until(t0, t1);
-        CABM_CHECK(D, from <= day && day <= until && D.imm[p] != 0);                       // a set bit means: inside the window today
-        if (until <= day) atomicAnd(&D.actbits[p >> 5], ~(1u << (p & 31)));                 // last day of the window: out of the set from tomorrow on
-        if (day < from || day > until) continue;                                            // (days were skipped by the caller: nothing to do any more)
-        ntoday++;
-        const int hm = D.home[p], dl = D.day_loc[p];
-        const PRow row = prow_load(D.prow, p);                                     // the patron row, in flight with the rest of the agent's state
-        const bool inhosp = tl_in(t0.hosp_begin, t0.severe_end, day);
-        const unsigned char npb = (unsigned char) ((pb & ~PB_INHOSP) | (inhosp ? PB_INHOSP : 0));
-        if (npb != pb) {                                                           // admissions and discharges: the status byte and the bit k_visit reads
-            D.pbyte[p] = npb;
-            if (inhosp) atomicOr(&D.inhosp[p >> 5], 1u << (p & 31)); else atomicAnd(&D.inhosp[p >> 5], ~(1u << (p & 31)));
-        }
-        if (!tl_in(t0.infectious_begin, t0.infectious_end, day)) continue;
-        // where this agent is infectious today (Person.cpp:475-486, Community.cpp:1031-1035): up to 2 + MAXV places
-        int locs[2 + MAXV]; unsigned long long cs[2 + MAXV]; int nl = 0;
-        const unsigned long long c = (unsigned long long) __double2ll_rn(CABM_MUL((double) t1.rel_inf, 4294967296.0));
-        if (inhosp) { const int h = D.loc_hospital[hm]; if (h >= 0 && c) { locs[0] = h; cs[0] = c; nl = 1; } }
-        else {
-            if (c) { locs[0] = hm; cs[0] = c; nl = 1; }
-            if (dl >= 0 && c && !(tl_in(t0.severe_begin, t0.severe_end, day) || tl_in(t1.critical_begin, t1.critical_end, day))) { locs[nl] = dl; cs[nl] = c; nl++; }
+    unsigned int nflag = 0, ntoday = 0, round = 0;
+    if (threadIdx.x < 2) s_n[threadIdx.x] = 0;
+    __syncthreads();
+    for (unsigned int base = blockIdx.x * TPB; base < n; base += gridDim.x * TPB, round ^= 1u) {
+        unsigned int* const cnt = &s_n[round];
+        const unsigned int i = base + threadIdx.x;
+        // ---- agents ----
+        if (i < n) do {
+            const unsigned int p = D.active_list[i];
+            CABM_CHECK(D, p < D.N && p >= D.own_lo && p < D.own_hi);
+            // everything of the agent is requested at once; its activity window is a function of the timeline (tl_until)
+            const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
+            const unsigned char pb = D.pbyte[p];
+            const int hm = D.home[p], dl = D.day_loc[p];
+            const PRow row = prow_load(D.prow, p);
+            const int from = t0.infected, until = tl_until(t0, t1);
+            CABM_CHECK(D, from <= day && day <= until && D.imm[p] != 0);                   // a set bit means: inside the window today
+            if (until <= day) atomicAnd(&D.actbits[p >> 5], ~(1u << (p & 31)));             // last day of the window: out of the set from tomorrow on
+            if (day < from || day > until) break;                                           // (days were skipped by the caller: nothing to do any more)
+            ntoday++;
+            const bool inhosp = tl_in(t0.hosp_begin, t0.severe_end, day);
+            const unsigned char npb = (unsigned char) ((pb & ~PB_INHOSP) | (inhosp ? PB_INHOSP : 0));
+            if (npb != pb) {                                                       // admissions and discharges: the status byte and the bit k_visit reads
+                D.pbyte[p] = npb;
+                if (inhosp) atomicOr(&D.inhosp[p >> 5], 1u << (p & 31)); else atomicAnd(&D.inhosp[p >> 5], ~(1u << (p & 31)));
+            }
+            if (!tl_in(t0.infectious_begin, t0.infectious_end, day)) break;
+            CABM_CHECK(D, t1.strain < CABM_N_STRAINS);
+            const unsigned long long tag = (unsigned long long) t1.strain << 56;
+            const unsigned long long c = (unsigned long long) __double2ll_rn(CABM_MUL((double) t1.rel_inf, 4294967296.0));
+            if (inhosp) { const int h = D.loc_hospital[hm]; if (h >= 0 && c) act_emit(s_e, cnt, h, p, c | tag); break; }
+            if (c) act_emit(s_e, cnt, hm, p, c | tag);
+            if (dl >= 0 && c && !(tl_in(t0.severe_begin, t0.severe_end, day) || tl_in(t1.critical_begin, t1.critical_end, day))) act_emit(s_e, cnt, dl, p, c | tag);
             const int npat = pb & PB_NPAT;
             if (npat) {
-                int qs[MAXV], hours[MAXV];
-                const int nv = gen_visits(D, cx, p, npat, row, qs, hours);
-                for (int j = 0; j < nv; ++j) {
-                    const unsigned long long cv = (unsigned long long) __double2ll_rn(CABM_MUL(CABM_MUL((double) t1.rel_inf, (double) hours[j]), 536870912.0));
-                    if (cv) { locs[nl] = D.pub_loc[qs[j]]; cs[nl] = cv; nl++; }
+                unsigned int qs[5], hours;
+                const int nv = gen_visits_r(D, cx, p, npat, row, qs, hours);
+#pragma unroll
+                for (int u = 0; u < 5; ++u) if (u < nv) {
+                    const int hrs = (int) ((hours >> (6 * u)) & 63u);
+                    const unsigned long long cv = (unsigned long long) __double2ll_rn(CABM_MUL(CABM_MUL((double) t1.rel_inf, (double) hrs), 536870912.0));
+                    if (cv) act_emit(s_e, cnt, ~(int) qs[u], p, cv | tag);
                 }
             }
-        }
-        if (nl == 0) continue;
-        for (int k = 0; k < nl; ++k) CABM_CHECK(D, locs[k] >= 0 && (unsigned int) locs[k] < D.L);
-        CABM_CHECK(D, t1.strain < CABM_N_STRAINS && nl <= 2 + MAXV);
-        // Community::flagInfectedLocation (Community.cpp:788-791) for all places of the agent at once: the static loads, the
-        // pressure REDs, the per-location slot atomics and the flag-list reservation are issued back to back (one round trip),
-        // then one reservation covers the hot-list entries of every location this agent was the first to flag
-        unsigned int slots[2 + MAXV]; int ltype[2 + MAXV], lpub[2 + MAXV];
-        cg::coalesced_group g = cg::coalesced_threads();
-        const unsigned int mine = (unsigned int) nl;
-        for (int k = 0; k < nl; ++k) { ltype[k] = D.loc_type[locs[k]]; lpub[k] = D.loc_pub[locs[k]]; }
-        for (int k = 0; k < nl; ++k) {
-            atomicAdd(&D.press[(size_t) locs[k] * CABM_N_STRAINS + t1.strain], cs[k]);
-            slots[k] = atomicAdd(&D.loc_cnt[locs[k]], 1u);
-        }
-        unsigned int nfirst = 0, nfh = 0;
-        for (int k = 0; k < nl; ++k) if (slots[k] == 0) { nfirst++; nfh += ltype[k] == CABM_HOSPITAL ? 1u : 0u; }
-        // flag records, hot-list entries and hot hospitals reserved together: the three counters are hit by every warp of the
-        // grid, and in a large epidemic their round trips (same-address atomics queue up) were a quarter of the kernel
-        unsigned int base, hbase, hhbase;
-        list_reserve3(&D.ctr->n_flags, mine, &D.ctr->n_hot, nfirst, &D.ctr->n_hot_hosp, nfh, base, hbase, hhbase);
-        for (int k = 0; k < nl; ++k) {
-            const unsigned int f = base + k;
-            if (f < D.cap_flags) { FlagRaw r; r.loc = locs[k]; r.slot = slots[k]; r.pid = p; r.pad = 0; r.c = cs[k] | ((unsigned long long) t1.strain << 56); D.flags_raw[f] = r; }
-            else atomicOr(&D.ctr->overflow, 128u);
-            if (slots[k] == 0) {
-                const unsigned int i = hbase++;
-                if (i < D.cap_hot) {
-                    D.hot_list[i] = locs[k]; D.loc_hot[locs[k]] = (int) i;
-                    if (ltype[k] == CABM_HOSPITAL) { const unsigned int j = hhbase++; if (j < D.cap_hot) D.hot_hosp[j] = (int) i; }
-                } else atomicOr(&D.ctr->overflow, 2u);
-                if (lpub[k] >= 0) atomicOr(&D.pub_hot[lpub[k] >> 5], 1u << (lpub[k] & 31));
+        } while (false);
+        __syncthreads();
+        const unsigned int total = *cnt;
+        if (threadIdx.x == 0) s_n[round ^ 1u] = 0;                                          // nobody touches the other counter until the next round
+        CABM_CHECK(D, total <= ACT_MAXL * TPB);
+        // ---- places ----
+        for (unsigned int j = threadIdx.x; j < total; j += TPB) {
+            const ActEntry e = s_e[j];
+            int loc = e.loc, lpub;
+            if (loc < 0) { lpub = ~loc; CABM_CHECK(D, (unsigned int) lpub < D.Q); loc = D.pub_loc[lpub]; } else lpub = D.loc_pub[loc];
+            CABM_CHECK(D, loc >= 0 && (unsigned int) loc < D.L);
+            const int ltype = D.loc_type[loc];
+            const unsigned int strain = (unsigned int) (e.c >> 56);
+            atomicAdd(&D.press[(size_t) loc * CABM_N_STRAINS + strain], e.c & 0x00FFFFFFFFFFFFFFull);
+            const unsigned int slot = atomicAdd(&D.loc_cnt[loc], 1u);
+            const unsigned int f = list_reserve(&ctr->n_flags);                             // does not depend on the slot: same round trip
+            if (f < D.cap_flags) { FlagRaw r; r.loc = loc; r.slot = slot; r.pid = e.pid; r.pad = 0; r.c = e.c; D.flags_raw[f] = r; }
+            else atomicOr(&ctr->overflow, 128u);
+            if (slot == 0) {                                                                // the location's first flag today: hot from now on
+                const bool fh = ltype == CABM_HOSPITAL;
+                cg::coalesced_group g = cg::coalesced_threads();
+                const unsigned int hi = group_reserve(g, &ctr->n_hot, 1u);
+                const unsigned int hh = group_reserve(g, &ctr->n_hot_hosp, fh ? 1u : 0u);
+                if (hi < D.cap_hot) {
+                    D.hot_list[hi] = loc; D.loc_hot[loc] = (int) hi;
+                    if (fh && hh < D.cap_hot) D.hot_hosp[hh] = (int) hi;
+                } else atomicOr(&ctr->overflow, 2u);
+                if (lpub >= 0) atomicOr(&D.pub_hot[lpub >> 5], 1u << (lpub & 31));
             }
+            nflag++;
         }
-        nflag += mine;
+        __syncthreads();                                                                    // the list is rewritten by the next round
     }
     pdl_launch_dependents();                             // the successor may start launching: only this block's counters are left
     nflag = warp_sum(nflag); ntoday = warp_sum(ntoday);
@@ -273,7 +348,7 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
     }
 }
 __global__ void __launch_bounds__(TPB) k_active(const Dev D) { k_active_body(D); }
-__global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_active_body(D); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB) k_active_b(const Dev* __restrict__ devs) { BATCH_DEV(D, devs) k_active_body(D); }   // one launch, replicate = blockIdx.y
 
 // ---------------------------------------------------------------------------------------------
 // k_visit: every agent with patronised locations that is not in hospital draws its visits (Community.cpp:1006-1039).
@@ -505,7 +580,7 @@ __device__ __forceinline__ void k_visit_body(const Dev& D, const unsigned int bi
     block_work_add<3>(D, ids, vals);
 }
 __global__ void __launch_bounds__(TPB, VIS_MINB) k_visit(const Dev D, const unsigned int bitmap_words) { k_visit_body(D, bitmap_words); }
-__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { const Dev D = devs[blockIdx.y]; k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB, VIS_MINB) k_visit_b(const Dev* __restrict__ devs, const unsigned int bitmap_words) { BATCH_DEV(D, devs) k_visit_body(D, bitmap_words); }   // one launch, replicate = blockIdx.y
 
 __device__ __forceinline__ double hazard_to_T(double hazard) { return CABM_SUB(1.0, cabm_exp(-hazard)); }
 
@@ -643,12 +718,16 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
     if ((threadIdx.x & 31) == 0 && edges && D.shard_rank == 0) atomicAdd(&D.ctr->work[CABM_W_NBR_EDGES], (unsigned long long) edges);
 }
 __global__ void __launch_bounds__(TPB) k_hazard(const Dev D) { k_hazard_body(D); }
-__global__ void __launch_bounds__(TPB) k_hazard_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_hazard_body(D); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB) k_hazard_b(const Dev* __restrict__ devs) { BATCH_DEV(D, devs) k_hazard_body(D); }   // one launch, replicate = blockIdx.y
 
 // ---------------------------------------------------------------------------------------------
 // k_trials: block-sized units: the 256-member items of big rosters, the visit records, the flag scatter, the small items.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_trials_body(const Dev& D) {
+    __shared__ double s_T[TPB];
+    __shared__ int s_begin[TPB], s_src[TPB];
+    __shared__ unsigned int s_off[TPB], s_wsum[TPB / 32];
+    __shared__ unsigned char s_purpose[TPB], s_owner[TPB];
     pdl_wait();
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n_items = min(D.ctr->n_items, D.cap_items), n_vis = min(D.ctr->n_vis, D.cap_vis);
@@ -656,15 +735,20 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
     const unsigned int n_sitems = min(D.ctr->n_sitems, D.cap_sitems);
     const unsigned int u_vis = n_items + (n_vis + TPB - 1) / TPB;
     const unsigned int u_flag = u_vis + (n_flags + TPB - 1) / TPB;
-    const unsigned int units = u_flag + (n_sitems + TPB / 8 - 1) / (TPB / 8);
+    const unsigned int units = u_flag + (n_sitems + TPB - 1) / TPB;
     unsigned int trials = 0;
     for (unsigned int u = blockIdx.x; u < units; u += gridDim.x) {
-        if (u >= u_flag) {                                   // small items: eight lanes per item
-            const unsigned int si = (u - u_flag) * (TPB / 8) + (threadIdx.x >> 3);
+        if (u >= u_flag) {
+            // small items, 256 per unit: one thread resolves one item (descriptor, neighbour, roster bounds, T: every item's
+            // chain in flight at once), a block scan lays the items' members end to end, and the trials run one per lane
+            // over that range, 256 at a time (a household has two or three members: with eight lanes per item, as before,
+            // 70 % of the lanes sat idle through the Philox blocks of the others)
+            const unsigned int si = (u - u_flag) * TPB + threadIdx.x;
+            unsigned int cnt = 0; int begin = 0, src = 0, purpose = 0; double T = 0.0;
             if (si < n_sitems) {
                 const SItem it = D.sitems[si];
-                unsigned int cnt = it.count_purpose >> 8; int begin = it.begin;
-                const int purpose = (int) (it.count_purpose & 0xFFu);
+                cnt = it.count_purpose >> 8; begin = it.begin; src = it.src;
+                purpose = (int) (it.count_purpose & 0xFFu);
                 if (purpose == CABM_P_EXPOSE_NB) {                   // a neighbour household: its roster, unless it keeps its distance today
                     CABM_CHECK(D, begin >= 0 && (unsigned int) begin < D.nbr_off[D.L]);
                     const int nb = D.nbr[begin];
@@ -672,12 +756,32 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
                     const unsigned int b = D.roster_off[nb], e = D.roster_off[nb + 1];
                     cnt = (double) D.loc_risk[nb] > cx.sd ? e - b : 0u; begin = (int) b;
                 }
-                if (cnt) {
-                    CABM_CHECK(D, it.t_idx < 2u * D.cap_hot && (unsigned int) begin + cnt <= D.roster_off[D.L] && (unsigned int) it.src < D.L);
-                    const double T = D.hot_T[it.t_idx];
-                    for (unsigned int m = threadIdx.x & 7; m < cnt; m += 8) trial(D, day, 0, (unsigned int) D.roster[begin + m], it.src, purpose, 0, T, trials);
-                }
+                CABM_CHECK(D, it.t_idx < 2u * D.cap_hot && (unsigned int) begin + cnt <= D.roster_off[D.L] && (unsigned int) src < D.L);
+                T = D.hot_T[it.t_idx];
             }
+            const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+            unsigned int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
+            if (lane == 31) s_wsum[wid] = incl;
+            s_begin[threadIdx.x] = begin; s_src[threadIdx.x] = src; s_purpose[threadIdx.x] = (unsigned char) purpose; s_T[threadIdx.x] = T;
+            __syncthreads();
+            unsigned int off = incl - cnt, total = 0;
+#pragma unroll
+            for (int k = 0; k < TPB / 32; ++k) { const unsigned int c = s_wsum[k]; if (k < (int) wid) off += c; total += c; }
+            s_off[threadIdx.x] = off;
+            for (unsigned int cb = 0; cb < total; cb += TPB) {
+                const unsigned int lo = max(off, cb), hi = min(off + cnt, cb + TPB);
+                for (unsigned int j = lo; j < hi; ++j) s_owner[j - cb] = (unsigned char) threadIdx.x;
+                __syncthreads();
+                const unsigned int j = cb + threadIdx.x;
+                if (j < total) {
+                    const unsigned int t = s_owner[threadIdx.x];
+                    trial(D, day, 0, (unsigned int) D.roster[s_begin[t] + (int) (j - s_off[t])], s_src[t], (int) s_purpose[t], 0, s_T[t], trials);
+                }
+                __syncthreads();
+            }
+            __syncthreads();                                          // the item arrays are rewritten by the block's next unit
         } else if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
             const unsigned int f = (u - u_vis) * TPB + threadIdx.x;
             if (f < n_flags) {
@@ -706,4 +810,4 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
     block_work_add<1>(D, ids, vals);
 }
 __global__ void __launch_bounds__(TPB) k_trials(const Dev D) { k_trials_body(D); }
-__global__ void __launch_bounds__(TPB) k_trials_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_trials_body(D); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB) k_trials_b(const Dev* __restrict__ devs) { BATCH_DEV(D, devs) k_trials_body(D); }   // one launch, replicate = blockIdx.y

@@ -137,7 +137,7 @@ __device__ __forceinline__ void k_gate_body(const Dev& D) {
     pdl_launch_dependents();
 }
 __global__ void __launch_bounds__(128) k_gate(const Dev D) { k_gate_body(D); }
-__global__ void __launch_bounds__(128) k_gate_b(const Dev* __restrict__ devs) { const Dev D = devs[blockIdx.y]; k_gate_body(D); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(128) k_gate_b(const Dev* __restrict__ devs) { BATCH_DEV(D, devs) k_gate_body(D); }   // one launch, replicate = blockIdx.y
 
 // Community::updatePersonStatus (Community.cpp:682-741) for one agent; returns the ledger increments as a bit mask
 __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p, int day) {
@@ -306,7 +306,7 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
     if (s_last) { __threadfence(); close_day(D, close & 1, (close >> 1) & 1); }
 }
 __global__ void __launch_bounds__(128, 8) k_apply_status(const Dev D, const int phase, const int close) { k_apply_status_body(D, phase, close); }
-__global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ devs, const int phase, const int close) { const Dev D = devs[blockIdx.y]; k_apply_status_body(D, phase, close); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ devs, const int phase, const int close) { BATCH_DEV(D, devs) k_apply_status_body(D, phase, close); }   // one launch, replicate = blockIdx.y
 
 // hospital_transmission (Community.cpp:931-941): census = staff + admitted patients; every consumer computes T itself
 __device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, const int hosp, unsigned int* denom_out, unsigned long long* pws) {
@@ -390,7 +390,7 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
     if (lane == 0 && trials) atomicAdd(&D.ctr->work[CABM_W_TRIALS], (unsigned long long) trials);
 }
 __global__ void __launch_bounds__(TPB) k_hosp_import(const Dev D, const int do_hosp, const int do_import) { k_hosp_import_body(D, do_hosp, do_import); }
-__global__ void __launch_bounds__(TPB) k_hosp_import_b(const Dev* __restrict__ devs, const int do_hosp, const int do_import) { const Dev D = devs[blockIdx.y]; k_hosp_import_body(D, do_hosp, do_import); }   // one launch, replicate = blockIdx.y
+__global__ void __launch_bounds__(TPB) k_hosp_import_b(const Dev* __restrict__ devs, const int do_hosp, const int do_import) { BATCH_DEV(D, devs) k_hosp_import_body(D, do_hosp, do_import); }   // one launch, replicate = blockIdx.y
 
 // Community::infect(id, strain) (Community.cpp:550-553): one agent, gate and commit in one go
 __global__ void k_seed_one(const Dev D, const unsigned int pid, const int strain, const int day, int* out, const int echo) {

@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--days", type=int, default=10)
     ap.add_argument("--graph", action="store_true")
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--chunk", type=int, default=0, help="print one line per CHUNK days instead of one for the whole window")
     args = ap.parse_args()
     import covid_abm_b200 as cabm
     import synthpop
@@ -35,17 +36,21 @@ def main():
     A = cabm.Community(P, pop, T, attrs=cabm.abi.immunity_attributes(n, P["seed"]))
     if args.start_day:
         A.run_days(args.start_day)
-    w0 = A.work_counters(); A.device_time_ms()
+    A.device_time_ms()
     if not args.graph:
         A.set_profile(True); A.kernel_times()
-    A.run_days(args.days)
-    ms, launches = A.device_time_ms()
-    w1 = A.work_counters()
-    out = {"agents": n, "start_day": args.start_day, "days": args.days, "device_us_per_day": round(ms * 1e3 / args.days, 2), "launches": launches,
-           "agent_days_per_s": n * args.days / (ms * 1e-3), "work_per_day": {k: (w1[k] - w0[k]) // args.days for k in w1}}
-    if not args.graph:
-        out["kernels_us_per_day"] = {k: round(v[0] * 1e3 / args.days, 2) for k, v in A.kernel_times().items() if v[1]}
-    print(json.dumps(out))
+    chunk = args.chunk if args.chunk > 0 else args.days
+    for d0 in range(0, args.days, chunk):
+        nd = min(chunk, args.days - d0)
+        w0 = A.work_counters()
+        A.run_days(nd)
+        ms, launches = A.device_time_ms()
+        w1 = A.work_counters()
+        out = {"agents": n, "start_day": args.start_day + d0, "days": nd, "device_us_per_day": round(ms * 1e3 / nd, 2), "launches": launches,
+               "agent_days_per_s": n * nd / (ms * 1e-3), "work_per_day": {k: (w1[k] - w0[k]) // nd for k in w1}}
+        if not args.graph:
+            out["kernels_us_per_day"] = {k: round(v[0] * 1e3 / nd, 2) for k, v in A.kernel_times().items() if v[1]}
+        print(json.dumps(out), flush=True)
 
 
 if __name__ == "__main__":
