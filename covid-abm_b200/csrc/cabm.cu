@@ -418,7 +418,8 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     int rc;
     // ---- static agents ----
     std::vector<int> home(pop->home, pop->home + N), dayl(pop->day, pop->day + N);
-    std::vector<unsigned char> age(pop->age, pop->age + N), pflags(N), pbyte(N, 0);
+    std::vector<unsigned char> age(pop->age, pop->age + N), pflags(N);
+    std::vector<AgRec> ag(N);                                                          // zeroed: no infection yet (imm == 0 says so)
     // patronised ("public") locations get a dense index q: the visit pass tests hotness in a shared-memory bitmap over q.
     // The riskiness of a household enters public_activity only through `risk < social_distancing[day]` (Community.cpp:1020),
     // so the patron row carries its RANK among the distinct household values and the day context the matching threshold.
@@ -451,7 +452,10 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         unsigned int& rank = home_rank[home[p]];
         if (rank == 0xFFFFFFFFu) rank = (unsigned int) (std::lower_bound(h->risk_sorted.begin(), h->risk_sorted.end(), pop->loc_risk[home[p]]) - h->risk_sorted.begin());
         { const PRow r = prow_pack(e, np, rank); std::memcpy(&prow[(size_t) p * PROW_WORDS], r.w, sizeof(r.w)); }
-        pbyte[p] = (unsigned char) np;
+        AgRec& a = ag[p];
+        std::memset(&a, 0, sizeof(a));
+        a.home = home[p]; a.day_loc = dayl[p]; a.hospital = pop->loc_hospital[home[p]];
+        a.pbyte = (unsigned char) np; a.prow = prow16_pack(e, np, rank);
     }
     D.Q = (unsigned int) pub_loc.size();
     h->bitmap_words = std::max<unsigned int>(1, (D.Q + 31) / 32);
@@ -491,6 +495,15 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = upload(h, (float**) &D.loc_risk, lrisk)) || (rc = upload(h, (int**) &D.loc_hospital, lhosp)) ||
         (rc = upload(h, (unsigned int**) &D.roster_off, roff)) || (rc = upload(h, (unsigned int**) &D.nbr_off, noff)) ||
         (rc = upload(h, (int**) &D.roster, roster)) || (rc = upload(h, (int**) &D.nbr, nbr))) return rc;
+    {   // the same static words, one 32-byte record per location
+        std::vector<LocS> locs(L);
+        for (uint32_t l = 0; l < L; ++l) {
+            LocS& r = locs[l]; std::memset(&r, 0, sizeof(r));
+            r.roster_begin = roff[l]; r.roster_size = roff[l + 1] - roff[l]; r.nbr_begin = noff[l]; r.nbr_deg = noff[l + 1] - noff[l];
+            r.risk = lrisk[l]; r.pub = loc_pub[l]; r.hospital = lhosp[l]; r.type = ltype[l]; r.flags = lflags[l];
+        }
+        if ((rc = upload(h, (LocS**) &D.locs, locs))) return rc;
+    }
     {   // hospitals, for the census exchange of a sharded community (cabm_shard_patients)
         std::vector<int> hosp_ids;
         for (uint32_t l = 0; l < L; ++l) if (ltype[l] == CABM_HOSPITAL) hosp_ids.push_back((int) l);
@@ -500,21 +513,21 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     }
     // ---- dynamic state ----
     const size_t Q1 = std::max<size_t>(D.Q, 1);
-    if ((rc = dalloc(h, &D.tl0, N, true)) || (rc = dalloc(h, &D.tl1, N, true)) ||
+    if ((rc = dalloc(h, &D.ag, N, true)) ||
         (rc = dalloc(h, &D.imm, N, true)) || (rc = dalloc(h, &D.vax, N, true)) || (rc = dalloc(h, &D.vax_days, (size_t) N * CABM_MAX_DOSES, true)) ||
-        (rc = dalloc(h, &D.quar, N, true)) || (rc = dalloc(h, &D.hosp_count, N, true)) || (rc = dalloc(h, &D.pbyte, N, true)) ||
+        (rc = dalloc(h, &D.quar, N, true)) ||
         (rc = dalloc(h, &D.cand, N)) || (rc = dalloc(h, &D.inf_place, N, true, 0xFF)) || (rc = dalloc(h, &D.inf_by, N, true, 0xFF)) ||
-        (rc = dalloc(h, &D.press, (size_t) L * CABM_N_STRAINS)) || (rc = dalloc(h, &D.loc_cnt, L)) || (rc = dalloc(h, &D.loc_hot, L)) || (rc = dalloc(h, &D.pat_count, L, true)) ||
+        (rc = dalloc(h, &D.locd, L)) || (rc = dalloc(h, &D.pat_count, L, true)) ||
         (rc = dalloc(h, &D.nvis, Q1)) || (rc = dalloc(h, &D.pub_T, Q1)) || (rc = dalloc(h, &D.pub_hot, ((size_t) h->bitmap_words + 3) & ~(size_t) 3)) ||
         (rc = dalloc(h, &D.inhosp, n_rows / 32 + 4, true)) || (rc = dalloc(h, &D.actbits, ((size_t) N + 1023) / 1024 * 32, true)) || (rc = dalloc(h, &D.active_list, (size_t) N))) return rc;
-    CK(cudaMemcpyAsync(D.pbyte, pbyte.data(), N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(D.ag, ag.data(), (size_t) N * sizeof(AgRec), cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----
     D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
     D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + roster.size() / SMALL_ROSTER + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
     if (const char* e = getenv("CABM_LOG_CAP")) D.cap_log = std::max<unsigned long long>(1, strtoull(e, nullptr, 10));   // test knob: force the log-overflow error
     D.cap_sitems = (unsigned int) std::min<size_t>(0x7FFFFFFF, (size_t) L + nbr.size() + 1024);
-    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, (size_t) 2 * D.cap_hot)) || (rc = dalloc(h, &D.sitems, D.cap_sitems)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
+    if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_meta, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, (size_t) 2 * D.cap_hot)) || (rc = dalloc(h, &D.sitems, D.cap_sitems)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
         (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
         (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
         (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||

@@ -2,12 +2,14 @@
 // per-exposure state-transition sampler (Person::infect, Person.cpp:320-494) for sm_100a.
 //
 // Layout (all structure-of-arrays in HBM, one element per agent / location):
-//   agents   : tl0/tl1 (latest Infection, 2 x 16 B), imm (infections per strain),
-//              vax (doses, last dose day, naive flag), quar, hosp_count, pbyte (patron count | flags),
-//              cand (64-bit winner key of today's exposure resolution), prow (20-byte packed patron row),
+//   agents   : ag (one 64-byte record: latest Infection, home, day location, hospital, status byte, patron row -- what the
+//              passes over the active agents read, in one line), imm (infections per strain),
+//              vax (doses, last dose day, naive flag), quar,
+//              cand (64-bit winner key of today's exposure resolution), prow (20-byte packed patron row, streamed by k_visit),
 //              inhosp (one bit per agent: in hospital today), actbits (one bit per agent: inside an infection window)
-//   locations: press[4] (u64 fixed-point infectious pressure by strain, 2^-32 units), hot_idx, nvis,
-//              pat_count + static type/flags/risk/hospital, roster CSR, neighbour CSR
+//   locations: locd (one 64-byte record: press[4] = u64 fixed-point infectious pressure by strain in 2^-32 units, flags today,
+//              hot-list index), nvis, pat_count; static: locs (one 32-byte record) + type/flags/risk/hospital arrays,
+//              roster CSR, neighbour CSR
 // Day-scoped lists (hot locations, active agents, visits landing on hot locations, exposure work
 // items, newly infected agents) are appended with atomics and consumed by grid-stride kernels, so
 // a whole day runs without returning to the host.
@@ -27,6 +29,38 @@ enum { PASS_HH = 3, PASS_NB = 4, PASS_WORK = 5, PASS_SCHOOL = 7, PASS_NH = 8, PA
 struct __align__(16) Tl0 { short infected, infectious_begin, infectious_end, symptom_begin, symptom_end, severe_begin, severe_end, hosp_begin; };
 struct __align__(16) Tl1 { short critical_begin, critical_end, icu_begin, death, report_day; unsigned char strain, detected; float rel_inf; };
 
+// One 64-byte record per agent: everything the passes over the ACTIVE agents need (k_active, the status pass, the hospital
+// pass), so that an active agent costs one line of HBM instead of a sector from each of six arrays. Scattered 32-byte reads
+// run at 40-90 G sectors/s on this GPU (profiles/r2_ubench_gather_rate.txt: 2 M agents out of 21.5 M, six arrays 131 us, one
+// 64-byte record 57 us) and the heavy-epidemic day at 21.5 M agents was bound by exactly that rate. The static members are
+// copies (home, day_loc and the 20-byte patron rows stay as arrays for the kernels that stream them).
+struct __align__(64) AgRec {
+    Tl0 t0; Tl1 t1;                                           // latest Infection (dynamic)
+    int home, day_loc, hospital;                              // static; hospital = loc_hospital[home]
+    unsigned char pbyte, hosp_count; unsigned short pad;      // dynamic: patron count | flags (PB_*), admissions not yet discharged
+    uint4 prow;                                               // static: the patron row in 16 bytes (prow16_*)
+};
+static_assert(sizeof(AgRec) == 64, "AgRec is one 64-byte line");
+
+// Locations the same way. LocS: the static words the flagging, hazard and reset passes need about a location, one 32-byte
+// sector (the separate arrays stay for the passes that stream or rarely touch them). LocD: a location's day state -- pressure by
+// strain, flags today (0 = not hot), index in the hot list -- one 64-byte line that a flag reads and writes once.
+struct __align__(32) LocS {
+    unsigned int roster_begin, roster_size, nbr_begin, nbr_deg;
+    float risk; int pub; int hospital;                       // pub: index among the patronised locations or -1
+    unsigned char type, flags; unsigned short pad;
+};
+static_assert(sizeof(LocS) == 32, "LocS is one sector");
+struct __align__(64) LocD {
+    unsigned long long press[CABM_N_STRAINS];                // u64 fixed point, 2^-32 units
+    unsigned int cnt; int hot; unsigned int pad[6];
+};
+static_assert(sizeof(LocD) == 64 && CABM_N_STRAINS == 4, "LocD is one 64-byte line");
+__device__ __forceinline__ void locd_reset(LocD* d) {           // updateHotLocations for one location: 48 bytes, three stores
+    uint4* q = reinterpret_cast<uint4*>(d);
+    q[0] = make_uint4(0u, 0u, 0u, 0u); q[1] = make_uint4(0u, 0u, 0u, 0u); q[2] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 struct __align__(16) Item { int src; int begin; int count; int purpose; double T; double pad; };   // a 256-member chunk of a big roster
 struct __align__(16) SItem { int src; int begin; unsigned int count_purpose; unsigned int t_idx; };   // a small roster: count << 8 | purpose, T = hot_T[t_idx]
 struct __align__(16) Hit  { unsigned int pid; unsigned int src; unsigned int purpose; unsigned int sub; }; // a trial with U < T, to be gated
@@ -35,6 +69,8 @@ struct __align__(16) Hit  { unsigned int pid; unsigned int src; unsigned int pur
 // k_trials scatters them into one contiguous segment per hot location (Flag), which k_apply_status searches.
 struct __align__(8)  FlagRaw { int loc; unsigned int slot; unsigned int pid; unsigned int pad; unsigned long long c; };
 struct __align__(16) Flag { unsigned int pid; unsigned int pad; unsigned long long c; };
+#define HOT_NOPUB 0x7FFFFFFFu
+#define HOT_IS_HOSP 0x80000000u
 #define FLAG_C(f) ((f).c & 0x00FFFFFFFFFFFFFFull)
 #define FLAG_STRAIN(f) ((int) ((f).c >> 56))
 
@@ -80,9 +116,10 @@ struct Dev {
     const unsigned int* roster_off; const int* roster; const unsigned int* nbr_off; const int* nbr;
     const int* loc_pub;                  // location -> index among patronised ("public") locations, or -1
     const int* pub_loc;                  // [Q] inverse
+    const LocS* locs;                    // the static words of a location in one sector (copies of the arrays above)
     // dynamic agents
-    Tl0* tl0; Tl1* tl1; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
-    unsigned char* hosp_count; unsigned char* pbyte; unsigned long long* cand; int* inf_place; int* inf_by; unsigned int* n_caused;
+    AgRec* ag; unsigned int* imm; unsigned int* vax; short* vax_days; unsigned int* quar;
+    unsigned long long* cand; int* inf_place; int* inf_by; unsigned int* n_caused;
     unsigned int* inhosp;                // [ceil(N / 128) * 4] one bit per agent: in hospital today (k_active keeps it, k_visit reads it)
     // The active set: one bit per agent, set when an infection is committed (infect_event), cleared by k_active on the last day
     // of the agent's activity window. k_active scans it every day (N / 8 bytes: 0.34 MB at 2.7 M agents, 2.7 MB at 21.5 M, i.e.
@@ -92,10 +129,11 @@ struct Dev {
     unsigned int* actbits;               // [ceil(N / 1024) * 32]
     unsigned int* active_list;           // today's active agents, written by k_active in chunks of ascending ids, read by the status pass
     // dynamic locations
-    unsigned long long* press; unsigned int* loc_cnt; int* loc_hot; unsigned int* pat_count;   // loc_cnt: flags today (0 = not hot), loc_hot: index in hot_list
+    LocD* locd; unsigned int* pat_count;                          // locd: pressure, flags today, index in hot_list (day-scoped)
     unsigned int* nvis; double* pub_T; unsigned int* pub_hot;     // [Q], [Q], [ceil(Q/32)] public-location visitor census, T, hot bitmap
     // day lists
     int* hot_list; int* hot_hosp; unsigned int* hot_off; double* hot_T; FlagRaw* flags_raw; Flag* flags; SItem* sitems;
+    unsigned int* hot_meta;              // [i]: public index of hot_list[i] (HOT_NOPUB if none) | HOT_IS_HOSP, for the end-of-day reset
     uint2* visit_rec; Item* items; Hit* hits; unsigned int* newinf_list; unsigned int* patient_list;
     unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_sitems, cap_hits, cap_new, cap_pat; unsigned long long cap_log;
     // outputs
@@ -155,6 +193,31 @@ __device__ __forceinline__ PRow prow_load(const unsigned int* __restrict__ rows,
 #pragma unroll
     for (int k = 0; k < PROW_WORDS; ++k) r.w[k] = q[k];
     return r;
+}
+
+// The same row in 16 bytes for the agent record (k_active draws a handful of rows a day, so the unpacking may cost a few
+// instructions more): a 128-bit little-endian word with entry k at bits 20 k .. 20 k + 19, the riskiness rank at bits 100-123
+// and npat at bits 124-126.
+__host__ __forceinline__ uint4 prow16_pack(const unsigned int e[5], const unsigned int npat, const unsigned int rank) {
+    uint4 r;
+    r.x = e[0] | (e[1] << 20);
+    r.y = (e[1] >> 12) | (e[2] << 8) | (e[3] << 28);
+    r.z = (e[3] >> 4) | (e[4] << 16);
+    r.w = (e[4] >> 16) | (rank << 4) | (npat << 28);
+    return r;
+}
+__host__ __device__ __forceinline__ unsigned int prow16_npat(const uint4& r) { return (r.w >> 28) & 7u; }
+__host__ __device__ __forceinline__ unsigned int prow16_rank(const uint4& r) { return (r.w >> 4) & 0xFFFFFFu; }
+__host__ __device__ __forceinline__ unsigned int prow16_entry(const uint4& r, const unsigned int j) {
+    const unsigned int v = j == 0 ? r.x : j == 1 ? ((r.x >> 20) | (r.y << 12)) : j == 2 ? (r.y >> 8) : j == 3 ? ((r.y >> 28) | (r.z << 4)) : ((r.z >> 16) | (r.w << 16));
+    return v & PROW_ENTRY_MASK;
+}
+// the whole record with four 16-byte loads of one line
+__device__ __forceinline__ AgRec ag_load(const AgRec* ag, const unsigned int p) {     // (no __restrict__: the record is written in the same kernels)
+    const uint4* q = reinterpret_cast<const uint4*>(ag + p);
+    union { AgRec r; uint4 v[4]; } u;
+    u.v[0] = q[0]; u.v[1] = q[1]; u.v[2] = q[2]; u.v[3] = q[3];
+    return u.r;
 }
 
 // Programmatic dependent launch (sm_90+): every kernel of the day pipeline lets its successor start launching when its own

@@ -22,7 +22,7 @@ __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const Infe
     const unsigned int vax = D.vax[pid];
     const int n_doses = (int) (vax & 0xFF); const bool naive_vax = (vax >> 8) & 1; const int last_dose = (int) (short) (vax >> 16);
     Tl0 o0; o0.infected = CABM_I16_MAX; o0.infectious_end = CABM_I16_MIN; o0.symptom_end = CABM_I16_MIN;
-    if (n_inf > 0) o0 = D.tl0[pid];
+    if (n_inf > 0) o0 = D.ag[pid].t0;
 
     // ---- isCrossProtected (Person.cpp:497-535) ----
     bool crossProtected = false;
@@ -183,7 +183,7 @@ __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const Infe
     n1.critical_begin = (short) t_critical_begin; n1.critical_end = (short) t_critical_end; n1.icu_begin = (short) t_icu_begin;
     n1.death = (short) t_death; n1.report_day = (short) report_day; n1.strain = (unsigned char) strain; n1.detected = (unsigned char) detected_state;
     n1.rel_inf = rel_inf;
-    D.tl0[pid] = n0; D.tl1[pid] = n1;
+    D.ag[pid].t0 = n0; D.ag[pid].t1 = n1;
     D.inf_place[pid] = c.has_source ? c.source : -1; D.inf_by[pid] = c.infector;
     const int until = tl_until(n0, n1);
     (void) until;

@@ -83,6 +83,32 @@ __device__ __forceinline__ void list_reserve3(unsigned int* c0, const unsigned i
     b0 = g.shfl(a0, g.size() - 1) + i0 - n0; b1 = g.shfl(a1, g.size() - 1) + i1 - n1; b2 = g.shfl(a2, g.size() - 1) + i2 - n2;
 }
 
+// The same for a whole block (every thread calls it, n* may be 0): warp scans, one thread adds the block's three totals to
+// the counters, two __syncthreads. One returning atomic per counter and BLOCK instead of per warp: the list counters share a
+// line, and the L2 serves returning atomics on one line at 1.5 G/s (profiles/r2_ubench_atomic_rate.txt).
+__device__ __forceinline__ void block_reserve3(unsigned int* c0, const unsigned int n0, unsigned int* c1, const unsigned int n1, unsigned int* c2, const unsigned int n2,
+                                               unsigned int& b0, unsigned int& b1, unsigned int& b2) {
+    __shared__ unsigned int s_w[TPB / 32][3], s_b[3];
+    const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned int i0 = n0, i1 = n1, i2 = n2;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int t0 = __shfl_up_sync(0xffffffffu, i0, o), t1 = __shfl_up_sync(0xffffffffu, i1, o), t2 = __shfl_up_sync(0xffffffffu, i2, o);
+        if (lane >= (unsigned int) o) { i0 += t0; i1 += t1; i2 += t2; }
+    }
+    if (lane == 31) { s_w[wid][0] = i0; s_w[wid][1] = i1; s_w[wid][2] = i2; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        unsigned int tot = 0;
+        for (unsigned int k = 0; k < blockDim.x / 32; ++k) { const unsigned int c = s_w[k][threadIdx.x]; s_w[k][threadIdx.x] = tot; tot += c; }
+        unsigned int* const ctr = threadIdx.x == 0 ? c0 : threadIdx.x == 1 ? c1 : c2;
+        s_b[threadIdx.x] = tot ? atomicAdd(ctr, tot) : 0u;
+    }
+    __syncthreads();
+    b0 = s_b[0] + s_w[wid][0] + i0 - n0; b1 = s_b[1] + s_w[wid][1] + i1 - n1; b2 = s_b[2] + s_w[wid][2] + i2 - n2;
+    __syncthreads();                                        // the arrays are reused by the block's next call
+}
+
 __device__ __forceinline__ unsigned int warp_sum(unsigned int v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -109,8 +135,9 @@ __device__ __forceinline__ void flag_location(const Dev& D, int loc, int strain,
     if (slot == 0) {
         const unsigned int i = list_reserve(&D.ctr->n_hot);
         if (i < D.cap_hot) {
-            D.hot_list[i] = loc; D.loc_hot[loc] = (int) i;
-            if (D.loc_type[loc] == CABM_HOSPITAL) { const unsigned int j = list_reserve(&D.ctr->n_hot_hosp); if (j < D.cap_hot) D.hot_hosp[j] = (int) i; }
+            const int q = D.loc_pub[loc]; const bool hosp = D.loc_type[loc] == CABM_HOSPITAL;
+            D.hot_list[i] = loc; D.locd[loc].hot = (int) i; D.hot_meta[i] = (q >= 0 ? (unsigned int) q : HOT_NOPUB) | (hosp ? HOT_IS_HOSP : 0u);
+            if (hosp) { const unsigned int j = list_reserve(&D.ctr->n_hot_hosp); if (j < D.cap_hot) D.hot_hosp[j] = (int) i; }
         } else atomicOr(&D.ctr->overflow, 2u);
         const int q = D.loc_pub[loc];
         if (q >= 0) atomicOr(&D.pub_hot[q >> 5], 1u << (q & 31));
@@ -216,7 +243,7 @@ struct __align__(16) ActEntry { int loc; unsigned int pid; unsigned long long c;
 
 // Community::public_activity draws of one agent as gen_visits makes them, kept in registers: the distinct places in qs[0..4]
 // in order of first appearance, their multiplicities six bits each in `hours` (k <= 31). Returns the number of distinct places.
-__device__ __forceinline__ int gen_visits_r(const Dev& D, const DayCtx& cx, const unsigned int pid, const int npat, const PRow& row, unsigned int (&qs)[5], unsigned int& hours) {
+__device__ __forceinline__ int gen_visits_r(const Dev& D, const DayCtx& cx, const unsigned int pid, const int npat, const uint4& row, unsigned int (&qs)[5], unsigned int& hours) {
     const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
     const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;
     uint4 b = philox4x32_10(make_uint4(0u, pid, 0u, dp), key);
@@ -228,13 +255,13 @@ __device__ __forceinline__ int gen_visits_r(const Dev& D, const DayCtx& cx, cons
     else if (b.x < D.visit_thr[3]) k = 3;
     else k = (int) table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
     int nv = 0;
-    const bool avoiding = prow_rank(row.w[1], row.w[2]) < cx.sd_rank;
+    const bool avoiding = prow16_rank(row) < cx.sd_rank;
     for (int i = 0; i < k; ++i) {
         const unsigned int idx1 = (unsigned int) i + 1u;              // draw index within the stream (0 was the Poisson draw)
         if ((idx1 & 3u) == 0) b = philox4x32_10(make_uint4(idx1 >> 2, pid, 0u, dp), key);
         const unsigned int w = idx1 & 3u;
         const unsigned int x = w == 0 ? b.x : w == 1 ? b.y : w == 2 ? b.z : b.w;
-        const unsigned int e = prow_entry(row, __umulhi(x, (unsigned int) npat));
+        const unsigned int e = prow16_entry(row, __umulhi(x, (unsigned int) npat));
         if (((e >> PROW_HIGH_BIT) & 1u) && avoiding) continue;
         const unsigned int q = e & PROW_Q_MASK;
         int t = nv;
@@ -258,13 +285,15 @@ __device__ __forceinline__ void act_emit(ActEntry* s_e, unsigned int* s_n, const
 
 __device__ __forceinline__ void k_active_body(const Dev& D) {
     __shared__ ActEntry s_e[ACT_MAXL * TPB];
-    __shared__ unsigned int s_n[2];                        // entries of the current round / of the next one (reset while idle)
+    __shared__ unsigned int s_slot[ACT_MAXL * TPB];        // what the slot atomic of entry j returned
+    __shared__ unsigned short s_first[ACT_MAXL * TPB];     // entries that were their location's first flag today
+    __shared__ unsigned int s_n[2], s_nf[2], s_base[2];    // entries / first flags of the current round and of the next one (reset while idle); list bases
     pdl_wait();
     Counters* const ctr = D.ctr;
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n = min(ctr->n_active, D.cap_active);
     unsigned int nflag = 0, ntoday = 0, round = 0;
-    if (threadIdx.x < 2) s_n[threadIdx.x] = 0;
+    if (threadIdx.x < 2) { s_n[threadIdx.x] = 0; s_nf[threadIdx.x] = 0; }
     __syncthreads();
     for (unsigned int base = blockIdx.x * TPB; base < n; base += gridDim.x * TPB, round ^= 1u) {
         unsigned int* const cnt = &s_n[round];
@@ -273,11 +302,11 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
         if (i < n) do {
             const unsigned int p = D.active_list[i];
             CABM_CHECK(D, p < D.N && p >= D.own_lo && p < D.own_hi);
-            // everything of the agent is requested at once; its activity window is a function of the timeline (tl_until)
-            const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
-            const unsigned char pb = D.pbyte[p];
-            const int hm = D.home[p], dl = D.day_loc[p];
-            const PRow row = prow_load(D.prow, p);
+            // the agent's record: one 64-byte line; its activity window is a function of the timeline (tl_until)
+            const AgRec ar = ag_load(D.ag, p);
+            const Tl0 t0 = ar.t0; const Tl1 t1 = ar.t1;
+            const unsigned char pb = ar.pbyte;
+            const int hm = ar.home, dl = ar.day_loc;
             const int from = t0.infected, until = tl_until(t0, t1);
             CABM_CHECK(D, from <= day && day <= until && D.imm[p] != 0);                   // a set bit means: inside the window today
             if (until <= day) atomicAnd(&D.actbits[p >> 5], ~(1u << (p & 31)));             // last day of the window: out of the set from tomorrow on
@@ -286,20 +315,20 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
             const bool inhosp = tl_in(t0.hosp_begin, t0.severe_end, day);
             const unsigned char npb = (unsigned char) ((pb & ~PB_INHOSP) | (inhosp ? PB_INHOSP : 0));
             if (npb != pb) {                                                       // admissions and discharges: the status byte and the bit k_visit reads
-                D.pbyte[p] = npb;
+                D.ag[p].pbyte = npb;
                 if (inhosp) atomicOr(&D.inhosp[p >> 5], 1u << (p & 31)); else atomicAnd(&D.inhosp[p >> 5], ~(1u << (p & 31)));
             }
             if (!tl_in(t0.infectious_begin, t0.infectious_end, day)) break;
             CABM_CHECK(D, t1.strain < CABM_N_STRAINS);
             const unsigned long long tag = (unsigned long long) t1.strain << 56;
             const unsigned long long c = (unsigned long long) __double2ll_rn(CABM_MUL((double) t1.rel_inf, 4294967296.0));
-            if (inhosp) { const int h = D.loc_hospital[hm]; if (h >= 0 && c) act_emit(s_e, cnt, h, p, c | tag); break; }
+            if (inhosp) { const int h = ar.hospital; if (h >= 0 && c) act_emit(s_e, cnt, h, p, c | tag); break; }
             if (c) act_emit(s_e, cnt, hm, p, c | tag);
             if (dl >= 0 && c && !(tl_in(t0.severe_begin, t0.severe_end, day) || tl_in(t1.critical_begin, t1.critical_end, day))) act_emit(s_e, cnt, dl, p, c | tag);
             const int npat = pb & PB_NPAT;
             if (npat) {
                 unsigned int qs[5], hours;
-                const int nv = gen_visits_r(D, cx, p, npat, row, qs, hours);
+                const int nv = gen_visits_r(D, cx, p, npat, ar.prow, qs, hours);
 #pragma unroll
                 for (int u = 0; u < 5; ++u) if (u < nv) {
                     const int hrs = (int) ((hours >> (6 * u)) & 63u);
@@ -310,35 +339,54 @@ __device__ __forceinline__ void k_active_body(const Dev& D) {
         } while (false);
         __syncthreads();
         const unsigned int total = *cnt;
-        if (threadIdx.x == 0) s_n[round ^ 1u] = 0;                                          // nobody touches the other counter until the next round
         CABM_CHECK(D, total <= ACT_MAXL * TPB);
-        // ---- places ----
+        // The block's flag records and hot-list entries are reserved by ONE thread, once per round (the list counters share a
+        // line; reserved per warp they were a hundred thousand returning atomics on it per day in a large epidemic, and the
+        // wait for them half of this kernel's stall samples). Both reservations are in flight while the block works.
+        unsigned int fbase = 0, hbase = 0;
+        if (threadIdx.x == 0) {
+            s_n[round ^ 1u] = 0; s_nf[round ^ 1u] = 0;                                      // nobody touches the other counters until the next round
+            if (total) fbase = atomicAdd(&ctr->n_flags, total);
+        }
+        // ---- places, the location's line: pressure, slot ----
         for (unsigned int j = threadIdx.x; j < total; j += TPB) {
             const ActEntry e = s_e[j];
-            int loc = e.loc, lpub;
-            if (loc < 0) { lpub = ~loc; CABM_CHECK(D, (unsigned int) lpub < D.Q); loc = D.pub_loc[lpub]; } else lpub = D.loc_pub[loc];
+            int loc = e.loc;
+            if (loc < 0) { CABM_CHECK(D, (unsigned int) ~loc < D.Q); loc = D.pub_loc[~loc]; s_e[j].loc = loc; }
             CABM_CHECK(D, loc >= 0 && (unsigned int) loc < D.L);
-            const int ltype = D.loc_type[loc];
             const unsigned int strain = (unsigned int) (e.c >> 56);
-            atomicAdd(&D.press[(size_t) loc * CABM_N_STRAINS + strain], e.c & 0x00FFFFFFFFFFFFFFull);
-            const unsigned int slot = atomicAdd(&D.loc_cnt[loc], 1u);
-            const unsigned int f = list_reserve(&ctr->n_flags);                             // does not depend on the slot: same round trip
-            if (f < D.cap_flags) { FlagRaw r; r.loc = loc; r.slot = slot; r.pid = e.pid; r.pad = 0; r.c = e.c; D.flags_raw[f] = r; }
-            else atomicOr(&ctr->overflow, 128u);
-            if (slot == 0) {                                                                // the location's first flag today: hot from now on
-                const bool fh = ltype == CABM_HOSPITAL;
-                cg::coalesced_group g = cg::coalesced_threads();
-                const unsigned int hi = group_reserve(g, &ctr->n_hot, 1u);
-                const unsigned int hh = group_reserve(g, &ctr->n_hot_hosp, fh ? 1u : 0u);
-                if (hi < D.cap_hot) {
-                    D.hot_list[hi] = loc; D.loc_hot[loc] = (int) hi;
-                    if (fh && hh < D.cap_hot) D.hot_hosp[hh] = (int) hi;
-                } else atomicOr(&ctr->overflow, 2u);
-                if (lpub >= 0) atomicOr(&D.pub_hot[lpub >> 5], 1u << (lpub & 31));
-            }
+            atomicAdd(&D.locd[loc].press[strain], e.c & 0x00FFFFFFFFFFFFFFull);
+            const unsigned int slot = atomicAdd(&D.locd[loc].cnt, 1u);
+            s_slot[j] = slot;
+            if (slot == 0) s_first[atomicAdd(&s_nf[round], 1u)] = (unsigned short) j;       // the location's first flag today: hot from now on
             nflag++;
         }
-        __syncthreads();                                                                    // the list is rewritten by the next round
+        if (threadIdx.x == 0) s_base[0] = fbase;
+        __syncthreads();
+        const unsigned int nfirst = s_nf[round];
+        if (threadIdx.x == 0 && nfirst) hbase = atomicAdd(&ctr->n_hot, nfirst);
+        // ---- the flag records, coalesced ----
+        for (unsigned int j = threadIdx.x; j < total; j += TPB) {
+            const ActEntry e = s_e[j];
+            const unsigned int f = s_base[0] + j;
+            if (f < D.cap_flags) { FlagRaw r; r.loc = e.loc; r.slot = s_slot[j]; r.pid = e.pid; r.pad = 0; r.c = e.c; D.flags_raw[f] = r; }
+            else atomicOr(&ctr->overflow, 128u);
+        }
+        if (threadIdx.x == 0) s_base[1] = hbase;
+        __syncthreads();
+        // ---- the locations that became hot ----
+        for (unsigned int k = threadIdx.x; k < nfirst; k += TPB) {
+            const int loc = s_e[s_first[k]].loc;
+            const LocS ls = D.locs[loc];                                                    // (only a first flag needs the static record)
+            const unsigned int hi = s_base[1] + k;
+            if (hi < D.cap_hot) {
+                D.hot_list[hi] = loc; D.locd[loc].hot = (int) hi;
+                D.hot_meta[hi] = (ls.pub >= 0 ? (unsigned int) ls.pub : HOT_NOPUB) | (ls.type == CABM_HOSPITAL ? HOT_IS_HOSP : 0u);   // for the end-of-day reset
+                if (ls.type == CABM_HOSPITAL) { const unsigned int hh = list_reserve(&ctr->n_hot_hosp); if (hh < D.cap_hot) D.hot_hosp[hh] = (int) hi; }
+            } else atomicOr(&ctr->overflow, 2u);
+            if (ls.pub >= 0) atomicOr(&D.pub_hot[ls.pub >> 5], 1u << (ls.pub & 31));
+        }
+        __syncthreads();                                                                    // the lists are rewritten by the next round
     }
     pdl_launch_dependents();                             // the successor may start launching: only this block's counters are left
     nflag = warp_sum(nflag); ntoday = warp_sum(ntoday);
@@ -644,19 +692,22 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
     const cabm_params* __restrict__ par = D.par;
     const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
     unsigned int edges = 0;
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_hot; i += gridDim.x * blockDim.x) {
-        const int loc = D.hot_list[i];
-        CABM_CHECK(D, loc >= 0 && (unsigned int) loc < D.L && D.loc_hot[loc] == (int) i);
+    for (unsigned int i0 = blockIdx.x * blockDim.x; i0 < n_hot; i0 += gridDim.x * blockDim.x) {       // block-uniform: the reservation below is the block's
+        const unsigned int i = i0 + threadIdx.x;
+        const bool have = i < n_hot;
+        const int loc = D.hot_list[have ? i : i0];                  // (idle threads of the last round read the round's first location and reserve nothing)
+        CABM_CHECK(D, loc >= 0 && (unsigned int) loc < D.L && (!have || D.locd[loc].hot == (int) i));
         // everything that depends on `loc` only is loaded in one go (one round trip)
-        const int type = D.loc_type[loc];
-        const unsigned int cnt = D.loc_cnt[loc];
-        const ulonglong2* pw = reinterpret_cast<const ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
+        const LocS ls = D.locs[loc];                          // one sector
+        const unsigned int cnt = D.locd[loc].cnt;             // one line
+        const ulonglong2* pw = reinterpret_cast<const ulonglong2*>(D.locd[loc].press);
         const ulonglong2 pa = pw[0], pb = pw[1];
-        const unsigned int rb = D.roster_off[loc], size = D.roster_off[loc + 1] - rb;
-        const unsigned int nb0 = D.nbr_off[loc], deg = D.nbr_off[loc + 1] - nb0;
-        const float lrisk = D.loc_risk[loc];
-        const unsigned char lf = D.loc_flags[loc];
-        const int q = D.loc_pub[loc];
+        const int type = ls.type;
+        const unsigned int rb = ls.roster_begin, size = ls.roster_size;
+        const unsigned int nb0 = ls.nbr_begin, deg = ls.nbr_deg;
+        const float lrisk = ls.risk;
+        const unsigned char lf = ls.flags;
+        const int q = ls.pub;
         const unsigned long long pws[4] = { pa.x, pa.y, pb.x, pb.y };
         const double w = CABM_MUL((double) (pws[0] + pws[1] + pws[2] + pws[3]), 1.0 / 4294967296.0);
         double T = 0.0, Ts = 0.0; unsigned int denom = size; int purpose = CABM_P_EXPOSE_HH;
@@ -664,8 +715,8 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
         if (type == CABM_HOUSE) {
             T = hazard_to_T(CABM_MUL(CABM_MUL(par->haz_mult[CABM_HOUSE], cx.season), w));
             const bool risky = (double) lrisk > cx.sd;
-            if (risky) { Ts = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_N_LOCTYPES], cx.season), w), (double) (int) size)); edges += deg; }
-            if (risky && Ts > 0.0) n_nb = deg;
+            if (risky) { Ts = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_N_LOCTYPES], cx.season), w), (double) (int) size)); if (have) edges += deg; }
+            if (have && risky && Ts > 0.0) n_nb = deg;
         } else if (type == CABM_WORK) {
             denom = size + (q >= 0 ? D.nvis[q] : 0u);
             const bool closed = !(lf & LF_ESSENTIAL) && cx.business_closure != 0.0;
@@ -683,12 +734,13 @@ __device__ __forceinline__ void k_hazard_body(const Dev& D) {
             if (size >= 2) T = hazard_to_T(CABM_DIV(CABM_MUL(CABM_MUL(par->haz_mult[CABM_NURSINGHOME], cx.season), w), CABM_SUB((double) (int) size, 1.0)));
             purpose = CABM_P_EXPOSE_NH;
         }                                                     // hospitals are left to k_hosp_import: T stays 0 here, no items
-        const bool own = type != CABM_HOSPITAL && T > 0.0;
+        const bool own = have && type != CABM_HOSPITAL && T > 0.0;
         const unsigned int n_small = n_nb + (own && size <= SMALL_ROSTER ? 1u : 0u);
         const unsigned int n_big = own && size > SMALL_ROSTER ? (size + CHUNK - 1) / CHUNK : 0u;
         // this location's segment of the sorted flag array, its small items and its big items: one round trip
         unsigned int seg, sbase, ibase;
-        list_reserve3(&D.ctr->n_seg, cnt, &D.ctr->n_sitems, n_small, &D.ctr->n_items, n_big, seg, sbase, ibase);
+        block_reserve3(&D.ctr->n_seg, have ? cnt : 0u, &D.ctr->n_sitems, n_small, &D.ctr->n_items, n_big, seg, sbase, ibase);
+        if (!have) continue;
         D.hot_off[i] = seg;
         CABM_CHECK(D, cnt >= 1 && (unsigned long long) seg + cnt <= D.cap_flags && (q < 0 || (unsigned int) q < D.Q));
         if (type == CABM_HOSPITAL) continue;
@@ -724,10 +776,8 @@ __global__ void __launch_bounds__(TPB) k_hazard_b(const Dev* __restrict__ devs) 
 // k_trials: block-sized units: the 256-member items of big rosters, the visit records, the flag scatter, the small items.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void k_trials_body(const Dev& D) {
-    __shared__ double s_T[TPB];
-    __shared__ int s_begin[TPB], s_src[TPB];
-    __shared__ unsigned int s_off[TPB], s_wsum[TPB / 32];
-    __shared__ unsigned char s_purpose[TPB], s_owner[TPB];
+    __shared__ unsigned char s_owner[TPB / 32][32];
+    const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     pdl_wait();
     const DayCtx& cx = day_ctx(D); const int day = cx.day;
     const unsigned int n_items = min(D.ctr->n_items, D.cap_items), n_vis = min(D.ctr->n_vis, D.cap_vis);
@@ -739,10 +789,10 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
     unsigned int trials = 0;
     for (unsigned int u = blockIdx.x; u < units; u += gridDim.x) {
         if (u >= u_flag) {
-            // small items, 256 per unit: one thread resolves one item (descriptor, neighbour, roster bounds, T: every item's
-            // chain in flight at once), a block scan lays the items' members end to end, and the trials run one per lane
-            // over that range, 256 at a time (a household has two or three members: with eight lanes per item, as before,
-            // 70 % of the lanes sat idle through the Philox blocks of the others)
+            // small items, 32 per warp: one lane resolves one item (descriptor, neighbour, roster bounds, T: every item's chain
+            // in flight at once), a warp scan lays the items' members end to end, and the trials run one per lane over that
+            // range, 32 at a time (a household has two or three members: with eight lanes per item, as before, 70 % of the lanes
+            // sat idle through the Philox blocks of the others). Warp-synchronous: no block barrier on the path.
             const unsigned int si = (u - u_flag) * TPB + threadIdx.x;
             unsigned int cnt = 0; int begin = 0, src = 0, purpose = 0; double T = 0.0;
             if (si < n_sitems) {
@@ -753,43 +803,36 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
                     CABM_CHECK(D, begin >= 0 && (unsigned int) begin < D.nbr_off[D.L]);
                     const int nb = D.nbr[begin];
                     CABM_CHECK(D, nb >= 0 && (unsigned int) nb < D.L);
-                    const unsigned int b = D.roster_off[nb], e = D.roster_off[nb + 1];
-                    cnt = (double) D.loc_risk[nb] > cx.sd ? e - b : 0u; begin = (int) b;
+                    const LocS ls = D.locs[nb];
+                    cnt = (double) ls.risk > cx.sd ? ls.roster_size : 0u; begin = (int) ls.roster_begin;
                 }
                 CABM_CHECK(D, it.t_idx < 2u * D.cap_hot && (unsigned int) begin + cnt <= D.roster_off[D.L] && (unsigned int) src < D.L);
                 T = D.hot_T[it.t_idx];
             }
-            const unsigned int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
             unsigned int incl = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
-            if (lane == 31) s_wsum[wid] = incl;
-            s_begin[threadIdx.x] = begin; s_src[threadIdx.x] = src; s_purpose[threadIdx.x] = (unsigned char) purpose; s_T[threadIdx.x] = T;
-            __syncthreads();
-            unsigned int off = incl - cnt, total = 0;
-#pragma unroll
-            for (int k = 0; k < TPB / 32; ++k) { const unsigned int c = s_wsum[k]; if (k < (int) wid) off += c; total += c; }
-            s_off[threadIdx.x] = off;
-            for (unsigned int cb = 0; cb < total; cb += TPB) {
-                const unsigned int lo = max(off, cb), hi = min(off + cnt, cb + TPB);
-                for (unsigned int j = lo; j < hi; ++j) s_owner[j - cb] = (unsigned char) threadIdx.x;
-                __syncthreads();
-                const unsigned int j = cb + threadIdx.x;
-                if (j < total) {
-                    const unsigned int t = s_owner[threadIdx.x];
-                    trial(D, day, 0, (unsigned int) D.roster[s_begin[t] + (int) (j - s_off[t])], s_src[t], (int) s_purpose[t], 0, s_T[t], trials);
-                }
-                __syncthreads();
+            const unsigned int off = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
+            for (unsigned int cb = 0; cb < total; cb += 32) {
+                const unsigned int lo = max(off, cb), hi = min(off + cnt, cb + 32);
+                for (unsigned int j = lo; j < hi; ++j) s_owner[wid][j - cb] = (unsigned char) lane;
+                __syncwarp();
+                const unsigned int j = cb + lane;
+                const unsigned int t = j < total ? s_owner[wid][lane] : 0u;
+                const int t_begin = __shfl_sync(0xffffffffu, begin, t), t_src = __shfl_sync(0xffffffffu, src, t), t_purpose = __shfl_sync(0xffffffffu, purpose, t);
+                const unsigned int t_off = __shfl_sync(0xffffffffu, off, t);
+                const double t_T = __shfl_sync(0xffffffffu, T, t);
+                if (j < total) trial(D, day, 0, (unsigned int) D.roster[t_begin + (int) (j - t_off)], t_src, t_purpose, 0, t_T, trials);
+                __syncwarp();
             }
-            __syncthreads();                                          // the item arrays are rewritten by the block's next unit
         } else if (u >= u_vis) {                                    // scatter the day's flags into per-location segments (offsets from k_hazard)
             const unsigned int f = (u - u_vis) * TPB + threadIdx.x;
             if (f < n_flags) {
                 const FlagRaw r = D.flags_raw[f];
-                CABM_CHECK(D, r.loc >= 0 && (unsigned int) r.loc < D.L && r.pid < D.N && (unsigned int) D.loc_hot[r.loc] < min(D.ctr->n_hot, D.cap_hot) &&
-                              r.slot < D.loc_cnt[r.loc] && (unsigned long long) D.hot_off[D.loc_hot[r.loc]] + r.slot < D.cap_flags);
+                CABM_CHECK(D, r.loc >= 0 && (unsigned int) r.loc < D.L && r.pid < D.N && (unsigned int) D.locd[r.loc].hot < min(D.ctr->n_hot, D.cap_hot) &&
+                              r.slot < D.locd[r.loc].cnt && (unsigned long long) D.hot_off[D.locd[r.loc].hot] + r.slot < D.cap_flags);
                 Flag o; o.pid = r.pid; o.pad = 0; o.c = r.c;
-                D.flags[D.hot_off[D.loc_hot[r.loc]] + r.slot] = o;
+                D.flags[D.hot_off[D.locd[r.loc].hot] + r.slot] = o;
             }
         } else if (u < n_items) {
             const Item it = D.items[u];
@@ -800,8 +843,8 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
             if (v < n_vis) {
                 const uint2 rec = D.visit_rec[v];
                 CABM_CHECK(D, rec.x < D.N && rec.y < D.Q);
-                const double T = D.pub_T[rec.y];
-                if (T > 0.0) trial(D, day, 0, rec.x, D.pub_loc[rec.y], CABM_P_EXPOSE_WORK_VIS, 0, T, trials);
+                const double T = D.pub_T[rec.y]; const int loc = D.pub_loc[rec.y];          // both requested before either is needed
+                if (T > 0.0) trial(D, day, 0, rec.x, loc, CABM_P_EXPOSE_WORK_VIS, 0, T, trials);
             }
         }
     }

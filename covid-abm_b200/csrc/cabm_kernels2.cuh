@@ -95,7 +95,7 @@ __device__ __forceinline__ void event_setup(const Dev& D, const DayCtx& cx, cons
     } else {
         s.begin(D.seed, (unsigned int) cx.day, purpose, pid, src, sub);
         (void) s.next();                                            // the U < T draw
-        c.strain = pick_strain(&D.press[(size_t) src * CABM_N_STRAINS], s.next(), &t_res);
+        c.strain = pick_strain(D.locd[src].press, s.next(), &t_res);
         (void) s.next();                                            // reserved (reference: uniform_choice inside the group)
         c.source = (int) src; c.has_source = true; c.key_a = pid; c.key_b = src;
     }
@@ -141,23 +141,24 @@ __global__ void __launch_bounds__(128) k_gate_b(const Dev* __restrict__ devs) { 
 
 // Community::updatePersonStatus (Community.cpp:682-741) for one agent; returns the ledger increments as a bit mask
 __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p, int day) {
-    const Tl0 t0 = D.tl0[p]; const Tl1 t1 = D.tl1[p];
-    const int hosp = D.loc_hospital[D.home[p]]; const int dl = D.day_loc[p];
+    const AgRec ar = ag_load(D.ag, p);                                             // timeline, day location, hospital, admission count: one line
+    const Tl0 t0 = ar.t0; const Tl1 t1 = ar.t1;
+    const int hosp = ar.hospital; const int dl = ar.day_loc;
     const bool inh = tl_in(t0.hosp_begin, t0.severe_end, day);
     if (hosp >= 0 && dl != hosp) {
         if (inh) {
             if (t0.hosp_begin == day) {                                             // goToHospital (Person.h:248)
-                D.hosp_count[p] = D.hosp_count[p] + 1; atomicAdd(&D.pat_count[hosp], 1u);
-                const unsigned char pb = D.pbyte[p];
+                D.ag[p].hosp_count = ar.hosp_count + 1; atomicAdd(&D.pat_count[hosp], 1u);
+                const unsigned char pb = ar.pbyte;
                 if (!(pb & PB_ONLIST)) {                                            // entries stay on the list; hosp_count == 0 means discharged
-                    D.pbyte[p] = pb | PB_ONLIST;
+                    D.ag[p].pbyte = pb | PB_ONLIST;
                     const unsigned int pi = list_reserve(&D.ctr->n_pat);
                     if (pi < D.cap_pat) D.patient_list[pi] = p; else atomicOr(&D.ctr->overflow, 64u);
                 }
             }
         } else if (day > 0 && tl_in(t0.hosp_begin, t0.severe_end, day - 1)) {     // leaveHospital (Person.h:249, Location.cpp:58-67)
-            const unsigned char c = D.hosp_count[p];
-            if (c > 0) { D.hosp_count[p] = c - 1; atomicSub(&D.pat_count[hosp], 1u); }
+            const unsigned char c = ar.hosp_count;
+            if (c > 0) { D.ag[p].hosp_count = c - 1; atomicSub(&D.pat_count[hosp], 1u); }
         }
     }
     unsigned int m = 0;
@@ -187,9 +188,7 @@ __device__ __forceinline__ void close_day(const Dev& D, const int tick_done, con
         const unsigned int nh = min(c->n_hot_hosp, D.cap_hot);
         for (unsigned int j = threadIdx.x; j < nh; j += blockDim.x) {
             const int loc = D.hot_list[D.hot_hosp[j]];
-            ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc * CABM_N_STRAINS]);
-            pw[0] = make_ulonglong2(0, 0); pw[1] = make_ulonglong2(0, 0);
-            D.loc_cnt[loc] = 0;
+            locd_reset(&D.locd[loc]);
             const int q = D.loc_pub[loc];
             if (q >= 0) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }
         }
@@ -255,8 +254,8 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
                 else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
                 event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);
                 if (c.has_source) {
-                    CABM_CHECK(D, src < D.L && D.loc_cnt[src] >= 1 && (unsigned int) D.loc_hot[src] < min(D.ctr->n_hot, D.cap_hot));
-                    seg_n = D.loc_cnt[src]; seg_off = D.hot_off[D.loc_hot[src]];
+                    CABM_CHECK(D, src < D.L && D.locd[src].cnt >= 1 && (unsigned int) D.locd[src].hot < min(D.ctr->n_hot, D.cap_hot));
+                    seg_n = D.locd[src].cnt; seg_off = D.hot_off[D.locd[src].hot];
                     CABM_CHECK(D, (unsigned long long) seg_off + seg_n <= D.cap_flags);
                     if (seg_n <= INFECTOR_THREAD_MAX) c.infector = pick_infector_thread(D.flags + seg_off, seg_n, c.strain, t_res);
                     else longseg = true;
@@ -310,7 +309,7 @@ __global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ 
 
 // hospital_transmission (Community.cpp:931-941): census = staff + admitted patients; every consumer computes T itself
 __device__ __forceinline__ double hospital_T(const Dev& D, const DayCtx& cx, const int hosp, unsigned int* denom_out, unsigned long long* pws) {
-    const unsigned long long* pw = &D.press[(size_t) hosp * CABM_N_STRAINS];
+    const unsigned long long* pw = D.locd[hosp].press;
     pws[0] = pw[0]; pws[1] = pw[1]; pws[2] = pw[2]; pws[3] = pw[3];
     const unsigned long long tot = pws[0] + pws[1] + pws[2] + pws[3];
     const unsigned int denom = D.roster_off[hosp + 1] - D.roster_off[hosp] + D.pat_count[hosp];
@@ -334,20 +333,13 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
         // and the winner keys of phase 0, which the status pass has finished reading. Independent stores issued first: they
         // drain while the dependent chains of the hospital pass wait for memory. Hot hospitals are reset by close_day.
         const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
-        for (unsigned int i0 = tid; i0 < n_hot; i0 += 4 * nth) {                      // four locations per thread in flight
-            int loc[4], typ[4], q[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) { const unsigned int i = i0 + k * nth; loc[k] = i < n_hot ? D.hot_list[i] : -1; }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) { typ[k] = loc[k] >= 0 ? D.loc_type[loc[k]] : CABM_HOSPITAL; q[k] = loc[k] >= 0 ? D.loc_pub[loc[k]] : -1; }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                if (typ[k] == CABM_HOSPITAL) continue;
-                ulonglong2* pw = reinterpret_cast<ulonglong2*>(&D.press[(size_t) loc[k] * CABM_N_STRAINS]);
-                pw[0] = make_ulonglong2(0, 0); pw[1] = make_ulonglong2(0, 0);
-                D.loc_cnt[loc[k]] = 0;
-                if (q[k] >= 0) { D.nvis[q[k]] = 0; D.pub_T[q[k]] = 0.0; D.pub_hot[q[k] >> 5] = 0; }   // the whole bitmap word: every set bit belongs to a hot location
-            }
+        for (unsigned int i = tid; i < n_hot; i += nth) {                              // location and (public index, hospital?) stream in: no gather before the stores
+            const unsigned int meta = D.hot_meta[i];
+            if (meta & HOT_IS_HOSP) continue;
+            const int loc = D.hot_list[i];
+            locd_reset(&D.locd[loc]);
+            const unsigned int q = meta & HOT_NOPUB;
+            if (q != HOT_NOPUB) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }   // the whole bitmap word: every set bit belongs to a hot location
         }
         const unsigned int n_new0 = min(D.ctr->n_new[0], D.cap_new);
         for (unsigned int i = tid; i < n_new0; i += nth) D.cand[D.newinf_list[i]] = CABM_CAND_EMPTY;
@@ -368,10 +360,10 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
         for (unsigned int i = tid; i < np; i += nth) {
             const unsigned int pid = D.patient_list[i];
             CABM_CHECK(D, pid < D.N);
-            const unsigned int c = D.hosp_count[pid];
+            const unsigned int c = D.ag[pid].hosp_count;
             if (c == 0) continue;
-            const int hosp = D.loc_hospital[D.home[pid]];
-            if (hosp < 0 || D.loc_cnt[hosp] == 0) continue;
+            const int hosp = D.ag[pid].hospital;
+            if (hosp < 0 || D.locd[hosp].cnt == 0) continue;
             unsigned int denom; unsigned long long pws[4];
             const double T = hospital_T(D, cx, hosp, &denom, pws);
             if (T > 0.0) for (unsigned int sub = 0; sub < c; ++sub) trial(D, day, 1, pid, hosp, CABM_P_EXPOSE_HOSP_PAT, sub, T, trials);
@@ -431,7 +423,7 @@ __global__ void k_vaccinate(const Dev D, const unsigned int* pids, const unsigne
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned int p = pids[i];
         const unsigned int imm = D.imm[p]; const bool had_inf = imm != 0;
-        const bool dead = had_inf && D.tl1[p].death <= day;
+        const bool dead = had_inf && D.ag[p].t1.death <= day;
         if (!dead) {
             const unsigned int v = D.vax[p]; const unsigned int nd = v & 0xFF;
             const unsigned int naive = (!had_inf && nd == 0) ? 1u : 0u;
@@ -452,7 +444,7 @@ __global__ void k_gather_infections(const Dev D, const unsigned int* pids, const
         const unsigned int p = pids ? pids[i] : i;
         cabm_infection r; r.person = p; r.infected_by = -1; r.infected_place = -1;
         if (D.imm[p]) {
-            const Tl0 a = D.tl0[p]; const Tl1 b = D.tl1[p];
+            const Tl0 a = D.ag[p].t0; const Tl1 b = D.ag[p].t1;
             r.t[0] = a.infected; r.t[1] = a.infectious_begin; r.t[2] = a.infectious_end; r.t[3] = a.symptom_begin; r.t[4] = a.symptom_end;
             r.t[5] = a.severe_begin; r.t[6] = a.severe_end; r.t[7] = a.hosp_begin; r.t[8] = b.critical_begin; r.t[9] = b.critical_end;
             r.t[10] = b.icu_begin; r.t[11] = b.death; r.report_day = b.report_day; r.strain = b.strain; r.detected_state = b.detected; r.rel_infectiousness = b.rel_inf;
@@ -474,7 +466,7 @@ __global__ void k_gather_infections(const Dev D, const unsigned int* pids, const
 // N-antibody positivity of one person on `day` (Community.cpp:1232-1252)
 __device__ __forceinline__ bool sero_positive(const Dev& D, const cabm_params* par, const unsigned int p, const int day) {
     if (D.imm[p] == 0) return false;
-    const Tl0 a = D.tl0[p];
+    const Tl0 a = D.ag[p].t0;
     const int last_end = max((int) a.infectious_end, (int) a.symptom_end);
     const int tsl = day - last_end;
     const bool converted = (double) a.infected >= par->seroconversion_lag;       // latest infection has the largest infectedBegin
@@ -502,7 +494,7 @@ __global__ void __launch_bounds__(256) k_diagnostics(const Dev D, const int day,
             if (full) bits |= 1u << CABM_D_FULLY_VAXD;
             const unsigned int imm = D.imm[p];
             if (imm) {
-                const Tl0 a = D.tl0[p]; const Tl1 b = D.tl1[p];
+                const Tl0 a = D.ag[p].t0; const Tl1 b = D.ag[p].t1;
                 const int o = full ? CABM_D_BT_INF : CABM_D_UV_INF;
                 if (a.infected == day) bits |= 1u << o;
                 if (a.symptom_begin == day) bits |= 1u << (o + 1);
@@ -542,7 +534,7 @@ __device__ __forceinline__ unsigned int person_bits(const Dev& D, const cabm_par
     const unsigned int imm = D.imm[p], v = D.vax[p], nd = v & 0xFF; const int last_dose = (short) (v >> 16);
     unsigned int b = 0; bool alive = true;
     if (imm) {
-        const Tl0 a = D.tl0[p]; const Tl1 t = D.tl1[p];
+        const Tl0 a = D.ag[p].t0; const Tl1 t = D.ag[p].t1;
         alive = !(t.death <= day);
         b |= CABM_EL_EVER_INFECTED;
         if (t.detected < CABM_N_OUTCOMES && t.report_day <= day) b |= CABM_EL_PRIOR_CASE;
@@ -577,7 +569,7 @@ __global__ void k_detected_today(const Dev D, const int day, unsigned int* out, 
         const unsigned int p = base + threadIdx.x;
         bool hit = false;
         if (p < D.N && D.imm[p]) {
-            const Tl1 b = D.tl1[p];
+            const Tl1 b = D.ag[p].t1;
             hit = b.detected < CABM_N_OUTCOMES && b.report_day == day && !(b.death <= day);
         }
         if (hit) { const unsigned int i = list_reserve(n_out); if (i < cap) out[i] = p; }
@@ -593,8 +585,8 @@ __global__ void k_flags_in(const Dev D, const FlagRaw* __restrict__ in, const un
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const FlagRaw r = in[i];
         const int strain = FLAG_STRAIN(r); const unsigned long long c = FLAG_C(r);
-        atomicAdd(&D.press[(size_t) r.loc * CABM_N_STRAINS + strain], c);
-        const unsigned int slot = atomicAdd(&D.loc_cnt[r.loc], 1u);
+        atomicAdd(&D.locd[r.loc].press[strain], c);
+        const unsigned int slot = atomicAdd(&D.locd[r.loc].cnt, 1u);
         const unsigned int f = list_reserve(&D.ctr->n_flags);
         flag_location(D, r.loc, strain, c, r.pid, slot, f);
     }
@@ -616,8 +608,8 @@ __global__ void k_flags_in_all(const Dev D, const FlagRaw* __restrict__ recv, un
         for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < min(n, cap); i += gridDim.x * blockDim.x) {
             const FlagRaw f = in[i];
             const int strain = FLAG_STRAIN(f); const unsigned long long c = FLAG_C(f);
-            atomicAdd(&D.press[(size_t) f.loc * CABM_N_STRAINS + strain], c);
-            const unsigned int slot = atomicAdd(&D.loc_cnt[f.loc], 1u);
+            atomicAdd(&D.locd[f.loc].press[strain], c);
+            const unsigned int slot = atomicAdd(&D.locd[f.loc].cnt, 1u);
             flag_location(D, f.loc, strain, c, f.pid, slot, list_reserve(&D.ctr->n_flags));
         }
     }
@@ -636,8 +628,8 @@ __global__ void k_flags_pull(const Dev D, const PeerFlags peers, const unsigned 
             const unsigned long long w0 = __ldcv(in + 3 * (size_t) i), w1 = __ldcv(in + 3 * (size_t) i + 1), c_raw = __ldcv(in + 3 * (size_t) i + 2);
             FlagRaw f; f.loc = (int) (unsigned int) w0; f.slot = (unsigned int) (w0 >> 32); f.pid = (unsigned int) w1; f.pad = 0; f.c = c_raw;
             const int strain = FLAG_STRAIN(f); const unsigned long long c = FLAG_C(f);
-            atomicAdd(&D.press[(size_t) f.loc * CABM_N_STRAINS + strain], c);
-            const unsigned int slot = atomicAdd(&D.loc_cnt[f.loc], 1u);
+            atomicAdd(&D.locd[f.loc].press[strain], c);
+            const unsigned int slot = atomicAdd(&D.locd[f.loc].cnt, 1u);
             flag_location(D, f.loc, strain, c, f.pid, slot, list_reserve(&D.ctr->n_flags));
         }
     }
