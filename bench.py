@@ -397,10 +397,12 @@ def bench_ours(args):
         "config": {"workload": f"configs[1]: {n} synthetic agents (tools/synthpop.py seed 20200210), WT+alpha+delta, active-vac parameter set",
                    "days_per_step": DAYS_PER_STEP, "agents": n, "locations": int(pop["n_loc"]), "parallelism": "1 community per GPU" + ("" if world == 1 else f" x {world} replicates"),
                    "l2": "256 MiB flush between steps; consecutive days inside a step reuse L2 as a real run does"},
-        # e2e bytes per day: H2D two day contexts (tick, import) + the day-index reset; D2H the ledger row + (overflow mask, import
-        # count) written to pinned memory by each of the two k_end launches
-        "e2e": {"value": agent_days_all / e2e_max, "unit": "agent-days/s", "h2d_bytes_per_step": DAYS_PER_STEP * (2 * 88 + 4),
-                "d2h_bytes_per_step": DAYS_PER_STEP * (cabm.abi.N_COUNTERS * 8 + 2 * 8), "calls_per_step": DAYS_PER_STEP * 3},
+        # e2e bytes per day: H2D one day context (cabm_tick stages the day, cabm_import of the same day completes it and launches ONE
+        # day graph) + the day-index reset; D2H what the block that closes the day writes into pinned host memory: the day's ledger
+        # row (read by cabm_ledger_row without another device round trip) and four status words (overflow mask, new infections,
+        # day, imported cases)
+        "e2e": {"value": agent_days_all / e2e_max, "unit": "agent-days/s", "h2d_bytes_per_step": DAYS_PER_STEP * (88 + 4),
+                "d2h_bytes_per_step": DAYS_PER_STEP * (cabm.abi.N_COUNTERS * 8 + 4 * 4), "calls_per_step": DAYS_PER_STEP * 3},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note, "kernel_avg_us": dom_ms * 1e3 / max(dom_n, 1),

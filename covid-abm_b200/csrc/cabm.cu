@@ -70,6 +70,11 @@ struct cabm {
     void* nccl_comm = nullptr; int world = 1; size_t xcap = 0, xcap_alloc = 0; unsigned int x_seen = UINT_MAX; FlagRaw* d_xrecv = nullptr; unsigned int* d_xcounts = nullptr; unsigned int* h_xcounts = nullptr;
     Dev* d_batch = nullptr; size_t batch_cap = 0; cudaGraphExec_t batch_graph = nullptr; size_t batch_graph_n = 0;   // cabm_batch_run_days: the communities of the batch, indexed by blockIdx.y
     int infect_seq = 0;                          // cabm_infect: sequence number the kernel echoes into h_pin[1] after the result
+    // cabm_tick only stages its day; the launch happens in the next call into the handle. When that call is cabm_import for the same
+    // day (the simulate_epidemic loop: tick(), then seed_epidemic(), simulator.h:338-374) both run as ONE day graph, 9 launches
+    // instead of 9 + 2 and one host synchronisation instead of two; any other call launches the staged tick first (settle()).
+    bool tick_pending = false; int pending_day = -1;
+    bool row_ok = false;                         // the ledger row in h_pin (written by close_day) is still the device's: no call has touched the ledger since
     int* h_pin = nullptr;                        // pinned, device-visible scratch: single-word results are written by the kernel itself (no staged copy)
     const FlagRaw* peer_flags[CABM_MAX_SHARDS] = { nullptr }; int peer_mode = 0;      // exchange A over peer memory (cudaIpc mappings of the other handles' flag lists)
     int* d_hosp_ids = nullptr; int* d_pat_save = nullptr; int* d_pat_buf = nullptr; unsigned int n_hosp = 0; unsigned int n_flags_own = 0;   // sharding
@@ -308,6 +313,7 @@ static const int SHARD_GROUP = 4;      // days enqueued between two host looks a
 
 
 extern "C" {
+static int settle(cabm_t* h);
 
 int cabm_create(cabm_t** out) {
     if (!out) return CABM_E_ARG;
@@ -319,9 +325,10 @@ int cabm_create(cabm_t** out) {
     h->sms = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
     cudaEventCreate(&h->e0); cudaEventCreate(&h->e1);
-    if (cudaHostAlloc((void**) &h->h_pin, 16 * sizeof(int), cudaHostAllocMapped) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
-    std::memset(h->h_pin, 0, 16 * sizeof(int));
-    h->d.host_status = reinterpret_cast<unsigned int*>(h->h_pin) + 4;       // written by close_day: [0] overflow mask, [1] new infections of the hospital pass + importation
+    if (cudaHostAlloc((void**) &h->h_pin, 64 * sizeof(int), cudaHostAllocMapped) != cudaSuccess) { delete h; *out = nullptr; return CABM_E_CUDA; }
+    std::memset(h->h_pin, 0, 64 * sizeof(int));
+    h->d.host_status = reinterpret_cast<unsigned int*>(h->h_pin) + 4;       // written by close_day: [0] overflow mask, [1] new infections of the hospital pass + importation,
+                                                                            // [2] the day it closed, [12..43] that day's ledger row (h_pin words 16-47)
     {   // device address of the static scratch: once per device, with that device current (it is: cudaGetDevice above)
         void*& addr = g_static_scratch_addr[h->device & 63];
         if (!addr) {
@@ -361,6 +368,8 @@ int cabm_destroy(cabm_t* h) {
 const char* cabm_last_error(const cabm_t* h) { return h ? h->err.c_str() : "null handle"; }
 
 int cabm_set_params(cabm_t* h, const cabm_params* par) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h || !par || !par->prob_first_detection || par->run_length <= 0 || par->run_length > 32000) return CABM_E_ARG;
     cudaSetDevice(h->device);
     const size_t R = (size_t) par->run_length;
@@ -398,6 +407,7 @@ int cabm_set_params(cabm_t* h, const cabm_params* par) {
 }
 
 int cabm_set_timed_intervention(cabm_t* h, int which, const double* v, size_t n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_par || which < 0 || which > 2 || !v || n == 0) return CABM_E_ARG;
     const size_t R = (size_t) h->hpar.run_length;
     for (size_t d = 0; d < R; ++d) h->h_ti[which][d] = v[std::min(d, n - 1)];
@@ -405,6 +415,8 @@ int cabm_set_timed_intervention(cabm_t* h, int which, const double* v, size_t n)
 }
 
 int cabm_load_population(cabm_t* h, const cabm_population* pop) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h || !pop) return CABM_E_ARG;
     if (!h->have_par) { h->err = "cabm_set_params must precede cabm_load_population"; return CABM_E_STATE; }
     if (h->have_pop) { h->err = "population already loaded"; return CABM_E_STATE; }
@@ -543,12 +555,10 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     return CABM_OK;
 }
 
-int cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday) {
-    if (!h) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
-    if (julian_day < 1 || julian_day > 366) return CABM_E_ARG;
+// the staged day of cabm_tick (h_ctx[0]) as its own launch sequence
+static int launch_tick_now(cabm_t* h) {
+    int rc;
     cudaSetDevice(h->device);
-    DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
-    fill_ctx(h, c, sim_day, julian_day, is_weekday);
     CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
     CK(cudaEventRecord(h->e0, h->stream));
@@ -558,28 +568,67 @@ int cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday) {
         CK(cudaGraphLaunch(h->tick_graph, h->stream)); h->launches += h->launches_tick;
     }
     if ((rc = timed_sync(h))) return rc;
+    h->row_ok = true;
     return check_overflow_host(h);
+}
+// every entry point but cabm_import calls this first: a tick that was staged and not yet launched runs now, and its errors are
+// this call's errors
+static int settle(cabm_t* h) {
+    if (!h || !h->tick_pending) return CABM_OK;
+    h->tick_pending = false;
+    return launch_tick_now(h);
+}
+
+int cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday) {
+    if (!h) return CABM_E_ARG; int rc = settle(h); if (rc) return rc;
+    if ((rc = ready(h, sim_day))) return rc;
+    if (julian_day < 1 || julian_day > 366) return CABM_E_ARG;
+    DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
+    fill_ctx(h, c, sim_day, julian_day, is_weekday);
+    if (h->profile || h->d.own_lo != 0 || h->d.own_hi != h->d.N || getenv("CABM_EAGER_TICK")) return launch_tick_now(h);
+    h->tick_pending = true; h->pending_day = sim_day;        // launched by the next call (see tick_pending)
+    return CABM_OK;
 }
 
 int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[CABM_N_STRAINS], int32_t* out_infected) {
-    if (!h || !strain_w) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (!h || !strain_w) return CABM_E_ARG;
+    int rc;
+    if (h->tick_pending && h->pending_day != sim_day && (rc = settle(h))) return rc;
+    if ((rc = ready(h, sim_day))) return rc;
     cudaSetDevice(h->device);
-    DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
-    c.day = sim_day; c.julian_day = 1; c.n_imports = expected > 0 ? import_count(h->hpar.seed, sim_day, expected) : 0;
-    for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
-    CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));   // no k_active in front: publish the context directly
-    CK(cudaEventRecord(h->e0, h->stream));
-    if (h->profile) launch_day(h, false, true, 0);
-    else {
-        if (!h->import_graph && (rc = capture_day(h, &h->import_graph, false, true, 0, &h->launches_import))) return rc;
-        CK(cudaGraphLaunch(h->import_graph, h->stream)); h->launches += h->launches_import;
+    const int n_imports = expected > 0 ? import_count(h->hpar.seed, sim_day, expected) : 0;
+    if (h->tick_pending) {
+        // tick(d) followed by the importation of day d: one day graph, exactly what cabm_run_days replays
+        h->tick_pending = false;
+        DayCtx& c = h->h_ctx[0];
+        c.n_imports = n_imports;
+        for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
+        CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
+        CK(cudaEventRecord(h->e0, h->stream));
+        if (!h->day_graph && (rc = capture_day(h, &h->day_graph, true, true, 1, &h->launches_per_day))) return rc;
+        CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day;
+    } else {
+        DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
+        c.day = sim_day; c.julian_day = 1; c.n_imports = n_imports;
+        for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
+        CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));   // no k_active in front: publish the context directly
+        CK(cudaEventRecord(h->e0, h->stream));
+        if (h->profile) launch_day(h, false, true, 0);
+        else {
+            if (!h->import_graph && (rc = capture_day(h, &h->import_graph, false, true, 0, &h->launches_import))) return rc;
+            CK(cudaGraphLaunch(h->import_graph, h->stream)); h->launches += h->launches_import;
+        }
     }
     if ((rc = timed_sync(h))) return rc;
-    if (out_infected) *out_infected = (int32_t) h->d.host_status[1];               // written by close_day before it zeroes the day counters
+    if (out_infected) *out_infected = (int32_t) h->d.host_status[3];               // winners whose exposure was an import, written by close_day before it zeroes the day counters
+    h->row_ok = true;
     return check_overflow_host(h);
 }
 
 int cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (pid >= h->d.N || strain < 0 || strain >= CABM_N_STRAINS) return CABM_E_ARG;
     cudaSetDevice(h->device);
@@ -597,6 +646,8 @@ int cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_i
 }
 
 int cabm_infect_batch(cabm_t* h, const uint32_t* pids, const uint8_t* strains, size_t n, int sim_day, uint8_t* out_infected) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h || ((!pids || !strains) && n)) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (n == 0) return CABM_OK;
     if (n > 0x7FFFFFFFu || h->d.N >= (1u << 29)) { h->err = "cabm_infect_batch: at most 2^31 calls and 2^29 agents"; return CABM_E_ARG; }
@@ -637,6 +688,7 @@ int cabm_infect_batch(cabm_t* h, const uint32_t* pids, const uint8_t* strains, s
 
 int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                   const double* expected_imports, const double* strain_w) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;
     int rc = ready(h, first_day); if (rc) return rc; if ((rc = ready(h, first_day + n_days - 1))) return rc;
     cudaSetDevice(h->device);
@@ -656,16 +708,19 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
             CK(cudaStreamSynchronize(h->stream)); prof_collect(h);
         }
         if ((rc = timed_sync(h))) return rc;
+        h->row_ok = true;
         return check_overflow(h);
     }
     if (!h->day_graph && (rc = capture_day(h, &h->day_graph, true, true, 1, &h->launches_per_day))) return rc;   // one day (tick + importation), captured once, replayed every day
     for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day; }
     if ((rc = timed_sync(h))) return rc;
+    h->row_ok = true;
     return check_overflow_host(h);
 }
 
 int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                         const double* expected_imports, const double* strain_w) {
+    for (size_t i = 0; hs && i < n; ++i) if (hs[i]) { hs[i]->row_ok = false; const int rc_settle = settle(hs[i]); if (rc_settle) return rc_settle; }
     if (!hs || n == 0 || n > 65535 || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;
     cabm_t* h = hs[0]; if (!h) return CABM_E_ARG;
     int rc = ready(h, first_day); if (rc) return rc; if ((rc = ready(h, first_day + n_days - 1))) return rc;
@@ -732,6 +787,7 @@ int cabm_batch_run_days(cabm_t* const* hs, size_t n, int first_day, int n_days, 
 }
 
 int cabm_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_ok) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || (!pids && n)) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (!h->hpar.immunity_leaky) { h->err = "vaccination requires leaky immunity (Person.cpp:622)"; return CABM_E_STATE; }
     if (n == 0) return CABM_OK;
@@ -749,6 +805,7 @@ int cabm_vaccinate(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8
 }
 
 int cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, int until_day) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || (!pids && n)) return CABM_E_ARG;
     if (!h->have_pop) return CABM_E_STATE;
     if (n == 0) return CABM_OK;
@@ -764,6 +821,7 @@ int cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, int
 }
 
 int cabm_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_par || counter < 0 || counter >= CABM_N_COUNTERS || !out) return CABM_E_ARG;
     cudaSetDevice(h->device);
     const size_t R = (size_t) h->hpar.run_length, m = std::min(n, R);
@@ -772,6 +830,7 @@ int cabm_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n) {
     return CABM_OK;
 }
 int cabm_ledger_table(cabm_t* h, uint64_t* out, size_t n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_par || !out) return CABM_E_ARG;
     cudaSetDevice(h->device);
     const size_t all = (size_t) h->hpar.run_length * CABM_N_COUNTERS, m = std::min(n, all);
@@ -780,18 +839,25 @@ int cabm_ledger_table(cabm_t* h, uint64_t* out, size_t n) {
     return CABM_OK;
 }
 int cabm_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
+    if (h->row_ok && (int) h->d.host_status[2] == sim_day) {                         // the day that was just closed: its row is already in pinned host memory
+        std::memcpy(out, h->d.host_status + 12, CABM_N_COUNTERS * sizeof(uint64_t));
+        return CABM_OK;
+    }
     cudaSetDevice(h->device);
     CK(cudaMemcpy2D(out, sizeof(uint64_t), h->d.ledger + sim_day, (size_t) h->hpar.run_length * sizeof(uint64_t), sizeof(uint64_t), CABM_N_COUNTERS, cudaMemcpyDeviceToHost));
     return CABM_OK;
 }
 int cabm_cumulative_outcomes(cabm_t* h, uint64_t out[CABM_N_OUTCOMES]) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_par || !out) return CABM_E_ARG;
     cudaSetDevice(h->device);
     CK(cudaMemcpy(out, h->d.ctr->cumul, sizeof(uint64_t) * CABM_N_OUTCOMES, cudaMemcpyDeviceToHost));
     return CABM_OK;
 }
 int cabm_work_counters(cabm_t* h, uint64_t out[CABM_N_WORK]) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_par || !out) return CABM_E_ARG;
     cudaSetDevice(h->device);
     CK(cudaMemcpy(out, h->d.ctr->work, sizeof(uint64_t) * CABM_N_WORK, cudaMemcpyDeviceToHost));
@@ -799,6 +865,7 @@ int cabm_work_counters(cabm_t* h, uint64_t out[CABM_N_WORK]) {
 }
 
 int cabm_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     unsigned long long n = 0;
@@ -809,6 +876,7 @@ int cabm_sync_histories(cabm_t* h, cabm_infection* out, size_t cap, size_t* out_
 }
 
 int cabm_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_t cap, size_t* out_n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     unsigned long long n = 0;
@@ -823,6 +891,7 @@ int cabm_sync_histories_from(cabm_t* h, size_t first, cabm_infection* out, size_
 // One community over several handles; see include/cabm.h for the protocol.
 // ---------------------------------------------------------------------------------------------
 int cabm_shard_config(cabm_t* h, int rank, int world, uint32_t pid_lo, uint32_t pid_hi) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_pop || world < 1 || rank < 0 || rank >= world || pid_lo > pid_hi || pid_hi > h->d.N) return CABM_E_ARG;
     cudaSetDevice(h->device);
     h->d.own_lo = pid_lo; h->d.own_hi = pid_hi; h->d.shard_rank = rank;
@@ -832,6 +901,8 @@ int cabm_shard_config(cabm_t* h, int rank, int world, uint32_t pid_lo, uint32_t 
 
 int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is_weekday, double expected_imports,
                         const double* strain_w, int32_t* out_imported) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h || part < 0 || part > 3 || julian_day < 1 || julian_day > 366) return CABM_E_ARG;
     int rc = ready(h, sim_day); if (rc) return rc;
     cudaSetDevice(h->device);
@@ -872,12 +943,15 @@ int cabm_shard_day_part(cabm_t* h, int part, int sim_day, int julian_day, int is
 }
 
 int cabm_shard_flags_out(cabm_t* h, void** records, size_t* n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !records || !n || !h->have_pop) return CABM_E_ARG;
     *records = h->d.flags_raw; *n = std::min<size_t>(h->n_flags_own, h->d.cap_flags);
     return CABM_OK;
 }
 
 int cabm_shard_flags_in(cabm_t* h, const void* records, size_t n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h || !h->have_pop || (!records && n)) return CABM_E_ARG;
     if (n == 0) return CABM_OK;
     cudaSetDevice(h->device);
@@ -888,12 +962,14 @@ int cabm_shard_flags_in(cabm_t* h, const void* records, size_t n) {
 }
 
 int cabm_shard_census(cabm_t* h, void** buf, size_t* n_u32) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !buf || !n_u32 || !h->have_pop) return CABM_E_ARG;
     *buf = h->d.nvis; *n_u32 = h->d.Q;
     return CABM_OK;
 }
 
 int cabm_shard_patients(cabm_t* h, void** buf, size_t* n_i32) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !buf || !n_i32 || !h->have_pop) return CABM_E_ARG;
     *buf = h->d_pat_buf; *n_i32 = h->n_hosp;
     return CABM_OK;
@@ -908,6 +984,7 @@ int cabm_shard_nccl_id(void* out_id) {
 }
 
 int cabm_shard_nccl_init(cabm_t* h, const void* id, int rank, int world) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !id || world < 1 || world > CABM_MAX_SHARDS || rank < 0 || rank >= world) return CABM_E_ARG;
     if (!h->have_pop) { h->err = "load the population and call cabm_shard_config first"; return CABM_E_STATE; }
     if (!nccl_api().ok) { h->err = "libnccl.so.2 not found"; return CABM_E_STATE; }
@@ -952,12 +1029,14 @@ int cabm_shard_nccl_init(cabm_t* h, const void* id, int rank, int world) {
 }
 
 int cabm_shard_exchange_capacity(cabm_t* h, size_t records_per_rank) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || records_per_rank == 0) return CABM_E_ARG;
     h->xcap = std::min<size_t>(records_per_rank, h->d.cap_flags);
     return CABM_OK;
 }
 
 int cabm_shard_exchange_mode(cabm_t* h, int* out_peer_memory) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out_peer_memory) return CABM_E_ARG;
     *out_peer_memory = h->peer_mode;
     return CABM_OK;
@@ -965,6 +1044,8 @@ int cabm_shard_exchange_mode(cabm_t* h, int* out_peer_memory) {
 
 int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                         const double* expected_imports, const double* strain_w) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;
     if (!h->nccl_comm) { h->err = "cabm_shard_nccl_init first"; return CABM_E_STATE; }
     int rc = ready(h, first_day); if (rc) return rc; if ((rc = ready(h, first_day + n_days - 1))) return rc;
@@ -1038,6 +1119,7 @@ int cabm_shard_run_days(cabm_t* h, int first_day, int n_days, const int32_t* jul
 }
 
 int cabm_detected_today(cabm_t* h, int sim_day, uint32_t* out_pids, size_t cap, size_t* out_n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out_n) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     cudaSetDevice(h->device);
     if (!h->d_det) { if ((rc = dalloc(h, &h->d_det, (size_t) h->d.N + 1))) return rc; }       // [0] = count, then ids
@@ -1057,6 +1139,7 @@ int cabm_detected_today(cabm_t* h, int sim_day, uint32_t* out_pids, size_t cap, 
 }
 
 int cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     cudaSetDevice(h->device);
     if (!h->d_diag) { int rc2 = dalloc(h, &h->d_diag, CABM_N_DIAG); if (rc2) return rc2; }
@@ -1068,6 +1151,7 @@ int cabm_diagnostics(cabm_t* h, int sim_day, uint64_t out[CABM_N_DIAG]) {
 }
 
 int cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out_seropos) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (!pids) n = h->d.N;
     *out_seropos = 0;
@@ -1091,6 +1175,7 @@ int cabm_serosurvey(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint
 }
 
 int cabm_eligibility(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint8_t* out_flags) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out_flags) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (!pids) n = h->d.N;
     if (n == 0) return CABM_OK;
@@ -1107,6 +1192,7 @@ int cabm_eligibility(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uin
 }
 
 int cabm_reduce(cabm_t* h, int what, int sim_day, const uint32_t* pids, size_t n, double* out_count) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out_count || what < 0 || what >= CABM_N_REDUCE) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (!pids) n = h->d.N;
     *out_count = 0.0;
@@ -1132,6 +1218,7 @@ int cabm_reduce(cabm_t* h, int what, int sim_day, const uint32_t* pids, size_t n
 // cabm_serosurvey without any allocation (include/cabm.h): ids and accumulator in the file-scope device array, the result
 // comes back through the handle's pinned word. No cudaMalloc / cudaFree / allocating library call on this path.
 int cabm_serosurvey_static(cabm_t* h, int sim_day, const uint32_t* pids, size_t n, uint64_t* out_seropos) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out_seropos) return CABM_E_ARG; int rc = ready(h, sim_day); if (rc) return rc;
     if (!pids) n = h->d.N;
     *out_seropos = 0;
@@ -1158,6 +1245,7 @@ int cabm_serosurvey_static(cabm_t* h, int sim_day, const uint32_t* pids, size_t 
 }
 
 int cabm_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infection* out) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_pop || !out) return CABM_E_ARG;
     if (n == 0) return CABM_OK;
     if (pids) { for (size_t i = 0; i < n; ++i) if (pids[i] >= h->d.N) return CABM_E_ARG; } else if (n > h->d.N) return CABM_E_ARG;
@@ -1173,6 +1261,7 @@ int cabm_get_infections(cabm_t* h, const uint32_t* pids, size_t n, cabm_infectio
 }
 
 int cabm_snapshot(cabm_t* h, cabm_snap_t** out) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !out || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     cabm_snap_t* s = new cabm_snap();
@@ -1194,6 +1283,8 @@ int cabm_snapshot(cabm_t* h, cabm_snap_t** out) {
     return CABM_OK;
 }
 int cabm_restore(cabm_t* h, const cabm_snap_t* s) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // the ledger row in pinned memory may no longer be the device's after this call
     if (!h || !s || s->bufs.size() != h->dyn.size()) return CABM_E_ARG;
     cudaSetDevice(h->device);
     for (size_t i = 0; i < s->bufs.size(); ++i) CK(cudaMemcpyAsync(h->dyn[i].first, s->bufs[i].first, s->bufs[i].second, cudaMemcpyDeviceToDevice, h->stream));
@@ -1211,6 +1302,7 @@ int cabm_snap_free(cabm_snap_t* s) {
 }
 
 int cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h || !h->have_pop) return CABM_E_ARG;
     cudaSetDevice(h->device);
     if (!h->d.foi_enabled) {       // first call switches the (otherwise skipped) row writes on; rows exist from the next tick
@@ -1225,6 +1317,7 @@ int cabm_dump_foi(cabm_t* h, cabm_foi_row* out, size_t cap, size_t* out_n) {
 }
 
 int cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h) return CABM_E_ARG;
     if (out_ms) *out_ms = h->acc_ms; if (out_launches) *out_launches = h->launches;
     h->acc_ms = 0.0; h->launches = 0;
@@ -1233,6 +1326,7 @@ int cabm_device_time_ms(cabm_t* h, double* out_ms, uint64_t* out_launches) {
 
 // per-kernel device time of the day pipeline; switching it on makes tick/import/run_days use plain stream launches
 int cabm_set_profile(cabm_t* h, int on) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h) return CABM_E_ARG;
     cudaSetDevice(h->device);
     if (on && h->marks.empty()) { h->marks.resize(160); h->mark_id.resize(160); for (auto& e : h->marks) cudaEventCreate(&e); }
@@ -1240,6 +1334,7 @@ int cabm_set_profile(cabm_t* h, int on) {
     return CABM_OK;
 }
 int cabm_kernel_times(cabm_t* h, double* out_ms, uint64_t* out_count, const char** out_names, size_t cap, size_t* out_n) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
     if (!h) return CABM_E_ARG;
     if (out_n) *out_n = KID_N;
     for (size_t k = 0; k < std::min<size_t>(cap, KID_N); ++k) {

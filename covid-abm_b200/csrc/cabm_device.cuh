@@ -89,7 +89,8 @@ struct Counters {
     unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;  // n_active: agents inside an infection window today (length of active_list)
     unsigned int n_new[2];                                   // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
     unsigned int n_hits;                                     // successful trials of the house..nursing-home passes waiting for the gate (k_gate)
-    unsigned int day_pad[5];
+    unsigned int n_imported;                                 // winners of the day whose exposure was an importation draw (cabm_import reports them)
+    unsigned int day_pad[4];
     // ---- persistent ----
     unsigned int n_pat;                                      // admitted-patient list length (entries are never removed, see k_status)
     unsigned int overflow;                                   // sticky: a list ran out of capacity

@@ -30,7 +30,6 @@ namespace cg = cooperative_groups;
 #define TPB 256
 #define CHUNK 256
 #define SMALL_ROSTER 64
-#define MAXV 8
 
 __device__ __forceinline__ const DayCtx& day_ctx(const Dev& D) { return *D.today; }
 
@@ -144,36 +143,6 @@ __device__ __forceinline__ void flag_location(const Dev& D, int loc, int strain,
     }
 }
 
-// Community::public_activity draws for one agent (Community.cpp:1012-1026): k ~ Poisson(1) from the first word of
-// the agent's Philox block, then k uniform picks among its patronised locations. Returns the number of distinct
-// locations; qs[] holds public-location indices, hours[] the multiplicities. `row` is the agent's packed patron row.
-__device__ __forceinline__ int gen_visits(const Dev& D, const DayCtx& cx, unsigned int pid, int npat, const PRow& row, int* qs, int* hours) {
-    uint4 b = philox4x32_10(make_uint4(0u, pid, 0u, ((unsigned int) cx.day << 8) | CABM_P_VISIT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
-    int k;
-    if (b.x < D.visit_thr[0]) return 0;
-    else if (b.x < D.visit_thr[1]) k = 1;
-    else if (b.x < D.visit_thr[2]) k = 2;
-    else if (b.x < D.visit_thr[3]) k = 3;
-    else k = (int) table_draw(D.par->visit_cdf, CABM_T_POISSON, (double) b.x * (1.0 / 4294967296.0));
-    int nv = 0;
-    const bool avoiding = prow_rank(row.w[1], row.w[2]) < cx.sd_rank;
-    for (int i = 0; i < k; ++i) {
-        const unsigned int idx1 = (unsigned int) i + 1u;              // draw index within the stream (0 was the Poisson draw)
-        if ((idx1 & 3u) == 0) b = philox4x32_10(make_uint4(idx1 >> 2, pid, 0u, ((unsigned int) cx.day << 8) | CABM_P_VISIT), make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
-        const unsigned int lane = idx1 & 3u;
-        const unsigned int x = lane == 0 ? b.x : lane == 1 ? b.y : lane == 2 ? b.z : b.w;
-        const unsigned int e = prow_entry(row, __umulhi(x, (unsigned int) npat));
-        if (((e >> PROW_HIGH_BIT) & 1u) && avoiding) continue;
-        const int q = (int) (e & PROW_Q_MASK);
-        int t = 0; while (t < nv && qs[t] != q) ++t;
-        if (t == nv) { qs[nv] = q; hours[nv] = 1; ++nv; } else hours[t]++;
-    }
-    return nv;
-}
-
-// ---------------------------------------------------------------------------------------------
-// k_active: one thread per active agent.
-// ---------------------------------------------------------------------------------------------
 // ---------------------------------------------------------------------------------------------
 // k_scan: the active bitmap -> today's list of active agents in ascending id order (a block's run is contiguous, blocks append
 // in any order). 128 agents (one uint4 of the bitmap) per thread; blocks without an active agent return after one
@@ -241,8 +210,10 @@ __global__ void __launch_bounds__(TPB) k_scan_b(const Dev* __restrict__ devs) { 
 #define ACT_MAXL 7            // home or hospital, day location, five distinct patronised places (Community.cpp:279-288)
 struct __align__(16) ActEntry { int loc; unsigned int pid; unsigned long long c; };   // loc < 0: ~(public index); c = pressure | strain << 56
 
-// Community::public_activity draws of one agent as gen_visits makes them, kept in registers: the distinct places in qs[0..4]
-// in order of first appearance, their multiplicities six bits each in `hours` (k <= 31). Returns the number of distinct places.
+// Community::public_activity draws for one agent (Community.cpp:1012-1026): k ~ Poisson(1) from the first word of the agent's
+// Philox block, then k uniform picks among its patronised locations. Kept in registers: the distinct places (public-location
+// indices) in qs[0..4] in order of first appearance, their multiplicities six bits each in `hours` (k <= 31). Returns the number
+// of distinct places. `row` is the agent's 16-byte patron row.
 __device__ __forceinline__ int gen_visits_r(const Dev& D, const DayCtx& cx, const unsigned int pid, const int npat, const uint4& row, unsigned int (&qs)[5], unsigned int& hours) {
     const uint2 key = make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32));
     const unsigned int dp = ((unsigned int) cx.day << 8) | CABM_P_VISIT;

@@ -199,7 +199,17 @@ __device__ __forceinline__ void close_day(const Dev& D, const int tick_done, con
             if (D.shard_rank == 0) c->work[CABM_W_HOT_LOCS] += n_hot;
             if (D.foi_enabled) *D.n_foi = n_hot;
         }
-        D.host_status[1] = c->n_new[1]; D.host_status[0] = c->overflow;             // over PCIe into pinned memory: the host reads them after its sync, no copy
+        D.host_status[1] = c->n_new[1]; D.host_status[3] = c->n_imported; D.host_status[0] = c->overflow;             // over PCIe into pinned memory: the host reads them after its sync, no copy
+        {   // and the ledger row of the day that closes (cabm_ledger_row of that day is then a host read): every writer of the row has
+            // finished (the status pass ran in an earlier kernel, this kernel's infections before the ticket)
+            const int day = D.today->day;
+            unsigned long long* hrow = reinterpret_cast<unsigned long long*>(D.host_status + 12);
+            if (day >= 0 && day < D.R) {
+#pragma unroll
+                for (int k = 0; k < CABM_N_COUNTERS; ++k) hrow[k] = __ldcg(&D.ledger[(size_t) k * D.R + day]);
+                D.host_status[2] = (unsigned int) day;
+            }
+        }
         __threadfence_system();
         unsigned int* w = reinterpret_cast<unsigned int*>(c);
 #pragma unroll
@@ -253,6 +263,7 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
                 if (pass == PASS_WORK) purpose = role ? CABM_P_EXPOSE_WORK : CABM_P_EXPOSE_WORK_VIS;
                 else if (pass == PASS_HOSP && role) { purpose = CABM_P_EXPOSE_HOSP_PAT; sub = role - 1; }
                 event_setup(D, cx, pid, src, purpose, sub, s, c, t_res);
+                if (pass == PASS_IMPORT) atomicAdd(&D.ctr->n_imported, 1u);
                 if (c.has_source) {
                     CABM_CHECK(D, src < D.L && D.locd[src].cnt >= 1 && (unsigned int) D.locd[src].hot < min(D.ctr->n_hot, D.cap_hot));
                     seg_n = D.locd[src].cnt; seg_off = D.hot_off[D.locd[src].hot];

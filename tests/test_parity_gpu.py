@@ -48,7 +48,7 @@ def test_small_community_daily_state_bit_exact():
         for pid in range(0, 3000, 7):
             c.infect(pid, 0, 0)
     for d in range(60):
-        g.step(); o.step()
+        assert g.step() == o.step(), f"day {d}: imported cases"       # tick + import of one day run as one day graph (cabm.cu, tick_pending)
         if d % 10 == 9 or d < 3:
             assert_same_state(g, o, f"day {d}")
     assert g.getNumNewlyInfected().sum() > 500          # the epidemic actually ran
@@ -239,3 +239,37 @@ def test_infect_batch_equals_consecutive_calls():
         assert_same_state(g, o, f"after day {day}")
     assert np.array_equal(g.ledger_table(), g1.ledger_table()) and np.array_equal(g.current_infections(), g1.current_infections())
     g1.close()
+
+
+def test_ledger_row_of_the_closed_day_is_the_devices_row():
+    """cabm_ledger_row of the day that was just closed is served from the row close_day left in pinned host memory (no device
+    round trip); it must equal the device's ledger at that moment, fall back to the device read once another call has touched
+    the ledger (cabm_infect on that day), and equal the oracle's row."""
+    import ctypes as C
+    pop, P, g, o = make_pair(20000, 40, T=0.15, pde=3e-3, seed=17)
+    for c in (g, o):
+        for pid in range(0, 3000, 5):
+            c.infect(pid, 0, 0)
+    row = np.zeros(cabm.abi.N_COUNTERS, dtype=np.uint64)
+
+    def gpu_row(day):
+        g._check(g.fn.ledger_row(g._h, int(day), row.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return row.copy()
+    for d in range(30):
+        g.tick(d)
+        after_tick = gpu_row(d)
+        assert np.array_equal(after_tick, g.ledger_table()[d]), f"day {d}: row after cabm_tick"
+        g.update_strain_mix(d); g.seed_epidemic(d); g.day += 1
+        o.step()
+        r = gpu_row(d)
+        assert np.array_equal(r, g.ledger_table()[d]) and np.array_equal(r, o.ledger_table()[d]), f"day {d}: row after cabm_import"
+        if d >= 1:
+            assert np.array_equal(gpu_row(d - 1), o.ledger_table()[d - 1])         # an older day: device read
+        if d == 12:                                                                # a seed on the closed day: the pinned row is stale, the device read is not
+            g.infect(19999, 1, d); o.infect(19999, 1, d)
+            assert np.array_equal(gpu_row(d), g.ledger_table()[d]) and np.array_equal(gpu_row(d), o.ledger_table()[d])
+    g.run_days(10)
+    for _ in range(10):
+        o.step()
+    assert np.array_equal(gpu_row(39), o.ledger_table()[39]) and np.array_equal(gpu_row(38), o.ledger_table()[38])
+    assert g.ledger_table()[:, 0].sum() > 300
