@@ -237,9 +237,15 @@ int  cabm_set_params(cabm_t* h, const cabm_params* par);
 /* replaces setSocialDistancingTimedIntervention / updateTimedIntervention (Community.h:396-425) */
 int  cabm_set_timed_intervention(cabm_t* h, int which, const double* v, size_t n);
 
-/* replaces Community::tick() (Community.cpp:1147-1192); julian_day/is_weekday come from Date (Date.h) */
+/* replaces Community::tick() (Community.cpp:1147-1192); julian_day/is_weekday come from Date (Date.h).
+ * The arguments are checked at once; the day itself is staged and runs in the NEXT call into the handle: together with the
+ * day's importation when that call is cabm_import for the same day (the simulate_epidemic loop, simulator.h:338-374: one
+ * launch sequence and one host synchronisation per day), on its own before anything else (every getter and every mutator
+ * sees the completed tick). A device-side error of the staged day (list overflow) is therefore returned by that next call.
+ * Environment CABM_EAGER_TICK=1 makes cabm_tick run the day before it returns. */
 int  cabm_tick(cabm_t* h, int sim_day, int julian_day, int is_weekday);
-/* replaces seed_epidemic(par, community, date, strain_weights) (simulator.h:201-223) */
+/* replaces seed_epidemic(par, community, date, strain_weights) (simulator.h:201-223); *out_infected = people whose
+ * infection today came from an importation draw */
 int  cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[CABM_N_STRAINS], int32_t* out_infected);
 /* replaces Community::infect(id, strain) (Community.cpp:550-553) */
 int  cabm_infect(cabm_t* h, uint32_t pid, int strain, int sim_day, int32_t* out_infected);
@@ -270,6 +276,7 @@ int  cabm_quarantine(cabm_t* h, const uint32_t* pids, size_t n, int from_day, in
 
 /* replaces the ledger getters (Community.h:353-375) */
 int  cabm_ledger_series(cabm_t* h, int counter, uint64_t* out, size_t n);
+/* the row of the day that was closed last is read from pinned host memory (left there by the kernel that closed the day) */
 int  cabm_ledger_row(cabm_t* h, int sim_day, uint64_t out[CABM_N_COUNTERS]);
 /* all series at once, counter-major: out[counter * run_length + day] (the 15+4 by-value getters of simulator.h:376-390,450-452) */
 int  cabm_ledger_table(cabm_t* h, uint64_t* out, size_t n);

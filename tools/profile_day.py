@@ -6,7 +6,7 @@
 Runs D days through the CUDA-graph path, then K days either with one CUDA event in front of every kernel
 (default; prints microseconds per kernel per day and the work counters of those days) or, with --graph,
 through graph replay (prints device microseconds per day). Under `ncu`, kernel launches of day d start at
-launch index 1 + 10 d (one k_init_state launch, then 10 kernels per day).
+launch index 1 + 9 d (one k_init_state launch, then 9 kernels per day).
 """
 import argparse
 import json
