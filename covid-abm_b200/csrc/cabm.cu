@@ -62,7 +62,7 @@ struct cabm {
     std::vector<std::pair<void*, size_t>> dyn;    // dynamic state buffers (snapshot set)
     DayCtx* h_ctx = nullptr; DayCtx* d_ctx = nullptr; int ctx_cap = 0;
     int* d_tmp_int = nullptr;
-    cudaGraphExec_t day_graph = nullptr, tick_graph = nullptr, import_graph = nullptr;   // run_days (tick + importation), cabm_tick, cabm_import
+    cudaGraphExec_t day_graph = nullptr, tick_graph = nullptr, import_graph = nullptr, step_graph = nullptr;   // run_days (tick + importation), cabm_tick, cabm_import, tick + import of one day through the per-day calls
     cabm_params* d_par = nullptr; double* d_pfd = nullptr; double* d_imr = nullptr;
     unsigned long long h_n_log_cap = 0;
     uint64_t launches_per_day = 9, launches_tick = 9, launches_import = 2;
@@ -219,6 +219,8 @@ static unsigned int scan_grid(const Dev& D) {
     const unsigned int w_lo = (D.own_lo >> 5) & ~3u, w_hi = (D.own_hi + 31u) >> 5;
     return std::max(1u, (w_hi - w_lo + TPB * 4 - 1) / (TPB * 4));
 }
+// advance: bit 0 = move on to the next staged day context (run_days), bit 1 = leave the day's ledger row in pinned host memory
+// (the per-day calls; a bulk run has no reader for it and saves the PCIe writes)
 static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
     const Dev& D = h->d;
     const unsigned int gSM = h->sms;
@@ -232,13 +234,13 @@ static void launch_day(cabm_t* h, bool tick, bool import, int advance) {
         LAUNCH(KID_APPLY_STATUS, launch_k(h, 4, k_apply_status, dim3(gSM * h->gm[4]), dim3(128), 0, D, 0, 0));
     }
     LAUNCH(KID_HOSP_IMPORT, launch_k(h, 5, k_hosp_import, dim3(gSM * h->gm[5]), dim3(TPB), 0, D, tick ? 1 : 0, import ? 1 : 0));
-    LAUNCH(KID_APPLY1, launch_k(h, 6, k_apply_status, dim3(gSM * h->gm[7]), dim3(128), 0, D, 1, (tick ? 1 : 0) | (advance ? 2 : 0)));
+    LAUNCH(KID_APPLY1, launch_k(h, 6, k_apply_status, dim3(gSM * h->gm[7]), dim3(128), 0, D, 1, (tick ? 1 : 0) | ((advance & 1) ? 2 : 0) | ((advance & 2) ? 4 : 0)));
     if (h->profile) prof_mark(h, -1);
 }
 
 // kernel arguments (the Dev record) are baked into the captured graphs: whatever changes it drops them
 static void drop_graphs(cabm_t* h) {
-    for (cudaGraphExec_t* g : { &h->day_graph, &h->tick_graph, &h->import_graph }) if (*g) { cudaGraphExecDestroy(*g); *g = nullptr; }
+    for (cudaGraphExec_t* g : { &h->day_graph, &h->tick_graph, &h->import_graph, &h->step_graph }) if (*g) { cudaGraphExecDestroy(*g); *g = nullptr; }
 }
 // capture one launch sequence of the day on the handle's stream; the launches it holds are returned through n_launches
 static int capture_day(cabm_t* h, cudaGraphExec_t* out, bool tick, bool import, int advance, uint64_t* n_launches) {
@@ -534,14 +536,14 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = dalloc(h, &D.inhosp, n_rows / 32 + 4, true)) || (rc = dalloc(h, &D.actbits, ((size_t) N + 1023) / 1024 * 32, true)) || (rc = dalloc(h, &D.active_list, (size_t) N))) return rc;
     CK(cudaMemcpyAsync(D.ag, ag.data(), (size_t) N * sizeof(AgRec), cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----
-    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024; D.cap_new = N; D.cap_pat = N;
+    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024 * HIT_LISTS; D.hit_sub = D.cap_hits / HIT_LISTS; D.cap_new = N; D.cap_pat = N;
     D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + roster.size() / SMALL_ROSTER + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
     if (const char* e = getenv("CABM_LOG_CAP")) D.cap_log = std::max<unsigned long long>(1, strtoull(e, nullptr, 10));   // test knob: force the log-overflow error
     D.cap_sitems = (unsigned int) std::min<size_t>(0x7FFFFFFF, (size_t) L + nbr.size() + 1024);
     if ((rc = dalloc(h, &D.hot_list, D.cap_hot)) || (rc = dalloc(h, &D.hot_meta, D.cap_hot)) || (rc = dalloc(h, &D.hot_hosp, D.cap_hot)) || (rc = dalloc(h, &D.hot_off, D.cap_hot)) || (rc = dalloc(h, &D.hot_T, (size_t) 2 * D.cap_hot)) || (rc = dalloc(h, &D.sitems, D.cap_sitems)) || (rc = dalloc(h, &D.flags_raw, D.cap_flags)) || (rc = dalloc(h, &D.flags, D.cap_flags)) ||
         (rc = dalloc(h, &D.visit_rec, D.cap_vis)) ||
-        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
+        (rc = dalloc(h, &D.items, D.cap_items)) || (rc = dalloc(h, &D.hits, D.cap_hits)) || (rc = dalloc(h, &D.hit_ctr, HIT_LISTS * 32)) || (rc = dalloc(h, &D.newinf_list, D.cap_new)) ||
         (rc = dalloc(h, &D.patient_list, D.cap_pat, true)) || (rc = dalloc(h, &D.log, D.cap_log)) || (rc = dalloc(h, &D.foi, D.cap_hot)) ||
         (rc = dalloc(h, &D.n_foi, 1))) return rc;
 #ifdef CABM_CHECKS
@@ -562,9 +564,9 @@ static int launch_tick_now(cabm_t* h) {
     CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
     CK(cudaEventRecord(h->e0, h->stream));
-    if (h->profile) launch_day(h, true, false, 0);
+    if (h->profile) launch_day(h, true, false, 2);
     else {
-        if (!h->tick_graph && (rc = capture_day(h, &h->tick_graph, true, false, 0, &h->launches_tick))) return rc;
+        if (!h->tick_graph && (rc = capture_day(h, &h->tick_graph, true, false, 2, &h->launches_tick))) return rc;
         CK(cudaGraphLaunch(h->tick_graph, h->stream)); h->launches += h->launches_tick;
     }
     if ((rc = timed_sync(h))) return rc;
@@ -606,17 +608,17 @@ int cabm_import(cabm_t* h, int sim_day, double expected, const double strain_w[C
         CK(cudaMemcpyAsync(h->d_ctx, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemsetAsync(&h->d.ctr->day_idx, 0, sizeof(unsigned int), h->stream));
         CK(cudaEventRecord(h->e0, h->stream));
-        if (!h->day_graph && (rc = capture_day(h, &h->day_graph, true, true, 1, &h->launches_per_day))) return rc;
-        CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day;
+        if (!h->step_graph && (rc = capture_day(h, &h->step_graph, true, true, 3, &h->launches_per_day))) return rc;
+        CK(cudaGraphLaunch(h->step_graph, h->stream)); h->launches += h->launches_per_day;
     } else {
         DayCtx& c = h->h_ctx[0]; std::memset(&c, 0, sizeof(c));
         c.day = sim_day; c.julian_day = 1; c.n_imports = n_imports;
         for (int s = 0; s < CABM_N_STRAINS; ++s) c.strain_w[s] = strain_w[s];
         CK(cudaMemcpyAsync(h->d_today, h->h_ctx, sizeof(DayCtx), cudaMemcpyHostToDevice, h->stream));   // no k_active in front: publish the context directly
         CK(cudaEventRecord(h->e0, h->stream));
-        if (h->profile) launch_day(h, false, true, 0);
+        if (h->profile) launch_day(h, false, true, 2);
         else {
-            if (!h->import_graph && (rc = capture_day(h, &h->import_graph, false, true, 0, &h->launches_import))) return rc;
+            if (!h->import_graph && (rc = capture_day(h, &h->import_graph, false, true, 2, &h->launches_import))) return rc;
             CK(cudaGraphLaunch(h->import_graph, h->stream)); h->launches += h->launches_import;
         }
     }
@@ -689,6 +691,7 @@ int cabm_infect_batch(cabm_t* h, const uint32_t* pids, const uint8_t* strains, s
 int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_day, const int32_t* is_weekday,
                   const double* expected_imports, const double* strain_w) {
     { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (h) h->row_ok = false;                       // a bulk run leaves no ledger row in pinned memory
     if (!h || n_days <= 0 || !julian_day || !is_weekday || !expected_imports || !strain_w) return CABM_E_ARG;
     int rc = ready(h, first_day); if (rc) return rc; if ((rc = ready(h, first_day + n_days - 1))) return rc;
     cudaSetDevice(h->device);
@@ -708,13 +711,11 @@ int cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_da
             CK(cudaStreamSynchronize(h->stream)); prof_collect(h);
         }
         if ((rc = timed_sync(h))) return rc;
-        h->row_ok = true;
         return check_overflow(h);
     }
     if (!h->day_graph && (rc = capture_day(h, &h->day_graph, true, true, 1, &h->launches_per_day))) return rc;   // one day (tick + importation), captured once, replayed every day
     for (int i = 0; i < n_days; ++i) { CK(cudaGraphLaunch(h->day_graph, h->stream)); h->launches += h->launches_per_day; }
     if ((rc = timed_sync(h))) return rc;
-    h->row_ok = true;
     return check_overflow_host(h);
 }
 

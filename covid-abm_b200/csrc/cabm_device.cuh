@@ -69,6 +69,7 @@ struct __align__(16) Hit  { unsigned int pid; unsigned int src; unsigned int pur
 // k_trials scatters them into one contiguous segment per hot location (Flag), which k_apply_status searches.
 struct __align__(8)  FlagRaw { int loc; unsigned int slot; unsigned int pid; unsigned int pad; unsigned long long c; };
 struct __align__(16) Flag { unsigned int pid; unsigned int pad; unsigned long long c; };
+#define HIT_LISTS 64u
 #define HOT_NOPUB 0x7FFFFFFFu
 #define HOT_IS_HOSP 0x80000000u
 #define FLAG_C(f) ((f).c & 0x00FFFFFFFFFFFFFFull)
@@ -88,7 +89,7 @@ struct Counters {
     // ---- day-scoped: zeroed by the block that closes the day (k_apply_status, phase 1) ----
     unsigned int n_active, n_hot, n_hot_hosp, n_flags, n_vis, n_items, n_seg, n_sitems;  // n_active: agents inside an infection window today (length of active_list)
     unsigned int n_new[2];                                   // [phase]: 0 = house..nursing home passes, 1 = hospital pass + importation
-    unsigned int n_hits;                                     // successful trials of the house..nursing-home passes waiting for the gate (k_gate)
+    unsigned int n_hits_unused;                              // (the hit list has its own counters: Dev::hit_ctr)
     unsigned int n_imported;                                 // winners of the day whose exposure was an importation draw (cabm_import reports them)
     unsigned int day_pad[4];
     // ---- persistent ----
@@ -134,6 +135,10 @@ struct Dev {
     unsigned int* nvis; double* pub_T; unsigned int* pub_hot;     // [Q], [Q], [ceil(Q/32)] public-location visitor census, T, hot bitmap
     // day lists
     int* hot_list; int* hot_hosp; unsigned int* hot_off; double* hot_T; FlagRaw* flags_raw; Flag* flags; SItem* sitems;
+    // Successful trials waiting for the gate: HIT_LISTS sub-lists of hit_sub records each, one counter per sub-list on its own
+    // 128-byte line (hit_ctr[k * 32]); a block of k_trials appends to sub-list blockIdx.x % HIT_LISTS. One list with one counter
+    // took a quarter of k_trials' stall samples in a large epidemic (a quarter of a million returning atomics on one address a day).
+    unsigned int* hit_ctr; unsigned int hit_sub;
     unsigned int* hot_meta;              // [i]: public index of hot_list[i] (HOT_NOPUB if none) | HOT_IS_HOSP, for the end-of-day reset
     uint2* visit_rec; Item* items; Hit* hits; unsigned int* newinf_list; unsigned int* patient_list;
     unsigned int cap_hot, cap_active, cap_flags, cap_vis, cap_items, cap_sitems, cap_hits, cap_new, cap_pat; unsigned long long cap_log;

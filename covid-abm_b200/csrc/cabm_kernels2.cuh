@@ -128,10 +128,26 @@ __device__ __forceinline__ void gate_hit(const Dev& D, const int phase, const un
 
 // k_gate: the hits of the house..nursing-home passes (k_trials) pass the susceptibility gate, one thread per hit
 __device__ __forceinline__ void k_gate_body(const Dev& D) {
+    __shared__ unsigned int s_pref[HIT_LISTS + 1];
     pdl_wait();
-    const unsigned int n = min(D.ctr->n_hits, D.cap_hits);
+    // the sub-lists end to end: prefix sums of their lengths (64 loads, one per thread), then hit i of the concatenation
+    if (threadIdx.x < HIT_LISTS) {
+        const unsigned int lane = threadIdx.x & 31;
+        unsigned int incl = min(D.hit_ctr[threadIdx.x * 32u], D.hit_sub);
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned int) o) incl += t; }
+        s_pref[threadIdx.x + 1] = incl;                     // per warp of 32 sub-lists; the second warp's base is added below
+    }
+    if (threadIdx.x == 0) s_pref[0] = 0;
+    __syncthreads();
+    if (threadIdx.x >= 32 && threadIdx.x < HIT_LISTS) { const unsigned int add = s_pref[32]; __syncwarp(); s_pref[threadIdx.x + 1] += add; }
+    __syncthreads();
+    const unsigned int n = s_pref[HIT_LISTS];
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const Hit h = D.hits[i];
+        unsigned int k = 0;
+#pragma unroll
+        for (unsigned int step = HIT_LISTS / 2; step; step >>= 1) if (s_pref[k + step] <= i) k += step;
+        const Hit h = D.hits[(size_t) k * D.hit_sub + (i - s_pref[k])];
         gate_hit(D, 0, h.pid, h.src, h.purpose, h.sub);
     }
     pdl_launch_dependents();
@@ -181,9 +197,10 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
 // Closing the day: runs in the last block of the day's last kernel (k_apply_status, phase 1) once every other block has
 // finished. tick_done: a whole tick ran (updateHotLocations for the hot hospitals, which the hospital pass and the phase-1
 // winners were still reading; list swap); advance: move on to the next staged day context.
-__device__ __forceinline__ void close_day(const Dev& D, const int tick_done, const int advance) {
+__device__ __forceinline__ void close_day(const Dev& D, const int tick_done, const int advance, const int host_row) {
     Counters* c = D.ctr;
     const unsigned int n_hot = min(c->n_hot, D.cap_hot);
+    for (unsigned int k = threadIdx.x; k < HIT_LISTS; k += blockDim.x) D.hit_ctr[k * 32u] = 0;   // the hit sub-lists are empty again
     if (tick_done) {
         const unsigned int nh = min(c->n_hot_hosp, D.cap_hot);
         for (unsigned int j = threadIdx.x; j < nh; j += blockDim.x) {
@@ -200,7 +217,7 @@ __device__ __forceinline__ void close_day(const Dev& D, const int tick_done, con
             if (D.foi_enabled) *D.n_foi = n_hot;
         }
         D.host_status[1] = c->n_new[1]; D.host_status[3] = c->n_imported; D.host_status[0] = c->overflow;             // over PCIe into pinned memory: the host reads them after its sync, no copy
-        {   // and the ledger row of the day that closes (cabm_ledger_row of that day is then a host read): every writer of the row has
+        if (host_row) {   // (per-day calls only) the ledger row of the day that closes: cabm_ledger_row of that day is then a host read. Every writer of the row has
             // finished (the status pass ran in an earlier kernel, this kernel's infections before the ticket)
             const int day = D.today->day;
             unsigned long long* hrow = reinterpret_cast<unsigned long long*>(D.host_status + 12);
@@ -224,7 +241,7 @@ __device__ __forceinline__ void close_day(const Dev& D, const int tick_done, con
 // below); every lane commits its own winner, the whole warp helps with the infector search of long flag segments. Then
 // ceil(n_list/32) warps run the status pass (phase 0) over the day's active list for the agents that were not re-infected
 // in phase 0: cand[] keeps the winner keys of phase 0 until k_hosp_import so the status half can tell who was.
-// Phase 1 (close >= 0 encodes tick_done | advance << 1) is the day's last kernel: winners reset their own candidate word,
+// Phase 1 (close encodes tick_done | advance << 1 | host_row << 2) is the day's last kernel: winners reset their own candidate word,
 // and the last block to finish closes the day.
 __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phase, const int close) {
     __shared__ unsigned int sm[CABM_N_COUNTERS];
@@ -313,7 +330,7 @@ __device__ __forceinline__ void k_apply_status_body(const Dev& D, const int phas
     // phase 1: the last block to get here closes the day (every other block is done with the day's lists and counters)
     if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&D.ctr->end_ticket, 1u) == gridDim.x - 1 ? 1u : 0u; }
     __syncthreads();
-    if (s_last) { __threadfence(); close_day(D, close & 1, (close >> 1) & 1); }
+    if (s_last) { __threadfence(); close_day(D, close & 1, (close >> 1) & 1, (close >> 2) & 1); }
 }
 __global__ void __launch_bounds__(128, 8) k_apply_status(const Dev D, const int phase, const int close) { k_apply_status_body(D, phase, close); }
 __global__ void __launch_bounds__(128) k_apply_status_b(const Dev* __restrict__ devs, const int phase, const int close) { BATCH_DEV(D, devs) k_apply_status_body(D, phase, close); }   // one launch, replicate = blockIdx.y
