@@ -166,7 +166,7 @@ __device__ __forceinline__ unsigned int status_one(const Dev& D, unsigned int p,
             if (t0.hosp_begin == day) {                                             // goToHospital (Person.h:248)
                 D.ag[p].hosp_count = ar.hosp_count + 1; atomicAdd(&D.pat_count[hosp], 1u);
                 const unsigned char pb = ar.pbyte;
-                if (!(pb & PB_ONLIST)) {                                            // entries stay on the list; hosp_count == 0 means discharged
+                if (!(pb & PB_ONLIST)) {                                            // one entry per stay: the patient walk drops it once hosp_count is back to 0
                     D.ag[p].pbyte = pb | PB_ONLIST;
                     const unsigned int pi = list_reserve(&D.ctr->n_pat);
                     if (pi < D.cap_pat) D.patient_list[pi] = p; else atomicOr(&D.ctr->overflow, 64u);
@@ -361,13 +361,17 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
         // and the winner keys of phase 0, which the status pass has finished reading. Independent stores issued first: they
         // drain while the dependent chains of the hospital pass wait for memory. Hot hospitals are reset by close_day.
         const unsigned int n_hot = min(D.ctr->n_hot, D.cap_hot);
-        for (unsigned int i = tid; i < n_hot; i += nth) {                              // location and (public index, hospital?) stream in: no gather before the stores
-            const unsigned int meta = D.hot_meta[i];
-            if (meta & HOT_IS_HOSP) continue;
-            const int loc = D.hot_list[i];
-            locd_reset(&D.locd[loc]);
-            const unsigned int q = meta & HOT_NOPUB;
-            if (q != HOT_NOPUB) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }   // the whole bitmap word: every set bit belongs to a hot location
+        for (unsigned int i0 = tid; i0 < n_hot; i0 += 4 * nth) {                      // location and (public index, hospital?) stream in, four per thread in flight
+            unsigned int meta[4]; int loc[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const unsigned int i = i0 + k * nth; meta[k] = i < n_hot ? D.hot_meta[i] : HOT_IS_HOSP; loc[k] = i < n_hot ? D.hot_list[i] : 0; }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (meta[k] & HOT_IS_HOSP) continue;
+                locd_reset(&D.locd[loc[k]]);
+                const unsigned int q = meta[k] & HOT_NOPUB;
+                if (q != HOT_NOPUB) { D.nvis[q] = 0; D.pub_T[q] = 0.0; D.pub_hot[q >> 5] = 0; }   // the whole bitmap word: every set bit belongs to a hot location
+            }
         }
         const unsigned int n_new0 = min(D.ctr->n_new[0], D.cap_new);
         for (unsigned int i = tid; i < n_new0; i += nth) D.cand[D.newinf_list[i]] = CABM_CAND_EMPTY;
@@ -387,9 +391,13 @@ __device__ __forceinline__ void k_hosp_import_body(const Dev& D, const int do_ho
         const unsigned int np = min(D.ctr->n_pat, D.cap_pat);
         for (unsigned int i = tid; i < np; i += nth) {
             const unsigned int pid = D.patient_list[i];
+            if (pid == 0xFFFFFFFFu) continue;                                         // a discharged patient's entry (below): costs the 4-byte read only
             CABM_CHECK(D, pid < D.N);
             const unsigned int c = D.ag[pid].hosp_count;
-            if (c == 0) continue;
+            if (c == 0) {                                                             // discharged: the entry becomes a hole and a later admission appends a new one (status_one);
+                D.patient_list[i] = 0xFFFFFFFFu; D.ag[pid].pbyte &= (unsigned char) ~PB_ONLIST;   // nobody else writes this agent's status byte in this kernel
+                continue;
+            }
             const int hosp = D.ag[pid].hospital;
             if (hosp < 0 || D.locd[hosp].cnt == 0) continue;
             unsigned int denom; unsigned long long pws[4];
