@@ -536,7 +536,7 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
         (rc = dalloc(h, &D.inhosp, n_rows / 32 + 4, true)) || (rc = dalloc(h, &D.actbits, ((size_t) N + 1023) / 1024 * 32, true)) || (rc = dalloc(h, &D.active_list, (size_t) N))) return rc;
     CK(cudaMemcpyAsync(D.ag, ag.data(), (size_t) N * sizeof(AgRec), cudaMemcpyHostToDevice, h->stream));
     // ---- day lists ----
-    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 1024 * HIT_LISTS; D.hit_sub = D.cap_hits / HIT_LISTS; D.cap_new = N; D.cap_pat = N;
+    D.cap_hot = L; D.cap_active = N; D.cap_flags = 3 * N + 1024; D.cap_vis = 2 * N + 1024; D.cap_hits = 2 * N + 4096 * HIT_LISTS; D.hit_sub = D.cap_hits / HIT_LISTS; D.cap_new = N; D.cap_pat = N;
     D.cap_items = (unsigned int) std::min<size_t>(0x7FFFFFFF, roster.size() / CHUNK + roster.size() / SMALL_ROSTER + 1024);
     D.cap_log = (unsigned long long) 3 * N + 1024;
     if (const char* e = getenv("CABM_LOG_CAP")) D.cap_log = std::max<unsigned long long>(1, strtoull(e, nullptr, 10));   // test knob: force the log-overflow error

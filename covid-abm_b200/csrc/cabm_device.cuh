@@ -136,7 +136,7 @@ struct Dev {
     // day lists
     int* hot_list; int* hot_hosp; unsigned int* hot_off; double* hot_T; FlagRaw* flags_raw; Flag* flags; SItem* sitems;
     // Successful trials waiting for the gate: HIT_LISTS sub-lists of hit_sub records each, one counter per sub-list on its own
-    // 128-byte line (hit_ctr[k * 32]); a block of k_trials appends to sub-list blockIdx.x % HIT_LISTS. One list with one counter
+    // 128-byte line (hit_ctr[k * 32]); a warp of k_trials appends to sub-list (its index in the grid) % HIT_LISTS. One list with one counter
     // took a quarter of k_trials' stall samples in a large epidemic (a quarter of a million returning atomics on one address a day).
     unsigned int* hit_ctr; unsigned int hit_sub;
     unsigned int* hot_meta;              // [i]: public index of hot_list[i] (HOT_NOPUB if none) | HOT_IS_HOSP, for the end-of-day reset
@@ -269,15 +269,35 @@ struct Stream {
     __device__ __forceinline__ double u01() { return (double) next() * (1.0 / 4294967296.0); }
 };
 
-__device__ __forceinline__ unsigned int table_draw(const double* __restrict__ cdf, int n, double u) {
+// Inverse-CDF draw on an integer-support table: the smallest k with u < cdf[k], at most n - 1. Four entries per step: their
+// addresses do not depend on one another, so a step is one round trip instead of four. These draws sit in the disease-course
+// sampler (Person::infect, ~10 tables per infection), which runs on a handful of lanes per SM at the end of the day: its
+// duration is the sum of its dependent loads. Out of line: the sampler's code size matters more than the call.
+__device__ __noinline__ unsigned int table_draw(const double* __restrict__ cdf, int n, double u) {
     int k = 0;
+    while (k + 4 <= n - 1) {
+        const double a = cdf[k], b = cdf[k + 1], c = cdf[k + 2], d = cdf[k + 3];
+        if (u < a) return (unsigned int) k;
+        if (u < b) return (unsigned int) (k + 1);
+        if (u < c) return (unsigned int) (k + 2);
+        if (u < d) return (unsigned int) (k + 3);
+        k += 4;
+    }
 #pragma unroll 1
-    while (k < n - 1 && !(u < cdf[k])) ++k;       // not unrolled: every iteration's load decides the next, and these draws sit in latency-bound code whose size matters
+    while (k < n - 1 && !(u < cdf[k])) ++k;
     return (unsigned int) k;
 }
-// Parameters::sampler (Parameters.h:433-436)
-__device__ __forceinline__ int ref_sampler(const double* __restrict__ cdf, int n, double r) {
+// Parameters::sampler (Parameters.h:433-436): the smallest i with !(cdf[i] < r), at most n
+__device__ __noinline__ int ref_sampler(const double* __restrict__ cdf, int n, double r) {
     int i = 0;
+    while (i + 4 <= n) {
+        const double a = cdf[i], b = cdf[i + 1], c = cdf[i + 2], d = cdf[i + 3];
+        if (!(a < r)) return i;
+        if (!(b < r)) return i + 1;
+        if (!(c < r)) return i + 2;
+        if (!(d < r)) return i + 3;
+        i += 4;
+    }
 #pragma unroll 1
     while (i < n && cdf[i] < r) ++i;
     return i;
