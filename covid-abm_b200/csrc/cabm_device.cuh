@@ -136,7 +136,7 @@ struct Dev {
     // day lists
     int* hot_list; int* hot_hosp; unsigned int* hot_off; double* hot_T; FlagRaw* flags_raw; Flag* flags; SItem* sitems;
     // Successful trials waiting for the gate: HIT_LISTS sub-lists of hit_sub records each, one counter per sub-list on its own
-    // 128-byte line (hit_ctr[k * 32]); a warp of k_trials appends to sub-list (its index in the grid) % HIT_LISTS. One list with one counter
+    // 128-byte line (hit_ctr[k * 32]); a block of k_trials appends to sub-list blockIdx.x % HIT_LISTS (in a grid of fewer blocks than lists: by warp). One list with one counter
     // took a quarter of k_trials' stall samples in a large epidemic (a quarter of a million returning atomics on one address a day).
     unsigned int* hit_ctr; unsigned int hit_sub;
     unsigned int* hot_meta;              // [i]: public index of hot_list[i] (HOT_NOPUB if none) | HOT_IS_HOSP, for the end-of-day reset

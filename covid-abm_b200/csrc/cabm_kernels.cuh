@@ -624,7 +624,7 @@ __device__ __forceinline__ void trial(const Dev& D, const int day, const int pha
                                   make_uint2((unsigned int) D.seed, (unsigned int) (D.seed >> 32)));
     if ((double) b.x * (1.0 / 4294967296.0) < T) {
         if (phase) { gate_hit(D, 1, pid, (unsigned int) src, (unsigned int) purpose, sub); return; }
-        const unsigned int k = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) & (HIT_LISTS - 1u);   // this warp's sub-list (by warp, so that a small grid still spreads over many): its counter has a line of its own
+        const unsigned int k = (gridDim.x >= HIT_LISTS ? blockIdx.x : blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) & (HIT_LISTS - 1u);   // this block's sub-list (in a small grid, as in the batch launches: this warp's), its counter has a line of its own
         const unsigned int h = list_reserve(&D.hit_ctr[k * 32u]);
         if (h < D.hit_sub) { Hit r; r.pid = pid; r.src = (unsigned int) src; r.purpose = (unsigned int) purpose; r.sub = sub; D.hits[(size_t) k * D.hit_sub + h] = r; }
         else atomicOr(&D.ctr->overflow, 256u);
@@ -824,5 +824,5 @@ __device__ __forceinline__ void k_trials_body(const Dev& D) {
     const int ids[1] = { CABM_W_TRIALS }; const unsigned int vals[1] = { trials };
     block_work_add<1>(D, ids, vals);
 }
-__global__ void __launch_bounds__(TPB) k_trials(const Dev D) { k_trials_body(D); }
+__global__ void __launch_bounds__(TPB, 8) k_trials(const Dev D) { k_trials_body(D); }
 __global__ void __launch_bounds__(TPB) k_trials_b(const Dev* __restrict__ devs) { BATCH_DEV(D, devs) k_trials_body(D); }   // one launch, replicate = blockIdx.y
