@@ -273,3 +273,49 @@ def test_ledger_row_of_the_closed_day_is_the_devices_row():
         o.step()
     assert np.array_equal(gpu_row(39), o.ledger_table()[39]) and np.array_equal(gpu_row(38), o.ledger_table()[38])
     assert g.ledger_table()[:, 0].sum() > 300
+
+
+def test_staged_tick_equals_eager_tick(monkeypatch):
+    """cabm_tick stages its day and the next call launches it (fused with cabm_import of the same day, on its own before anything
+    else). The same call sequence with CABM_EAGER_TICK=1 (every tick runs before it returns) must leave the same state, whatever
+    comes between tick and import: a getter, a mutator, another tick, nothing."""
+    pop = synthpop.generate(20000, seed=11)
+    P = cabm.params.default_params(run_length=40, seed=23, T=0.15, prob_daily_exposure=3e-3)
+    tab = cabm.params.build_tables(P)
+    attrs = cabm.abi.immunity_attributes(int(pop["n_people"]), P["seed"])
+    rng = np.random.default_rng(3)
+    vax_ids = rng.choice(int(pop["n_people"]), size=2000, replace=False)
+    quar_ids = rng.choice(int(pop["n_people"]), size=1500, replace=False)
+
+    def run(eager):
+        if eager:
+            monkeypatch.setenv("CABM_EAGER_TICK", "1")
+        else:
+            monkeypatch.delenv("CABM_EAGER_TICK", raising=False)
+        c = cabm.Community(P, pop, tab, attrs=attrs)
+        for pid in range(0, 3000, 5):
+            c.infect(pid, 0, 0)
+        imported = []
+        for d in range(30):
+            c.tick(d)
+            if d % 7 == 1:
+                c.vaccinate(vax_ids[(d // 7) * 400:(d // 7 + 1) * 400], d)        # a mutator between tick and import
+            elif d % 7 == 2:
+                c.quarantine(quar_ids[(d // 7) * 300:(d // 7 + 1) * 300], d, d + 4)
+            elif d % 7 == 3:
+                c.diagnostics(d)                                                     # a getter
+            elif d % 7 == 4:
+                c.detected_today(d)
+            c.update_strain_mix(d)
+            imported.append(c.seed_epidemic(d))
+            c.day = d + 1
+        c.tick(30)                                                                   # a tick that no import follows: the ledger read launches it
+        led = c.ledger_table().copy()
+        state = c.current_infections().copy()
+        hist = sorted_hist(c)
+        c.close()
+        return imported, led, state, hist
+    a = run(True); b = run(False)
+    assert a[0] == b[0], "imported cases per day"
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
+    assert a[1][:, 0].sum() > 300 and a[1][30].sum() > 0
