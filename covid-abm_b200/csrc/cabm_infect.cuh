@@ -62,6 +62,9 @@ __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const Infe
     if (n_inf > 0 && tl_in(o0.infected, o0.infectious_end, time)) return false;
     if (s.u01() > pr_inf) return false;
     if (!commit) return true;
+    // the infection is certain from here on: its log entry is reserved now, so the round trip of the returning atomic runs beside the
+    // disease course below instead of at the end of this chain (a winner's lane is alone in its warp on a light day)
+    const unsigned long long li = atomicAdd(&D.ctr->n_log, 1ull);
 
     // ---- event probabilities (Person.cpp:284-315) ----
     const bool vaccinated = n_doses > 0, prior = n_inf > 0;
@@ -194,7 +197,6 @@ __device__ __forceinline__ bool infect_event(const Dev& D, Stream& s, const Infe
 #pragma unroll
     for (int o = 0; o < CABM_N_OUTCOMES; ++o) if (tally & (1ull << o)) atomicAdd(&D.ctr->cumul[o], 1ull);
     atomicAdd(&D.ctr->work[CABM_W_INFECTIONS], 1ull);
-    const unsigned long long li = atomicAdd(&D.ctr->n_log, 1ull);
     if (li < D.cap_log) {
         cabm_infection rec;
         rec.person = (unsigned int) pid; rec.infected_by = c.infector; rec.infected_place = c.has_source ? c.source : -1;

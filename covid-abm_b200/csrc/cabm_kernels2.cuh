@@ -227,13 +227,13 @@ __device__ __forceinline__ void close_day(const Dev& D, const int tick_done, con
                 D.host_status[2] = (unsigned int) day;
             }
         }
-        __threadfence_system();
+        // (no fence: the host reads the pinned words after it has synchronised with the stream, the next kernel reads the counters
+        // behind the kernel boundary; a system-scope fence here waited for the PCIe writes, 1-2 us at the end of every day)
         unsigned int* w = reinterpret_cast<unsigned int*>(c);
 #pragma unroll
         for (int k = 0; k < CABM_DAY_SCOPED_WORDS; ++k) w[k] = 0;
         if (advance) c->day_idx++;
         c->end_ticket = 0;
-        __threadfence();
     }
 }
 
