@@ -260,7 +260,7 @@ int  cabm_run_days(cabm_t* h, int first_day, int n_days, const int32_t* julian_d
                    const double* expected_imports, const double* strain_w /* [n_days][4] */);
 
 /* MANY COMMUNITIES, ONE LAUNCH PER KERNEL. Calibration runs thousands of replicates of one small population with different
-   parameters and seeds (exp/abc-*, SLURM arrays; BASELINE configs[4]); a 100k-agent day is ten launches of a few
+   parameters and seeds (exp/abc-*, SLURM arrays; BASELINE configs[4]); a 100k-agent day is nine launches of a few
    microseconds each, so replicates on separate streams are bound by the device's launch rate. cabm_batch_run_days advances
    `n` handles of the same shape (same N, locations and rosters; own parameters, seed, state and ledger) together: each of
    the day's kernels is ONE launch whose blockIdx.y selects the community. Same arguments as cabm_run_days, shared by all
