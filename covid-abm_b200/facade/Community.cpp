@@ -14,6 +14,7 @@
 #include <gsl/gsl_rng.h>
 #include <gsl/gsl_randist.h>
 #include "fast_text.h"
+#include "pop_cache.h"
 #include "Community.h"
 #include "Person.h"
 #include "../../include/cabm.h"
@@ -66,8 +67,10 @@ struct Ft {
     explicit Ft(int k_) : k(k_) { if (ft_on) t0 = std::chrono::steady_clock::now(); }
     ~Ft() { if (ft_on) { ft_slots[k].s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); ft_slots[k].n++; } }
 };
+int ft_cache[2] = { -1, -1 };              // loadLocations / loadPopulation: 1 = rows from the binary cache, 0 = from the text, -1 = not called
 void ft_report() {
     if (!ft_on) return;
+    cerr << "facade_pop_cache {\"locations\": " << ft_cache[0] << ", \"population\": " << ft_cache[1] << "}" << endl;
     cerr << "facade_timing {";
     for (int k = 0; k < FT_N; ++k) cerr << (k ? ", " : "") << '"' << ft_slots[k].name << "\": [" << ft_slots[k].s << ", " << ft_slots[k].n << "]";
     cerr << "}" << endl;
@@ -211,101 +214,78 @@ static double pixel_of(double coord) { return floor(coord / 0.01) * 0.01 + 0.005
 
 bool Community::loadLocations(string locationFilename, string networkFilename) {
     Ft ft(FT_LOADLOC);
-    cabm_text::Table in(locationFilename);
-    if (!in.ok()) { cerr << "ERROR: locations file " << locationFilename << " not found." << endl; return false; }
+    // text (or its binary cache, pop_cache.h) -> rows, then the proxies in row order
+    cabm_pop::LocRows R;
+    const int type_codes[5] = { (int) HOUSE, (int) WORK, (int) SCHOOL, (int) HOSPITAL, (int) NURSINGHOME };
+    if (!cabm_pop::location_rows(locationFilename, networkFilename, type_codes, R, &_loc_from_cache)) return false;
+    ft_cache[0] = _loc_from_cache ? 1 : 0;
     _location.clear();
-    vector<pair<Location*, int>> hospital_of;
-    while (in.next_row()) {
-        int locid, hfid; double x, y, compliance;
-        if (!(in.number(locid) and in.number(x) and in.number(y))) continue;               // header or malformed line
-        const string_view type_s = in.field(), ess_s = in.field();
-        if (type_s.empty() or ess_s.empty() or !in.number(hfid)) continue;
-        if (locid != (int) _location.size()) { cerr << "ERROR: Location ID's must be sequential integers starting at 0" << endl; return false; }
-        LocationType lt = type_s == "h" ? HOUSE : type_s == "w" ? WORK : type_s == "s" ? SCHOOL : type_s == "hf" ? HOSPITAL : type_s == "n" ? NURSINGHOME
-                                                                                                                             : NUM_OF_LOCATION_TYPES;
-        if (lt == NUM_OF_LOCATION_TYPES) { cerr << "ERROR: Parsed unknown location type: " << type_s << " from location file: " << locationFilename << endl; return false; }
-        const bool known_ess = ess_s == "y" or ess_s == "NA" or ess_s == "n";
-        if (!known_ess) { cerr << "ERROR: Unknown value for \"essential\" status: " << ess_s << " from location file: " << locationFilename << endl; return false; }
+    const size_t L = R.x.size();
+    _location.reserve(L);
+    for (size_t i = 0; i < L; ++i) {
+        const LocationType lt = (LocationType) R.type[i];
+        const unsigned int fl = R.flags[i];
         Location* loc = new Location();
-        loc->setX(x); loc->setY(y); loc->setType(lt); loc->setEssential(ess_s != "n");
-        loc->setPixel(pixel_of(x), pixel_of(y));
+        loc->setX(R.x[i]); loc->setY(R.y[i]); loc->setType(lt); loc->setEssential((fl & 2u) != 0);
+        loc->setPixel(pixel_of(R.x[i]), pixel_of(R.y[i]));
         _pixelMap[{ loc->getXPixel(), loc->getYPixel() }].push_back(loc);
-        const bool have_compliance = in.number(compliance);                                 // a field that is not a number ends the row, as a failed stream does
-        if (have_compliance and compliance >= 0) loc->setRiskiness(1.0 - compliance);
+        if ((fl & 1u) and R.compliance[i] >= 0) loc->setRiskiness(1.0 - R.compliance[i]);
         else if (lt == HOUSE) loc->setRiskiness(gsl_rng_uniform(RNG));                     // Community.cpp:461-464
-        PublicTransmissionType pt = NO_PUBLIC_TRANSMISSION;
-        const string_view pub_s = have_compliance ? in.field() : string_view();
-        if (not pub_s.empty() and pub_s != "N") {
-            pt = pub_s == "H" ? HIGH_PUBLIC_TRANSMISSION : pub_s == "L" ? LOW_PUBLIC_TRANSMISSION : NUM_OF_PUBLIC_TRANSMISSION_TYPES;
-            if (pt == NUM_OF_PUBLIC_TRANSMISSION_TYPES) { cerr << "ERROR: Unknown value for \"public transmission\" status: " << pub_s << endl; return false; }
-            _public_locations.push_back(loc);
-        }
+        const unsigned int pub = (fl >> 2) & 3u;
+        const PublicTransmissionType pt = pub == 2 ? HIGH_PUBLIC_TRANSMISSION : pub == 1 ? LOW_PUBLIC_TRANSMISSION : NO_PUBLIC_TRANSMISSION;
+        if (pt != NO_PUBLIC_TRANSMISSION) _public_locations.push_back(loc);
         loc->setPublicTransmissionRisk(pt);
         _location.push_back(loc);
         _location_map[lt].insert(loc);
-        if (hfid >= 0) hospital_of.push_back({ loc, hfid });
     }
-    for (auto& kv : hospital_of) {
-        if (kv.second >= (int) _location.size() or _location[kv.second]->getType() != HOSPITAL) { cerr << "ERROR: hospital id " << kv.second << " is not a hospital" << endl; return false; }
-        kv.first->setHospital(_location[kv.second]);
+    for (size_t i = 0; i < L; ++i) {
+        const int hf = R.hfid[i];
+        if (hf < 0) continue;
+        if (hf >= (int) L or _location[hf]->getType() != HOSPITAL) { cerr << "ERROR: hospital id " << hf << " is not a hospital" << endl; return false; }
+        _location[i]->setHospital(_location[hf]);
     }
-    cabm_text::Table net(networkFilename);
-    if (!net.ok()) { cerr << "ERROR: network file " << networkFilename << " not found." << endl; return false; }
-    while (net.next_row()) {
-        int a, b;
-        if (net.number(a) and net.number(b)) {
-            assert(a >= 0 and b >= 0 and a < (int) _location.size() and b < (int) _location.size());
-            _location[a]->addNeighbor(_location[b]); _location[b]->addNeighbor(_location[a]);
-        }
+    for (size_t e = 0; e + 1 < R.net.size(); e += 2) {
+        const int a = R.net[e], b = R.net[e + 1];
+        assert(a >= 0 and b >= 0 and a < (int) L and b < (int) L);
+        _location[a]->addNeighbor(_location[b]); _location[b]->addNeighbor(_location[a]);
     }
     return true;
 }
 
 bool Community::loadPopulation(string populationFilename, string comorbidityFilename, string publicActivityFilename, string immunityFilename) {
     Ft ft(FT_LOADPOP);
-    {
-        cabm_text::Table in(populationFilename);
-        if (!in.ok()) { cerr << "ERROR: " << populationFilename << " not found." << endl; return false; }
-        while (in.next_row()) {
-            int pid, hid, sex, age, did;
-            if (!(in.number(pid) and in.number(hid) and in.number(sex) and in.number(age) and in.number(did))) continue;
-            if (pid != (int) _people.size()) { cerr << "ERROR: Person ID's must be sequential integers starting at 0" << endl; return false; }
-            assert((int) _location.size() > hid and (int) _location.size() > did);
-            Person* p = new Person();
-            _people.push_back(p);
-            p->setAge(age); p->setSex((SexType) sex);
-            // load-time immunity attributes, drawn exactly as the reference does (Community.cpp:212-215) with its own Parameters methods
-            p->setStartingNaturalEfficacy(_par->sampleStartingNaturalEfficacy(RNG));
-            p->setImmunityQuantile(gsl_rng_uniform(RNG));
-            p->setNaturalImmunityDuration(_par->immunityDuration(p->getImmunityQuantile(), p->getStartingNaturalEfficacy()));
-            p->setCrossProtectionProbability(gsl_rng_uniform(RNG));
-            p->setHomeLoc(_location[hid]); _location[hid]->addPerson(p);
-            if (did >= 0) { p->setDayLoc(_location[did]); _location[did]->addPerson(p); }
-            if (_location[hid]->getType() == NURSINGHOME) p->setLongTermCare(true);
-        }
+    cabm_pop::PopRows R;
+    if (!cabm_pop::population_rows(populationFilename, comorbidityFilename, publicActivityFilename, R, &_pop_from_cache)) return false;
+    ft_cache[1] = _pop_from_cache ? 1 : 0;
+    const size_t N = R.hid.size();
+    _people.reserve(_people.size() + N);
+    for (size_t i = 0; i < N; ++i) {
+        const int hid = R.hid[i], did = R.did[i];
+        if ((int) i != (int) _people.size()) { cerr << "ERROR: Person ID's must be sequential integers starting at 0" << endl; return false; }
+        assert(hid >= 0 and (int) _location.size() > hid and (int) _location.size() > did);
+        Person* p = new Person();
+        _people.push_back(p);
+        p->setAge(R.age[i]); p->setSex((SexType) R.sex[i]);
+        // load-time immunity attributes, drawn exactly as the reference does (Community.cpp:212-215) with its own Parameters methods
+        p->setStartingNaturalEfficacy(_par->sampleStartingNaturalEfficacy(RNG));
+        p->setImmunityQuantile(gsl_rng_uniform(RNG));
+        p->setNaturalImmunityDuration(_par->immunityDuration(p->getImmunityQuantile(), p->getStartingNaturalEfficacy()));
+        p->setCrossProtectionProbability(gsl_rng_uniform(RNG));
+        p->setHomeLoc(_location[hid]); _location[hid]->addPerson(p);
+        if (did >= 0) { p->setDayLoc(_location[did]); _location[did]->addPerson(p); }
+        if (_location[hid]->getType() == NURSINGHOME) p->setLongTermCare(true);
     }
-    if (comorbidityFilename.length() > 0) {
-        cabm_text::Table in(comorbidityFilename);
-        if (!in.ok()) { cerr << "ERROR: " << comorbidityFilename << " not found." << endl; return false; }
-        while (in.next_row()) {
-            int pid, sex, age, com;
-            if (in.number(pid) and in.number(sex) and in.number(age) and in.number(com) and com == 1) getPersonByID(pid)->setComorbidity(COMORBID);
-        }
-    }
-    if (publicActivityFilename.length() > 0) {
-        cabm_text::Table in(publicActivityFilename);
-        if (!in.ok()) { cerr << "ERROR: " << publicActivityFilename << " not found." << endl; return false; }
-        while (in.next_row()) {
-            int pid, locid;
-            if (!in.number(pid)) continue;
-            Person* p = getPersonByID(pid);
-            if (p->getAge() < 18 or p->getLongTermCare()) continue;                      // Community.cpp:286-288
-            while (in.number(locid)) {
-                assert((int) _location.size() > locid);
-                Location* loc = _location[locid];
-                assert(loc->getPublicTransmissionRisk() == LOW_PUBLIC_TRANSMISSION or loc->getPublicTransmissionRisk() == HIGH_PUBLIC_TRANSMISSION);
-                p->addPatronizedLocation(loc);
-            }
+    for (const int pid : R.comorbid) getPersonByID(pid)->setComorbidity(COMORBID);
+    for (size_t r = 0; r < R.pub_pid.size(); ++r) {
+        Person* p = getPersonByID(R.pub_pid[r]);
+        if (p->getAge() < 18 or p->getLongTermCare()) continue;                          // Community.cpp:286-288
+        assert(R.pub_off[r] <= R.pub_off[r + 1] and R.pub_off[r + 1] <= (int64_t) R.pub_loc.size());
+        for (int64_t k = R.pub_off[r]; k < R.pub_off[r + 1]; ++k) {
+            const int locid = R.pub_loc[k];
+            assert(locid >= 0 and (int) _location.size() > locid);
+            Location* loc = _location[locid];
+            assert(loc->getPublicTransmissionRisk() == LOW_PUBLIC_TRANSMISSION or loc->getPublicTransmissionRisk() == HIGH_PUBLIC_TRANSMISSION);
+            p->addPatronizedLocation(loc);
         }
     }
     if (immunityFilename.length() > 0) { cerr << "ERROR: Reading in immunity file not currently supported." << endl; return false; }

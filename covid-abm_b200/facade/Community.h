@@ -152,6 +152,7 @@ class Community {
 
     cabm* _h;
     bool _uploaded, _ti_dirty;
+    bool _loc_from_cache = false, _pop_from_cache = false;   // the loaders read their rows from the binary cache (pop_cache.h, CABM_POP_CACHE)
     unsigned long long _epoch;                            // bumped whenever the device state changes
     unsigned long long _ledger_epoch, _diag_epoch; int _diag_day;
     std::vector<unsigned long long> _ledger_cache, _diag_cache;

@@ -347,3 +347,48 @@ def test_sim_data_dump_cuda_equals_oracle(tmp_path):
     io, to = _sim_db(DRV_ORACLE, tmp_path, P, tab, "oracle")
     assert ic["infections"] == io["infections"] > 3000
     assert _canonical(tc) == _canonical(to)
+
+
+# ---- binary cache of the population files (covid-abm_b200/facade/pop_cache.h) ----
+def _run_env(driver, tmp, P, tab, tag, env):
+    pf = os.path.join(str(tmp), f"params_{tag}.txt"); cabm.params.write_text(P, tab, pf)
+    prefix = os.path.join(str(tmp), f"out_{tag}")
+    e = dict(os.environ); e.update(env); e["CABM_FACADE_TIMING"] = "1"
+    r = subprocess.run([driver, "sim", pf, str(tmp), "f", prefix, "1"], capture_output=True, text=True, timeout=900, env=e)
+    assert r.returncode == 0, r.stderr[-2000:]
+    hits = [json.loads(l.split(" ", 1)[1]) for l in r.stderr.splitlines() if l.startswith("facade_pop_cache ")]
+    outs = tuple(open(prefix + ext).read() for ext in (".ledger.csv", ".plot.csv", ".rt.csv"))
+    return hits[-1], outs
+
+
+@needs_oracle_driver
+def test_population_cache_gives_the_same_run_and_notices_edited_files(tmp_path):
+    """First run with CABM_POP_CACHE parses the text and writes the cache, the second reads the cache: ledger, plot log and Rt
+    file are byte-identical to a run without a cache (same RNG consumption at load time: the cache holds what the files say,
+    not the drawn attributes). Editing a file (size / mtime) makes the next run parse again; a truncated cache file is ignored."""
+    pop, P, tab = _case(tmp_path, n=8000, days=40)
+    cache = tmp_path / "cache"; cache.mkdir()
+    st0, plain = _run_env(DRV_ORACLE, tmp_path, P, tab, "plain", {})
+    assert st0 == {"locations": 0, "population": 0} and not list(cache.iterdir())
+    st1, cold = _run_env(DRV_ORACLE, tmp_path, P, tab, "cold", {"CABM_POP_CACHE": str(cache)})
+    files = sorted(f.name for f in cache.iterdir())
+    assert st1 == {"locations": 0, "population": 0} and len(files) == 2 and files[0].startswith("cabm_loc_") and files[1].startswith("cabm_pop_")
+    st2, warm = _run_env(DRV_ORACLE, tmp_path, P, tab, "warm", {"CABM_POP_CACHE": str(cache)})
+    assert st2 == {"locations": 1, "population": 1}
+    assert plain == cold == warm
+    assert float(plain[0].count("\n")) > 30
+    # an edited population file: new key, parsed again (the locations cache still serves), results follow the edit
+    popfile = tmp_path / "population-f.txt"
+    lines = popfile.read_text().splitlines()
+    pid, hid, sex, age, did = lines[-1].split()[:5]
+    lines[-1] = " ".join([pid, hid, sex, str((int(age) + 30) % 90), did])
+    popfile.write_text("\n".join(lines) + "\n")
+    st3, edited = _run_env(DRV_ORACLE, tmp_path, P, tab, "edited", {"CABM_POP_CACHE": str(cache)})
+    assert st3 == {"locations": 1, "population": 0} and len(list(cache.iterdir())) == 3
+    st3b, edited_plain = _run_env(DRV_ORACLE, tmp_path, P, tab, "edited_plain", {})
+    assert edited == edited_plain
+    # a damaged cache file is not trusted
+    for f in cache.iterdir():
+        data = f.read_bytes(); f.write_bytes(data[: len(data) // 2])
+    st4, again = _run_env(DRV_ORACLE, tmp_path, P, tab, "damaged", {"CABM_POP_CACHE": str(cache)})
+    assert st4 == {"locations": 0, "population": 0} and again == edited
