@@ -4,4 +4,4 @@ The directory name carries a hyphen (it mirrors the reference repository's name)
 through the root-level shim `covid_abm_b200.py`; inside, modules use relative imports.
 """
 from . import abi, params, replicates, sharded   # noqa: F401
-from .community import Community, CabmError, Backend, cuda_backend, LIB_PATH   # noqa: F401
+from .community import Community, CabmError, Backend, cuda_backend, save_population, LIB_PATH   # noqa: F401

@@ -84,6 +84,8 @@ assert INFECTION_DTYPE.itemsize == 44 and FOI_DTYPE.itemsize == 64
 _vp = C.c_void_p
 _PROTOS = {
     "create": [C.POINTER(_vp)], "destroy": [_vp], "load_population": [_vp, C.POINTER(Population)],
+    "population_save": [C.POINTER(Population), C.c_char_p],
+    "load_population_file": [_vp, C.c_char_p, C.POINTER(d), C.POINTER(f), C.POINTER(i32)],
     "set_params": [_vp, C.POINTER(Params)], "set_timed_intervention": [_vp, C.c_int, C.POINTER(d), C.c_size_t],
     "tick": [_vp, C.c_int, C.c_int, C.c_int], "import": [_vp, C.c_int, d, C.POINTER(d), C.POINTER(i32)],
     "infect": [_vp, C.c_uint32, C.c_int, C.c_int, C.POINTER(i32)],

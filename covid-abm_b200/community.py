@@ -44,10 +44,25 @@ def cuda_backend() -> Backend:
     return _cuda_backend
 
 
+def save_population(pop: dict, path: str, backend: Backend | None = None):
+    """Write the built population (SoA + CSRs of a tools/synthpop.py dict) as one binary file (cabm_population_save, cabm.h);
+    host code only: works without a GPU."""
+    be = backend or cuda_backend()
+    n = int(pop["n_people"])
+    dummy = (np.zeros(n), np.zeros(n, dtype=np.float32), np.zeros(n, dtype=np.int32))          # the attributes are not part of the file
+    pstruct, keep = abi.pack_population(pop, dummy)
+    rc = be.fn.population_save(C.byref(pstruct), os.fsencode(path))
+    del keep
+    if rc != 0:
+        raise CabmError(f"cabm_population_save failed rc={rc} ({path})")
+
+
 class Community:
     """One simulated community bound to one GPU (reference: `class Community`, Community.h:138)."""
 
-    def __init__(self, P: dict, pop: dict, tables: dict | None = None, backend: Backend | None = None, attrs=None):
+    def __init__(self, P: dict, pop: dict, tables: dict | None = None, backend: Backend | None = None, attrs=None, population_file: str | None = None):
+        """pop: a tools/synthpop.py dict; with population_file only its n_people / n_loc are read and the arrays come from the
+        binary file written by save_population (cabm_load_population_file: one read + the device copies)."""
         self.backend = backend or cuda_backend()
         self.fn = self.backend.fn
         self.P = P
@@ -59,9 +74,17 @@ class Community:
         self._par_struct, self._par_keep = abi.pack_params(P, self.T)
         self._check(self.fn.set_params(self._h, C.byref(self._par_struct)))
         attrs = attrs if attrs is not None else abi.immunity_attributes(self.n_people, P["seed"])
-        pstruct, keep = abi.pack_population(pop, attrs)
-        self._check(self.fn.load_population(self._h, C.byref(pstruct)))
-        del keep
+        if population_file is None:
+            pstruct, keep = abi.pack_population(pop, attrs)
+            self._check(self.fn.load_population(self._h, C.byref(pstruct)))
+            del keep
+        else:
+            ne = np.ascontiguousarray(attrs[0], dtype=np.float64)
+            xp = np.ascontiguousarray(attrs[1], dtype=np.float32)
+            nd = np.ascontiguousarray(attrs[2], dtype=np.int32)
+            assert ne.size == xp.size == nd.size == self.n_people
+            self._check(self.fn.load_population_file(self._h, os.fsencode(population_file), ne.ctypes.data_as(C.POINTER(C.c_double)),
+                                                     xp.ctypes.data_as(C.POINTER(C.c_float)), nd.ctypes.data_as(C.POINTER(C.c_int32))))
         for which, key in ((0, "school_closure"), (1, "business_closure"), (2, "social_distancing")):
             self.setTimedIntervention(which, P[key])
         self.julian_day, self.is_weekday = _params.calendar(P["start_julian_year"], P["start_day_of_year"], self.run_length)

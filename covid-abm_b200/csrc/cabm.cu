@@ -11,6 +11,7 @@
 #include <dlfcn.h>
 #include <nccl.h>
 #include "cabm_kernels2.cuh"
+#include "../../include/cabm_popfile.h"
 
 namespace {
 
@@ -555,6 +556,21 @@ int cabm_load_population(cabm_t* h, const cabm_population* pop) {
     CK(cudaGetLastError());
     h->have_pop = true;
     return CABM_OK;
+}
+
+// ---- the built population as one binary file (cabm.h: cabm_population_save / cabm_load_population_file; format in cabm_popfile.h) ----
+int cabm_population_save(const cabm_population* pop, const char* path) { return cabm_popfile::save(pop, path); }
+
+int cabm_load_population_file(cabm_t* h, const char* path, const double* starting_natural_efficacy,
+                              const float* cross_protection_probability, const int32_t* natural_immunity_duration) {
+    { const int rc_settle = settle(h); if (rc_settle) return rc_settle; }
+    if (!h || !path) return CABM_E_ARG;
+    cabm_popfile::Mapped m;
+    int rc = m.open_file(path, &h->err);
+    if (rc) return rc;
+    m.pop.starting_natural_efficacy = starting_natural_efficacy; m.pop.cross_protection_probability = cross_protection_probability;
+    m.pop.natural_immunity_duration = natural_immunity_duration;
+    return cabm_load_population(h, &m.pop);                 // the mapping goes away with `m`
 }
 
 // the staged day of cabm_tick (h_ctx[0]) as its own launch sequence

@@ -232,6 +232,15 @@ const char* cabm_last_error(const cabm_t* h);
 
 /* replaces loadLocations + loadPopulation (Community.cpp:174-524) */
 int  cabm_load_population(cabm_t* h, const cabm_population* pop);
+/* The built population (the arrays of cabm_population: per-location and per-person SoA, roster and neighbour CSRs) as ONE binary
+ * file, so that a later run loads it with a read and the host-to-device copies instead of parsing the five text files and
+ * rebuilding the CSRs (Community.cpp:174-524). cabm_population_save writes `pop` without its load-time
+ * immunity attributes -- they depend on the run's seed (Community.cpp:212-215); cabm_load_population_file maps the file, checks
+ * its header and sizes, and loads it with the attributes the caller passes (same requirements as cabm_load_population). The file
+ * is little-endian, self-describing (magic "CABMPOP1", counts, then the arrays 8-byte aligned in the order of the struct). */
+int  cabm_population_save(const cabm_population* pop, const char* path);
+int  cabm_load_population_file(cabm_t* h, const char* path, const double* starting_natural_efficacy,
+                               const float* cross_protection_probability, const int32_t* natural_immunity_duration);
 /* replaces the `static const Parameters* _par` reads (Community.cpp:28, Person.cpp:24); re-callable */
 int  cabm_set_params(cabm_t* h, const cabm_params* par);
 /* replaces setSocialDistancingTimedIntervention / updateTimedIntervention (Community.h:396-425) */

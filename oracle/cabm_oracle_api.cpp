@@ -5,6 +5,7 @@
 #include <new>
 #include "cabm_oracle.h"
 #include "cabm_det_math.h"
+#include "cabm_popfile.h"
 
 using cabm_oracle::Sim;
 struct cabm { Sim sim; };
@@ -17,6 +18,20 @@ extern "C" {
 int cabm_oracle_create(cabm_t** out) { if (!out) return CABM_E_ARG; *out = new (std::nothrow) cabm(); return *out ? CABM_OK : CABM_E_NOMEM; }
 int cabm_oracle_destroy(cabm_t* h) { delete h; return CABM_OK; }
 const char* cabm_oracle_last_error(const cabm_t* h) { return h ? h->sim.err.c_str() : "null handle"; }
+
+// the binary population file (include/cabm_popfile.h): the same host code as the CUDA library's
+int cabm_oracle_population_save(const cabm_population* pop, const char* path) { return cabm_popfile::save(pop, path); }
+int cabm_oracle_load_population(cabm_t* h, const cabm_population* pop);
+int cabm_oracle_load_population_file(cabm_t* h, const char* path, const double* starting_natural_efficacy,
+                                     const float* cross_protection_probability, const int32_t* natural_immunity_duration) {
+    H_OK(h); if (!path) return CABM_E_ARG;
+    cabm_popfile::Mapped m;
+    const int rc = m.open_file(path, &h->sim.err);
+    if (rc) return rc;
+    m.pop.starting_natural_efficacy = starting_natural_efficacy; m.pop.cross_protection_probability = cross_protection_probability;
+    m.pop.natural_immunity_duration = natural_immunity_duration;
+    return cabm_oracle_load_population(h, &m.pop);
+}
 
 int cabm_oracle_load_population(cabm_t* h, const cabm_population* pop) {
     H_OK(h); if (!pop) return CABM_E_ARG;

@@ -341,3 +341,43 @@ def test_eligibility_and_reduce_follow_the_person_records():
     cohort = rng.choice(n, size=700, replace=False)
     assert c.reduce("infectious", cohort, day) == (ever & (rec["t"][:, 1] <= day) & (day < rec["t"][:, 2]))[cohort].sum()
     assert np.array_equal(c.eligibility(cohort, day), el[cohort])
+
+
+def test_population_file_round_trip_and_rejections(tmp_path):
+    """cabm_population_save / cabm_load_population_file (cabm.h, include/cabm_popfile.h): a community loaded
+    from the binary file runs exactly like one loaded from the arrays; the file written by the CUDA library's host code equals
+    the oracle's byte for byte; truncated files, foreign files and a missing file are refused with a message."""
+    import ctypes as C
+    pop = synthpop.generate(6000, seed=7)
+    P = cabm.params.default_params(run_length=25, seed=3, T=0.15, prob_daily_exposure=3e-3)
+    tab = cabm.params.build_tables(P)
+    attrs = cabm.abi.immunity_attributes(int(pop["n_people"]), P["seed"])
+    f_cuda, f_or = str(tmp_path / "pop_cuda.bin"), str(tmp_path / "pop_oracle.bin")
+    cabm.save_population(pop, f_cuda)                                    # host code of libcabm.so: needs no GPU
+    cabm.save_population(pop, f_or, backend=oracle_lib.oracle_backend())
+    data = open(f_cuda, "rb").read()
+    assert data == open(f_or, "rb").read() and data[:8] == b"CABMPOP1" and len(data) % 8 == 0
+    a = oracle_lib.oracle_community(P, pop, tab, attrs=attrs)
+    b = cabm.Community(P, pop, tab, backend=oracle_lib.oracle_backend(), attrs=attrs, population_file=f_cuda)
+    for c in (a, b):
+        for pid in range(0, 1500, 3):
+            c.infect(pid, 0, 0)
+        for _ in range(25):
+            c.step()
+    assert np.array_equal(a.ledger_table(), b.ledger_table()) and a.ledger_table()[:, 0].sum() > 100
+    assert np.array_equal(a.current_infections(), b.current_infections())
+    # refusals
+    def load(path):
+        h = cabm.Community.__new__(cabm.Community)
+        be = oracle_lib.oracle_backend()
+        hh = C.c_void_p(); assert be.fn.create(C.byref(hh)) == 0
+        ne, xp, nd = (np.ascontiguousarray(attrs[0], dtype=np.float64), np.ascontiguousarray(attrs[1], dtype=np.float32), np.ascontiguousarray(attrs[2], dtype=np.int32))
+        rc = be.fn.load_population_file(hh, path.encode(), ne.ctypes.data_as(C.POINTER(C.c_double)), xp.ctypes.data_as(C.POINTER(C.c_float)),
+                                        nd.ctypes.data_as(C.POINTER(C.c_int32)))
+        msg = (be.fn.last_error(hh) or b"").decode()
+        be.fn.destroy(hh)
+        return rc, msg
+    rc, msg = load(str(tmp_path / "nothing.bin")); assert rc != 0 and "not found" in msg
+    (tmp_path / "short.bin").write_bytes(data[: len(data) // 2]); rc, msg = load(str(tmp_path / "short.bin")); assert rc != 0 and "size does not match" in msg
+    (tmp_path / "foreign.bin").write_bytes(b"NOTAPOPF" + data[8:]); rc, msg = load(str(tmp_path / "foreign.bin")); assert rc != 0 and "bad magic" in msg
+    (tmp_path / "tiny.bin").write_bytes(b"CABM"); rc, msg = load(str(tmp_path / "tiny.bin")); assert rc != 0 and "too short" in msg

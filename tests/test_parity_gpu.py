@@ -319,3 +319,24 @@ def test_staged_tick_equals_eager_tick(monkeypatch):
     assert a[0] == b[0], "imported cases per day"
     assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
     assert a[1][:, 0].sum() > 300 and a[1][30].sum() > 0
+
+
+def test_community_loaded_from_the_population_file_equals_one_loaded_from_arrays(tmp_path):
+    """cabm_load_population_file on the CUDA library: same state, ledger and histories as cabm_load_population of the arrays."""
+    pop = synthpop.generate(20000, seed=11)
+    P = cabm.params.default_params(run_length=30, seed=29, T=0.15, prob_daily_exposure=3e-3)
+    tab = cabm.params.build_tables(P)
+    attrs = cabm.abi.immunity_attributes(int(pop["n_people"]), P["seed"])
+    path = str(tmp_path / "pop.bin")
+    cabm.save_population(pop, path)
+    a = cabm.Community(P, pop, tab, attrs=attrs)
+    b = cabm.Community(P, pop, tab, attrs=attrs, population_file=path)
+    for c in (a, b):
+        for pid in range(0, 3000, 5):
+            c.infect(pid, 0, 0)
+        c.run_days(30)
+    assert np.array_equal(a.ledger_table(), b.ledger_table()) and a.ledger_table()[:, 0].sum() > 300
+    assert np.array_equal(a.current_infections(), b.current_infections())
+    assert np.array_equal(sorted_hist(a), sorted_hist(b))
+    with pytest.raises(cabm.CabmError, match="not found"):
+        cabm.Community(P, pop, tab, attrs=attrs, population_file=str(tmp_path / "absent.bin"))
